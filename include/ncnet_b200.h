@@ -1,0 +1,137 @@
+/*
+ * ncnet_b200 -- C ABI of the B200-native NCNet matching head.
+ *
+ * The reference (leejaeyong7/ncnet) has no FFI layer: its head is pure
+ * PyTorch.  Each entry point below replaces the body of one reference
+ * function/module (cited as file:line relative to the reference checkout);
+ * the Python drop-in modules in ncnet_b200/ call them through ctypes.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless named host_*; all tensors are
+ *     dense, row-major, in the reference's own layout;
+ *   - the library never allocates or frees device memory and keeps no pointer
+ *     after returning; scratch is passed in by the caller (sizes from the
+ *     *_scratch_bytes queries);
+ *   - `stream` is a cudaStream_t passed as void*; launches are asynchronous,
+ *     nothing synchronises the device;
+ *   - return 0 on success, non-zero on error; ncnet_last_error() returns the
+ *     message of the calling thread's last failure;
+ *   - dtype: NCNET_F32 (0) or NCNET_F16 (1) = storage type of the activation
+ *     tensors.  Arithmetic is always fp32 (fp32 accumulation).
+ */
+#ifndef NCNET_B200_H
+#define NCNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define NCNET_F32 0
+#define NCNET_F16 1
+
+/* weight layouts accepted by the Conv4d entry points */
+#define NCNET_W_OIKKKK 0 /* [Cout,Cin,k,k,k,k]   (lib/conv4d.py:16-18, permute_filters=True) */
+#define NCNET_W_KOIKKK 1 /* [k,Cout,Cin,k,k,k]   (the stored, pre-permuted layout, lib/conv4d.py:76-77) */
+
+/* Conv4d compute modes */
+#define NCNET_CONV_FP32 0 /* fp32 FMA on CUDA cores */
+#define NCNET_CONV_TC16 1 /* fp16 operands, fp32 accumulate, tcgen05 tensor cores */
+
+int ncnet_version(void);
+const char *ncnet_last_error(void);
+
+/* featureL2Norm -- lib/model.py:14-17.   x,y: [B,C,HW];  y = x / sqrt(sum_c x^2 + 1e-6) */
+int ncnet_feature_l2norm(const void *x, void *y, int B, int C, int HW, int dtype, void *stream);
+
+/* FeatureCorrelation(shape='4D') -- lib/model.py:106-118.
+ * fa: [B,C,nA], fb: [B,C,nB] -> out: [B,nA,nB];  out[b,a,t] = sum_c fa[b,c,a]*fb[b,c,t].
+ * relu_l2norm != 0 applies the module's normalization=True branch (ReLU, then L2 norm
+ * over the singleton channel dim: v/sqrt(v*v+1e-6)).
+ * The 3D shape (lib/model.py:97-105) is the same product with fa's two spatial axes swapped
+ * and the roles of A and B exchanged; the Python wrapper does that re-indexing. */
+int ncnet_corr4d_fwd(const void *fa, const void *fb, void *out, int B, int C, int nA, int nB,
+                     int dtype, int relu_l2norm, void *stream);
+/* gradient of the plain (un-normalised) correlation wrt both feature maps (autograd of lib/model.py:113) */
+int ncnet_corr4d_bwd(const void *grad_out, const void *fa, const void *fb, void *grad_fa, void *grad_fb,
+                     int B, int C, int nA, int nB, int dtype, void *stream);
+
+/* MutualMatching -- lib/model.py:155-175.  x,y: [B,nA,nB] (the volume seen as a matrix,
+ * nA=fs1*fs2, nB=fs3*fs4).  keys: scratch/saved state, (B*(nA+nB)) uint64: packed
+ * (max value, first arg-max) per source cell then per target cell; it is also what the
+ * backward pass consumes.  in_groups=2 reads x as [B,2,nA,nB] and uses x[:,0]+x[:,1]
+ * (the sum of the two symmetric NeighConsensus branches, lib/model.py:147). */
+size_t ncnet_mutual_matching_keys_bytes(int B, int nA, int nB);
+int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB,
+                              int in_groups, int dtype, void *stream);
+/* backward: grad_x = d(y)/d(x)^T grad_y incl. the flow through both max reductions.
+ * sums: scratch, B*(nA+nB) floats.  x is the forward input (in_groups as in forward;
+ * grad_x is [B,nA,nB]: the gradient of the summed volume). */
+int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t *keys, float *sums,
+                              void *grad_x, int B, int nA, int nB, int in_groups, int dtype, void *stream);
+
+/* conv4d / Conv4d.forward -- lib/conv4d.py:11-51,81-82  (+ fused ReLU, lib/model.py:137-138,
+ * + the symmetric second branch of NeighConsensus.forward, lib/model.py:147).
+ *
+ * x: [B, Gin*Cin, d1,d2,d3,d4]   y: [B, G*Cout, d1,d2,d3,d4]   weight: fp32, layout w_layout,
+ * bias: fp32 [Cout] or NULL.  symmetric=0: G=1.  symmetric=1: G=2 -- group 0 uses the
+ * weights as stored, group 1 uses them with the (A,B) tap pairs exchanged
+ * (W'[o,c,a,b,c',d'] = W[o,c,c',d',a,b]), which equals running the layer on the A<->B
+ * transposed volume and transposing back.  shared_input!=0: both groups read the same
+ * Cin channels (Gin=1, first layer); else group g reads channels [g*Cin,(g+1)*Cin).
+ * relu!=0 fuses max(0,.) after the bias.  mode: NCNET_CONV_FP32 / NCNET_CONV_TC16.
+ * scratch: ncnet_conv4d_scratch_bytes(...) bytes (re-laid-out weights). */
+size_t ncnet_conv4d_scratch_bytes(int Cin, int Cout, int k, int symmetric, int mode);
+int ncnet_conv4d_fwd(const void *x, const float *weight, const float *bias, void *y, void *scratch,
+                     int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                     int w_layout, int symmetric, int shared_input, int relu, int dtype, int mode,
+                     void *stream);
+/* gradient wrt the layer input (autograd of lib/conv4d.py:39-48).  grad_y: [B,G*Cout,...];
+ * grad_x: [B,Gin*Cin,...].  y_prev_mask (may be NULL): a tensor shaped like grad_x; where it is
+ * <= 0 the result is zeroed (the ReLU of the previous layer folded into this epilogue).
+ * With shared_input the two groups' gradients are summed into the Cin channels. */
+int ncnet_conv4d_dgrad(const void *grad_y, const float *weight, const void *y_prev_mask, void *grad_x,
+                       void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                       int w_layout, int symmetric, int shared_input, int dtype, int mode, void *stream);
+/* gradient wrt weight (same layout as `weight`, fp32, OVERWRITTEN) and bias (fp32 [Cout], may be
+ * NULL).  With symmetric=1 the two groups' contributions are folded back into the one weight. */
+size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                                        int symmetric, int mode);
+int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, float *grad_bias,
+                       void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                       int w_layout, int symmetric, int shared_input, int dtype, int mode, void *stream);
+
+/* ReLU backward on the last layer's two branch outputs (lib/model.py:137-138,147):
+ * gz[b,g,p] = (y[b,g,p] > 0) ? grad[b,p] : 0 for g < G.   y,gz: [B,G,n]; grad: [B,n]. */
+int ncnet_relu_mask_bcast(const void *y, const void *grad, void *gz, int B, int G, long long n,
+                          int dtype, void *stream);
+
+/* maxpool4d -- lib/model.py:177-191.  x: [H1,H2,H3,H4] (batch 1, channel 0), each divisible by k.
+ * value: [H1/k,...] same dtype; offsets: four tensors of that shape, window-relative arg-max
+ * coordinates, (i,j,k,l) row-major window scan, ties -> first.  idx_bytes: 8 (int64, what the
+ * reference returns) or 1 (uint8). */
+int ncnet_maxpool4d_fwd(const void *x, void *value, void *max_i, void *max_j, void *max_k, void *max_l,
+                        int H1, int H2, int H3, int H4, int k, int idx_bytes, int dtype, void *stream);
+
+/* corr_to_matches -- lib/point_tnf.py:12-80.  corr: [B,nA,nB] with nA=fs1*fs2, nB=fs3*fs4.
+ * invert=0: one match per target cell (arg-max over the source axis), N=nB;
+ * invert=1: one per source cell, N=nA.  do_softmax: soft-max along the reduced axis first,
+ * arg-max taken on the soft-max values, ties -> first index.  delta_*: the four maxpool4d
+ * offset tensors [fs1,fs2,fs3,fs4] (batch 1 only, may be NULL), idx_bytes as above, k_size the
+ * pooling factor.  lut_*: fp32 coordinate tables of lengths fs2*k, fs1*k, fs4*k, fs3*k built
+ * by the caller exactly like lib/point_tnf.py:16-27.  Outputs [B,N]: xA,yA,xB,yB,score fp32;
+ * iA,jA,iB,jB int64. */
+int ncnet_corr_to_matches(const void *corr, int B, int fs1, int fs2, int fs3, int fs4,
+                          int do_softmax, int invert, int k_size,
+                          const void *delta_iA, const void *delta_jA, const void *delta_iB,
+                          const void *delta_jB, int idx_bytes,
+                          const float *lut_xA, const float *lut_yA, const float *lut_xB, const float *lut_yB,
+                          float *xA, float *yA, float *xB, float *yB, float *score,
+                          int64_t *iA, int64_t *jA, int64_t *iB, int64_t *jB, int dtype, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* NCNET_B200_H */

@@ -1,0 +1,284 @@
+// MutualMatching forward/backward  (reference lib/model.py:155-175)
+//
+// The volume [B,1,fs1,fs2,fs3,fs4] is a row-major matrix [nA x nB] per batch item.
+//   r[a] = max_b x[a,b]   c[b] = max_a x[a,b]
+//   y = x * ((x/(r+eps)) * (x/(c+eps)))          eps = 1e-5, evaluation order as written
+// HBM-bound: algorithmic traffic is one read + one write of the volume.  Pass 1 reads
+// the matrix once and leaves packed (max, first-argmax) keys for rows and columns; pass 2
+// re-reads it (L2-resident up to ~60 MB volumes on the 126 MB L2) and writes y.
+#include "common.cuh"
+
+namespace ncnet {
+
+constexpr float kMMEps = 1e-5f;
+constexpr int kMMThreads = 256;
+constexpr int kMMColsPerTile = 256;          // 8 warps x 32 lanes, one column per lane per slot
+constexpr int kMMSlots = kMMColsPerTile / 32;  // columns per lane
+
+template <typename T>
+__device__ __forceinline__ float mm_load(const T *x, size_t off, size_t group_stride, int groups) {
+    float v = ldf(x + off);
+    if (groups == 2) v = rnd<T>(v + ldf(x + off + group_stride));
+    return v;
+}
+
+// grid: (col tiles, row strips, B); each warp walks rows warp, warp+8, ... of the strip
+template <typename T>
+__global__ void __launch_bounds__(kMMThreads)
+mm_max_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, int nA, int nB,
+              int rows_per_block, int groups) {
+    const int b = blockIdx.z;
+    const int row0 = blockIdx.y * rows_per_block;
+    const int col0 = blockIdx.x * kMMColsPerTile;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t mat = (size_t)nA * nB;
+    const T *xb = x + (size_t)b * mat * groups;
+    unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
+    unsigned long long *colkeys = rowkeys + nA;
+
+    unsigned long long cbest[kMMSlots];
+#pragma unroll
+    for (int s = 0; s < kMMSlots; ++s) cbest[s] = 0ull;
+
+    const int row_end = min(row0 + rows_per_block, nA);
+    for (int a = row0 + warp; a < row_end; a += kMMThreads / 32) {
+        unsigned long long rbest = 0ull;
+        const size_t roff = (size_t)a * nB;
+#pragma unroll
+        for (int s = 0; s < kMMSlots; ++s) {
+            const int c = col0 + s * 32 + lane;
+            if (c < nB) {
+                const float v = mm_load(xb, roff + c, mat, groups);
+                const unsigned long long kr = pack_key(v, (uint32_t)c);
+                const unsigned long long kc = pack_key(v, (uint32_t)a);
+                rbest = kr > rbest ? kr : rbest;
+                cbest[s] = kc > cbest[s] ? kc : cbest[s];
+            }
+        }
+        rbest = warp_max_u64(rbest);
+        if (lane == 0 && rbest) atomicMax(rowkeys + a, rbest);
+    }
+
+    __shared__ unsigned long long sm[kMMThreads / 32][kMMColsPerTile];
+#pragma unroll
+    for (int s = 0; s < kMMSlots; ++s) sm[warp][s * 32 + lane] = cbest[s];
+    __syncthreads();
+    const int c = col0 + threadIdx.x;
+    if (c < nB) {
+        unsigned long long best = 0ull;
+#pragma unroll
+        for (int w = 0; w < kMMThreads / 32; ++w) {
+            const unsigned long long k = sm[w][threadIdx.x];
+            best = k > best ? k : best;
+        }
+        if (best) atomicMax(colkeys + c, best);
+    }
+}
+
+// elementwise pass: 4 consecutive elements of the flattened matrix per thread
+template <typename T>
+__global__ void __launch_bounds__(256)
+mm_apply_kernel(const T *__restrict__ x, T *__restrict__ y, const unsigned long long *__restrict__ keys,
+                int nA, int nB, int groups) {
+    const int b = blockIdx.y;
+    const size_t mat = (size_t)nA * nB;
+    const size_t e0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (e0 >= mat) return;
+    const T *xb = x + (size_t)b * mat * groups;
+    T *yb = y + (size_t)b * mat;
+    const unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
+    const unsigned long long *colkeys = rowkeys + nA;
+    int a = (int)(e0 / nB), c = (int)(e0 - (size_t)a * nB);
+    float rden = rnd<T>(key_val(rowkeys[a]) + kMMEps);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const size_t e = e0 + i;
+        if (e < mat) {
+            const float v = mm_load(xb, e, mat, groups);
+            const float cden = rnd<T>(key_val(colkeys[c]) + kMMEps);
+            const float qa = rnd<T>(v / rden);      // x / (max over B + eps)   (corr4d_A)
+            const float qb = rnd<T>(v / cden);      // x / (max over A + eps)   (corr4d_B)
+            stf(yb + e, v * rnd<T>(qa * qb));
+        }
+        if (++c == nB) {
+            c = 0;
+            ++a;
+            if (a < nA) rden = rnd<T>(key_val(rowkeys[a]) + kMMEps);
+        }
+    }
+}
+
+// backward pass 1: Sr[a] = sum_b g*y, Sc[b] = sum_a g*y  (y recomputed in fp32)
+template <typename T>
+__global__ void __launch_bounds__(kMMThreads)
+mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsigned long long *__restrict__ keys,
+                   float *__restrict__ sums, int nA, int nB, int rows_per_block, int groups) {
+    const int b = blockIdx.z;
+    const int row0 = blockIdx.y * rows_per_block;
+    const int col0 = blockIdx.x * kMMColsPerTile;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t mat = (size_t)nA * nB;
+    const T *xb = x + (size_t)b * mat * groups;
+    const T *gb = gy + (size_t)b * mat;
+    const unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
+    const unsigned long long *colkeys = rowkeys + nA;
+    float *rsum = sums + (size_t)b * (nA + nB);
+    float *csum = rsum + nA;
+
+    float cden[kMMSlots], cacc[kMMSlots];
+#pragma unroll
+    for (int s = 0; s < kMMSlots; ++s) {
+        const int c = col0 + s * 32 + lane;
+        cden[s] = c < nB ? key_val(colkeys[c]) + kMMEps : 1.f;
+        cacc[s] = 0.f;
+    }
+    const int row_end = min(row0 + rows_per_block, nA);
+    for (int a = row0 + warp; a < row_end; a += kMMThreads / 32) {
+        const float rden = key_val(rowkeys[a]) + kMMEps;
+        const size_t roff = (size_t)a * nB;
+        float racc = 0.f;
+#pragma unroll
+        for (int s = 0; s < kMMSlots; ++s) {
+            const int c = col0 + s * 32 + lane;
+            if (c < nB) {
+                const float v = mm_load(xb, roff + c, mat, groups);
+                const float gyv = ldf(gb + roff + c);
+                const float t = gyv * (v * ((v / rden) * (v / cden[s])));
+                racc += t;
+                cacc[s] += t;
+            }
+        }
+        racc = warp_sum(racc);
+        if (lane == 0) atomicAdd(rsum + a, racc);
+    }
+    __shared__ float sm[kMMThreads / 32][kMMColsPerTile];
+#pragma unroll
+    for (int s = 0; s < kMMSlots; ++s) sm[warp][s * 32 + lane] = cacc[s];
+    __syncthreads();
+    const int c = col0 + threadIdx.x;
+    if (c < nB) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kMMThreads / 32; ++w) t += sm[w][threadIdx.x];
+        atomicAdd(csum + c, t);
+    }
+}
+
+// backward pass 2
+template <typename T>
+__global__ void __launch_bounds__(256)
+mm_bwd_apply_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsigned long long *__restrict__ keys,
+                    const float *__restrict__ sums, T *__restrict__ gx, int nA, int nB, int groups) {
+    const int b = blockIdx.y;
+    const size_t mat = (size_t)nA * nB;
+    const size_t e0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (e0 >= mat) return;
+    const T *xb = x + (size_t)b * mat * groups;
+    const T *gb = gy + (size_t)b * mat;
+    T *ob = gx + (size_t)b * mat;
+    const unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
+    const unsigned long long *colkeys = rowkeys + nA;
+    const float *rsum = sums + (size_t)b * (nA + nB);
+    const float *csum = rsum + nA;
+    int a = (int)(e0 / nB), c = (int)(e0 - (size_t)a * nB);
+    unsigned long long rk = rowkeys[a];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const size_t e = e0 + i;
+        if (e < mat) {
+            const float rden = key_val(rk) + kMMEps;
+            const unsigned long long ck = colkeys[c];
+            const float cden = key_val(ck) + kMMEps;
+            const float v = mm_load(xb, e, mat, groups);
+            const float g = ldf(gb + e);
+            const float qa = v / rden, qb = v / cden;
+            // y = v*(qa*qb):  d/dv through the three occurrences of v
+            float d = g * (qa * qb) + (g * v * qb) / rden + (g * v * qa) / cden;
+            // flow through the maxima lands on their (first) arg-max element
+            if ((int)key_idx(rk) == c) d -= rsum[a] / rden;
+            if ((int)key_idx(ck) == a) d -= csum[c] / cden;
+            stf(ob + e, d);
+        }
+        if (++c == nB) {
+            c = 0;
+            ++a;
+            if (a < nA) rk = rowkeys[a];
+        }
+    }
+}
+
+static int rows_per_block_for(int B, int nA, int nB) {
+    const int col_tiles = (nB + kMMColsPerTile - 1) / kMMColsPerTile;
+    // aim for >= 4 blocks per SM; a strip is a multiple of 8 rows (one per warp)
+    long long want = 4ll * kNumSMs;
+    long long strips = (want + (long long)B * col_tiles - 1) / ((long long)B * col_tiles);
+    int rpb = (int)((nA + strips - 1) / strips);
+    rpb = ((rpb + 7) / 8) * 8;
+    if (rpb < 8) rpb = 8;
+    if (rpb > 256) rpb = 256;
+    return rpb;
+}
+
+template <typename T>
+static int mm_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB, int groups, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(keys, 0, (size_t)B * (nA + nB) * sizeof(uint64_t), st);
+    NC_CHECK(e == cudaSuccess, "mutual_matching: memset keys: %s", cudaGetErrorString(e));
+    const int rpb = rows_per_block_for(B, nA, nB);
+    dim3 g1((nB + kMMColsPerTile - 1) / kMMColsPerTile, (nA + rpb - 1) / rpb, B);
+    mm_max_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb, groups);
+    NC_LAUNCH_OK("mm_max_kernel");
+    const size_t mat = (size_t)nA * nB;
+    dim3 g2((unsigned)((mat + 1023) / 1024), B);
+    mm_apply_kernel<T><<<g2, 256, 0, st>>>((const T *)x, (T *)y, (const unsigned long long *)keys, nA, nB, groups);
+    NC_LAUNCH_OK("mm_apply_kernel");
+    return 0;
+}
+
+template <typename T>
+static int mm_bwd(const void *x, const void *gy, const uint64_t *keys, float *sums, void *gx, int B, int nA, int nB,
+                  int groups, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(sums, 0, (size_t)B * (nA + nB) * sizeof(float), st);
+    NC_CHECK(e == cudaSuccess, "mutual_matching_bwd: memset sums: %s", cudaGetErrorString(e));
+    const int rpb = rows_per_block_for(B, nA, nB);
+    dim3 g1((nB + kMMColsPerTile - 1) / kMMColsPerTile, (nA + rpb - 1) / rpb, B);
+    mm_bwd_sums_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (const T *)gy, (const unsigned long long *)keys,
+                                                     sums, nA, nB, rpb, groups);
+    NC_LAUNCH_OK("mm_bwd_sums_kernel");
+    const size_t mat = (size_t)nA * nB;
+    dim3 g2((unsigned)((mat + 1023) / 1024), B);
+    mm_bwd_apply_kernel<T><<<g2, 256, 0, st>>>((const T *)x, (const T *)gy, (const unsigned long long *)keys, sums,
+                                               (T *)gx, nA, nB, groups);
+    NC_LAUNCH_OK("mm_bwd_apply_kernel");
+    return 0;
+}
+
+}  // namespace ncnet
+
+using namespace ncnet;
+
+extern "C" size_t ncnet_mutual_matching_keys_bytes(int B, int nA, int nB) {
+    return (size_t)B * ((size_t)nA + nB) * sizeof(uint64_t);
+}
+
+extern "C" int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB,
+                                         int in_groups, int dtype, void *stream) {
+    NC_CHECK(x && y && keys, "mutual_matching_fwd: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "mutual_matching_fwd: bad shape B=%d nA=%d nB=%d", B, nA, nB);
+    NC_CHECK(in_groups == 1 || in_groups == 2, "mutual_matching_fwd: in_groups must be 1 or 2");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NCNET_F32) return mm_fwd<float>(x, y, keys, B, nA, nB, in_groups, st);
+    if (dtype == NCNET_F16) return mm_fwd<__half>(x, y, keys, B, nA, nB, in_groups, st);
+    return fail("mutual_matching_fwd: unsupported dtype %d", dtype);
+}
+
+extern "C" int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t *keys, float *sums,
+                                         void *grad_x, int B, int nA, int nB, int in_groups, int dtype,
+                                         void *stream) {
+    NC_CHECK(x && grad_y && keys && sums && grad_x, "mutual_matching_bwd: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "mutual_matching_bwd: bad shape");
+    NC_CHECK(in_groups == 1 || in_groups == 2, "mutual_matching_bwd: in_groups must be 1 or 2");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NCNET_F32) return mm_bwd<float>(x, grad_y, keys, sums, grad_x, B, nA, nB, in_groups, st);
+    if (dtype == NCNET_F16) return mm_bwd<__half>(x, grad_y, keys, sums, grad_x, B, nA, nB, in_groups, st);
+    return fail("mutual_matching_bwd: unsupported dtype %d", dtype);
+}

@@ -1,0 +1,417 @@
+"""torch.autograd.Functions over the C ABI (include/ncnet_b200.h).
+
+PyTorch is plumbing here: it owns device memory and streams; every arithmetic step of the
+matching head is one of this library's kernels.  CUDA tensors only -- CPU tensors raise.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+
+from . import _cabi
+from ._cabi import CONV_FP32, CONV_TC16, F16, F32, W_KOIKKK, W_OIKKKK
+
+# number of kernel launches issued through the C ABI (bench.py reports it as gpu_launches)
+LAUNCHES = {"n": 0}
+# when a list: (tag, start_event, end_event) per 16->16 Conv4d forward launch (bench.py's roofline)
+EVENT_LOG = None
+
+
+def default_conv_mode() -> int:
+    """NCNET_CONV_MODE=fp32|tc16 selects the Conv4d back end (default fp32 until told otherwise)."""
+    return CONV_TC16 if os.environ.get("NCNET_CONV_MODE", "fp32").lower() in ("tc16", "tc", "1") else CONV_FP32
+
+
+def _dt(t: torch.Tensor) -> int:
+    if t.dtype == torch.float32:
+        return F32
+    if t.dtype == torch.float16:
+        return F16
+    raise TypeError(f"ncnet_b200: unsupported dtype {t.dtype} (float32 or float16)")
+
+
+def _need_cuda(*ts: torch.Tensor) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("ncnet_b200: CUDA tensors required -- this library has no CPU path")
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _count(n: int) -> None:
+    LAUNCHES["n"] += n
+
+
+# ------------------------------------------------------------------------------------------- #
+# featureL2Norm / FeatureCorrelation
+# ------------------------------------------------------------------------------------------- #
+def feature_l2norm(x: torch.Tensor) -> torch.Tensor:
+    _need_cuda(x)
+    xc = x.contiguous()
+    b, c = xc.shape[0], xc.shape[1]
+    hw = xc.numel() // (b * c)
+    y = torch.empty_like(xc)
+    with torch.cuda.device(xc.device):
+        _cabi.check(_cabi.lib().ncnet_feature_l2norm(_ptr(xc), _ptr(y), b, c, hw, _dt(xc), _stream()), "feature_l2norm")
+    _count(1)
+    return y
+
+
+def _corr_fwd_raw(fa: torch.Tensor, fb: torch.Tensor, norm: bool) -> torch.Tensor:
+    b, c = fa.shape[0], fa.shape[1]
+    na, nb = fa[0, 0].numel(), fb[0, 0].numel()
+    out = torch.empty(b, na, nb, device=fa.device, dtype=fa.dtype)
+    with torch.cuda.device(fa.device):
+        _cabi.check(_cabi.lib().ncnet_corr4d_fwd(_ptr(fa), _ptr(fb), _ptr(out), b, c, na, nb, _dt(fa), int(norm),
+                                                 _stream()), "corr4d_fwd")
+    _count(1)
+    return out
+
+
+class _CorrFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, fa, fb):
+        fa, fb = fa.contiguous(), fb.contiguous()
+        ctx.save_for_backward(fa, fb)
+        return _corr_fwd_raw(fa, fb, False)
+
+    @staticmethod
+    def backward(ctx, g):
+        fa, fb = ctx.saved_tensors
+        g = g.contiguous()
+        b, c = fa.shape[0], fa.shape[1]
+        na, nb = fa[0, 0].numel(), fb[0, 0].numel()
+        ga = torch.empty_like(fa) if ctx.needs_input_grad[0] else None
+        gb = torch.empty_like(fb) if ctx.needs_input_grad[1] else None
+        with torch.cuda.device(fa.device):
+            _cabi.check(_cabi.lib().ncnet_corr4d_bwd(_ptr(g), _ptr(fa), _ptr(fb), _ptr(ga), _ptr(gb), b, c, na, nb,
+                                                     _dt(fa), _stream()), "corr4d_bwd")
+        _count((ga is not None) + (gb is not None))
+        return ga, gb
+
+
+def feature_correlation(fa: torch.Tensor, fb: torch.Tensor, shape: str = "4D", normalization: bool = True) -> torch.Tensor:
+    """FeatureCorrelation.forward (reference lib/model.py:96-120)."""
+    _need_cuda(fa, fb)
+    if fa.dtype != fb.dtype:
+        raise TypeError("feature_correlation: dtype mismatch")
+    b, c, ha, wa = fa.shape
+    _, _, hb, wb = fb.shape
+    needs_grad = torch.is_grad_enabled() and (fa.requires_grad or fb.requires_grad)
+    if shape == "4D":
+        lhs, rhs = fa, fb
+    elif shape == "3D":       # out[b, j*h+i, k, l]: source index column-major, target cells as the plane
+        lhs, rhs = fa.transpose(2, 3), fb
+    else:
+        raise ValueError(shape)
+    if needs_grad:
+        m = _CorrFn.apply(lhs, rhs)
+        if normalization:     # ReLU + L2 norm over the channel dim, elementwise tail kept differentiable
+            m = m.reshape(b, 1, ha, wa, hb, wb) if shape == "4D" else m.reshape(b, ha * wa, hb, wb)
+            m = torch.relu(m)
+            m = m / (m.pow(2).sum(1, keepdim=True) + 1e-6).pow(0.5)
+            return m
+    else:
+        fuse = normalization and shape == "4D"
+        m = _corr_fwd_raw(lhs.contiguous(), rhs.contiguous(), fuse)
+        if normalization and shape == "3D":
+            m = feature_l2norm(torch.relu(m.reshape(b, ha * wa, hb, wb)))
+            return m
+    if shape == "4D":
+        return m.reshape(b, 1, ha, wa, hb, wb)
+    return m.reshape(b, ha * wa, hb, wb)
+
+
+# ------------------------------------------------------------------------------------------- #
+# MutualMatching
+# ------------------------------------------------------------------------------------------- #
+class _MutualMatchingFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        b, g, f1, f2, f3, f4 = x.shape
+        if g not in (1, 2):
+            raise RuntimeError("MutualMatching: channel dim must be 1 (or 2 = the two NeighConsensus branches)")
+        xc = x.contiguous()
+        na, nb = f1 * f2, f3 * f4
+        y = torch.empty(b, 1, f1, f2, f3, f4, device=x.device, dtype=x.dtype)
+        keys = torch.empty(b * (na + nb), device=x.device, dtype=torch.int64)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().ncnet_mutual_matching_fwd(_ptr(xc), _ptr(y), _ptr(keys), b, na, nb, g, _dt(xc),
+                                                              _stream()), "mutual_matching_fwd")
+        _count(2)
+        ctx.save_for_backward(xc, keys)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        xc, keys = ctx.saved_tensors
+        b, g, f1, f2, f3, f4 = xc.shape
+        na, nb = f1 * f2, f3 * f4
+        gy = gy.contiguous()
+        gx = torch.empty(b, 1, f1, f2, f3, f4, device=xc.device, dtype=xc.dtype)
+        sums = torch.empty(b * (na + nb), device=xc.device, dtype=torch.float32)
+        with torch.cuda.device(xc.device):
+            _cabi.check(_cabi.lib().ncnet_mutual_matching_bwd(_ptr(xc), _ptr(gy), _ptr(keys), _ptr(sums), _ptr(gx), b,
+                                                              na, nb, g, _dt(xc), _stream()), "mutual_matching_bwd")
+        _count(2)
+        return gx.expand(b, g, f1, f2, f3, f4) if g == 2 else gx
+
+
+def mutual_matching(corr4d: torch.Tensor, sum_branches: bool = False) -> torch.Tensor:
+    """MutualMatching (reference lib/model.py:155-175).  With ``sum_branches`` a 2-channel input is
+    read as the two symmetric NeighConsensus branch outputs and summed on the fly."""
+    _need_cuda(corr4d)
+    if corr4d.dim() != 6 or corr4d.shape[1] != (2 if sum_branches else 1):
+        raise RuntimeError(f"MutualMatching: expected [B,{2 if sum_branches else 1},fs1,fs2,fs3,fs4], got {tuple(corr4d.shape)}")
+    return _MutualMatchingFn.apply(corr4d)
+
+
+# ------------------------------------------------------------------------------------------- #
+# Conv4d / NeighConsensus
+# ------------------------------------------------------------------------------------------- #
+def _wdims(w: torch.Tensor, layout: int) -> Tuple[int, int, int]:
+    if layout == W_KOIKKK:
+        return w.shape[2], w.shape[1], w.shape[0]       # Cin, Cout, k
+    return w.shape[1], w.shape[0], w.shape[2]
+
+
+def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode):
+    cin, cout, k = _wdims(w32, layout)
+    bsz, _, d1, d2, d3, d4 = x.shape
+    g = 2 if symmetric else 1
+    y = torch.empty(bsz, g * cout, d1, d2, d3, d4, device=x.device, dtype=x.dtype)
+    L = _cabi.lib()
+    scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(cin, cout, k, int(symmetric), mode), device=x.device,
+                          dtype=torch.uint8)
+    log = EVENT_LOG is not None and cin == 16 and cout == 16
+    with torch.cuda.device(x.device):
+        if log:
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
+        _cabi.check(L.ncnet_conv4d_fwd(_ptr(x), _ptr(w32), _ptr(b32), _ptr(y), _ptr(scratch), bsz, cin, cout, d1, d2, d3,
+                                       d4, k, layout, int(symmetric), int(shared_input), int(relu), _dt(x), mode,
+                                       _stream()), "conv4d_fwd")
+        if log:
+            ev1.record()
+            EVENT_LOG.append(("conv4d_fwd_16_16", ev0, ev1))
+    _count(2)
+    return y
+
+
+def _conv_dgrad(gy, w32, mask, layout, symmetric, shared_input, mode):
+    cin, cout, k = _wdims(w32, layout)
+    bsz, _, d1, d2, d3, d4 = gy.shape
+    gin = 1 if (shared_input or not symmetric) else 2
+    gx = torch.empty(bsz, gin * cin, d1, d2, d3, d4, device=gy.device, dtype=gy.dtype)
+    L = _cabi.lib()
+    scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(cin, cout, k, int(symmetric), mode), device=gy.device,
+                          dtype=torch.uint8)
+    with torch.cuda.device(gy.device):
+        _cabi.check(L.ncnet_conv4d_dgrad(_ptr(gy), _ptr(w32), _ptr(mask), _ptr(gx), _ptr(scratch), bsz, cin, cout, d1, d2,
+                                         d3, d4, k, layout, int(symmetric), int(shared_input), _dt(gy), mode, _stream()),
+                    "conv4d_dgrad")
+    _count(2)
+    return gx
+
+
+def _conv_wgrad(x, gy, w_like, want_bias, layout, symmetric, shared_input, mode):
+    cin, cout, k = _wdims(w_like, layout)
+    bsz, _, d1, d2, d3, d4 = x.shape
+    gw = torch.empty(w_like.shape, device=x.device, dtype=torch.float32)
+    gb = torch.empty(cout, device=x.device, dtype=torch.float32) if want_bias else None
+    L = _cabi.lib()
+    nbytes = L.ncnet_conv4d_wgrad_scratch_bytes(bsz, cin, cout, d1, d2, d3, d4, k, int(symmetric), mode)
+    scratch = torch.empty(nbytes, device=x.device, dtype=torch.uint8)
+    with torch.cuda.device(x.device):
+        _cabi.check(L.ncnet_conv4d_wgrad(_ptr(x), _ptr(gy), _ptr(gw), _ptr(gb), _ptr(scratch), bsz, cin, cout, d1, d2, d3,
+                                         d4, k, layout, int(symmetric), int(shared_input), _dt(x), mode, _stream()),
+                    "conv4d_wgrad")
+    _count(4 if want_bias else 3)
+    return gw, gb
+
+
+class _Conv4dFn(torch.autograd.Function):
+    """One Conv4d layer, no activation (reference lib/conv4d.py:11-51)."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, layout, mode):
+        xc = x.contiguous()
+        w32 = weight.detach().float().contiguous()
+        b32 = None if bias is None else bias.detach().float().contiguous()
+        ctx.layout, ctx.mode = layout, mode
+        ctx.has_bias = bias is not None
+        ctx.save_for_backward(xc, w32)
+        ctx.wdtype = weight.dtype
+        return _conv_fwd(xc, w32, b32, layout, False, True, False, mode)
+
+    @staticmethod
+    def backward(ctx, gy):
+        xc, w32 = ctx.saved_tensors
+        gy = gy.contiguous()
+        gx = gw = gb = None
+        if ctx.needs_input_grad[0]:
+            gx = _conv_dgrad(gy, w32, None, ctx.layout, False, True, ctx.mode)
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            gw, gb = _conv_wgrad(xc, gy, w32, ctx.has_bias, ctx.layout, False, True, ctx.mode)
+            gw = gw.to(ctx.wdtype)
+            gb = None if gb is None else gb.to(ctx.wdtype)
+        return gx, gw, gb, None, None
+
+
+def conv4d(data: torch.Tensor, filters: torch.Tensor, bias: Optional[torch.Tensor] = None,
+           permute_filters: bool = True, use_half: bool = False, mode: Optional[int] = None) -> torch.Tensor:
+    """Drop-in for the reference ``conv4d`` (lib/conv4d.py:11).  ``permute_filters=True`` means
+    ``filters`` is [Cout,Cin,k,k,k,k]; False means the stored pre-permuted [k,Cout,Cin,k,k,k]."""
+    _need_cuda(data, filters, bias)
+    layout = W_OIKKKK if permute_filters else W_KOIKKK
+    return _Conv4dFn.apply(data, filters, bias, layout, default_conv_mode() if mode is None else mode)
+
+
+class _NeighConsensusFn(torch.autograd.Function):
+    """The whole [Conv4d + ReLU] x L stack, both symmetric branches per launch, ReLU fused into the
+    conv epilogue and ReLU-backward fused into the dgrad epilogue (reference lib/model.py:143-153).
+    Returns [B, G*Clast, ...] (G=2 branches when symmetric; the caller sums them)."""
+
+    @staticmethod
+    def forward(ctx, x, symmetric, mode, *wb):
+        n_layers = len(wb) // 2
+        xc = x.contiguous()
+        acts = [xc]
+        w32s = []
+        cur = xc
+        for l in range(n_layers):
+            w32 = wb[2 * l].detach().float().contiguous()
+            b32 = wb[2 * l + 1].detach().float().contiguous()
+            w32s.append(w32)
+            cur = _conv_fwd(cur, w32, b32, W_KOIKKK, symmetric, l == 0, True, mode)
+            acts.append(cur)
+        ctx.symmetric, ctx.mode, ctx.n_layers = symmetric, mode, n_layers
+        ctx.wdtype = wb[0].dtype
+        ctx.save_for_backward(*acts, *w32s)
+        return cur
+
+    @staticmethod
+    def backward(ctx, g):
+        n = ctx.n_layers
+        saved = ctx.saved_tensors
+        acts, w32s = saved[: n + 1], saved[n + 1:]
+        sym, mode = ctx.symmetric, ctx.mode
+        out = acts[n]
+        bsz = out.shape[0]
+        g = g.contiguous()
+        # ReLU of the last layer: gz = g where the branch output is positive
+        gz = torch.empty_like(out)
+        per = out[0].numel()
+        with torch.cuda.device(out.device):
+            _cabi.check(_cabi.lib().ncnet_relu_mask_bcast(_ptr(out), _ptr(g), _ptr(gz), bsz, 1, per, _dt(out), _stream()),
+                        "relu_mask_bcast")
+        _count(1)
+        grads: List[Optional[torch.Tensor]] = [None] * (2 * n)
+        gx = None
+        for l in range(n - 1, -1, -1):
+            gw, gb = _conv_wgrad(acts[l], gz, w32s[l], True, W_KOIKKK, sym, l == 0, mode)
+            grads[2 * l], grads[2 * l + 1] = gw.to(ctx.wdtype), gb.to(ctx.wdtype)
+            if l > 0:
+                gz = _conv_dgrad(gz, w32s[l], acts[l], W_KOIKKK, sym, False, mode)
+            elif ctx.needs_input_grad[0]:
+                gx = _conv_dgrad(gz, w32s[0], None, W_KOIKKK, sym, True, mode)
+        return (gx, None, None, *grads)
+
+
+def neigh_consensus_branches(x: torch.Tensor, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor],
+                             symmetric: bool = True, mode: Optional[int] = None) -> torch.Tensor:
+    """Runs the NeighConsensus stack; returns the branch outputs [B, G*Clast, fs1..fs4] un-summed."""
+    _need_cuda(x, *weights, *biases)
+    wb = []
+    for w, b in zip(weights, biases):
+        wb += [w, b]
+    return _NeighConsensusFn.apply(x, bool(symmetric), default_conv_mode() if mode is None else mode, *wb)
+
+
+# ------------------------------------------------------------------------------------------- #
+# maxpool4d / corr_to_matches
+# ------------------------------------------------------------------------------------------- #
+def maxpool4d(corr4d_hres: torch.Tensor, k_size: int = 4, index_dtype: torch.dtype = torch.int64):
+    """maxpool4d (reference lib/model.py:177-191): batch-1 4D max-pool + window-relative arg-max
+    offsets.  index_dtype=torch.uint8 writes 1-byte offsets (8x less index traffic)."""
+    _need_cuda(corr4d_hres)
+    if corr4d_hres.shape[0] != 1:
+        raise RuntimeError("maxpool4d: batch size must be 1 (the reference mixes batch items otherwise)")
+    x = corr4d_hres[0, 0].contiguous()
+    h1, h2, h3, h4 = x.shape
+    k = int(k_size)
+    if any(s % k for s in x.shape):
+        raise RuntimeError(f"maxpool4d: dims {tuple(x.shape)} not divisible by k_size {k}")
+    shp = (1, 1, h1 // k, h2 // k, h3 // k, h4 // k)
+    val = torch.empty(shp, device=x.device, dtype=x.dtype)
+    idx = [torch.empty(shp, device=x.device, dtype=index_dtype) for _ in range(4)]
+    nbytes = {torch.int64: 8, torch.uint8: 1}[index_dtype]
+    with torch.cuda.device(x.device):
+        _cabi.check(_cabi.lib().ncnet_maxpool4d_fwd(_ptr(x), _ptr(val), *[_ptr(t) for t in idx], h1, h2, h3, h4, k, nbytes,
+                                                    _dt(x), _stream()), "maxpool4d")
+    _count(1)
+    return (val, idx[0], idx[1], idx[2], idx[3])
+
+
+_LUT_CACHE = {}
+
+
+def _axis_lut(lo: float, n: int, device) -> torch.Tensor:
+    key = (lo, n, str(device))
+    t = _LUT_CACHE.get(key)
+    if t is None:     # float64 linspace cast to fp32, as the reference builds it (lib/point_tnf.py:16-27)
+        t = torch.from_numpy(np.linspace(lo, 1, n)).float().to(device)
+        _LUT_CACHE[key] = t
+    return t
+
+
+def corr_to_matches(corr4d, delta4d=None, k_size=1, do_softmax=False, scale="centered", return_indices=False,
+                    invert_matching_direction=False):
+    """corr_to_matches (reference lib/point_tnf.py:12-80)."""
+    _need_cuda(corr4d)
+    b, ch, f1, f2, f3, f4 = corr4d.shape
+    x = corr4d.detach().contiguous()
+    if scale == "centered":
+        lo = -1.0
+    elif scale == "positive":
+        lo = 0.0
+    else:
+        raise ValueError(scale)
+    dev = x.device
+    luts = [_axis_lut(lo, f2 * k_size, dev), _axis_lut(lo, f1 * k_size, dev), _axis_lut(lo, f4 * k_size, dev),
+            _axis_lut(lo, f3 * k_size, dev)]
+    n = f1 * f2 if invert_matching_direction else f3 * f4
+    fo = [torch.empty(b, n, device=dev, dtype=torch.float32) for _ in range(5)]
+    io = [torch.empty(b, n, device=dev, dtype=torch.int64) for _ in range(4)]
+    deltas = [None] * 4
+    idx_bytes = 8
+    if delta4d is not None:
+        deltas = []
+        for d in delta4d:
+            if d.dtype not in (torch.int64, torch.uint8):
+                d = d.long()
+            deltas.append(d.contiguous())
+        idx_bytes = 8 if deltas[0].dtype == torch.int64 else 1
+        if any(d.dtype != deltas[0].dtype for d in deltas):
+            raise TypeError("corr_to_matches: delta4d tensors must share one integer dtype")
+    with torch.cuda.device(dev):
+        _cabi.check(_cabi.lib().ncnet_corr_to_matches(
+            _ptr(x), b, f1, f2, f3, f4, int(bool(do_softmax)), int(bool(invert_matching_direction)), int(k_size),
+            *[_ptr(d) for d in deltas], idx_bytes, *[_ptr(t) for t in luts], *[_ptr(t) for t in fo],
+            *[_ptr(t) for t in io], _dt(x), _stream()), "corr_to_matches")
+    _count(1)
+    xa, ya, xb, yb, score = fo
+    if x.dtype != torch.float32:
+        score = score.to(x.dtype)
+    if return_indices:
+        return (xa, ya, xb, yb, score, io[0], io[1], io[2], io[3])
+    return (xa, ya, xb, yb, score)

@@ -1,0 +1,43 @@
+"""Weak-supervision loss of the reference's training script (train.py:110-156), restated so that
+``train.py``'s step can be driven on the new head.  The soft-max/max score itself is still
+composed from PyTorch reductions here; SURVEY.md §8(f1) lists its fusion as the next row."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+
+def match_score(corr4d: torch.Tensor, normalization="softmax") -> torch.Tensor:
+    """mean over cells of (max over A of norm_A(x) + max over B of norm_B(x)) / 2  (train.py:123-134)."""
+    b = corr4d.size(0)
+    f1, f2, f3, f4 = corr4d.shape[2:]
+    nc_b_avec = corr4d.view(b, f1 * f2, f3, f4)
+    nc_a_bvec = corr4d.view(b, f1, f2, f3 * f4).permute(0, 3, 1, 2)
+    if normalization is None:
+        norm = lambda x: x
+    elif normalization == "softmax":
+        norm = lambda x: torch.nn.functional.softmax(x, 1)
+    elif normalization == "l1":
+        norm = lambda x: x / (torch.sum(x, dim=1, keepdim=True) + 0.0001)
+    else:
+        raise ValueError(normalization)
+    scores_b, _ = torch.max(norm(nc_b_avec), dim=1)
+    scores_a, _ = torch.max(norm(nc_a_bvec), dim=1)
+    return torch.mean(scores_a + scores_b) / 2
+
+
+def weak_loss(model, batch, normalization="softmax", alpha=30):
+    """Same call signature and side effect as train.py:110 (the batch's source images are rolled)."""
+    b = batch["source_image"].size(0)
+    score_pos = match_score(model(batch), normalization)
+    batch["source_image"] = batch["source_image"][np.roll(np.arange(b), -1), :]
+    score_neg = match_score(model(batch), normalization)
+    return score_neg - score_pos
+
+
+def weak_loss_from_features(model, feature_A, feature_B, normalization="softmax"):
+    """weak_loss with the trunk factored out: the negative pass pairs target b with source b+1
+    (rolling the images rolls their features).  Used by the head-only bench and tests."""
+    score_pos = match_score(model.match_features(feature_A, feature_B), normalization)
+    score_neg = match_score(model.match_features(torch.roll(feature_A, shifts=-1, dims=0), feature_B), normalization)
+    return score_neg - score_pos

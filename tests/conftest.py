@@ -1,0 +1,44 @@
+import os
+import sys
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+
+
+def load_golden(name, device="cpu"):
+    """tests/golden/<name>.npz -> dict of torch tensors (fixtures written by oracle/make_golden.py)."""
+    out = {}
+    with np.load(os.path.join(GOLD, name + ".npz"), allow_pickle=False) as z:
+        for k in z.files:
+            a = z[k]
+            if a.dtype.kind in "US":
+                out[k] = str(a)
+            else:
+                out[k] = torch.from_numpy(np.ascontiguousarray(a)).to(device)
+    return out
+
+
+def nerr(a, b):
+    """max-abs error normalised by the reference's max-abs (the tolerance metric of DESIGN.md)."""
+    a, b = a.detach().double().cpu(), b.detach().double().cpu()
+    assert a.shape == b.shape, (a.shape, b.shape)
+    if a.numel() == 0:
+        return 0.0
+    return ((a - b).abs().max() / b.abs().max().clamp_min(1e-30)).item()
+
+
+@pytest.fixture(scope="session")
+def cuda():
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return torch.device("cuda:0")
