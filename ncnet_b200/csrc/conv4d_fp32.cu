@@ -227,7 +227,7 @@ conv4d_fwd_thin_kernel(ConvArgs p) {
                     s_in[e] = v;
                 }
                 const float *wsrc = wg + (((size_t)c * KS + t1) * KS + t2) * (KS * KS);
-                if (tid < KS * KS) s_w[tid] = __ldg(wsrc + tid);
+                for (int e = tid; e < KS * KS; e += nthr) s_w[e] = __ldg(wsrc + e);
                 __syncthreads();
                 float w[KS * KS];
 #pragma unroll

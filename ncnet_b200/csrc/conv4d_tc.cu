@@ -1,15 +1,538 @@
-// tcgen05 Conv4d back end (placeholder until the implicit-GEMM kernel lands): reports an error,
-// never silently falls back.
+// Conv4d on the 5th-gen tensor cores (mode NCNET_CONV_TC16): fp16 operands, fp32 accumulation in
+// TMEM, one implicit-GEMM kernel per layer (reference semantics: lib/conv4d.py:11-51).
+//
+// GEMM view.  For one (batch, group, iA, jA) the CTA owns a chunk of the (iB,jB) plane, flattened
+// with the padded pitch P = d4 + k - 1 so that a tap shift is an affine row offset:
+//     A (M x K)  = activation rows: M = 128 consecutive flattened positions, K = 16 channels,
+//                  K-major, no swizzle: smem [channel-half][position][8 x fp16] -> a tap is just a
+//                  different descriptor start address (16 B per position);
+//     B (N x K)  = weights of one (d1,d2[,d3]) tap for N = (tap-in-N, out-channel) columns;
+//     D (M x N)  = fp32 accumulators in TMEM, NT tiles of N columns, live for the whole CTA.
+// The taps that are folded into N are summed in the epilogue with the matching row shift
+// (out[m] = sum_g D[m + shift_g][g]), which keeps N large enough (80 for a 16->16, k=5 layer)
+// that one 4 KB A tile is amortised over 5 taps -- with N=16 the MMA would be bound by the
+// 128 B/clk shared-memory read rate at 22 % of the tensor peak.
+//   mode M1 (Cin<=16, Cout>1): channels = input channels, N = (d4, o), K-steps per plane = d3 taps
+//   mode M2 (Cout == 1)      : channels = input channels, N = (d3, d4), one K-step per plane
+//   mode M3 (Cin == 1)       : channels = the k taps along d4 (im2col in the pack kernel),
+//                              N = (d3, o), one K-step per plane
+// Pipeline: warp 0 streams (d1,d2) planes + their weight slice with cp.async.bulk (TMA engine,
+// mbarrier complete_tx) through a 3-stage ring; one thread of warp 1 issues tcgen05.mma and
+// commits to the stage's "empty" barrier; warps 2-5 drain TMEM (tcgen05.ld), apply the shifted
+// sums, bias, ReLU / ReLU-mask, and store.
 #include "conv4d_tc.cuh"
+#include "conv4d_common.cuh"
 
 namespace ncnet {
-size_t conv4d_tc_scratch_bytes(int, int, int, int) { return 0; }
-int conv4d_tc_fwd(const void *, const float *, const float *, void *, void *, int, int, int, int, int, int, int, int,
-                  int, int, int, int, int, cudaStream_t) {
-    return fail("conv4d_fwd: NCNET_CONV_TC16 is not built into this library");
+
+constexpr int kTcThreads = 192;
+constexpr int kStages = 3;
+constexpr int kMaxGroups = 32;      // column groups (taps folded into N)
+constexpr int kMaxKSteps = 8;
+constexpr int kOutStride = 20;      // floats per outbuf row (16 channels + pad: conflict-free float4 RMW)
+
+struct TcArgs {
+    const __half *act;      // [B*Gx][2][d1*d2][d3][d4][8] fp16 (channel-blocked)
+    const __half *wp;       // [G][k*k][KSTEPS][2][N][8] fp16
+    const float *bias;      // [Cout] or null
+    const void *mask;       // planar tensor shaped like the output, or null
+    void *out;              // planar [B, G*Cout, vol] (out_f16 ? half : float)
+    int B, G, Gx, Cout, CoutPad;
+    int d1, d2, d3, d4, KS, P;
+    int lpad;               // column offset of l=0 inside a smem row (pad, or 0 for M3)
+    int R, nchunks;         // output k-rows per CTA, chunks per plane
+    int NT, N, NG, KSTEPS;
+    int npos_pad;           // positions per channel-half in a smem stage
+    int relu, out_f16, mask_f16;
+    uint32_t idesc;
+    int aoff[kMaxKSteps];   // A row offset (positions) per K-step
+    int gshift[kMaxGroups]; // epilogue row shift per column group
+    uint32_t stage_bytes, data_bytes, w_bytes;
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
 }
-int conv4d_tc_dgrad(const void *, const float *, const void *, void *, void *, int, int, int, int, int, int, int, int,
-                    int, int, int, int, cudaStream_t) {
-    return fail("conv4d_dgrad: NCNET_CONV_TC16 is not built into this library");
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// bounded wait: a protocol bug traps (kernel error) instead of hanging the GPU
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    const uint32_t addr = smem_u32(bar);
+    const long long t0 = clock64();
+    for (;;) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
+        if (ok) return;
+        if (clock64() - t0 > 4000000000ll) __trap();
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    // SWIZZLE_NONE K-major: core matrix = 8 rows x 16 B; LBO = stride between the two K halves,
+    // SBO = stride between 8-row groups; version field = 1 (sm_100)
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr >> 4) & 0x3fff);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
+    d |= (uint64_t)1 << 46;
+    return d;
+}
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv4d_tc_kernel(const TcArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar;
+    __shared__ uint32_t tmem_base_s;
+    __shared__ int s_gshift[kMaxGroups];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int bx = blockIdx.x;
+    const int chunk = bx % p.nchunks; bx /= p.nchunks;
+    const int j = bx % p.d2; bx /= p.d2;
+    const int i = bx % p.d1; bx /= p.d1;
+    const int g = bx % p.G;
+    const int b = bx / p.G;
+    const int PAD = p.KS / 2;
+    const int k0 = chunk * p.R;
+    const int rows_out = min(p.R, p.d3 - k0);
+
+    uint8_t *stage0 = smem;
+    float *outbuf = reinterpret_cast<float *>(smem + (size_t)kStages * p.stage_bytes);
+    const int out_rows = p.NT * 128;
+
+    // ---- one-time setup -------------------------------------------------------------------
+    if (threadIdx.x < kMaxGroups) s_gshift[threadIdx.x] = p.gshift[threadIdx.x];
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {    // TMEM: all 512 columns (one CTA per SM: the ring + outbuf fill shared memory)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    // zero the activation part of every stage once: halo columns/rows and the tail padding are
+    // never written by the row copies, so they stay zero (= the conv's zero padding)
+    {
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        for (int s = 0; s < kStages; ++s) {
+            uint4 *d = reinterpret_cast<uint4 *>(stage0 + (size_t)s * p.stage_bytes);
+            for (uint32_t e = threadIdx.x; e < p.data_bytes / 16; e += kTcThreads) d[e] = z;
+        }
+        // outbuf starts at the bias
+        if (p.CoutPad >= 16) {
+            for (int e = threadIdx.x; e < out_rows * kOutStride; e += kTcThreads) {
+                const int o = e % kOutStride;
+                outbuf[e] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
+            }
+        } else {
+            const float b0 = p.bias ? __ldg(p.bias) : 0.f;
+            for (int e = threadIdx.x; e < 4 * out_rows; e += kTcThreads) outbuf[e] = e < out_rows ? b0 : 0.f;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy zeros -> visible to TMA/UMMA
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+
+    // list of valid (d1,d2) planes is implicit: both roles walk the same loop
+    const size_t plane_pos = (size_t)p.d3 * p.d4;
+    const size_t ij_count = (size_t)p.d1 * p.d2;
+
+    if (warp == 0) {
+        // ===== producer =====
+        int stage = 0;
+        uint32_t phase = 0;
+        const int kin0 = max(k0 - PAD, 0), kin1 = min(k0 + rows_out + PAD, p.d3);   // valid input rows
+        const int nrows = kin1 - kin0;
+        const uint32_t row_bytes = (uint32_t)p.d4 * 16u;
+        const uint32_t tx_bytes = 2u * nrows * row_bytes + p.w_bytes;
+        const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
+        for (int t1 = 0; t1 < p.KS; ++t1) {
+            const int ii = i + t1 - PAD;
+            if (ii < 0 || ii >= p.d1) continue;
+            for (int t2 = 0; t2 < p.KS; ++t2) {
+                const int jj = j + t2 - PAD;
+                if (jj < 0 || jj >= p.d2) continue;
+                mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t *sb = stage0 + (size_t)stage * p.stage_bytes;
+                if (lane == 0) mbar_expect_tx(&full_bar[stage], tx_bytes);
+                __syncwarp();
+                for (int r = lane; r < 2 * nrows; r += 32) {
+                    const int half = r / nrows, kin = kin0 + (r - half * nrows);
+                    const __half *src = p.act + ((((bg * 2 + half) * ij_count + (size_t)ii * p.d2 + jj) * p.d3 + kin) * p.d4) * 8;
+                    uint8_t *dst = sb + ((size_t)half * p.npos_pad + (size_t)(kin - (k0 - PAD)) * p.P + p.lpad) * 16;
+                    bulk_g2s(dst, src, row_bytes, &full_bar[stage]);
+                }
+                if (lane == 0) {
+                    const __half *wsrc = p.wp + ((size_t)g * p.KS * p.KS + (size_t)t1 * p.KS + t2) * (p.w_bytes / 2);
+                    bulk_g2s(sb + p.data_bytes, wsrc, p.w_bytes, &full_bar[stage]);
+                }
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer (one thread) =====
+        int stage = 0;
+        uint32_t phase = 0;
+        bool first = true;
+        const uint32_t lbo_a = (uint32_t)p.npos_pad * 16u;
+        const uint32_t lbo_b = (uint32_t)p.N * 16u;
+        for (int t1 = 0; t1 < p.KS; ++t1) {
+            const int ii = i + t1 - PAD;
+            if (ii < 0 || ii >= p.d1) continue;
+            for (int t2 = 0; t2 < p.KS; ++t2) {
+                const int jj = j + t2 - PAD;
+                if (jj < 0 || jj >= p.d2) continue;
+                mbar_wait(&full_bar[stage], phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                if (lane == 0) {
+                    const uint32_t sa = smem_u32(stage0 + (size_t)stage * p.stage_bytes);
+                    const uint32_t sw = sa + p.data_bytes;
+                    for (int ks = 0; ks < p.KSTEPS; ++ks) {
+                        const uint64_t bdesc = make_desc(sw + (uint32_t)ks * 2u * lbo_b, lbo_b, 128u);
+                        for (int t = 0; t < p.NT; ++t) {
+                            const uint64_t adesc = make_desc(sa + (uint32_t)(t * 128 + p.aoff[ks]) * 16u, lbo_a, 128u);
+                            umma_f16(tmem_base + (uint32_t)(t * p.N), adesc, bdesc, p.idesc, (first && ks == 0) ? 0u : 1u);
+                        }
+                    }
+                    umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
+                }
+                __syncwarp();
+                first = false;
+                if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
+        }
+        if (lane == 0) umma_commit(&accum_bar);
+        __syncwarp();
+    } else {
+        // ===== epilogue (warps 2..5 <-> TMEM lane quadrants warp%4) =====
+        const int q = warp & 3;
+        const int et = threadIdx.x - 64;                 // 0..127
+        mbar_wait(&accum_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        if (p.CoutPad >= 16) {
+            // column group gi = 16 out-channels of one folded tap: out[m - shift_gi][o] += D[m][gi*16 + o].
+            // Within a group every thread owns a distinct row; groups are separated by a barrier.
+            for (int t = 0; t < p.NT; ++t) {
+                const int m = t * 128 + q * 32 + lane;
+                for (int gi = 0; gi < p.NG; ++gi) {
+                    float v[16];
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.N + gi * 16), v);
+                    const int dest = m - s_gshift[gi];
+                    if (dest >= 0) {
+                        float4 *dst = reinterpret_cast<float4 *>(outbuf + (size_t)dest * kOutStride);
+#pragma unroll
+                        for (int w4 = 0; w4 < 4; ++w4) {
+                            float4 a = dst[w4];
+                            a.x += v[4 * w4 + 0]; a.y += v[4 * w4 + 1]; a.z += v[4 * w4 + 2]; a.w += v[4 * w4 + 3];
+                            dst[w4] = a;
+                        }
+                    }
+                    asm volatile("bar.sync 1, 128;" ::: "memory");
+                }
+            }
+        } else {
+            // single out-channel: one column per folded (d3,d4) tap.  Each warp accumulates into its
+            // own copy of the plane (stride 1), so no cross-warp ordering is needed; the store sums them.
+            float *mine = outbuf + (size_t)q * out_rows;
+            for (int t = 0; t < p.NT; ++t) {
+                const int m = t * 128 + q * 32 + lane;
+                for (int c0 = 0; c0 < p.NG; c0 += 16) {
+                    float v[16];
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.N + c0), v);
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) {
+                        if (c0 + u < p.NG) {
+                            const int dest = m - s_gshift[c0 + u];
+                            if (dest >= 0) mine[dest] += v[u];
+                        }
+                        __syncwarp();
+                    }
+                }
+            }
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        // ---- store: planar output, coalesced along l -----------------------------------------
+        const size_t vol = ij_count * plane_pos;
+        const int total = p.Cout * rows_out * p.d4;
+        for (int e = et; e < total; e += 128) {
+            const int l = e % p.d4;
+            const int rr = (e / p.d4) % rows_out;
+            const int o = e / (p.d4 * rows_out);
+            const int row = rr * p.P + l;
+            float v;
+            if (p.CoutPad >= 16) v = outbuf[(size_t)row * kOutStride + o];
+            else v = outbuf[row] + outbuf[out_rows + row] + outbuf[2 * out_rows + row] + outbuf[3 * out_rows + row];
+            if (p.relu) v = fmaxf(v, 0.f);
+            const size_t off = ((size_t)b * p.G * p.Cout + (size_t)g * p.Cout + o) * vol +
+                               ((size_t)i * p.d2 + j) * plane_pos + (size_t)(k0 + rr) * p.d4 + l;
+            if (p.mask) {
+                const float mv = p.mask_f16 ? __half2float(((const __half *)p.mask)[off]) : ((const float *)p.mask)[off];
+                if (!(mv > 0.f)) v = 0.f;
+            }
+            if (p.out_f16) ((__half *)p.out)[off] = __float2half_rn(v);
+            else ((float *)p.out)[off] = v;
+        }
+    }
+
+    // ---- teardown ------------------------------------------------------------------------------
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// operand packing
+// ---------------------------------------------------------------------------------------------
+// planar [B, Gx*Cin, vol] (T) -> channel-blocked fp16 [B*Gx][2][vol][8].
+// taps_as_channels (mode M3, Cin == 1): channel c' of position (.., l) is x[.., l + c' - pad].
+template <typename T>
+__global__ void __launch_bounds__(256)
+pack_act_kernel(const T *__restrict__ x, __half *__restrict__ act, int Cin, size_t vol, int d4, int taps, int pad) {
+    const size_t bg = blockIdx.y;
+    const int half = blockIdx.z;
+    for (size_t pos = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pos < vol; pos += (size_t)gridDim.x * blockDim.x) {
+        __align__(16) __half v[8];
+        if (taps == 0) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int ch = half * 8 + c;
+                v[c] = ch < Cin ? __float2half_rn(ldf(x + (bg * Cin + ch) * vol + pos)) : __float2half_rn(0.f);
+            }
+        } else {
+            const int l = (int)(pos % d4);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int tap = half * 8 + c;
+                const int ll = l + tap - pad;
+                v[c] = (tap < taps && ll >= 0 && ll < d4) ? __float2half_rn(ldf(x + bg * vol + pos + (tap - pad)))
+                                                           : __float2half_rn(0.f);
+            }
+        }
+        *reinterpret_cast<uint4 *>(act + ((bg * 2 + half) * vol + pos) * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
+struct TcPackW {
+    PackDesc d;
+    int mode;       // 1,2,3
+    int KSTEPS, N, CoutPad;
+};
+
+// -> [G][k*k][KSTEPS][2][N][8] fp16
+__global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict__ wp, TcPackW a) {
+    const int k = a.d.k;
+    const long long total = (long long)a.d.G_e * k * k * a.KSTEPS * 2 * a.N * 8;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        long long r = idx;
+        const int c8 = (int)(r % 8); r /= 8;
+        const int n = (int)(r % a.N); r /= a.N;
+        const int half = (int)(r % 2); r /= 2;
+        const int ks = (int)(r % a.KSTEPS); r /= a.KSTEPS;
+        const int t2 = (int)(r % k); r /= k;
+        const int t1 = (int)(r % k); r /= k;
+        const int g = (int)r;
+        const int kch = half * 8 + c8;
+        int oe, ci, t3, t4;
+        bool ok = true;
+        if (a.mode == 1) {          // N = (t4, o), K-step = t3, channel = ci
+            t3 = ks; t4 = n / a.CoutPad; oe = n % a.CoutPad; ci = kch;
+        } else if (a.mode == 2) {   // N = (t3, t4), single out channel, channel = ci
+            t3 = n / k; t4 = n % k; oe = 0; ci = kch;
+            ok = n < k * k;
+        } else {                    // N = (t3, o), channel = t4 tap, single in channel
+            t3 = n / a.CoutPad; oe = n % a.CoutPad; t4 = kch; ci = 0;
+            ok = kch < k;
+        }
+        float v = 0.f;
+        if (ok && t3 < k && t4 < k && oe < a.d.Cout_e && ci < a.d.Cin_e)
+            v = w[packed_source_index(a.d, g, oe, ci, t1, t2, t3, t4)];
+        wp[idx] = __float2half_rn(v);
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+struct TcPlan {
+    int mode, KSTEPS, N, NG, CoutPad, P, lpad, R, nchunks, NT, npos_pad;
+    uint32_t data_bytes, w_bytes, stage_bytes;
+    size_t smem_bytes;
+    bool ok;
+};
+
+static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
+    TcPlan pl{};
+    pl.ok = false;
+    if (Cin_e > 16 || Cout_e > 16 || (k != 3 && k != 5)) return pl;
+    if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = 1; pl.lpad = 0; }
+    else if (Cout_e == 1)          { pl.mode = 2; pl.CoutPad = 1; pl.NG = k * k; pl.KSTEPS = 1; pl.lpad = k / 2; }
+    else                           { pl.mode = 1; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = k; pl.lpad = k / 2; }
+    pl.N = pl.mode == 2 ? ((k * k + 15) / 16) * 16 : k * 16;
+    pl.P = d4 + k - 1;
+    if (pl.P * 16 > 65535 * 16) return pl;
+    const int max_aoff = pl.mode == 1 ? (k - 1) * pl.P : 0;
+    const int max_shift = pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : (k - 1) * pl.P);
+    pl.w_bytes = (uint32_t)pl.KSTEPS * 2u * pl.N * 16u;
+    auto fit = [&](int R, TcPlan &o) {
+        const int mrows = (R - 1) * o.P + d4 + max_shift;
+        const int NT = (mrows + 127) / 128;
+        if (NT * o.N > 512) return false;
+        int npos = NT * 128 + max_aoff;
+        const int need = (R + k - 1) * o.P;
+        if (need > npos) npos = need;
+        npos = ((npos + 7) / 8) * 8;
+        if (npos > 16383) return false;                      // 14-bit LBO field (16 B units)
+        const uint32_t data = 2u * npos * 16u;
+        const uint32_t stage = ((data + o.w_bytes + 127) / 128) * 128;
+        const size_t outb = o.CoutPad >= 16 ? (size_t)NT * 128 * kOutStride * sizeof(float) : (size_t)NT * 128 * 4 * sizeof(float);
+        const size_t smem = (size_t)kStages * stage + outb;
+        if (smem > 220 * 1024) return false;
+        o.R = R; o.NT = NT; o.npos_pad = npos; o.data_bytes = data; o.stage_bytes = stage; o.smem_bytes = smem;
+        return true;
+    };
+    for (int R = d3; R >= 1; --R) {
+        if (!fit(R, pl)) continue;
+        pl.nchunks = (d3 + R - 1) / R;
+        const int balanced = (d3 + pl.nchunks - 1) / pl.nchunks;    // equal chunks; smaller R always fits too
+        if (!fit(balanced, pl)) return pl;
+        pl.ok = true;
+        break;
+    }
+    return pl;
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
+
+size_t conv4d_tc_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric) {
+    const size_t vol = (size_t)d1 * d2 * d3 * d4;
+    const int G = symmetric ? 2 : 1;
+    (void)Cin; (void)Cout;
+    // activations: up to G groups, 16 channels fp16 each; weights: largest N is 5*16=80 -> bound generously
+    const size_t act = (size_t)B * G * 2 * vol * 16;
+    const size_t wts = (size_t)G * k * k * k * 2 * 96 * 16;
+    return align256(act) + align256(wts) + 512;
+}
+
+static bool tc_supported(int Cin_e, int Cout_e, int k, int d3, int d4) { return tc_plan(Cin_e, Cout_e, k, d3, d4).ok; }
+
+// runs one effective convolution on the tensor cores; returns 2 when the shape is unsupported
+static int run_tc(const void *x, const float *w, const float *bias, const void *mask, void *y, void *scratch,
+                  PackDesc d, int B, int Gx, int d1, int d2, int d3, int d4, int relu, int dtype, cudaStream_t st) {
+    const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4);
+    if (!pl.ok) return 2;
+    const size_t vol = (size_t)d1 * d2 * d3 * d4;
+    __half *act = reinterpret_cast<__half *>(scratch);
+    __half *wp = reinterpret_cast<__half *>((uint8_t *)scratch + align256((size_t)B * Gx * 2 * vol * 16));
+
+    // 1. activations -> channel-blocked fp16
+    {
+        unsigned gx = (unsigned)((vol + 255) / 256 < 4096 ? (vol + 255) / 256 : 4096);
+        dim3 grid(gx, B * Gx, 2);
+        NC_CHECK(B * Gx <= 65535, "conv4d(tc): batch too large");
+        const int taps = pl.mode == 3 ? d.k : 0;
+        if (dtype == NCNET_F32)
+            pack_act_kernel<float><<<grid, 256, 0, st>>>((const float *)x, act, d.Cin_e, vol, d4, taps, d.k / 2);
+        else
+            pack_act_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, act, d.Cin_e, vol, d4, taps, d.k / 2);
+        NC_LAUNCH_OK("pack_act_kernel");
+    }
+    // 2. weights
+    {
+        TcPackW a{};
+        a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad;
+        const long long total = (long long)d.G_e * d.k * d.k * pl.KSTEPS * 2 * pl.N * 8;
+        const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
+        pack_w_tc_kernel<<<blocks, 256, 0, st>>>(w, wp, a);
+        NC_LAUNCH_OK("pack_w_tc_kernel");
+    }
+    // 3. the implicit GEMM
+    TcArgs a{};
+    a.act = act; a.wp = wp; a.bias = bias; a.mask = mask; a.out = y;
+    a.B = B; a.G = d.G_e; a.Gx = Gx; a.Cout = d.Cout_e; a.CoutPad = pl.CoutPad;
+    a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = d.k; a.P = pl.P; a.lpad = pl.lpad;
+    a.R = pl.R; a.nchunks = pl.nchunks; a.NT = pl.NT; a.N = pl.N; a.NG = pl.NG; a.KSTEPS = pl.KSTEPS;
+    a.npos_pad = pl.npos_pad; a.relu = relu; a.out_f16 = dtype == NCNET_F16; a.mask_f16 = dtype == NCNET_F16;
+    a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes;
+    // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
+    a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    for (int ks = 0; ks < kMaxKSteps; ++ks) a.aoff[ks] = (pl.mode == 1 && ks < d.k) ? ks * pl.P : 0;
+    for (int gi = 0; gi < kMaxGroups; ++gi) {
+        int s = 0;
+        if (gi < pl.NG) {
+            if (pl.mode == 1) s = gi;                                   // group = d4 tap
+            else if (pl.mode == 2) s = (gi / d.k) * pl.P + (gi % d.k);  // group = (d3, d4)
+            else s = gi * pl.P;                                         // group = d3 tap
+        }
+        a.gshift[gi] = s;
+    }
+    cudaError_t e = cudaFuncSetAttribute(conv4d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes);
+    NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
+    const long long ctas = (long long)B * d.G_e * d1 * d2 * pl.nchunks;
+    NC_CHECK(ctas < (1ll << 31), "conv4d(tc): grid too large");
+    conv4d_tc_kernel<<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a);
+    NC_LAUNCH_OK("conv4d_tc_kernel");
+    return 0;
+}
+
+int conv4d_tc_fwd(const void *x, const float *w, const float *bias, void *y, void *scratch, int B, int Cin, int Cout,
+                  int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input, int relu,
+                  int dtype, cudaStream_t st) {
+    PackDesc d{};
+    d.Cin = Cin; d.Cout = Cout; d.k = k; d.w_layout = w_layout; d.dgrad = 0; d.merge_groups = 0;
+    d.G_e = symmetric ? 2 : 1; d.Cin_e = Cin; d.Cout_e = Cout;
+    const int Gx = (symmetric && !shared_input) ? 2 : 1;
+    return run_tc(x, w, bias, nullptr, y, scratch, d, B, Gx, d1, d2, d3, d4, relu, dtype, st);
+}
+
+int conv4d_tc_dgrad(const void *gy, const float *w, const void *mask, void *gx, void *scratch, int B, int Cin,
+                    int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
+                    int dtype, cudaStream_t st) {
+    PackDesc d{};
+    d.Cin = Cin; d.Cout = Cout; d.k = k; d.w_layout = w_layout; d.dgrad = 1;
+    const int G = symmetric ? 2 : 1;
+    int Gx;
+    if (G == 2 && shared_input) { d.merge_groups = 1; d.G_e = 1; d.Cin_e = 2 * Cout; d.Cout_e = Cin; Gx = 1; }
+    else { d.merge_groups = 0; d.G_e = G; d.Cin_e = Cout; d.Cout_e = Cin; Gx = G; }
+    return run_tc(gy, w, nullptr, mask, gx, scratch, d, B, Gx, d1, d2, d3, d4, 0, dtype, st);
+}
+
+bool conv4d_tc_supports(int Cin_e, int Cout_e, int k, int d3, int d4) { return tc_supported(Cin_e, Cout_e, k, d3, d4); }
+
 }  // namespace ncnet
