@@ -82,8 +82,10 @@ int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t 
  * transposed volume and transposing back.  shared_input!=0: both groups read the same
  * Cin channels (Gin=1, first layer); else group g reads channels [g*Cin,(g+1)*Cin).
  * relu!=0 fuses max(0,.) after the bias.  mode: NCNET_CONV_FP32 / NCNET_CONV_TC16.
- * scratch: ncnet_conv4d_scratch_bytes(...) bytes (re-laid-out weights). */
-size_t ncnet_conv4d_scratch_bytes(int Cin, int Cout, int k, int symmetric, int mode);
+ * scratch: ncnet_conv4d_scratch_bytes(...) bytes (re-laid-out weights; in TC16 mode also the
+ * channel-blocked fp16 copy of the input).  One query covers fwd and dgrad of the layer. */
+size_t ncnet_conv4d_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                                  int symmetric, int mode);
 int ncnet_conv4d_fwd(const void *x, const float *weight, const float *bias, void *y, void *scratch,
                      int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
                      int w_layout, int symmetric, int shared_input, int relu, int dtype, int mode,

@@ -36,10 +36,11 @@ using namespace ncnet;
 extern "C" int ncnet_version(void) { return 100; }   // 0.1.0
 extern "C" const char *ncnet_last_error(void) { return last_error_buf(); }
 
-extern "C" size_t ncnet_conv4d_scratch_bytes(int Cin, int Cout, int k, int symmetric, int mode) {
+extern "C" size_t ncnet_conv4d_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                                             int symmetric, int mode) {
     size_t a = conv4d_fp32_scratch_bytes(Cin, Cout, k, symmetric);
     if (mode == NCNET_CONV_TC16) {
-        size_t b = conv4d_tc_scratch_bytes(Cin, Cout, k, symmetric);
+        size_t b = conv4d_tc_scratch_bytes(B, Cin, Cout, d1, d2, d3, d4, k, symmetric);
         return a > b ? a : b;
     }
     return a;
@@ -51,9 +52,11 @@ extern "C" int ncnet_conv4d_fwd(const void *x, const float *weight, const float 
     NC_CHECK(x && weight && y && scratch, "conv4d_fwd: null pointer");
     if (check_conv("conv4d_fwd", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, dtype, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
-    if (mode == NCNET_CONV_TC16)
-        return conv4d_tc_fwd(x, weight, bias, y, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
-                             shared_input, relu, dtype, st);
+    if (mode == NCNET_CONV_TC16) {
+        const int rc = conv4d_tc_fwd(x, weight, bias, y, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+                                     shared_input, relu, dtype, st);
+        if (rc != 2) return rc;      // 2: shape outside the tensor-core kernel's envelope -> CUDA-core kernel
+    }
     return conv4d_fp32_fwd(x, weight, bias, y, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
                            shared_input, relu, dtype, st);
 }
@@ -64,9 +67,11 @@ extern "C" int ncnet_conv4d_dgrad(const void *grad_y, const float *weight, const
     NC_CHECK(grad_y && weight && grad_x && scratch, "conv4d_dgrad: null pointer");
     if (check_conv("conv4d_dgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, dtype, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
-    if (mode == NCNET_CONV_TC16)
-        return conv4d_tc_dgrad(grad_y, weight, y_prev_mask, grad_x, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout,
-                               symmetric, shared_input, dtype, st);
+    if (mode == NCNET_CONV_TC16) {
+        const int rc = conv4d_tc_dgrad(grad_y, weight, y_prev_mask, grad_x, scratch, B, Cin, Cout, d1, d2, d3, d4, k,
+                                       w_layout, symmetric, shared_input, dtype, st);
+        if (rc != 2) return rc;
+    }
     return conv4d_fp32_dgrad(grad_y, weight, y_prev_mask, grad_x, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout,
                              symmetric, shared_input, dtype, st);
 }

@@ -190,8 +190,8 @@ def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode):
     g = 2 if symmetric else 1
     y = torch.empty(bsz, g * cout, d1, d2, d3, d4, device=x.device, dtype=x.dtype)
     L = _cabi.lib()
-    scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(cin, cout, k, int(symmetric), mode), device=x.device,
-                          dtype=torch.uint8)
+    scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(bsz, cin, cout, d1, d2, d3, d4, k, int(symmetric), mode),
+                          device=x.device, dtype=torch.uint8)
     log = EVENT_LOG is not None and cin == 16 and cout == 16
     with torch.cuda.device(x.device):
         if log:
@@ -213,8 +213,8 @@ def _conv_dgrad(gy, w32, mask, layout, symmetric, shared_input, mode):
     gin = 1 if (shared_input or not symmetric) else 2
     gx = torch.empty(bsz, gin * cin, d1, d2, d3, d4, device=gy.device, dtype=gy.dtype)
     L = _cabi.lib()
-    scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(cin, cout, k, int(symmetric), mode), device=gy.device,
-                          dtype=torch.uint8)
+    scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(bsz, cin, cout, d1, d2, d3, d4, k, int(symmetric), mode),
+                          device=gy.device, dtype=torch.uint8)
     with torch.cuda.device(gy.device):
         _cabi.check(L.ncnet_conv4d_dgrad(_ptr(gy), _ptr(w32), _ptr(mask), _ptr(gx), _ptr(scratch), bsz, cin, cout, d1, d2,
                                          d3, d4, k, layout, int(symmetric), int(shared_input), _dt(gy), mode, _stream()),

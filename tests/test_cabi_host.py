@@ -39,7 +39,7 @@ def test_argument_validation_without_gpu():
     rc = lib.ncnet_maxpool4d_fwd(one, one, one, one, one, one, 5, 4, 4, 4, 2, 8, 0, None)
     assert rc != 0 and b"divisible" in lib.ncnet_last_error()
     assert lib.ncnet_mutual_matching_keys_bytes(2, 10, 12) == 2 * 22 * 8
-    assert lib.ncnet_conv4d_scratch_bytes(16, 16, 5, 1, 0) >= 2 * 16 * 16 * 625 * 4
+    assert lib.ncnet_conv4d_scratch_bytes(1, 16, 16, 25, 25, 25, 25, 5, 1, 0) >= 2 * 16 * 16 * 625 * 4
 
 
 def test_cpu_tensors_raise_no_fallback():
