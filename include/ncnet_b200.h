@@ -72,6 +72,21 @@ int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys, int B, int
 int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t *keys, float *sums,
                               void *grad_x, int B, int nA, int nB, int in_groups, int dtype, void *stream);
 
+/* MutualMatching forward for callers that cannot allocate device memory (no counterpart in the
+ * reference: it exists for hosts such as inference plugins or real-time loops whose contract
+ * forbids cudaMalloc where the head runs, so they have no way to provide the `keys` table).
+ * Same result as ncnet_mutual_matching_fwd; the key table is a 2 MiB array built into the library
+ * (held on every GPU that loads it, until the process exits), so B*(nA+nB) must be <= 262144 --
+ * larger problems are rejected with an error.  Calls no cudaMalloc/cudaFree or allocating routine.
+ * The first call on each device looks up the table's device address (cudaGetSymbolAddress); make
+ * that first call with the device current and before starting any stream capture.  All calls on a
+ * device share the one table: it still holds the previous call's maxima on entry (the part a call
+ * uses is cleared on its stream first), and two calls whose kernels overlap on the GPU -- different
+ * streams without an ordering between them -- race on it.  The arg-max keys are not returned, so
+ * this variant serves inference; the backward pass needs ncnet_mutual_matching_fwd. */
+int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, int nA, int nB, int in_groups,
+                                      int dtype, void *stream);
+
 /* conv4d / Conv4d.forward -- lib/conv4d.py:11-51,81-82  (+ fused ReLU, lib/model.py:137-138,
  * + the symmetric second branch of NeighConsensus.forward, lib/model.py:147).
  *

@@ -30,6 +30,7 @@ SIGNATURES = {
     "ncnet_mutual_matching_keys_bytes": (_sz, [_i, _i, _i]),
     "ncnet_mutual_matching_fwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "ncnet_mutual_matching_fwd_noalloc": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_conv4d_scratch_bytes": (_sz, [_i] * 10),
     "ncnet_conv4d_fwd": (_i, [_p, _p, _p, _p, _p] + [_i] * 14 + [_p]),
     "ncnet_conv4d_dgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 13 + [_p]),

@@ -282,3 +282,64 @@ extern "C" int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, cons
     if (dtype == NCNET_F16) return mm_bwd<__half>(x, grad_y, keys, sums, grad_x, B, nA, nB, in_groups, st);
     return fail("mutual_matching_bwd: unsupported dtype %d", dtype);
 }
+
+// ---------------------------------------------------------------------------------------------
+// Allocation-free variant of the forward pass.
+//
+// Who needs it: a host that is not allowed to allocate device memory at the point where it runs
+// the matching head -- for instance a plugin whose "enqueue" contract forbids cudaMalloc, a
+// real-time loop that must not take the allocator's locks, or a process whose whole device
+// budget was handed to another framework's memory pool.  Such a caller can own x and y but has
+// nowhere to get the (max, arg-max) key table from, so the table lives inside the library.
+//
+// The table is a file-scope device array: every GPU that loads this library carries these 2 MiB
+// until the process exits.  Host code cannot use the array's name as a pointer (on the host the
+// symbol is only a handle); the real device address is looked up once per device with
+// cudaGetSymbolAddress while that device is current, and that address is what the kernels get.
+// ---------------------------------------------------------------------------------------------
+namespace ncnet {
+
+constexpr size_t kStaticKeyCapacity = (size_t)1 << 18;      // 262 144 keys = 2 MiB
+static __device__ __align__(256) unsigned long long g_static_keys[kStaticKeyCapacity];
+
+constexpr int kMaxDevices = 64;
+static unsigned long long *g_static_keys_addr[kMaxDevices] = {};    // per device, filled on first use
+
+// Resolves (once per device) the device address of g_static_keys for the current device.
+static int static_keys_for_current_device(unsigned long long **out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    NC_CHECK(e == cudaSuccess, "mutual_matching_fwd_noalloc: cudaGetDevice: %s", cudaGetErrorString(e));
+    NC_CHECK(dev >= 0 && dev < kMaxDevices, "mutual_matching_fwd_noalloc: device ordinal %d out of range", dev);
+    unsigned long long *p = __atomic_load_n(&g_static_keys_addr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {
+        void *sym = nullptr;
+        e = cudaGetSymbolAddress(&sym, g_static_keys);      // this device's copy of the array
+        NC_CHECK(e == cudaSuccess && sym, "mutual_matching_fwd_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e));
+        p = static_cast<unsigned long long *>(sym);
+        __atomic_store_n(&g_static_keys_addr[dev], p, __ATOMIC_RELEASE);   // racing threads store the same value
+    }
+    *out = p;
+    return 0;
+}
+
+}  // namespace ncnet
+
+extern "C" int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, int nA, int nB, int in_groups,
+                                                 int dtype, void *stream) {
+    NC_CHECK(x && y, "mutual_matching_fwd_noalloc: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "mutual_matching_fwd_noalloc: bad shape B=%d nA=%d nB=%d", B, nA, nB);
+    NC_CHECK(in_groups == 1 || in_groups == 2, "mutual_matching_fwd_noalloc: in_groups must be 1 or 2");
+    const size_t need = (size_t)B * ((size_t)nA + (size_t)nB);
+    NC_CHECK(need <= kStaticKeyCapacity,
+             "mutual_matching_fwd_noalloc: B*(nA+nB) = %zu keys exceeds the built-in table of %zu; use "
+             "ncnet_mutual_matching_fwd with caller-provided keys",
+             need, kStaticKeyCapacity);
+    unsigned long long *keys = nullptr;
+    if (static_keys_for_current_device(&keys)) return 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    // mm_fwd clears the `need` keys it is about to use (they still hold the previous call's maxima)
+    if (dtype == NCNET_F32) return mm_fwd<float>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, st);
+    if (dtype == NCNET_F16) return mm_fwd<__half>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, st);
+    return fail("mutual_matching_fwd_noalloc: unsupported dtype %d", dtype);
+}
