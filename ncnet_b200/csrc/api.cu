@@ -78,8 +78,12 @@ extern "C" int ncnet_conv4d_dgrad(const void *grad_y, const float *weight, const
 
 extern "C" size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
                                                    int symmetric, int mode) {
-    (void)mode;
-    return conv4d_fp32_wgrad_scratch_bytes(B, Cin, Cout, d1, d2, d3, d4, k, symmetric);
+    size_t a = conv4d_fp32_wgrad_scratch_bytes(B, Cin, Cout, d1, d2, d3, d4, k, symmetric);
+    if (mode == NCNET_CONV_TC16) {
+        size_t b = conv4d_tc_wgrad_scratch_bytes(B, Cin, Cout, d1, d2, d3, d4, k, symmetric);
+        return a > b ? a : b;
+    }
+    return a;
 }
 
 extern "C" int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, float *grad_bias,
@@ -88,7 +92,11 @@ extern "C" int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad
     NC_CHECK(x && grad_y && grad_weight && scratch, "conv4d_wgrad: null pointer");
     if (check_conv("conv4d_wgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, dtype, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
-    // the weight gradient is a reduction over all positions; it runs on the fp32 path in both modes
+    if (mode == NCNET_CONV_TC16) {
+        const int rc = conv4d_tc_wgrad(x, grad_y, grad_weight, grad_bias, scratch, B, Cin, Cout, d1, d2, d3, d4, k,
+                                       w_layout, symmetric, shared_input, dtype, st);
+        if (rc != 2) return rc;      // 2: outside the tensor-core kernel's envelope -> CUDA-core kernel
+    }
     return conv4d_fp32_wgrad(x, grad_y, grad_weight, grad_bias, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout,
                              symmetric, shared_input, dtype, st);
 }

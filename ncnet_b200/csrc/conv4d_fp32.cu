@@ -591,6 +591,27 @@ static int launch_wgrad(WgradArgs a, const WgradPlan &w, cudaStream_t st) {
     return 0;
 }
 
+// shared tail of both wgrad back ends: slice partials -> reference layout (+ bias gradient)
+int wgrad_finish(const float *part, float *gw, float *gb, const void *gy, int S, int G, int B, int Cin, int Cout, int k,
+                 int cop, int w_layout, size_t vol, int dtype, cudaStream_t st) {
+    const int total = Cout * Cin * k * k * k * k;
+    unpack_wgrad_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, gw, S, G, Cin, Cout, k, cop, w_layout);
+    NC_LAUNCH_OK("unpack_wgrad_kernel");
+    if (gb) {
+        cudaError_t e = cudaMemsetAsync(gb, 0, Cout * sizeof(float), st);
+        NC_CHECK(e == cudaSuccess, "wgrad: memset bias: %s", cudaGetErrorString(e));
+        int chunks = (int)((vol + 65535) / 65536);
+        if (chunks < 1) chunks = 1;
+        NC_CHECK(B * G * Cout <= 65535, "wgrad: too many channels for bias grid");
+        if (dtype == NCNET_F32)
+            bias_grad_kernel<float><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const float *)gy, gb, Cout, G, vol, chunks);
+        else
+            bias_grad_kernel<__half><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const __half *)gy, gb, Cout, G, vol, chunks);
+        NC_LAUNCH_OK("bias_grad_kernel");
+    }
+    return 0;
+}
+
 template <typename T>
 static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout,
                      int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
@@ -609,21 +630,8 @@ static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *
     int rc = (k == 3) ? launch_wgrad<3, T>(a, w, st) : (k == 5 ? launch_wgrad<5, T>(a, w, st)
                                                               : fail("conv4d_wgrad: kernel size %d not supported", k));
     if (rc) return rc;
-    const int total = Cout * Cin * k * k * k * k;
-    unpack_wgrad_kernel<<<(total + 255) / 256, 256, 0, st>>>((const float *)scratch, gw, w.S, G, Cin, Cout, k, w.cop,
-                                                            w_layout);
-    NC_LAUNCH_OK("unpack_wgrad_kernel");
-    if (gb) {
-        e = cudaMemsetAsync(gb, 0, Cout * sizeof(float), st);
-        NC_CHECK(e == cudaSuccess, "wgrad: memset bias: %s", cudaGetErrorString(e));
-        const size_t vol = (size_t)d1 * d2 * d3 * d4;
-        int chunks = (int)((vol + 65535) / 65536);
-        if (chunks < 1) chunks = 1;
-        NC_CHECK(B * G * Cout <= 65535, "wgrad: too many channels for bias grid");
-        bias_grad_kernel<T><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const T *)gy, gb, Cout, G, vol, chunks);
-        NC_LAUNCH_OK("bias_grad_kernel");
-    }
-    return 0;
+    return wgrad_finish((const float *)scratch, gw, gb, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout,
+                        (size_t)d1 * d2 * d3 * d4, sizeof(T) == 4 ? NCNET_F32 : NCNET_F16, st);
 }
 
 int conv4d_fp32_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout,

@@ -22,6 +22,7 @@
 // sums, bias, ReLU / ReLU-mask, and store.
 #include "conv4d_tc.cuh"
 #include "conv4d_common.cuh"
+#include "tc_common.cuh"
 
 namespace ncnet {
 
@@ -48,69 +49,13 @@ struct TcArgs {
     int aoff[kMaxKSteps];   // A row offset (positions) per K-step
     int gshift[kMaxGroups]; // epilogue row shift per column group
     uint32_t stage_bytes, data_bytes, w_bytes;
+    long long *dbg;         // development only: per-CTA phase timestamps (8 per CTA) or null
 };
 
-__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
-
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-// bounded wait: a protocol bug traps (kernel error) instead of hanging the GPU
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-    const uint32_t addr = smem_u32(bar);
-    const long long t0 = clock64();
-    for (;;) {
-        uint32_t ok;
-        asm volatile(
-            "{\n\t.reg .pred p;\n\t"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
-            "selp.u32 %0, 1, 0, p;\n\t}"
-            : "=r"(ok) : "r"(addr), "r"(parity) : "memory");
-        if (ok) return;
-        if (clock64() - t0 > 4000000000ll) __trap();
-    }
-}
-__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
-                 ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ uint64_t make_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
-    // SWIZZLE_NONE K-major: core matrix = 8 rows x 16 B; LBO = stride between the two K halves,
-    // SBO = stride between 8-row groups; version field = 1 (sm_100)
-    uint64_t d = 0;
-    d |= (uint64_t)((saddr >> 4) & 0x3fff);
-    d |= (uint64_t)((lbo_bytes >> 4) & 0x3fff) << 16;
-    d |= (uint64_t)((sbo_bytes >> 4) & 0x3fff) << 32;
-    d |= (uint64_t)1 << 46;
-    return d;
-}
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "setp.ne.b32 p, %4, 0;\n\t"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-        ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
-}
-__device__ __forceinline__ void umma_commit(uint64_t *bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
-    uint32_t r[16];
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
-          "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr) : "memory");
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-    for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
-}
+using namespace tc;
 
 __global__ void __launch_bounds__(kTcThreads, 1)
-conv4d_tc_kernel(const TcArgs p) {
+conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar;
     __shared__ uint32_t tmem_base_s;
@@ -166,6 +111,8 @@ conv4d_tc_kernel(const TcArgs p) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
+    const long long t_start = clock64();
+#define TC_STAMP(slot) do { if (p.dbg && blockIdx.x < 4096) p.dbg[blockIdx.x * 8 + (slot)] = clock64() - t_start; } while (0)
 
     // list of valid (d1,d2) planes is implicit: both roles walk the same loop
     const size_t plane_pos = (size_t)p.d3 * p.d4;
@@ -175,11 +122,11 @@ conv4d_tc_kernel(const TcArgs p) {
         // ===== producer =====
         int stage = 0;
         uint32_t phase = 0;
-        const int kin0 = max(k0 - PAD, 0), kin1 = min(k0 + rows_out + PAD, p.d3);   // valid input rows
-        const int nrows = kin1 - kin0;
-        const uint32_t row_bytes = (uint32_t)p.d4 * 16u;
-        const uint32_t tx_bytes = 2u * nrows * row_bytes + p.w_bytes;
-        const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
+        const int box_rows = p.R + p.KS - 1;
+        const uint32_t half_bytes = (uint32_t)p.P * box_rows * 16u;       // one TMA tile: the halo'd plane chunk of one channel half
+        const uint32_t tx_bytes = 2u * half_bytes + p.w_bytes;
+        const int bg = b * p.Gx + (p.Gx == 1 ? 0 : g);
+        if (elect_one()) prefetch_tmap(&amap);
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
             if (ii < 0 || ii >= p.d1) continue;
@@ -187,19 +134,17 @@ conv4d_tc_kernel(const TcArgs p) {
                 const int jj = j + t2 - PAD;
                 if (jj < 0 || jj >= p.d2) continue;
                 mbar_wait(&empty_bar[stage], phase ^ 1);
-                uint8_t *sb = stage0 + (size_t)stage * p.stage_bytes;
-                if (lane == 0) mbar_expect_tx(&full_bar[stage], tx_bytes);
-                __syncwarp();
-                for (int r = lane; r < 2 * nrows; r += 32) {
-                    const int half = r / nrows, kin = kin0 + (r - half * nrows);
-                    const __half *src = p.act + ((((bg * 2 + half) * ij_count + (size_t)ii * p.d2 + jj) * p.d3 + kin) * p.d4) * 8;
-                    uint8_t *dst = sb + ((size_t)half * p.npos_pad + (size_t)(kin - (k0 - PAD)) * p.P + p.lpad) * 16;
-                    bulk_g2s(dst, src, row_bytes, &full_bar[stage]);
-                }
-                if (lane == 0) {
+                if (elect_one()) {
+                    uint8_t *sb = stage0 + (size_t)stage * p.stage_bytes;
+                    mbar_expect_tx(&full_bar[stage], tx_bytes);
+                    // rows/columns outside the volume arrive as zeros: that is the convolution's zero padding
+                    tma_tile_5d(sb, &amap, 0, -p.lpad, k0 - PAD, ii * p.d2 + jj, bg * 2 + 0, &full_bar[stage]);
+                    tma_tile_5d(sb + (size_t)p.npos_pad * 16, &amap, 0, -p.lpad, k0 - PAD, ii * p.d2 + jj, bg * 2 + 1,
+                                &full_bar[stage]);
                     const __half *wsrc = p.wp + ((size_t)g * p.KS * p.KS + (size_t)t1 * p.KS + t2) * (p.w_bytes / 2);
                     bulk_g2s(sb + p.data_bytes, wsrc, p.w_bytes, &full_bar[stage]);
                 }
+                __syncwarp();
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
         }
@@ -210,6 +155,8 @@ conv4d_tc_kernel(const TcArgs p) {
         bool first = true;
         const uint32_t lbo_a = (uint32_t)p.npos_pad * 16u;
         const uint32_t lbo_b = (uint32_t)p.N * 16u;
+        const uint32_t lbo_a_field = (lbo_a >> 4) << 16, lbo_b_field = (lbo_b >> 4) << 16;
+        const uint64_t desc_hi = ((uint64_t)((128u >> 4) | (1u << 14))) << 32;      // SBO = 128 B, descriptor version 1
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
             if (ii < 0 || ii >= p.d1) continue;
@@ -218,30 +165,44 @@ conv4d_tc_kernel(const TcArgs p) {
                 if (jj < 0 || jj >= p.d2) continue;
                 mbar_wait(&full_bar[stage], phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                if (lane == 0) {
-                    const uint32_t sa = smem_u32(stage0 + (size_t)stage * p.stage_bytes);
-                    const uint32_t sw = sa + p.data_bytes;
-                    for (int ks = 0; ks < p.KSTEPS; ++ks) {
-                        const uint64_t bdesc = make_desc(sw + (uint32_t)ks * 2u * lbo_b, lbo_b, 128u);
-                        for (int t = 0; t < p.NT; ++t) {
-                            const uint64_t adesc = make_desc(sa + (uint32_t)(t * 128 + p.aoff[ks]) * 16u, lbo_a, 128u);
-                            umma_f16(tmem_base + (uint32_t)(t * p.N), adesc, bdesc, p.idesc, (first && ks == 0) ? 0u : 1u);
+                if (lane == 0 && first) TC_STAMP(0);
+                // Descriptor arithmetic stays warp-uniform (no lane dependence) and only the low 32 bits
+                // change, so ptxas keeps it on the uniform datapath; lane 0 alone executes the MMAs.
+                const uint32_t sa4 = smem_u32(stage0 + (size_t)stage * p.stage_bytes) >> 4;
+                const uint32_t sw4 = sa4 + (p.data_bytes >> 4);
+                if (elect_one()) {
+#pragma unroll
+                for (int ks = 0; ks < kMaxKSteps; ++ks) {
+                    if (ks < p.KSTEPS) {
+                        const uint64_t bdesc = desc_hi | (uint64_t)(lbo_b_field | (sw4 + (uint32_t)ks * 2u * (lbo_b >> 4)));
+                        const uint32_t a_lo0 = lbo_a_field | (sa4 + (uint32_t)p.aoff[ks]);
+                        const uint32_t acc = (first && ks == 0) ? 0u : 1u;
+                        for (int t0 = 0; t0 < p.NT; t0 += 8) {
+#pragma unroll
+                            for (int u = 0; u < 8; ++u) {
+                                const int t = t0 + u;
+                                if (t < p.NT)
+                                    umma_f16(tmem_base + (uint32_t)(t * p.N), desc_hi | (uint64_t)(a_lo0 + (uint32_t)t * 128u),
+                                             bdesc, p.idesc, acc);
+                            }
                         }
                     }
-                    umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
+                }
+                umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
                 }
                 __syncwarp();
                 first = false;
                 if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
         }
-        if (lane == 0) umma_commit(&accum_bar);
+        if (elect_one()) { TC_STAMP(1); umma_commit(&accum_bar); }
         __syncwarp();
     } else {
         // ===== epilogue (warps 2..5 <-> TMEM lane quadrants warp%4) =====
         const int q = warp & 3;
         const int et = threadIdx.x - 64;                 // 0..127
         mbar_wait(&accum_bar, 0);
+        if (et == 0) TC_STAMP(2);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         if (p.CoutPad >= 16) {
             // column group gi = 16 out-channels of one folded tap: out[m - shift_gi][o] += D[m][gi*16 + o].
@@ -285,29 +246,33 @@ conv4d_tc_kernel(const TcArgs p) {
             }
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) TC_STAMP(3);
         // ---- store: planar output, coalesced along l -----------------------------------------
         const size_t vol = ij_count * plane_pos;
-        const int total = p.Cout * rows_out * p.d4;
-        for (int e = et; e < total; e += 128) {
-            const int l = e % p.d4;
-            const int rr = (e / p.d4) % rows_out;
-            const int o = e / (p.d4 * rows_out);
-            const int row = rr * p.P + l;
-            float v;
-            if (p.CoutPad >= 16) v = outbuf[(size_t)row * kOutStride + o];
-            else v = outbuf[row] + outbuf[out_rows + row] + outbuf[2 * out_rows + row] + outbuf[3 * out_rows + row];
-            if (p.relu) v = fmaxf(v, 0.f);
-            const size_t off = ((size_t)b * p.G * p.Cout + (size_t)g * p.Cout + o) * vol +
-                               ((size_t)i * p.d2 + j) * plane_pos + (size_t)(k0 + rr) * p.d4 + l;
-            if (p.mask) {
-                const float mv = p.mask_f16 ? __half2float(((const __half *)p.mask)[off]) : ((const float *)p.mask)[off];
-                if (!(mv > 0.f)) v = 0.f;
+        const int ew = et >> 5;                                   // epilogue warp 0..3
+        const int npairs = p.Cout * rows_out;                     // (channel, output row) pairs, one warp each
+        for (int pr = ew; pr < npairs; pr += 4) {
+            const int o = pr / rows_out, rr = pr - o * rows_out;
+            const size_t off0 = ((size_t)b * p.G * p.Cout + (size_t)g * p.Cout + o) * vol +
+                                ((size_t)i * p.d2 + j) * plane_pos + (size_t)(k0 + rr) * p.d4;
+            for (int l = lane; l < p.d4; l += 32) {
+                const int row = rr * p.P + l;
+                float v;
+                if (p.CoutPad >= 16) v = outbuf[(size_t)row * kOutStride + o];
+                else v = outbuf[row] + outbuf[out_rows + row] + outbuf[2 * out_rows + row] + outbuf[3 * out_rows + row];
+                if (p.relu) v = fmaxf(v, 0.f);
+                const size_t off = off0 + l;
+                if (p.mask) {
+                    const float mv = p.mask_f16 ? __half2float(((const __half *)p.mask)[off]) : ((const float *)p.mask)[off];
+                    if (!(mv > 0.f)) v = 0.f;
+                }
+                if (p.out_f16) ((__half *)p.out)[off] = __float2half_rn(v);
+                else ((float *)p.out)[off] = v;
             }
-            if (p.out_f16) ((__half *)p.out)[off] = __float2half_rn(v);
-            else ((float *)p.out)[off] = v;
         }
     }
 
+    if (threadIdx.x == 64) TC_STAMP(4);
     // ---- teardown ------------------------------------------------------------------------------
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -390,6 +355,8 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
+long long *g_tc_debug_buffer = nullptr;     // set through ncnet_debug_set_tc_timing (development only)
+
 struct TcPlan {
     int mode, KSTEPS, N, NG, CoutPad, P, lpad, R, nchunks, NT, npos_pad;
     uint32_t data_bytes, w_bytes, stage_bytes;
@@ -491,6 +458,7 @@ static int run_tc(const void *x, const float *w, const float *bias, const void *
     a.npos_pad = pl.npos_pad; a.relu = relu; a.out_f16 = dtype == NCNET_F16; a.mask_f16 = dtype == NCNET_F16;
     a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes;
     // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
+    a.dbg = g_tc_debug_buffer;
     a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     for (int ks = 0; ks < kMaxKSteps; ++ks) a.aoff[ks] = (pl.mode == 1 && ks < d.k) ? ks * pl.P : 0;
     for (int gi = 0; gi < kMaxGroups; ++gi) {
@@ -506,7 +474,9 @@ static int run_tc(const void *x, const float *w, const float *bias, const void *
     NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
     const long long ctas = (long long)B * d.G_e * d1 * d2 * pl.nchunks;
     NC_CHECK(ctas < (1ll << 31), "conv4d(tc): grid too large");
-    conv4d_tc_kernel<<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a);
+    CUtensorMap amap;
+    if (make_act_tmap(&amap, act, (size_t)B * Gx * 2, d1, d2, d3, d4, pl.P, pl.R + d.k - 1)) return 1;
+    conv4d_tc_kernel<<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a, amap);
     NC_LAUNCH_OK("conv4d_tc_kernel");
     return 0;
 }
@@ -536,3 +506,6 @@ int conv4d_tc_dgrad(const void *gy, const float *w, const void *mask, void *gx, 
 bool conv4d_tc_supports(int Cin_e, int Cout_e, int k, int d3, int d4) { return tc_supported(Cin_e, Cout_e, k, d3, d4); }
 
 }  // namespace ncnet
+
+// development hook (not part of include/ncnet_b200.h): device buffer of 4096*8 int64 phase timestamps
+extern "C" void ncnet_debug_set_tc_timing(void *device_buffer) { ncnet::g_tc_debug_buffer = (long long *)device_buffer; }

@@ -1,0 +1,407 @@
+// Conv4d weight gradient on the tensor cores (mode NCNET_CONV_TC16).
+//
+//   dW[o,c,t1,t2,t3,t4] = sum_{b,i,j,k,l} G[b,o,i,j,k,l] * X[b,c,i+t1-p,j+t2-p,k+t3-p,l+t4-p]
+//
+// The contraction runs over POSITIONS, so both operands are "MN-major" for tcgen05: in the
+// channel-blocked fp16 layout ([half][position][8 channels], 16 B per position) eight consecutive
+// positions are the eight K rows of a core matrix and the 8 channels are its 16 B.  Channels alone
+// would give M = N = 16; the MMA's M/N "8-row groups" are addressed with ONE stride (SBO), which is
+// exactly what a tap shift is, so the groups of an operand are 8 shifted views of the same staged
+// plane (5 of them are taps, 3 are ignored):
+//   V2 (Cin,Cout<=16): A = X half hc, groups = t4 shifts (+16 B);  B = G half ho, groups = t3 row
+//                      shifts (+P*16 B, stored reversed).  D[hc][ho] (64x64) = dW[o,c,t3,t4] of one
+//                      (t1,t2), accumulated in TMEM over every plane of the CTA's slice.
+//   V1 (Cin == 1):     A = X' whose 8 "channels" are the t4 taps (im2col by the pack kernel),
+//                      groups = t3 row shifts;  B = G, both halves as the two N groups (N = 16).
+//   V3 (Cout == 1):    A as V2;  B = G8 whose 8 "channels" are the t2 taps (pack kernel, shifts along
+//                      the second volume axis), groups = t3 row shifts: one CTA covers all t2.
+// CTA = (group, t1[, t2], slice of the (b,i,j) plane list); 3-stage cp.async.bulk ring, one thread
+// issues the MMAs, the accumulators are flushed once at the end as per-slice partial sums which
+// unpack_wgrad_kernel reduces deterministically (shared with the fp32 path).
+#include "conv4d_tc.cuh"
+#include "conv4d_common.cuh"
+#include "tc_common.cuh"
+
+namespace ncnet {
+
+constexpr int kWgThreads = 192;
+constexpr int kWgStages = 3;
+
+struct WgArgs {
+    const __half *xa;   // A side, blocked [B*GxA][HA][d1*d2][d3][d4][8]
+    const __half *gb;   // B side, blocked [B*G][HB][d1*d2][d3][d4][8]
+    float *part;        // [S][G][Cin][k][k][k][k][cop]
+    int B, G, GxA, HA, HB;
+    int d1, d2, d3, d4, KS, P;
+    int variant, NAv, NBv, N, nb_copy;      // nb_copy: B halves copied per stage
+    uint32_t a_sbo, b_sbo;
+    int a_row0, a_col0, b_row0;
+    int npos_a, npos_b, nkb;
+    int S, Cin, Cout, cop;
+    uint32_t idesc, tmem_cols;
+    uint32_t stage_bytes, a_bytes, b_start;
+};
+
+using namespace tc;
+
+// which (x plane, g plane) pair the CTA's tap pairs with output plane index `pl`; false = skipped
+__device__ __forceinline__ bool wg_pair(const WgArgs &p, int pl, int t1, int t2, int &b, size_t &ij_x, size_t &ij_g) {
+    const int PAD = p.KS / 2;
+    b = pl / (p.d1 * p.d2);
+    const int ij = pl - b * (p.d1 * p.d2);
+    const int i = ij / p.d2, j = ij - i * p.d2;
+    if (p.variant == 3) {       // pl enumerates X planes (i',j'); G8 plane = (i' - t1 + pad, j'), t2 lives in its channels
+        const int ig = i - t1 + PAD;
+        if (ig < 0 || ig >= p.d1) return false;
+        ij_x = (size_t)i * p.d2 + j;
+        ij_g = (size_t)ig * p.d2 + j;
+        return true;
+    }
+    const int ii = i + t1 - PAD, jj = j + t2 - PAD;
+    if (ii < 0 || ii >= p.d1 || jj < 0 || jj >= p.d2) return false;
+    ij_x = (size_t)ii * p.d2 + jj;
+    ij_g = (size_t)i * p.d2 + j;
+    return true;
+}
+
+__global__ void __launch_bounds__(kWgThreads, 1)
+conv4d_tc_wgrad_kernel(const WgArgs p, const __grid_constant__ CUtensorMap xmap,
+                       const __grid_constant__ CUtensorMap gmap) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[kWgStages], empty_bar[kWgStages], accum_bar;
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int by = blockIdx.y;
+    int t2 = 0;
+    if (p.variant != 3) { t2 = by % p.KS; by /= p.KS; }
+    const int t1 = by % p.KS; by /= p.KS;
+    const int g = by;
+    const int s = blockIdx.x;
+    const int nplanes = p.B * p.d1 * p.d2;
+    const int per = (nplanes + p.S - 1) / p.S;
+    const int pbeg = s * per, pend = min(nplanes, pbeg + per);
+
+    if (warp == 1 && lane == 0) {
+        for (int st = 0; st < kWgStages; ++st) { mbar_init(&full_bar[st], 1); mbar_init(&empty_bar[st], 1); }
+        mbar_init(&accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(p.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {   // zero the whole ring once: halo rows/columns and tails are never written by the row copies
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        uint4 *d = reinterpret_cast<uint4 *>(smem);
+        const uint32_t n16 = (uint32_t)kWgStages * p.stage_bytes / 16;
+        for (uint32_t e = threadIdx.x; e < n16; e += kWgThreads) d[e] = z;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+
+    if (warp == 0) {
+        // ===== producer =====
+        int stage = 0;
+        uint32_t phase = 0;
+        // one TMA tile per staged channel half: X with its halo (zeros outside the volume), G as is
+        const uint32_t a_tile = (uint32_t)p.P * (p.d3 + p.KS - 1) * 16u, b_tile = (uint32_t)p.P * p.d3 * 16u;
+        const uint32_t tx = (uint32_t)p.NAv * a_tile + (uint32_t)p.nb_copy * b_tile;
+        if (elect_one()) { prefetch_tmap(&xmap); prefetch_tmap(&gmap); }
+        for (int pl = pbeg; pl < pend; ++pl) {
+            int b; size_t ij_x, ij_g;
+            if (!wg_pair(p, pl, t1, t2, b, ij_x, ij_g)) continue;
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (elect_one()) {
+                uint8_t *sa = smem + (size_t)stage * p.stage_bytes;
+                uint8_t *sb = sa + p.a_bytes;
+                mbar_expect_tx(&full_bar[stage], tx);
+                const int bga = b * p.GxA + (p.GxA == 1 ? 0 : g);
+                const int bgb = b * p.G + g;
+                for (int h = 0; h < p.NAv; ++h)
+                    tma_tile_5d(sa + (size_t)h * p.npos_a * 16, &xmap, 0, -p.a_col0, -p.a_row0, (int)ij_x, bga * p.HA + h,
+                                &full_bar[stage]);
+                for (int h = 0; h < p.nb_copy; ++h)
+                    tma_tile_5d(sb + ((size_t)h * p.npos_b + (size_t)p.b_row0 * p.P) * 16, &gmap, 0, 0, 0, (int)ij_g,
+                                bgb * p.HB + h, &full_bar[stage]);
+            }
+            __syncwarp();
+            if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        int stage = 0;
+        uint32_t phase = 0;
+        bool first = true;
+        const bool two_a = p.NAv == 2, two_b = p.NBv == 2;
+        const uint32_t nb = (uint32_t)p.NBv;
+        const uint32_t lbo_field = (128u >> 4) << 16;                                   // LBO = 128 B (next 8 positions)
+        const uint64_t a_hi = ((uint64_t)((p.a_sbo >> 4) | (1u << 14))) << 32;           // SBO + descriptor version 1
+        const uint64_t b_hi = ((uint64_t)((p.b_sbo >> 4) | (1u << 14))) << 32;
+        for (int pl = pbeg; pl < pend; ++pl) {
+            int b; size_t ij_x, ij_g;
+            if (!wg_pair(p, pl, t1, t2, b, ij_x, ij_g)) continue;
+            mbar_wait(&full_bar[stage], phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // warp-uniform descriptor arithmetic (only the low word changes); lane 0 issues
+            const uint32_t sa4 = smem_u32(smem + (size_t)stage * p.stage_bytes) >> 4;
+            const uint32_t sb4 = sa4 + ((p.a_bytes + p.b_start) >> 4);
+            const uint32_t a_lo0 = lbo_field | sa4, a_lo1 = a_lo0 + (uint32_t)p.npos_a;
+            const uint32_t b_lo0 = lbo_field | sb4, b_lo1 = b_lo0 + (uint32_t)p.npos_b;
+            const uint32_t n = (uint32_t)p.N;
+            if (elect_one()) {
+            {   // first K block: clears the accumulators on the CTA's first plane
+                const uint32_t acc = first ? 0u : 1u;
+                {
+                    umma_f16(tmem_base, a_hi | a_lo0, b_hi | b_lo0, p.idesc, acc);
+                    if (two_b) umma_f16(tmem_base + n, a_hi | a_lo0, b_hi | b_lo1, p.idesc, acc);
+                    if (two_a) {
+                        umma_f16(tmem_base + nb * n, a_hi | a_lo1, b_hi | b_lo0, p.idesc, acc);
+                        if (two_b) umma_f16(tmem_base + (nb + 1) * n, a_hi | a_lo1, b_hi | b_lo1, p.idesc, acc);
+                    }
+                }
+            }
+#pragma unroll 4
+            for (int kb = 1; kb < p.nkb; ++kb) {
+                const uint32_t ko = (uint32_t)kb * 16u;                  // 16 positions x 16 B, in 16-byte units
+                {
+                    umma_f16(tmem_base, a_hi | (a_lo0 + ko), b_hi | (b_lo0 + ko), p.idesc, 1u);
+                    if (two_b) umma_f16(tmem_base + n, a_hi | (a_lo0 + ko), b_hi | (b_lo1 + ko), p.idesc, 1u);
+                    if (two_a) {
+                        umma_f16(tmem_base + nb * n, a_hi | (a_lo1 + ko), b_hi | (b_lo0 + ko), p.idesc, 1u);
+                        if (two_b) umma_f16(tmem_base + (nb + 1) * n, a_hi | (a_lo1 + ko), b_hi | (b_lo1 + ko), p.idesc, 1u);
+                    }
+                }
+            }
+            umma_commit(&empty_bar[stage]);
+            }
+            __syncwarp();
+            first = false;
+            if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+        }
+        if (elect_one()) umma_commit(&accum_bar);
+        __syncwarp();
+    } else {
+        // ===== epilogue: flush the accumulators as this slice's partial sums =====
+        const int q = warp & 3;
+        mbar_wait(&accum_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        bool any = false;       // did the issuer touch the accumulators at all? (same walk as the other roles)
+        for (int pl = pbeg; pl < pend && !any; ++pl) {
+            int b; size_t ij_x, ij_g;
+            any = wg_pair(p, pl, t1, t2, b, ij_x, ij_g);
+        }
+        if (any) {
+            const int KS = p.KS;
+            const size_t per_group = (size_t)p.Cin * KS * KS * KS * KS * p.cop;
+            float *dst = p.part + ((size_t)s * p.G + g) * per_group;
+            const int m = q * 16 + lane;           // M = 64: rows 16q..16q+15 sit in lanes 0..15 of quadrant q
+            for (int av = 0; av < p.NAv; ++av)
+                for (int bv = 0; bv < p.NBv; ++bv)
+                    for (int n0 = 0; n0 < p.N; n0 += 8) {
+                        float v[8];
+                        tmem_ld8(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)((av * p.NBv + bv) * p.N + n0), v);
+                        if (lane >= 16) continue;
+                        const int sA = m >> 3, c8 = m & 7;
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const int n = n0 + u;
+                            int o, c, t3, t4, tt2 = t2;
+                            if (p.variant == 2) { t4 = sA; c = av * 8 + c8; t3 = 7 - (n >> 3); o = bv * 8 + (n & 7); }
+                            else if (p.variant == 1) { t3 = sA; t4 = c8; c = 0; o = n; }
+                            else { t4 = sA; c = av * 8 + c8; t3 = 7 - (n >> 3); tt2 = n & 7; o = 0; }
+                            if (t3 < 0 || t3 >= KS || t4 >= KS || tt2 >= KS || c >= p.Cin || o >= p.Cout) continue;
+                            dst[(((((size_t)c * KS + t1) * KS + tt2) * KS + t3) * KS + t4) * p.cop + o] = v[u];
+                        }
+                    }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+    }
+}
+
+// planar [B*Gsrc, C, vol] (T) -> channel-blocked fp16 [B*Gsrc][H][vol][8]
+//   tap_mode 0: channels = the tensor's channels (zero padded to 8*H)
+//   tap_mode 1: single channel, channel t = value at l + t - pad        (taps along the last axis)
+//   tap_mode 2: single channel, channel t = value at j - t + pad        (taps along the second axis)
+template <typename T>
+__global__ void __launch_bounds__(256)
+wg_pack_kernel(const T *__restrict__ x, __half *__restrict__ act, int C, int H, int d2, int d3, int d4, size_t vol,
+               int tap_mode, int taps, int pad) {
+    const size_t bg = blockIdx.y;
+    const int half = blockIdx.z;
+    const size_t plane = (size_t)d3 * d4;
+    for (size_t pos = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pos < vol; pos += (size_t)gridDim.x * blockDim.x) {
+        __align__(16) __half v[8];
+        if (tap_mode == 0) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int ch = half * 8 + c;
+                v[c] = __float2half_rn(ch < C ? ldf(x + (bg * C + ch) * vol + pos) : 0.f);
+            }
+        } else if (tap_mode == 1) {
+            const int l = (int)(pos % d4);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int ll = l + c - pad;
+                v[c] = __float2half_rn((c < taps && ll >= 0 && ll < d4) ? ldf(x + bg * vol + pos + (c - pad)) : 0.f);
+            }
+        } else {
+            const int j = (int)((pos / plane) % d2);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int jj = j - c + pad;
+                v[c] = __float2half_rn((c < taps && jj >= 0 && jj < d2)
+                                           ? ldf(x + bg * vol + pos + (ptrdiff_t)(pad - c) * (ptrdiff_t)plane) : 0.f);
+            }
+        }
+        *reinterpret_cast<uint4 *>(act + ((bg * H + half) * vol + pos) * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
+// conv4d_fp32.cu: reduces the per-slice partial sums into the reference layout and sums the bias gradient
+int wgrad_finish(const float *part, float *gw, float *gb, const void *gy, int S, int G, int B, int Cin, int Cout, int k,
+                 int cop, int w_layout, size_t vol, int dtype, cudaStream_t st);
+
+struct WgPlan {
+    bool ok;
+    int variant, NAv, NBv, N, nb_copy, HA, HB, P, a_row0, a_col0, b_row0, npos_a, npos_b, nkb, S, cop;
+    uint32_t a_sbo, b_sbo, a_bytes, stage_bytes, tmem_cols;
+    size_t smem, xa_bytes, gb_bytes, part_bytes;
+};
+
+static size_t wg_align(size_t v) { return (v + 255) & ~(size_t)255; }
+
+static WgPlan wg_plan(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int G, int GxA) {
+    WgPlan w{};
+    w.ok = false;
+    if (Cin > 16 || Cout > 16 || (k != 3 && k != 5)) return w;
+    const size_t vol = (size_t)d1 * d2 * d3 * d4;
+    w.P = d4 + k - 1;
+    const int pad = k / 2;
+    if (Cin == 1 && Cout > 1) {
+        w.variant = 1; w.NAv = 1; w.HA = 1; w.NBv = 1; w.N = 16; w.nb_copy = 2; w.HB = 2;
+        w.a_sbo = (uint32_t)w.P * 16u;                 // groups = t3 row shifts
+        w.a_row0 = pad; w.a_col0 = 0; w.b_row0 = 0;
+        const int kpos = d3 * w.P;                      // K range: every G position
+        w.nkb = (kpos + 15) / 16;
+        w.npos_a = w.nkb * 16 + 7 * w.P + 8;
+        w.npos_b = w.nkb * 16 + 8;
+        w.b_sbo = (uint32_t)w.npos_b * 16u;             // the two channel halves of G are the two N groups
+        w.cop = ((Cout + 3) / 4) * 4;
+    } else if (Cout == 1) {
+        w.variant = 3; w.NAv = (Cin + 7) / 8; w.HA = 2; w.NBv = 1; w.N = 64; w.nb_copy = 1; w.HB = 1;
+        w.a_sbo = 16u;                                  // groups = t4 shifts
+        w.b_sbo = (uint32_t)w.P * 16u;                  // groups = reversed t3 row shifts
+        w.a_row0 = pad; w.a_col0 = pad; w.b_row0 = 8;
+        const int kpos = (d3 + k - 1) * w.P;
+        w.nkb = (kpos + 15) / 16;
+        w.npos_a = w.nkb * 16 + 8;
+        w.npos_b = w.nkb * 16 + 8 * w.P + 8;
+        w.cop = 4;
+    } else {
+        w.variant = 2; w.NAv = (Cin + 7) / 8; w.HA = 2; w.NBv = (Cout + 7) / 8; w.N = 64; w.nb_copy = w.NBv; w.HB = 2;
+        w.a_sbo = 16u;
+        w.b_sbo = (uint32_t)w.P * 16u;
+        w.a_row0 = pad; w.a_col0 = pad; w.b_row0 = 8;
+        const int kpos = (d3 + k - 1) * w.P;
+        w.nkb = (kpos + 15) / 16;
+        w.npos_a = w.nkb * 16 + 8;
+        w.npos_b = w.nkb * 16 + 8 * w.P + 8;
+        w.cop = ((Cout + 3) / 4) * 4;
+    }
+    w.npos_a = ((w.npos_a + 7) / 8) * 8;
+    w.npos_b = ((w.npos_b + 7) / 8) * 8;
+    if (w.npos_a > 16383 || w.npos_b > 16383 || w.P > 1023) return w;
+    w.a_bytes = (uint32_t)w.NAv * w.npos_a * 16u;
+    const uint32_t b_bytes = (uint32_t)(w.variant == 1 ? 2 : w.NBv) * w.npos_b * 16u;
+    w.stage_bytes = ((w.a_bytes + b_bytes + 127) / 128) * 128;
+    w.smem = (size_t)kWgStages * w.stage_bytes;
+    if (w.smem > 220 * 1024) return w;
+    const int cols = w.NAv * w.NBv * w.N;
+    w.tmem_cols = cols <= 32 ? 32 : (cols <= 64 ? 64 : (cols <= 128 ? 128 : (cols <= 256 ? 256 : 512)));
+    // slices: enough CTAs for ~4 waves, balanced
+    const long long base = (long long)G * k * (w.variant == 3 ? 1 : k);
+    const long long planes = (long long)B * d1 * d2;
+    long long S = (4ll * kNumSMs + base - 1) / base;
+    if (S > planes) S = planes;
+    if (S < 1) S = 1;
+    w.S = (int)S;
+    w.xa_bytes = wg_align((size_t)B * GxA * w.HA * vol * 16);
+    w.gb_bytes = wg_align((size_t)B * G * w.HB * vol * 16);
+    w.part_bytes = wg_align((size_t)w.S * G * Cin * k * k * k * k * w.cop * sizeof(float));
+    w.ok = true;
+    return w;
+}
+
+size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric) {
+    const int G = symmetric ? 2 : 1;
+    const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G, G);
+    if (!w.ok) return 0;
+    return w.xa_bytes + w.gb_bytes + w.part_bytes + 1024;
+}
+
+template <typename T>
+static int wg_run(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout, int d1,
+                  int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input, cudaStream_t st) {
+    const int G = symmetric ? 2 : 1;
+    const int GxA = (G == 2 && !shared_input) ? 2 : 1;
+    const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G, GxA);
+    if (!w.ok) return 2;
+    const size_t vol = (size_t)d1 * d2 * d3 * d4;
+    uint8_t *base = (uint8_t *)scratch;
+    __half *xa = (__half *)base;
+    __half *gbk = (__half *)(base + w.xa_bytes);
+    float *part = (float *)(base + w.xa_bytes + w.gb_bytes);
+    const unsigned gx = (unsigned)((vol + 255) / 256 < 4096 ? (vol + 255) / 256 : 4096);
+    NC_CHECK(B * G <= 65535, "conv4d_wgrad(tc): batch too large");
+    // A side
+    wg_pack_kernel<T><<<dim3(gx, B * GxA, w.HA), 256, 0, st>>>((const T *)x, xa, Cin, w.HA, d2, d3, d4, vol,
+                                                               w.variant == 1 ? 1 : 0, k, k / 2);
+    NC_LAUNCH_OK("wg_pack_kernel(x)");
+    // B side
+    wg_pack_kernel<T><<<dim3(gx, B * G, w.HB), 256, 0, st>>>((const T *)gy, gbk, Cout, w.HB, d2, d3, d4, vol,
+                                                             w.variant == 3 ? 2 : 0, k, k / 2);
+    NC_LAUNCH_OK("wg_pack_kernel(gy)");
+    cudaError_t e = cudaMemsetAsync(part, 0, w.part_bytes, st);
+    NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): memset: %s", cudaGetErrorString(e));
+
+    WgArgs a{};
+    a.xa = xa; a.gb = gbk; a.part = part;
+    a.B = B; a.G = G; a.GxA = GxA; a.HA = w.HA; a.HB = w.HB;
+    a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = k; a.P = w.P;
+    a.variant = w.variant; a.NAv = w.NAv; a.NBv = w.NBv; a.N = w.N; a.nb_copy = w.nb_copy;
+    a.a_sbo = w.a_sbo; a.b_sbo = w.b_sbo; a.a_row0 = w.a_row0; a.a_col0 = w.a_col0; a.b_row0 = w.b_row0;
+    a.npos_a = w.npos_a; a.npos_b = w.npos_b; a.nkb = w.nkb; a.S = w.S; a.Cin = Cin; a.Cout = Cout; a.cop = w.cop;
+    a.tmem_cols = w.tmem_cols; a.stage_bytes = w.stage_bytes; a.a_bytes = w.a_bytes;
+    a.b_start = w.variant == 1 ? 0u : (uint32_t)w.P * 16u;
+    // D = f32, A = B = f16, both MN-major (bits 15/16), N>>3 at bit 17, M=64 -> 4 at bit 24
+    a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
+    e = cudaFuncSetAttribute(conv4d_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem);
+    NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): smem attribute: %s", cudaGetErrorString(e));
+    dim3 grid(w.S, G * k * (w.variant == 3 ? 1 : k));
+    CUtensorMap xmap, gmap;
+    if (make_act_tmap(&xmap, xa, (size_t)B * GxA * w.HA, d1, d2, d3, d4, w.P, d3 + k - 1)) return 1;
+    if (make_act_tmap(&gmap, gbk, (size_t)B * G * w.HB, d1, d2, d3, d4, w.P, d3)) return 1;
+    conv4d_tc_wgrad_kernel<<<grid, kWgThreads, w.smem, st>>>(a, xmap, gmap);
+    NC_LAUNCH_OK("conv4d_tc_wgrad_kernel");
+
+    return wgrad_finish(part, gw, gb, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol,
+                        sizeof(T) == 4 ? NCNET_F32 : NCNET_F16, st);
+}
+
+int conv4d_tc_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout,
+                    int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input, int dtype,
+                    cudaStream_t st) {
+    if (dtype == NCNET_F32)
+        return wg_run<float>(x, gy, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric, shared_input, st);
+    return wg_run<__half>(x, gy, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric, shared_input, st);
+}
+
+}  // namespace ncnet

@@ -27,8 +27,14 @@ def run(cin, cout, k, dims, bsz, sym, shared, relu=True):
     ogx = F_._conv_dgrad(gy, w, mask, W_KOIKKK, sym, shared, CONV_TC16)
     torch.cuda.synchronize()
     e2 = nerr(ogx, rgx)
-    print(f"cin={cin} cout={cout} k={k} dims={dims} B={bsz} sym={sym} shared={shared}: fwd nerr {e:.2e}  dgrad nerr {e2:.2e}", flush=True)
-    return e, e2
+    # wgrad
+    gyp = gy * (torch.rand_like(gy) > 0.3)
+    rgw, rgb = F_._conv_wgrad(x, gyp, w, True, W_KOIKKK, sym, shared, CONV_FP32)
+    ogw, ogb = F_._conv_wgrad(x, gyp, w, True, W_KOIKKK, sym, shared, CONV_TC16)
+    torch.cuda.synchronize()
+    e3 = max(nerr(ogw, rgw), nerr(ogb, rgb))
+    print(f"cin={cin} cout={cout} k={k} dims={dims} B={bsz} sym={sym} shared={shared}: fwd nerr {e:.2e}  dgrad nerr {e2:.2e}  wgrad nerr {e3:.2e}", flush=True)
+    return e, max(e2, e3)
 
 cases = [
     (16, 16, 5, (6, 7, 9, 10), 1, False, True),
@@ -59,4 +65,15 @@ for mode in (CONV_TC16, CONV_FP32):
         F_._conv_fwd(x, w, b, W_KOIKKK, True, False, True, mode)
     torch.cuda.synchronize()
     dt = (time.perf_counter() - t0) / n
-    print(f"mode {mode}: 16->16 k=5 B=16 sym: {dt*1e3:.2f} ms  {2*16*25**4*16*16*625*2/dt/1e12:.1f} TFLOP/s dense", flush=True)
+    print(f"mode {mode}: fwd 16->16 k=5 B=16 sym: {dt*1e3:.2f} ms  {2*16*25**4*16*16*625*2/dt/1e12:.1f} TFLOP/s dense", flush=True)
+    gy = torch.randn(16, 32, 25, 25, 25, 25, device="cuda")
+    for _ in range(2):
+        F_._conv_wgrad(x, gy, w, True, W_KOIKKK, True, False, mode)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        F_._conv_wgrad(x, gy, w, True, W_KOIKKK, True, False, mode)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / 3
+    print(f"mode {mode}: wgrad 16->16 k=5 B=16 sym: {dt*1e3:.2f} ms  {2*16*25**4*16*16*625*2/dt/1e12:.1f} TFLOP/s dense", flush=True)
+    del gy
