@@ -31,6 +31,11 @@ extern "C" {
 
 #define NCNET_F32 0
 #define NCNET_F16 1
+/* Conv4d activations only, TC16 mode only: channel-blocked, zero-haloed fp16 ("CB16"),
+ * [blocks of 16 channels][2 halves][d1*d2][d3+2p][d4+2p][8], p = k/2 of the layer that reads or writes
+ * it; a tensor [B, G*C] (C<=16 per group) has B*G blocks.  Lets a stack of layers hand activations
+ * from one tensor-core launch to the next without layout passes (sizes: ncnet_cb16_bytes). */
+#define NCNET_CB16 2
 
 /* weight layouts accepted by the Conv4d entry points */
 #define NCNET_W_OIKKKK 0 /* [Cout,Cin,k,k,k,k]   (lib/conv4d.py:16-18, permute_filters=True) */
@@ -103,22 +108,38 @@ size_t ncnet_conv4d_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int 
                                   int symmetric, int mode);
 int ncnet_conv4d_fwd(const void *x, const float *weight, const float *bias, void *y, void *scratch,
                      int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
-                     int w_layout, int symmetric, int shared_input, int relu, int dtype, int mode,
-                     void *stream);
+                     int w_layout, int symmetric, int shared_input, int relu, int x_dtype, int y_dtype,
+                     int mode, void *stream);
 /* gradient wrt the layer input (autograd of lib/conv4d.py:39-48).  grad_y: [B,G*Cout,...];
  * grad_x: [B,Gin*Cin,...].  y_prev_mask (may be NULL): a tensor shaped like grad_x; where it is
- * <= 0 the result is zeroed (the ReLU of the previous layer folded into this epilogue).
- * With shared_input the two groups' gradients are summed into the Cin channels. */
+ * <= 0 the result is zeroed (the ReLU of the previous layer folded into this epilogue); it must be
+ * CB16 exactly when grad_x is.  With shared_input the two groups' gradients are summed into the
+ * Cin channels. */
 int ncnet_conv4d_dgrad(const void *grad_y, const float *weight, const void *y_prev_mask, void *grad_x,
                        void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
-                       int w_layout, int symmetric, int shared_input, int dtype, int mode, void *stream);
+                       int w_layout, int symmetric, int shared_input, int gy_dtype, int mask_dtype,
+                       int gx_dtype, int mode, void *stream);
 /* gradient wrt weight (same layout as `weight`, fp32, OVERWRITTEN) and bias (fp32 [Cout], may be
  * NULL).  With symmetric=1 the two groups' contributions are folded back into the one weight. */
 size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
                                         int symmetric, int mode);
 int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, float *grad_bias,
                        void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
-                       int w_layout, int symmetric, int shared_input, int dtype, int mode, void *stream);
+                       int w_layout, int symmetric, int shared_input, int x_dtype, int gy_dtype, int mode,
+                       void *stream);
+
+/* 1 when a layer with Cin -> Cout channels per group (kernel k, last two volume dims d3,d4) runs
+ * entirely on the tensor-core kernels in TC16 mode (forward, dgrad and wgrad), i.e. can take and
+ * produce CB16 activations; otherwise TC16 mode routes it to the CUDA-core kernels (planar only). */
+int ncnet_conv4d_tc_supported(int Cin, int Cout, int k, int d3, int d4);
+
+/* CB16 helpers: byte size of a tensor of `nblk` 16-channel blocks; conversion from / to the planar
+ * reference layout [nblk, C, d1,d2,d3,d4] (C <= 16, dtype NCNET_F32/F16). */
+size_t ncnet_cb16_bytes(int nblk, int d1, int d2, int d3, int d4, int k);
+int ncnet_cb16_pack(const void *planar, void *cb16, int nblk, int C, int d1, int d2, int d3, int d4, int k,
+                    int dtype, void *stream);
+int ncnet_cb16_unpack(const void *cb16, void *planar, int nblk, int C, int d1, int d2, int d3, int d4, int k,
+                      int dtype, void *stream);
 
 /* ReLU backward on the last layer's two branch outputs (lib/model.py:137-138,147):
  * gz[b,g,p] = (y[b,g,p] > 0) ? grad[b,p] : 0 for g < G.   y,gz: [B,G,n]; grad: [B,n]. */

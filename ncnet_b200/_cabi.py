@@ -14,7 +14,7 @@ from . import build as _build
 _lock = threading.Lock()
 _lib = None
 
-F32, F16 = 0, 1
+F32, F16, CB16 = 0, 1, 2
 W_OIKKKK, W_KOIKKK = 0, 1
 CONV_FP32, CONV_TC16 = 0, 1
 
@@ -32,10 +32,14 @@ SIGNATURES = {
     "ncnet_mutual_matching_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_fwd_noalloc": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_conv4d_scratch_bytes": (_sz, [_i] * 10),
-    "ncnet_conv4d_fwd": (_i, [_p, _p, _p, _p, _p] + [_i] * 14 + [_p]),
-    "ncnet_conv4d_dgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 13 + [_p]),
+    "ncnet_conv4d_fwd": (_i, [_p, _p, _p, _p, _p] + [_i] * 15 + [_p]),
+    "ncnet_conv4d_dgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 15 + [_p]),
     "ncnet_conv4d_wgrad_scratch_bytes": (_sz, [_i] * 10),
-    "ncnet_conv4d_wgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 13 + [_p]),
+    "ncnet_conv4d_wgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 14 + [_p]),
+    "ncnet_conv4d_tc_supported": (_i, [_i] * 5),
+    "ncnet_cb16_bytes": (_sz, [_i] * 6),
+    "ncnet_cb16_pack": (_i, [_p, _p] + [_i] * 8 + [_p]),
+    "ncnet_cb16_unpack": (_i, [_p, _p] + [_i] * 8 + [_p]),
     "ncnet_relu_mask_bcast": (_i, [_p, _p, _p, _i, _i, _ll, _i, _p]),
     "ncnet_maxpool4d_fwd": (_i, [_p] * 6 + [_i] * 7 + [_p]),
     "ncnet_corr_to_matches": (_i, [_p] + [_i] * 8 + [_p] * 4 + [_i] + [_p] * 4 + [_p] * 9 + [_i, _p]),

@@ -46,34 +46,42 @@ extern "C" size_t ncnet_conv4d_scratch_bytes(int B, int Cin, int Cout, int d1, i
     return a;
 }
 
+static bool planar(int dt) { return dt == NCNET_F32 || dt == NCNET_F16; }
+
 extern "C" int ncnet_conv4d_fwd(const void *x, const float *weight, const float *bias, void *y, void *scratch, int B,
                                 int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric,
-                                int shared_input, int relu, int dtype, int mode, void *stream) {
+                                int shared_input, int relu, int x_dtype, int y_dtype, int mode, void *stream) {
     NC_CHECK(x && weight && y && scratch, "conv4d_fwd: null pointer");
-    if (check_conv("conv4d_fwd", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, dtype, mode)) return 1;
+    if (check_conv("conv4d_fwd", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, NCNET_F32, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
     if (mode == NCNET_CONV_TC16) {
-        const int rc = conv4d_tc_fwd(x, weight, bias, y, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
-                                     shared_input, relu, dtype, st);
-        if (rc != 2) return rc;      // 2: shape outside the tensor-core kernel's envelope -> CUDA-core kernel
+        const int rc = conv4d_tc_fwd(x, x_dtype, weight, bias, y, y_dtype, scratch, B, Cin, Cout, d1, d2, d3, d4, k,
+                                     w_layout, symmetric, shared_input, relu, st);
+        if (rc != 2) return rc;      // 2: outside the tensor-core kernel's envelope -> CUDA-core kernel
     }
+    NC_CHECK(planar(x_dtype) && x_dtype == y_dtype,
+             "conv4d_fwd: this shape runs on the CUDA-core kernel, which needs planar tensors of one dtype (got %d -> %d)",
+             x_dtype, y_dtype);
     return conv4d_fp32_fwd(x, weight, bias, y, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
-                           shared_input, relu, dtype, st);
+                           shared_input, relu, x_dtype, st);
 }
 
 extern "C" int ncnet_conv4d_dgrad(const void *grad_y, const float *weight, const void *y_prev_mask, void *grad_x,
                                   void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
-                                  int w_layout, int symmetric, int shared_input, int dtype, int mode, void *stream) {
+                                  int w_layout, int symmetric, int shared_input, int gy_dtype, int mask_dtype,
+                                  int gx_dtype, int mode, void *stream) {
     NC_CHECK(grad_y && weight && grad_x && scratch, "conv4d_dgrad: null pointer");
-    if (check_conv("conv4d_dgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, dtype, mode)) return 1;
+    if (check_conv("conv4d_dgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, NCNET_F32, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
     if (mode == NCNET_CONV_TC16) {
-        const int rc = conv4d_tc_dgrad(grad_y, weight, y_prev_mask, grad_x, scratch, B, Cin, Cout, d1, d2, d3, d4, k,
-                                       w_layout, symmetric, shared_input, dtype, st);
+        const int rc = conv4d_tc_dgrad(grad_y, gy_dtype, weight, y_prev_mask, mask_dtype, grad_x, gx_dtype, scratch, B,
+                                       Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric, shared_input, st);
         if (rc != 2) return rc;
     }
+    NC_CHECK(planar(gy_dtype) && gy_dtype == gx_dtype && (!y_prev_mask || mask_dtype == gx_dtype),
+             "conv4d_dgrad: this shape runs on the CUDA-core kernel, which needs planar tensors of one dtype");
     return conv4d_fp32_dgrad(grad_y, weight, y_prev_mask, grad_x, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout,
-                             symmetric, shared_input, dtype, st);
+                             symmetric, shared_input, gy_dtype, st);
 }
 
 extern "C" size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
@@ -88,17 +96,46 @@ extern "C" size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int
 
 extern "C" int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, float *grad_bias,
                                   void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
-                                  int w_layout, int symmetric, int shared_input, int dtype, int mode, void *stream) {
+                                  int w_layout, int symmetric, int shared_input, int x_dtype, int gy_dtype, int mode,
+                                  void *stream) {
     NC_CHECK(x && grad_y && grad_weight && scratch, "conv4d_wgrad: null pointer");
-    if (check_conv("conv4d_wgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, dtype, mode)) return 1;
+    if (check_conv("conv4d_wgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, NCNET_F32, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
     if (mode == NCNET_CONV_TC16) {
-        const int rc = conv4d_tc_wgrad(x, grad_y, grad_weight, grad_bias, scratch, B, Cin, Cout, d1, d2, d3, d4, k,
-                                       w_layout, symmetric, shared_input, dtype, st);
+        const int rc = conv4d_tc_wgrad(x, x_dtype, grad_y, gy_dtype, grad_weight, grad_bias, scratch, B, Cin, Cout, d1, d2,
+                                       d3, d4, k, w_layout, symmetric, shared_input, st);
         if (rc != 2) return rc;      // 2: outside the tensor-core kernel's envelope -> CUDA-core kernel
     }
+    NC_CHECK(planar(x_dtype) && x_dtype == gy_dtype,
+             "conv4d_wgrad: this shape runs on the CUDA-core kernel, which needs planar tensors of one dtype");
     return conv4d_fp32_wgrad(x, grad_y, grad_weight, grad_bias, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout,
-                             symmetric, shared_input, dtype, st);
+                             symmetric, shared_input, x_dtype, st);
+}
+
+extern "C" int ncnet_conv4d_tc_supported(int Cin, int Cout, int k, int d3, int d4) {
+    if (Cin < 1 || Cout < 1 || (k != 3 && k != 5) || d3 < 1 || d4 < 1) return 0;
+    const bool fwd = conv4d_tc_supports(Cin, Cout, k, d3, d4);
+    const bool bwd = conv4d_tc_supports(Cout, Cin, k, d3, d4);
+    const bool wg = conv4d_tc_wgrad_scratch_bytes(1, Cin, Cout, 1, 1, d3, d4, k, 0) > 0;
+    return fwd && bwd && wg ? 1 : 0;
+}
+
+extern "C" size_t ncnet_cb16_bytes(int nblk, int d1, int d2, int d3, int d4, int k) {
+    return cb16_bytes((size_t)nblk, d1, d2, d3, d4, k);
+}
+
+extern "C" int ncnet_cb16_pack(const void *planar_t, void *cb16, int nblk, int C, int d1, int d2, int d3, int d4, int k,
+                               int dtype, void *stream) {
+    NC_CHECK(planar_t && cb16, "cb16_pack: null pointer");
+    NC_CHECK(d1 > 0 && d2 > 0 && d3 > 0 && d4 > 0 && (k == 3 || k == 5), "cb16_pack: bad shape");
+    return cb16_pack(planar_t, dtype, cb16, nblk, C, d1, d2, d3, d4, k, 0, (cudaStream_t)stream);
+}
+
+extern "C" int ncnet_cb16_unpack(const void *cb16, void *planar_t, int nblk, int C, int d1, int d2, int d3, int d4, int k,
+                                 int dtype, void *stream) {
+    NC_CHECK(planar_t && cb16, "cb16_unpack: null pointer");
+    NC_CHECK(d1 > 0 && d2 > 0 && d3 > 0 && d4 > 0 && (k == 3 || k == 5), "cb16_unpack: bad shape");
+    return cb16_unpack(cb16, planar_t, dtype, nblk, C, d1, d2, d3, d4, k, (cudaStream_t)stream);
 }
 
 extern "C" int ncnet_relu_mask_bcast(const void *y, const void *grad, void *gz, int B, int G, long long n, int dtype,

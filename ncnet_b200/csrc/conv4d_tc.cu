@@ -1,11 +1,16 @@
 // Conv4d on the 5th-gen tensor cores (mode NCNET_CONV_TC16): fp16 operands, fp32 accumulation in
 // TMEM, one implicit-GEMM kernel per layer (reference semantics: lib/conv4d.py:11-51).
 //
+// Activation layout ("CB16", dtype code NCNET_CB16): channel-blocked, zero-haloed fp16
+//     [block of 16 channels][channel half][iA*jA][iB + 2p][P = jB + 2p][8]        p = k/2
+// One (iB,jB) plane with its halo is ONE contiguous run of (iB+2p)*P*16 bytes, so a pipeline stage is
+// filled by one cp.async.bulk per channel half, and every position is one 16-byte UMMA core-matrix
+// row.  Kernels that produce CB16 write the halo zeros themselves.
+//
 // GEMM view.  For one (batch, group, iA, jA) the CTA owns a chunk of the (iB,jB) plane, flattened
-// with the padded pitch P = d4 + k - 1 so that a tap shift is an affine row offset:
+// with the pitch P so that a tap shift is an affine row offset:
 //     A (M x K)  = activation rows: M = 128 consecutive flattened positions, K = 16 channels,
-//                  K-major, no swizzle: smem [channel-half][position][8 x fp16] -> a tap is just a
-//                  different descriptor start address (16 B per position);
+//                  K-major, no swizzle -> a tap is just a different descriptor start address;
 //     B (N x K)  = weights of one (d1,d2[,d3]) tap for N = (tap-in-N, out-channel) columns;
 //     D (M x N)  = fp32 accumulators in TMEM, NT tiles of N columns, live for the whole CTA.
 // The taps that are folded into N are summed in the epilogue with the matching row shift
@@ -16,10 +21,10 @@
 //   mode M2 (Cout == 1)      : channels = input channels, N = (d3, d4), one K-step per plane
 //   mode M3 (Cin == 1)       : channels = the k taps along d4 (im2col in the pack kernel),
 //                              N = (d3, o), one K-step per plane
-// Pipeline: warp 0 streams (d1,d2) planes + their weight slice with cp.async.bulk (TMA engine,
-// mbarrier complete_tx) through a 3-stage ring; one thread of warp 1 issues tcgen05.mma and
-// commits to the stage's "empty" barrier; warps 2-5 drain TMEM (tcgen05.ld), apply the shifted
-// sums, bias, ReLU / ReLU-mask, and store.
+// Pipeline: one elected lane of warp 0 streams the (d1,d2) planes + their weight slab with
+// cp.async.bulk (TMA engine, mbarrier complete_tx) through a 3-stage ring; one elected lane of warp 1
+// issues tcgen05.mma and commits to the stage's "empty" barrier; warps 2-5 drain TMEM (tcgen05.ld),
+// apply the shifted sums, bias, ReLU / ReLU-mask, and store planar or CB16.
 #include "conv4d_tc.cuh"
 #include "conv4d_common.cuh"
 #include "tc_common.cuh"
@@ -29,22 +34,23 @@ namespace ncnet {
 constexpr int kTcThreads = 192;
 constexpr int kStages = 3;
 constexpr int kMaxGroups = 32;      // column groups (taps folded into N)
-constexpr int kMaxKSteps = 8;
-constexpr int kOutStride = 20;      // floats per outbuf row (16 channels + pad: conflict-free float4 RMW)
+constexpr int kMaxKSteps = 5;
+constexpr int kOutStride = 20;      // floats per outbuf row (16 channels + pad: conflict-free float4 access)
 
 struct TcArgs {
-    const __half *act;      // [B*Gx][2][d1*d2][d3][d4][8] fp16 (channel-blocked)
+    const __half *act;      // CB16 input
     const __half *wp;       // [G][k*k][KSTEPS][2][N][8] fp16
     const float *bias;      // [Cout] or null
-    const void *mask;       // planar tensor shaped like the output, or null
-    void *out;              // planar [B, G*Cout, vol] (out_f16 ? half : float)
+    const void *mask;       // null | planar tensor shaped like the output | CB16 tensor shaped like the output
+    void *out;              // planar [B, G*Cout, vol] (fp32/fp16) or CB16
     int B, G, Gx, Cout, CoutPad;
     int d1, d2, d3, d4, KS, P;
-    int lpad;               // column offset of l=0 inside a smem row (pad, or 0 for M3)
     int R, nchunks;         // output k-rows per CTA, chunks per plane
     int NT, N, NG, KSTEPS;
     int npos_pad;           // positions per channel-half in a smem stage
-    int relu, out_f16, mask_f16;
+    int relu;
+    int out_mode;           // 0 planar fp32, 1 planar fp16, 2 CB16
+    int mask_mode;          // 0 none, 1 planar fp32, 2 planar fp16, 3 CB16
     uint32_t idesc;
     int aoff[kMaxKSteps];   // A row offset (positions) per K-step
     int gshift[kMaxGroups]; // epilogue row shift per column group
@@ -55,7 +61,7 @@ struct TcArgs {
 using namespace tc;
 
 __global__ void __launch_bounds__(kTcThreads, 1)
-conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
+conv4d_tc_kernel(const TcArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar;
     __shared__ uint32_t tmem_base_s;
@@ -71,6 +77,9 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
     const int PAD = p.KS / 2;
     const int k0 = chunk * p.R;
     const int rows_out = min(p.R, p.d3 - k0);
+    const int rows_pad = p.d3 + 2 * PAD;                 // rows of a haloed plane
+    const size_t plane_cb = (size_t)rows_pad * p.P;      // positions of a haloed plane
+    const size_t ij_count = (size_t)p.d1 * p.d2;
 
     uint8_t *stage0 = smem;
     float *outbuf = reinterpret_cast<float *>(smem + (size_t)kStages * p.stage_bytes);
@@ -87,9 +96,9 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    // zero the activation part of every stage once: halo columns/rows and the tail padding are
-    // never written by the row copies, so they stay zero (= the conv's zero padding)
     {
+        // zero the activation part of every stage once: the tail behind the copied rows is read by the
+        // last tiles' (discarded) rows and must stay finite
         const uint4 z = make_uint4(0, 0, 0, 0);
         for (int s = 0; s < kStages; ++s) {
             uint4 *d = reinterpret_cast<uint4 *>(stage0 + (size_t)s * p.stage_bytes);
@@ -114,19 +123,15 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
     const long long t_start = clock64();
 #define TC_STAMP(slot) do { if (p.dbg && blockIdx.x < 4096) p.dbg[blockIdx.x * 8 + (slot)] = clock64() - t_start; } while (0)
 
-    // list of valid (d1,d2) planes is implicit: both roles walk the same loop
-    const size_t plane_pos = (size_t)p.d3 * p.d4;
-    const size_t ij_count = (size_t)p.d1 * p.d2;
-
     if (warp == 0) {
         // ===== producer =====
         int stage = 0;
         uint32_t phase = 0;
-        const int box_rows = p.R + p.KS - 1;
-        const uint32_t half_bytes = (uint32_t)p.P * box_rows * 16u;       // one TMA tile: the halo'd plane chunk of one channel half
+        // the chunk's input rows (haloed coordinates k0 .. k0+R+KS-2), clipped to the plane
+        const int rows_in = min(p.R + p.KS - 1, rows_pad - k0);
+        const uint32_t half_bytes = (uint32_t)rows_in * p.P * 16u;
         const uint32_t tx_bytes = 2u * half_bytes + p.w_bytes;
-        const int bg = b * p.Gx + (p.Gx == 1 ? 0 : g);
-        if (elect_one()) prefetch_tmap(&amap);
+        const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
             if (ii < 0 || ii >= p.d1) continue;
@@ -137,10 +142,10 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
                 if (elect_one()) {
                     uint8_t *sb = stage0 + (size_t)stage * p.stage_bytes;
                     mbar_expect_tx(&full_bar[stage], tx_bytes);
-                    // rows/columns outside the volume arrive as zeros: that is the convolution's zero padding
-                    tma_tile_5d(sb, &amap, 0, -p.lpad, k0 - PAD, ii * p.d2 + jj, bg * 2 + 0, &full_bar[stage]);
-                    tma_tile_5d(sb + (size_t)p.npos_pad * 16, &amap, 0, -p.lpad, k0 - PAD, ii * p.d2 + jj, bg * 2 + 1,
-                                &full_bar[stage]);
+                    const __half *src0 = p.act + (((bg * 2 + 0) * ij_count + (size_t)ii * p.d2 + jj) * plane_cb + (size_t)k0 * p.P) * 8;
+                    const __half *src1 = src0 + ij_count * plane_cb * 8;
+                    bulk_g2s(sb, src0, half_bytes, &full_bar[stage]);
+                    bulk_g2s(sb + (size_t)p.npos_pad * 16, src1, half_bytes, &full_bar[stage]);
                     const __half *wsrc = p.wp + ((size_t)g * p.KS * p.KS + (size_t)t1 * p.KS + t2) * (p.w_bytes / 2);
                     bulk_g2s(sb + p.data_bytes, wsrc, p.w_bytes, &full_bar[stage]);
                 }
@@ -149,7 +154,7 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
             }
         }
     } else if (warp == 1) {
-        // ===== MMA issuer (one thread) =====
+        // ===== MMA issuer =====
         int stage = 0;
         uint32_t phase = 0;
         bool first = true;
@@ -165,30 +170,29 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
                 if (jj < 0 || jj >= p.d2) continue;
                 mbar_wait(&full_bar[stage], phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                if (lane == 0 && first) TC_STAMP(0);
-                // Descriptor arithmetic stays warp-uniform (no lane dependence) and only the low 32 bits
-                // change, so ptxas keeps it on the uniform datapath; lane 0 alone executes the MMAs.
-                const uint32_t sa4 = smem_u32(stage0 + (size_t)stage * p.stage_bytes) >> 4;
-                const uint32_t sw4 = sa4 + (p.data_bytes >> 4);
                 if (elect_one()) {
+                    if (first) TC_STAMP(0);
+                    // only the low descriptor word changes from MMA to MMA
+                    const uint32_t sa4 = smem_u32(stage0 + (size_t)stage * p.stage_bytes) >> 4;
+                    const uint32_t sw4 = sa4 + (p.data_bytes >> 4);
 #pragma unroll
-                for (int ks = 0; ks < kMaxKSteps; ++ks) {
-                    if (ks < p.KSTEPS) {
-                        const uint64_t bdesc = desc_hi | (uint64_t)(lbo_b_field | (sw4 + (uint32_t)ks * 2u * (lbo_b >> 4)));
-                        const uint32_t a_lo0 = lbo_a_field | (sa4 + (uint32_t)p.aoff[ks]);
-                        const uint32_t acc = (first && ks == 0) ? 0u : 1u;
-                        for (int t0 = 0; t0 < p.NT; t0 += 8) {
+                    for (int ks = 0; ks < kMaxKSteps; ++ks) {
+                        if (ks < p.KSTEPS) {
+                            const uint64_t bdesc = desc_hi | (uint64_t)(lbo_b_field | (sw4 + (uint32_t)ks * 2u * (lbo_b >> 4)));
+                            const uint32_t a_lo0 = lbo_a_field | (sa4 + (uint32_t)p.aoff[ks]);
+                            const uint32_t acc = (first && ks == 0) ? 0u : 1u;
+                            for (int t0 = 0; t0 < p.NT; t0 += 8) {
 #pragma unroll
-                            for (int u = 0; u < 8; ++u) {
-                                const int t = t0 + u;
-                                if (t < p.NT)
-                                    umma_f16(tmem_base + (uint32_t)(t * p.N), desc_hi | (uint64_t)(a_lo0 + (uint32_t)t * 128u),
-                                             bdesc, p.idesc, acc);
+                                for (int u = 0; u < 8; ++u) {
+                                    const int t = t0 + u;
+                                    if (t < p.NT)
+                                        umma_f16(tmem_base + (uint32_t)(t * p.N), desc_hi | (uint64_t)(a_lo0 + (uint32_t)t * 128u),
+                                                 bdesc, p.idesc, acc);
+                                }
                             }
                         }
                     }
-                }
-                umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
+                    umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
                 }
                 __syncwarp();
                 first = false;
@@ -247,27 +251,66 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
         if (et == 0) TC_STAMP(3);
-        // ---- store: planar output, coalesced along l -----------------------------------------
-        const size_t vol = ij_count * plane_pos;
-        const int ew = et >> 5;                                   // epilogue warp 0..3
-        const int npairs = p.Cout * rows_out;                     // (channel, output row) pairs, one warp each
-        for (int pr = ew; pr < npairs; pr += 4) {
-            const int o = pr / rows_out, rr = pr - o * rows_out;
-            const size_t off0 = ((size_t)b * p.G * p.Cout + (size_t)g * p.Cout + o) * vol +
-                                ((size_t)i * p.d2 + j) * plane_pos + (size_t)(k0 + rr) * p.d4;
-            for (int l = lane; l < p.d4; l += 32) {
-                const int row = rr * p.P + l;
-                float v;
-                if (p.CoutPad >= 16) v = outbuf[(size_t)row * kOutStride + o];
-                else v = outbuf[row] + outbuf[out_rows + row] + outbuf[2 * out_rows + row] + outbuf[3 * out_rows + row];
-                if (p.relu) v = fmaxf(v, 0.f);
-                const size_t off = off0 + l;
-                if (p.mask) {
-                    const float mv = p.mask_f16 ? __half2float(((const __half *)p.mask)[off]) : ((const float *)p.mask)[off];
-                    if (!(mv > 0.f)) v = 0.f;
+
+        if (p.out_mode == 2) {
+            // ---- CB16 store: this chunk's rows of the haloed plane (halo columns/rows written as zeros), 16 B per
+            //      (position, channel half), lanes along the contiguous position axis
+            const int ra = chunk == 0 ? 0 : k0 + PAD;
+            const int rb = chunk == p.nchunks - 1 ? rows_pad : k0 + PAD + rows_out;
+            const int npos = (rb - ra) * p.P;
+            const size_t base_off = ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8;
+            __half *ob = (__half *)p.out + base_off;
+            const __half *mb = (const __half *)p.mask + base_off;
+            for (int e = et; e < 2 * npos; e += 128) {
+                const int half = e / npos, pp = e - half * npos;
+                const int kk = ra + pp / p.P, ll = pp % p.P;
+                const int kr = kk - PAD - k0, lc = ll - PAD;
+                const size_t goff = ((size_t)half * ij_count * plane_cb + (size_t)kk * p.P + ll) * 8;
+                __align__(16) __half hv[8];
+                if (kr >= 0 && kr < rows_out && lc >= 0 && lc < p.d4) {
+                    const float4 *src = reinterpret_cast<const float4 *>(outbuf + (size_t)(kr * p.P + lc) * kOutStride + half * 8);
+                    const float4 a = src[0], c = src[1];
+                    float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+                    if (p.mask_mode == 3) {
+                        const uint4 mraw = *reinterpret_cast<const uint4 *>(mb + goff);
+                        const __half *mh = reinterpret_cast<const __half *>(&mraw);
+#pragma unroll
+                        for (int c8 = 0; c8 < 8; ++c8) if (!(__half2float(mh[c8]) > 0.f)) v[c8] = 0.f;
+                    }
+#pragma unroll
+                    for (int c8 = 0; c8 < 8; ++c8) {
+                        float x = v[c8];
+                        if (p.relu) x = fmaxf(x, 0.f);
+                        hv[c8] = __float2half_rn((half * 8 + c8) < p.Cout ? x : 0.f);
+                    }
+                } else {
+#pragma unroll
+                    for (int c8 = 0; c8 < 8; ++c8) hv[c8] = __float2half_rn(0.f);
                 }
-                if (p.out_f16) ((__half *)p.out)[off] = __float2half_rn(v);
-                else ((float *)p.out)[off] = v;
+                *reinterpret_cast<uint4 *>(ob + goff) = *reinterpret_cast<const uint4 *>(hv);
+            }
+        } else {
+            // ---- planar store: one warp per (channel, output row), lanes along l ----------------------
+            const size_t plane_pos = (size_t)p.d3 * p.d4;
+            const size_t vol = ij_count * plane_pos;
+            const int ew = et >> 5;
+            const int npairs = p.Cout * rows_out;
+            for (int pr = ew; pr < npairs; pr += 4) {
+                const int o = pr / rows_out, rr = pr - o * rows_out;
+                const size_t off0 = ((size_t)b * p.G * p.Cout + (size_t)g * p.Cout + o) * vol +
+                                    ((size_t)i * p.d2 + j) * plane_pos + (size_t)(k0 + rr) * p.d4;
+                for (int l = lane; l < p.d4; l += 32) {
+                    const int row = rr * p.P + l;
+                    float v;
+                    if (p.CoutPad >= 16) v = outbuf[(size_t)row * kOutStride + o];
+                    else v = outbuf[row] + outbuf[out_rows + row] + outbuf[2 * out_rows + row] + outbuf[3 * out_rows + row];
+                    if (p.relu) v = fmaxf(v, 0.f);
+                    const size_t off = off0 + l;
+                    if (p.mask_mode == 1) { if (!(((const float *)p.mask)[off] > 0.f)) v = 0.f; }
+                    else if (p.mask_mode == 2) { if (!(__half2float(((const __half *)p.mask)[off]) > 0.f)) v = 0.f; }
+                    if (p.out_mode == 1) ((__half *)p.out)[off] = __float2half_rn(v);
+                    else ((float *)p.out)[off] = v;
+                }
             }
         }
     }
@@ -282,35 +325,112 @@ conv4d_tc_kernel(const TcArgs p, const __grid_constant__ CUtensorMap amap) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// operand packing
+// CB16 packing
 // ---------------------------------------------------------------------------------------------
-// planar [B, Gx*Cin, vol] (T) -> channel-blocked fp16 [B*Gx][2][vol][8].
-// taps_as_channels (mode M3, Cin == 1): channel c' of position (.., l) is x[.., l + c' - pad].
+// planar [nblk, C, vol] (T) -> CB16 [nblk][2][ij][d3+2p][P][8], halo = 0.
+//   tap_mode 0: channels = the tensor's C (<= 16) channels
+//   tap_mode 1: C == 1, channel t = x[.., l + t - p]                 (taps along the last axis)
+//   tap_mode 2: C == 1, channel t = x[.., j - t + p, ..]             (taps along the second axis, mirrored)
 template <typename T>
 __global__ void __launch_bounds__(256)
-pack_act_kernel(const T *__restrict__ x, __half *__restrict__ act, int Cin, size_t vol, int d4, int taps, int pad) {
-    const size_t bg = blockIdx.y;
+cb16_pack_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1, int d2, int d3, int d4, int pad,
+                 int tap_mode, int taps) {
+    const size_t blk = blockIdx.y;
     const int half = blockIdx.z;
-    for (size_t pos = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pos < vol; pos += (size_t)gridDim.x * blockDim.x) {
+    const int P = d4 + 2 * pad, rows = d3 + 2 * pad;
+    const size_t ij = (size_t)d1 * d2, plane = (size_t)d3 * d4, vol = ij * plane;
+    const size_t npad = ij * rows * P;
+    for (size_t pp = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pp < npad; pp += (size_t)gridDim.x * blockDim.x) {
+        const int ll = (int)(pp % P);
+        const int kk = (int)((pp / P) % rows);
+        const size_t ijx = pp / ((size_t)P * rows);
+        const int k = kk - pad, l = ll - pad;
         __align__(16) __half v[8];
-        if (taps == 0) {
+        if (k >= 0 && k < d3 && l >= 0 && l < d4) {
+            const size_t pos = ijx * plane + (size_t)k * d4 + l;
+            if (tap_mode == 0) {
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int ch = half * 8 + c;
-                v[c] = ch < Cin ? __float2half_rn(ldf(x + (bg * Cin + ch) * vol + pos)) : __float2half_rn(0.f);
+                for (int c = 0; c < 8; ++c) {
+                    const int ch = half * 8 + c;
+                    v[c] = __float2half_rn(ch < C ? ldf(x + (blk * C + ch) * vol + pos) : 0.f);
+                }
+            } else if (tap_mode == 1) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int t = half * 8 + c, lt = l + t - pad;
+                    v[c] = __float2half_rn((t < taps && lt >= 0 && lt < d4) ? ldf(x + blk * vol + pos + (t - pad)) : 0.f);
+                }
+            } else {
+                const int jx = (int)(ijx % d2);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int t = half * 8 + c, jt = jx - t + pad;
+                    v[c] = __float2half_rn((t < taps && jt >= 0 && jt < d2)
+                                               ? ldf(x + blk * vol + pos + (ptrdiff_t)(pad - t) * (ptrdiff_t)plane) : 0.f);
+                }
             }
         } else {
-            const int l = (int)(pos % d4);
 #pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int tap = half * 8 + c;
-                const int ll = l + tap - pad;
-                v[c] = (tap < taps && ll >= 0 && ll < d4) ? __float2half_rn(ldf(x + bg * vol + pos + (tap - pad)))
-                                                           : __float2half_rn(0.f);
-            }
+            for (int c = 0; c < 8; ++c) v[c] = __float2half_rn(0.f);
         }
-        *reinterpret_cast<uint4 *>(act + ((bg * 2 + half) * vol + pos) * 8) = *reinterpret_cast<const uint4 *>(v);
+        *reinterpret_cast<uint4 *>(cb + ((blk * 2 + half) * npad + pp) * 8) = *reinterpret_cast<const uint4 *>(v);
     }
+}
+
+// CB16 -> planar [nblk, C, vol] (T); interior only
+template <typename T>
+__global__ void __launch_bounds__(256)
+cb16_unpack_kernel(const __half *__restrict__ cb, T *__restrict__ x, int C, int d1, int d2, int d3, int d4, int pad) {
+    const size_t blk = blockIdx.y;
+    const int P = d4 + 2 * pad, rows = d3 + 2 * pad;
+    const size_t ij = (size_t)d1 * d2, plane = (size_t)d3 * d4, vol = ij * plane;
+    const size_t npad = ij * rows * P;
+    for (size_t pos = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pos < vol; pos += (size_t)gridDim.x * blockDim.x) {
+        const int l = (int)(pos % d4);
+        const int k = (int)((pos / d4) % d3);
+        const size_t ijx = pos / plane;
+        const size_t pp = (ijx * rows + (k + pad)) * P + (l + pad);
+        for (int ch = 0; ch < C; ++ch)
+            stf(x + (blk * C + ch) * vol + pos, __half2float(cb[((blk * 2 + (ch >> 3)) * npad + pp) * 8 + (ch & 7)]));
+    }
+}
+
+size_t cb16_bytes(size_t nblk, int d1, int d2, int d3, int d4, int k) {
+    const int p = k / 2;
+    return nblk * 2 * (size_t)d1 * d2 * (d3 + 2 * p) * (d4 + 2 * p) * 16;
+}
+
+int cb16_pack(const void *x, int dtype, void *cb, int nblk, int C, int d1, int d2, int d3, int d4, int k, int tap_mode,
+              cudaStream_t st) {
+    NC_CHECK(nblk > 0 && nblk <= 65535 && C >= 1 && C <= 16, "cb16_pack: bad shape (blocks %d, channels %d)", nblk, C);
+    NC_CHECK(tap_mode == 0 || C == 1, "cb16_pack: tap modes need a single-channel input");
+    const int pad = k / 2;
+    const size_t npad = (size_t)d1 * d2 * (d3 + 2 * pad) * (d4 + 2 * pad);
+    const unsigned gx = (unsigned)((npad + 255) / 256 < 8192 ? (npad + 255) / 256 : 8192);
+    dim3 grid(gx, nblk, 2);
+    if (dtype == NCNET_F32)
+        cb16_pack_kernel<float><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+    else if (dtype == NCNET_F16)
+        cb16_pack_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+    else
+        return fail("cb16_pack: source dtype %d must be planar fp32/fp16", dtype);
+    NC_LAUNCH_OK("cb16_pack_kernel");
+    return 0;
+}
+
+int cb16_unpack(const void *cb, void *x, int dtype, int nblk, int C, int d1, int d2, int d3, int d4, int k, cudaStream_t st) {
+    NC_CHECK(nblk > 0 && nblk <= 65535 && C >= 1 && C <= 16, "cb16_unpack: bad shape");
+    const size_t vol = (size_t)d1 * d2 * d3 * d4;
+    const unsigned gx = (unsigned)((vol + 255) / 256 < 8192 ? (vol + 255) / 256 : 8192);
+    dim3 grid(gx, nblk);
+    if (dtype == NCNET_F32)
+        cb16_unpack_kernel<float><<<grid, 256, 0, st>>>((const __half *)cb, (float *)x, C, d1, d2, d3, d4, k / 2);
+    else if (dtype == NCNET_F16)
+        cb16_unpack_kernel<__half><<<grid, 256, 0, st>>>((const __half *)cb, (__half *)x, C, d1, d2, d3, d4, k / 2);
+    else
+        return fail("cb16_unpack: destination dtype %d must be planar fp32/fp16", dtype);
+    NC_LAUNCH_OK("cb16_unpack_kernel");
+    return 0;
 }
 
 struct TcPackW {
@@ -358,7 +478,7 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
 long long *g_tc_debug_buffer = nullptr;     // set through ncnet_debug_set_tc_timing (development only)
 
 struct TcPlan {
-    int mode, KSTEPS, N, NG, CoutPad, P, lpad, R, nchunks, NT, npos_pad;
+    int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad;
     uint32_t data_bytes, w_bytes, stage_bytes;
     size_t smem_bytes;
     bool ok;
@@ -368,14 +488,15 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
     TcPlan pl{};
     pl.ok = false;
     if (Cin_e > 16 || Cout_e > 16 || (k != 3 && k != 5)) return pl;
-    if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = 1; pl.lpad = 0; }
-    else if (Cout_e == 1)          { pl.mode = 2; pl.CoutPad = 1; pl.NG = k * k; pl.KSTEPS = 1; pl.lpad = k / 2; }
-    else                           { pl.mode = 1; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = k; pl.lpad = k / 2; }
+    if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = 1; }
+    else if (Cout_e == 1)          { pl.mode = 2; pl.CoutPad = 1; pl.NG = k * k; pl.KSTEPS = 1; }
+    else                           { pl.mode = 1; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = k; }
     pl.N = pl.mode == 2 ? ((k * k + 15) / 16) * 16 : k * 16;
     pl.P = d4 + k - 1;
-    if (pl.P * 16 > 65535 * 16) return pl;
+    const int pad = k / 2;
     const int max_aoff = pl.mode == 1 ? (k - 1) * pl.P : 0;
-    const int max_shift = pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : (k - 1) * pl.P);
+    // largest epilogue row shift (mode 3 reads the haloed row at column l + pad, hence the extra pad)
+    const int max_shift = pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : (k - 1) * pl.P + pad);
     pl.w_bytes = (uint32_t)pl.KSTEPS * 2u * pl.N * 16u;
     auto fit = [&](int R, TcPlan &o) {
         const int mrows = (R - 1) * o.P + d4 + max_shift;
@@ -408,39 +529,37 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
 size_t conv4d_tc_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric) {
-    const size_t vol = (size_t)d1 * d2 * d3 * d4;
     const int G = symmetric ? 2 : 1;
     (void)Cin; (void)Cout;
-    // activations: up to G groups, 16 channels fp16 each; weights: largest N is 5*16=80 -> bound generously
-    const size_t act = (size_t)B * G * 2 * vol * 16;
+    // a CB16 copy of a planar input (up to G blocks per batch item) + the re-laid-out weights
+    const size_t act = cb16_bytes((size_t)B * G, d1, d2, d3, d4, k);
     const size_t wts = (size_t)G * k * k * k * 2 * 96 * 16;
     return align256(act) + align256(wts) + 512;
 }
 
-static bool tc_supported(int Cin_e, int Cout_e, int k, int d3, int d4) { return tc_plan(Cin_e, Cout_e, k, d3, d4).ok; }
+bool conv4d_tc_supports(int Cin_e, int Cout_e, int k, int d3, int d4) { return tc_plan(Cin_e, Cout_e, k, d3, d4).ok; }
 
-// runs one effective convolution on the tensor cores; returns 2 when the shape is unsupported
-static int run_tc(const void *x, const float *w, const float *bias, const void *mask, void *y, void *scratch,
-                  PackDesc d, int B, int Gx, int d1, int d2, int d3, int d4, int relu, int dtype, cudaStream_t st) {
+// runs one effective convolution on the tensor cores; returns 2 when the shape/layout is outside the envelope
+static int run_tc(const void *x, int x_dtype, const float *w, const float *bias, const void *mask, int mask_dtype, void *y,
+                  int y_dtype, void *scratch, PackDesc d, int B, int Gx, int d1, int d2, int d3, int d4, int relu,
+                  cudaStream_t st) {
     const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4);
     if (!pl.ok) return 2;
-    const size_t vol = (size_t)d1 * d2 * d3 * d4;
-    __half *act = reinterpret_cast<__half *>(scratch);
-    __half *wp = reinterpret_cast<__half *>((uint8_t *)scratch + align256((size_t)B * Gx * 2 * vol * 16));
-
-    // 1. activations -> channel-blocked fp16
-    {
-        unsigned gx = (unsigned)((vol + 255) / 256 < 4096 ? (vol + 255) / 256 : 4096);
-        dim3 grid(gx, B * Gx, 2);
-        NC_CHECK(B * Gx <= 65535, "conv4d(tc): batch too large");
-        const int taps = pl.mode == 3 ? d.k : 0;
-        if (dtype == NCNET_F32)
-            pack_act_kernel<float><<<grid, 256, 0, st>>>((const float *)x, act, d.Cin_e, vol, d4, taps, d.k / 2);
-        else
-            pack_act_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, act, d.Cin_e, vol, d4, taps, d.k / 2);
-        NC_LAUNCH_OK("pack_act_kernel");
+    if (x_dtype == NCNET_CB16 && pl.mode == 3) return 2;        // the tap im2col needs the planar single-channel input
+    if (y_dtype == NCNET_CB16 && pl.CoutPad < 16) return 2;
+    if (mask && ((mask_dtype == NCNET_CB16) != (y_dtype == NCNET_CB16))) return 2;
+    uint8_t *sc = (uint8_t *)scratch;
+    const __half *act;
+    size_t used = 0;
+    if (x_dtype == NCNET_CB16) {
+        act = (const __half *)x;
+    } else {
+        int rc = cb16_pack(x, x_dtype, sc, B * Gx, d.Cin_e, d1, d2, d3, d4, d.k, pl.mode == 3 ? 1 : 0, st);
+        if (rc) return rc;
+        act = (const __half *)sc;
+        used = align256(cb16_bytes((size_t)B * Gx, d1, d2, d3, d4, d.k));
     }
-    // 2. weights
+    __half *wp = (__half *)(sc + used);
     {
         TcPackW a{};
         a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad;
@@ -449,24 +568,26 @@ static int run_tc(const void *x, const float *w, const float *bias, const void *
         pack_w_tc_kernel<<<blocks, 256, 0, st>>>(w, wp, a);
         NC_LAUNCH_OK("pack_w_tc_kernel");
     }
-    // 3. the implicit GEMM
     TcArgs a{};
     a.act = act; a.wp = wp; a.bias = bias; a.mask = mask; a.out = y;
     a.B = B; a.G = d.G_e; a.Gx = Gx; a.Cout = d.Cout_e; a.CoutPad = pl.CoutPad;
-    a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = d.k; a.P = pl.P; a.lpad = pl.lpad;
+    a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = d.k; a.P = pl.P;
     a.R = pl.R; a.nchunks = pl.nchunks; a.NT = pl.NT; a.N = pl.N; a.NG = pl.NG; a.KSTEPS = pl.KSTEPS;
-    a.npos_pad = pl.npos_pad; a.relu = relu; a.out_f16 = dtype == NCNET_F16; a.mask_f16 = dtype == NCNET_F16;
+    a.npos_pad = pl.npos_pad; a.relu = relu;
+    a.out_mode = y_dtype == NCNET_CB16 ? 2 : (y_dtype == NCNET_F16 ? 1 : 0);
+    a.mask_mode = !mask ? 0 : (mask_dtype == NCNET_CB16 ? 3 : (mask_dtype == NCNET_F16 ? 2 : 1));
     a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes;
-    // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
     a.dbg = g_tc_debug_buffer;
+    // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
     a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const int pad = d.k / 2;
     for (int ks = 0; ks < kMaxKSteps; ++ks) a.aoff[ks] = (pl.mode == 1 && ks < d.k) ? ks * pl.P : 0;
     for (int gi = 0; gi < kMaxGroups; ++gi) {
         int s = 0;
         if (gi < pl.NG) {
             if (pl.mode == 1) s = gi;                                   // group = d4 tap
             else if (pl.mode == 2) s = (gi / d.k) * pl.P + (gi % d.k);  // group = (d3, d4)
-            else s = gi * pl.P;                                         // group = d3 tap
+            else s = gi * pl.P + pad;                                   // group = d3 tap; the d4 taps sit in the channels of column l + pad
         }
         a.gshift[gi] = s;
     }
@@ -474,36 +595,32 @@ static int run_tc(const void *x, const float *w, const float *bias, const void *
     NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
     const long long ctas = (long long)B * d.G_e * d1 * d2 * pl.nchunks;
     NC_CHECK(ctas < (1ll << 31), "conv4d(tc): grid too large");
-    CUtensorMap amap;
-    if (make_act_tmap(&amap, act, (size_t)B * Gx * 2, d1, d2, d3, d4, pl.P, pl.R + d.k - 1)) return 1;
-    conv4d_tc_kernel<<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a, amap);
+    conv4d_tc_kernel<<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a);
     NC_LAUNCH_OK("conv4d_tc_kernel");
     return 0;
 }
 
-int conv4d_tc_fwd(const void *x, const float *w, const float *bias, void *y, void *scratch, int B, int Cin, int Cout,
-                  int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input, int relu,
-                  int dtype, cudaStream_t st) {
+int conv4d_tc_fwd(const void *x, int x_dtype, const float *w, const float *bias, void *y, int y_dtype, void *scratch, int B,
+                  int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
+                  int relu, cudaStream_t st) {
     PackDesc d{};
     d.Cin = Cin; d.Cout = Cout; d.k = k; d.w_layout = w_layout; d.dgrad = 0; d.merge_groups = 0;
     d.G_e = symmetric ? 2 : 1; d.Cin_e = Cin; d.Cout_e = Cout;
     const int Gx = (symmetric && !shared_input) ? 2 : 1;
-    return run_tc(x, w, bias, nullptr, y, scratch, d, B, Gx, d1, d2, d3, d4, relu, dtype, st);
+    return run_tc(x, x_dtype, w, bias, nullptr, 0, y, y_dtype, scratch, d, B, Gx, d1, d2, d3, d4, relu, st);
 }
 
-int conv4d_tc_dgrad(const void *gy, const float *w, const void *mask, void *gx, void *scratch, int B, int Cin,
-                    int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
-                    int dtype, cudaStream_t st) {
+int conv4d_tc_dgrad(const void *gy, int gy_dtype, const float *w, const void *mask, int mask_dtype, void *gx, int gx_dtype,
+                    void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
+                    int symmetric, int shared_input, cudaStream_t st) {
     PackDesc d{};
     d.Cin = Cin; d.Cout = Cout; d.k = k; d.w_layout = w_layout; d.dgrad = 1;
     const int G = symmetric ? 2 : 1;
     int Gx;
     if (G == 2 && shared_input) { d.merge_groups = 1; d.G_e = 1; d.Cin_e = 2 * Cout; d.Cout_e = Cin; Gx = 1; }
     else { d.merge_groups = 0; d.G_e = G; d.Cin_e = Cout; d.Cout_e = Cin; Gx = G; }
-    return run_tc(gy, w, nullptr, mask, gx, scratch, d, B, Gx, d1, d2, d3, d4, 0, dtype, st);
+    return run_tc(gy, gy_dtype, w, nullptr, mask, mask_dtype, gx, gx_dtype, scratch, d, B, Gx, d1, d2, d3, d4, 0, st);
 }
-
-bool conv4d_tc_supports(int Cin_e, int Cout_e, int k, int d3, int d4) { return tc_supported(Cin_e, Cout_e, k, d3, d4); }
 
 }  // namespace ncnet
 

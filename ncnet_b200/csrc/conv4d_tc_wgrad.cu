@@ -28,14 +28,14 @@ constexpr int kWgThreads = 192;
 constexpr int kWgStages = 3;
 
 struct WgArgs {
-    const __half *xa;   // A side, blocked [B*GxA][HA][d1*d2][d3][d4][8]
-    const __half *gb;   // B side, blocked [B*G][HB][d1*d2][d3][d4][8]
+    const __half *xa;   // A side, CB16 [B*GxA][2][d1*d2][d3+2p][P][8]
+    const __half *gb;   // B side, CB16 [B*G][2][d1*d2][d3+2p][P][8]
     float *part;        // [S][G][Cin][k][k][k][k][cop]
-    int B, G, GxA, HA, HB;
+    int B, G, GxA;
     int d1, d2, d3, d4, KS, P;
     int variant, NAv, NBv, N, nb_copy;      // nb_copy: B halves copied per stage
     uint32_t a_sbo, b_sbo;
-    int a_row0, a_col0, b_row0;
+    int a_r0, b_r0;                         // buffer row at which the haloed X / G plane is placed
     int npos_a, npos_b, nkb;
     int S, Cin, Cout, cop;
     uint32_t idesc, tmem_cols;
@@ -65,8 +65,7 @@ __device__ __forceinline__ bool wg_pair(const WgArgs &p, int pl, int t1, int t2,
 }
 
 __global__ void __launch_bounds__(kWgThreads, 1)
-conv4d_tc_wgrad_kernel(const WgArgs p, const __grid_constant__ CUtensorMap xmap,
-                       const __grid_constant__ CUtensorMap gmap) {
+conv4d_tc_wgrad_kernel(const WgArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[kWgStages], empty_bar[kWgStages], accum_bar;
     __shared__ uint32_t tmem_base_s;
@@ -107,10 +106,11 @@ conv4d_tc_wgrad_kernel(const WgArgs p, const __grid_constant__ CUtensorMap xmap,
         // ===== producer =====
         int stage = 0;
         uint32_t phase = 0;
-        // one TMA tile per staged channel half: X with its halo (zeros outside the volume), G as is
-        const uint32_t a_tile = (uint32_t)p.P * (p.d3 + p.KS - 1) * 16u, b_tile = (uint32_t)p.P * p.d3 * 16u;
-        const uint32_t tx = (uint32_t)p.NAv * a_tile + (uint32_t)p.nb_copy * b_tile;
-        if (elect_one()) { prefetch_tmap(&xmap); prefetch_tmap(&gmap); }
+        // a haloed plane is one contiguous run in CB16: one bulk copy per staged channel half
+        const size_t plane_cb = (size_t)(p.d3 + 2 * (p.KS / 2)) * p.P;
+        const size_t ijn = (size_t)p.d1 * p.d2;
+        const uint32_t tile = (uint32_t)(plane_cb * 16);
+        const uint32_t tx = (uint32_t)(p.NAv + p.nb_copy) * tile;
         for (int pl = pbeg; pl < pend; ++pl) {
             int b; size_t ij_x, ij_g;
             if (!wg_pair(p, pl, t1, t2, b, ij_x, ij_g)) continue;
@@ -119,14 +119,14 @@ conv4d_tc_wgrad_kernel(const WgArgs p, const __grid_constant__ CUtensorMap xmap,
                 uint8_t *sa = smem + (size_t)stage * p.stage_bytes;
                 uint8_t *sb = sa + p.a_bytes;
                 mbar_expect_tx(&full_bar[stage], tx);
-                const int bga = b * p.GxA + (p.GxA == 1 ? 0 : g);
-                const int bgb = b * p.G + g;
+                const size_t bga = (size_t)b * p.GxA + (p.GxA == 1 ? 0 : g);
+                const size_t bgb = (size_t)b * p.G + g;
                 for (int h = 0; h < p.NAv; ++h)
-                    tma_tile_5d(sa + (size_t)h * p.npos_a * 16, &xmap, 0, -p.a_col0, -p.a_row0, (int)ij_x, bga * p.HA + h,
-                                &full_bar[stage]);
+                    bulk_g2s(sa + ((size_t)h * p.npos_a + (size_t)p.a_r0 * p.P) * 16,
+                             p.xa + (((bga * 2 + h) * ijn + ij_x) * plane_cb) * 8, tile, &full_bar[stage]);
                 for (int h = 0; h < p.nb_copy; ++h)
-                    tma_tile_5d(sb + ((size_t)h * p.npos_b + (size_t)p.b_row0 * p.P) * 16, &gmap, 0, 0, 0, (int)ij_g,
-                                bgb * p.HB + h, &full_bar[stage]);
+                    bulk_g2s(sb + ((size_t)h * p.npos_b + (size_t)p.b_r0 * p.P) * 16,
+                             p.gb + (((bgb * 2 + h) * ijn + ij_g) * plane_cb) * 8, tile, &full_bar[stage]);
             }
             __syncwarp();
             if (++stage == kWgStages) { stage = 0; phase ^= 1; }
@@ -226,115 +226,97 @@ conv4d_tc_wgrad_kernel(const WgArgs p, const __grid_constant__ CUtensorMap xmap,
     }
 }
 
-// planar [B*Gsrc, C, vol] (T) -> channel-blocked fp16 [B*Gsrc][H][vol][8]
-//   tap_mode 0: channels = the tensor's channels (zero padded to 8*H)
-//   tap_mode 1: single channel, channel t = value at l + t - pad        (taps along the last axis)
-//   tap_mode 2: single channel, channel t = value at j - t + pad        (taps along the second axis)
-template <typename T>
-__global__ void __launch_bounds__(256)
-wg_pack_kernel(const T *__restrict__ x, __half *__restrict__ act, int C, int H, int d2, int d3, int d4, size_t vol,
-               int tap_mode, int taps, int pad) {
-    const size_t bg = blockIdx.y;
-    const int half = blockIdx.z;
-    const size_t plane = (size_t)d3 * d4;
-    for (size_t pos = (size_t)blockIdx.x * blockDim.x + threadIdx.x; pos < vol; pos += (size_t)gridDim.x * blockDim.x) {
-        __align__(16) __half v[8];
-        if (tap_mode == 0) {
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int ch = half * 8 + c;
-                v[c] = __float2half_rn(ch < C ? ldf(x + (bg * C + ch) * vol + pos) : 0.f);
-            }
-        } else if (tap_mode == 1) {
-            const int l = (int)(pos % d4);
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int ll = l + c - pad;
-                v[c] = __float2half_rn((c < taps && ll >= 0 && ll < d4) ? ldf(x + bg * vol + pos + (c - pad)) : 0.f);
-            }
-        } else {
-            const int j = (int)((pos / plane) % d2);
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int jj = j - c + pad;
-                v[c] = __float2half_rn((c < taps && jj >= 0 && jj < d2)
-                                           ? ldf(x + bg * vol + pos + (ptrdiff_t)(pad - c) * (ptrdiff_t)plane) : 0.f);
-            }
-        }
-        *reinterpret_cast<uint4 *>(act + ((bg * H + half) * vol + pos) * 8) = *reinterpret_cast<const uint4 *>(v);
-    }
-}
-
 // conv4d_fp32.cu: reduces the per-slice partial sums into the reference layout and sums the bias gradient
 int wgrad_finish(const float *part, float *gw, float *gb, const void *gy, int S, int G, int B, int Cin, int Cout, int k,
                  int cop, int w_layout, size_t vol, int dtype, cudaStream_t st);
 
+// bias gradient from a CB16 grad_y: db[o] += sum over blocks and positions (halo is zero)
+__global__ void __launch_bounds__(256)
+cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int Cout, size_t npad, int chunks) {
+    const size_t blkhalf = blockIdx.y;            // (block, half)
+    const int half = (int)(blkhalf & 1);
+    const __half *src = gy + blkhalf * npad * 8;
+    const size_t per = (npad + chunks - 1) / chunks;
+    const size_t beg = (size_t)blockIdx.x * per, end = beg + per < npad ? beg + per : npad;
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (size_t e = beg + threadIdx.x; e < end; e += blockDim.x) {
+        const uint4 raw = *reinterpret_cast<const uint4 *>(src + e * 8);
+        const __half *h = reinterpret_cast<const __half *>(&raw);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[c] += __half2float(h[c]);
+    }
+    __shared__ float sm[8][8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) {
+        const float v = warp_sum(acc[c]);
+        if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5][c] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 8) {
+        float t = 0.f;
+        for (int w8 = 0; w8 < 8; ++w8) t += sm[w8][threadIdx.x];
+        const int o = half * 8 + threadIdx.x;
+        if (o < Cout) atomicAdd(db + o, t);
+    }
+}
+
 struct WgPlan {
     bool ok;
-    int variant, NAv, NBv, N, nb_copy, HA, HB, P, a_row0, a_col0, b_row0, npos_a, npos_b, nkb, S, cop;
-    uint32_t a_sbo, b_sbo, a_bytes, stage_bytes, tmem_cols;
-    size_t smem, xa_bytes, gb_bytes, part_bytes;
+    int variant, NAv, NBv, N, nb_copy, P, a_r0, b_r0, npos_a, npos_b, nkb, S, cop;
+    uint32_t a_sbo, b_sbo, a_bytes, stage_bytes, tmem_cols, b_start;
+    size_t smem, part_bytes;
 };
 
 static size_t wg_align(size_t v) { return (v + 255) & ~(size_t)255; }
 
-static WgPlan wg_plan(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int G, int GxA) {
+static WgPlan wg_plan(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int G) {
     WgPlan w{};
     w.ok = false;
     if (Cin > 16 || Cout > 16 || (k != 3 && k != 5)) return w;
-    const size_t vol = (size_t)d1 * d2 * d3 * d4;
-    w.P = d4 + k - 1;
     const int pad = k / 2;
+    w.P = d4 + 2 * pad;
+    const int plane_cb = (d3 + 2 * pad) * w.P;          // the K range: every position of a haloed plane
+    w.nkb = (plane_cb + 15) / 16;
     if (Cin == 1 && Cout > 1) {
-        w.variant = 1; w.NAv = 1; w.HA = 1; w.NBv = 1; w.N = 16; w.nb_copy = 2; w.HB = 2;
-        w.a_sbo = (uint32_t)w.P * 16u;                 // groups = t3 row shifts
-        w.a_row0 = pad; w.a_col0 = 0; w.b_row0 = 0;
-        const int kpos = d3 * w.P;                      // K range: every G position
-        w.nkb = (kpos + 15) / 16;
+        // A = X' (d4 taps in the channels of half 0), groups = d3 row shifts; B = G, the two halves are the N groups
+        w.variant = 1; w.NAv = 1; w.NBv = 1; w.N = 16; w.nb_copy = 2;
+        w.a_sbo = (uint32_t)w.P * 16u;
+        w.a_r0 = pad; w.b_r0 = 0; w.b_start = 0;
         w.npos_a = w.nkb * 16 + 7 * w.P + 8;
+        if (w.npos_a < (pad + d3 + 2 * pad) * w.P) w.npos_a = (pad + d3 + 2 * pad) * w.P;
         w.npos_b = w.nkb * 16 + 8;
-        w.b_sbo = (uint32_t)w.npos_b * 16u;             // the two channel halves of G are the two N groups
         w.cop = ((Cout + 3) / 4) * 4;
-    } else if (Cout == 1) {
-        w.variant = 3; w.NAv = (Cin + 7) / 8; w.HA = 2; w.NBv = 1; w.N = 64; w.nb_copy = 1; w.HB = 1;
-        w.a_sbo = 16u;                                  // groups = t4 shifts
-        w.b_sbo = (uint32_t)w.P * 16u;                  // groups = reversed t3 row shifts
-        w.a_row0 = pad; w.a_col0 = pad; w.b_row0 = 8;
-        const int kpos = (d3 + k - 1) * w.P;
-        w.nkb = (kpos + 15) / 16;
-        w.npos_a = w.nkb * 16 + 8;
-        w.npos_b = w.nkb * 16 + 8 * w.P + 8;
-        w.cop = 4;
     } else {
-        w.variant = 2; w.NAv = (Cin + 7) / 8; w.HA = 2; w.NBv = (Cout + 7) / 8; w.N = 64; w.nb_copy = w.NBv; w.HB = 2;
+        // A = X half, groups = d4 shifts; B = G half (V2) or G8 with the d2 taps in its channels (V3),
+        // groups = d3 row shifts in reversed order (group r' <-> tap 7 - r')
+        w.variant = Cout == 1 ? 3 : 2;
+        w.NAv = (Cin + 7) / 8; w.NBv = w.variant == 3 ? 1 : (Cout + 7) / 8; w.N = 64; w.nb_copy = w.NBv;
         w.a_sbo = 16u;
         w.b_sbo = (uint32_t)w.P * 16u;
-        w.a_row0 = pad; w.a_col0 = pad; w.b_row0 = 8;
-        const int kpos = (d3 + k - 1) * w.P;
-        w.nkb = (kpos + 15) / 16;
+        w.a_r0 = 0; w.b_r0 = 8 - pad; w.b_start = (uint32_t)(w.P + pad) * 16u;
         w.npos_a = w.nkb * 16 + 8;
-        w.npos_b = w.nkb * 16 + 8 * w.P + 8;
-        w.cop = ((Cout + 3) / 4) * 4;
+        w.npos_b = w.nkb * 16 + 8 * w.P + pad + 8;
+        if (w.npos_b < (w.b_r0 + d3 + 2 * pad) * w.P) w.npos_b = (w.b_r0 + d3 + 2 * pad) * w.P;
+        w.cop = w.variant == 3 ? 4 : ((Cout + 3) / 4) * 4;
     }
     w.npos_a = ((w.npos_a + 7) / 8) * 8;
     w.npos_b = ((w.npos_b + 7) / 8) * 8;
+    if (w.variant == 1) w.b_sbo = (uint32_t)w.npos_b * 16u;
     if (w.npos_a > 16383 || w.npos_b > 16383 || w.P > 1023) return w;
     w.a_bytes = (uint32_t)w.NAv * w.npos_a * 16u;
-    const uint32_t b_bytes = (uint32_t)(w.variant == 1 ? 2 : w.NBv) * w.npos_b * 16u;
+    const uint32_t b_bytes = (uint32_t)w.nb_copy * w.npos_b * 16u;
     w.stage_bytes = ((w.a_bytes + b_bytes + 127) / 128) * 128;
     w.smem = (size_t)kWgStages * w.stage_bytes;
     if (w.smem > 220 * 1024) return w;
     const int cols = w.NAv * w.NBv * w.N;
     w.tmem_cols = cols <= 32 ? 32 : (cols <= 64 ? 64 : (cols <= 128 ? 128 : (cols <= 256 ? 256 : 512)));
-    // slices: enough CTAs for ~4 waves, balanced
+    // slices: enough CTAs for ~4 waves
     const long long base = (long long)G * k * (w.variant == 3 ? 1 : k);
     const long long planes = (long long)B * d1 * d2;
     long long S = (4ll * kNumSMs + base - 1) / base;
     if (S > planes) S = planes;
     if (S < 1) S = 1;
     w.S = (int)S;
-    w.xa_bytes = wg_align((size_t)B * GxA * w.HA * vol * 16);
-    w.gb_bytes = wg_align((size_t)B * G * w.HB * vol * 16);
     w.part_bytes = wg_align((size_t)w.S * G * Cin * k * k * k * k * w.cop * sizeof(float));
     w.ok = true;
     return w;
@@ -342,66 +324,80 @@ static WgPlan wg_plan(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, 
 
 size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric) {
     const int G = symmetric ? 2 : 1;
-    const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G, G);
+    const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G);
     if (!w.ok) return 0;
-    return w.xa_bytes + w.gb_bytes + w.part_bytes + 1024;
+    // CB16 copies of planar operands (worst case both) + the per-slice partial sums
+    return 2 * wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k)) + w.part_bytes + 1024;
 }
 
-template <typename T>
-static int wg_run(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout, int d1,
-                  int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input, cudaStream_t st) {
+// returns 2 when the shape/layout is outside the tensor-core kernel's envelope
+static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch, int B,
+                  int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
+                  cudaStream_t st) {
     const int G = symmetric ? 2 : 1;
     const int GxA = (G == 2 && !shared_input) ? 2 : 1;
-    const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G, GxA);
+    const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G);
     if (!w.ok) return 2;
+    if (w.variant == 1 && x_dtype == NCNET_CB16) return 2;      // the tap im2col needs the planar single-channel tensors
+    if (w.variant == 3 && gy_dtype == NCNET_CB16) return 2;
     const size_t vol = (size_t)d1 * d2 * d3 * d4;
-    uint8_t *base = (uint8_t *)scratch;
-    __half *xa = (__half *)base;
-    __half *gbk = (__half *)(base + w.xa_bytes);
-    float *part = (float *)(base + w.xa_bytes + w.gb_bytes);
-    const unsigned gx = (unsigned)((vol + 255) / 256 < 4096 ? (vol + 255) / 256 : 4096);
-    NC_CHECK(B * G <= 65535, "conv4d_wgrad(tc): batch too large");
-    // A side
-    wg_pack_kernel<T><<<dim3(gx, B * GxA, w.HA), 256, 0, st>>>((const T *)x, xa, Cin, w.HA, d2, d3, d4, vol,
-                                                               w.variant == 1 ? 1 : 0, k, k / 2);
-    NC_LAUNCH_OK("wg_pack_kernel(x)");
-    // B side
-    wg_pack_kernel<T><<<dim3(gx, B * G, w.HB), 256, 0, st>>>((const T *)gy, gbk, Cout, w.HB, d2, d3, d4, vol,
-                                                             w.variant == 3 ? 2 : 0, k, k / 2);
-    NC_LAUNCH_OK("wg_pack_kernel(gy)");
+    uint8_t *sc = (uint8_t *)scratch;
+    size_t used = 0;
+    const __half *xa, *gbk;
+    if (x_dtype == NCNET_CB16) xa = (const __half *)x;
+    else {
+        int rc = cb16_pack(x, x_dtype, sc + used, B * GxA, Cin, d1, d2, d3, d4, k, w.variant == 1 ? 1 : 0, st);
+        if (rc) return rc;
+        xa = (const __half *)(sc + used);
+        used += wg_align(cb16_bytes((size_t)B * GxA, d1, d2, d3, d4, k));
+    }
+    if (gy_dtype == NCNET_CB16) gbk = (const __half *)gy;
+    else {
+        int rc = cb16_pack(gy, gy_dtype, sc + used, B * G, Cout, d1, d2, d3, d4, k, w.variant == 3 ? 2 : 0, st);
+        if (rc) return rc;
+        gbk = (const __half *)(sc + used);
+        used += wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));
+    }
+    float *part = (float *)(sc + used);
     cudaError_t e = cudaMemsetAsync(part, 0, w.part_bytes, st);
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): memset: %s", cudaGetErrorString(e));
 
     WgArgs a{};
     a.xa = xa; a.gb = gbk; a.part = part;
-    a.B = B; a.G = G; a.GxA = GxA; a.HA = w.HA; a.HB = w.HB;
+    a.B = B; a.G = G; a.GxA = GxA;
     a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = k; a.P = w.P;
     a.variant = w.variant; a.NAv = w.NAv; a.NBv = w.NBv; a.N = w.N; a.nb_copy = w.nb_copy;
-    a.a_sbo = w.a_sbo; a.b_sbo = w.b_sbo; a.a_row0 = w.a_row0; a.a_col0 = w.a_col0; a.b_row0 = w.b_row0;
+    a.a_sbo = w.a_sbo; a.b_sbo = w.b_sbo; a.a_r0 = w.a_r0; a.b_r0 = w.b_r0;
     a.npos_a = w.npos_a; a.npos_b = w.npos_b; a.nkb = w.nkb; a.S = w.S; a.Cin = Cin; a.Cout = Cout; a.cop = w.cop;
-    a.tmem_cols = w.tmem_cols; a.stage_bytes = w.stage_bytes; a.a_bytes = w.a_bytes;
-    a.b_start = w.variant == 1 ? 0u : (uint32_t)w.P * 16u;
+    a.tmem_cols = w.tmem_cols; a.stage_bytes = w.stage_bytes; a.a_bytes = w.a_bytes; a.b_start = w.b_start;
     // D = f32, A = B = f16, both MN-major (bits 15/16), N>>3 at bit 17, M=64 -> 4 at bit 24
     a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
     e = cudaFuncSetAttribute(conv4d_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem);
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): smem attribute: %s", cudaGetErrorString(e));
     dim3 grid(w.S, G * k * (w.variant == 3 ? 1 : k));
-    CUtensorMap xmap, gmap;
-    if (make_act_tmap(&xmap, xa, (size_t)B * GxA * w.HA, d1, d2, d3, d4, w.P, d3 + k - 1)) return 1;
-    if (make_act_tmap(&gmap, gbk, (size_t)B * G * w.HB, d1, d2, d3, d4, w.P, d3)) return 1;
-    conv4d_tc_wgrad_kernel<<<grid, kWgThreads, w.smem, st>>>(a, xmap, gmap);
+    conv4d_tc_wgrad_kernel<<<grid, kWgThreads, w.smem, st>>>(a);
     NC_LAUNCH_OK("conv4d_tc_wgrad_kernel");
-
-    return wgrad_finish(part, gw, gb, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol,
-                        sizeof(T) == 4 ? NCNET_F32 : NCNET_F16, st);
+    if (gy_dtype != NCNET_CB16)
+        return wgrad_finish(part, gw, gb, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, gy_dtype, st);
+    int rc = wgrad_finish(part, gw, nullptr, nullptr, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, NCNET_F32, st);
+    if (rc || !gb) return rc;
+    e = cudaMemsetAsync(gb, 0, Cout * sizeof(float), st);
+    NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): memset bias: %s", cudaGetErrorString(e));
+    const int pad = k / 2;
+    const size_t npad = (size_t)d1 * d2 * (d3 + 2 * pad) * (d4 + 2 * pad);
+    int chunks = (int)((npad + 65535) / 65536);
+    if (chunks < 1) chunks = 1;
+    NC_CHECK(B * G * 2 <= 65535, "conv4d_wgrad(tc): too many blocks for the bias grid");
+    cb16_bias_grad_kernel<<<dim3(chunks, B * G * 2), 256, 0, st>>>(gbk, gb, Cout, npad, chunks);
+    NC_LAUNCH_OK("cb16_bias_grad_kernel");
+    return 0;
 }
 
-int conv4d_tc_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout,
-                    int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input, int dtype,
-                    cudaStream_t st) {
-    if (dtype == NCNET_F32)
-        return wg_run<float>(x, gy, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric, shared_input, st);
-    return wg_run<__half>(x, gy, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric, shared_input, st);
+int conv4d_tc_wgrad(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch, int B,
+                    int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric,
+                    int shared_input, cudaStream_t st) {
+    return wg_run(x, x_dtype, gy, gy_dtype, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+                  shared_input, st);
 }
 
 }  // namespace ncnet

@@ -184,11 +184,42 @@ def _wdims(w: torch.Tensor, layout: int) -> Tuple[int, int, int]:
     return w.shape[1], w.shape[0], w.shape[2]
 
 
-def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode):
+class _CB16:
+    """Handle of a channel-blocked, zero-haloed fp16 activation tensor (include/ncnet_b200.h: NCNET_CB16).
+    ``buf`` is a flat uint8 torch tensor owned by PyTorch; ``shape`` is the planar shape it stands for."""
+    __slots__ = ("buf", "shape", "k", "dtype")
+
+    def __init__(self, buf, shape, k, dtype):
+        self.buf, self.shape, self.k, self.dtype = buf, tuple(shape), k, dtype
+
+    @staticmethod
+    def empty(shape, k, device, dtype, per_group):
+        bsz, ch, d1, d2, d3, d4 = shape
+        nblk = bsz * (ch // per_group)
+        nbytes = _cabi.lib().ncnet_cb16_bytes(nblk, d1, d2, d3, d4, k)
+        return _CB16(torch.empty(nbytes, device=device, dtype=torch.uint8), shape, k, dtype)
+
+    @property
+    def device(self):
+        return self.buf.device
+
+    def data_ptr(self):
+        return self.buf.data_ptr()
+
+
+def _adt(t) -> int:
+    return _cabi.CB16 if isinstance(t, _CB16) else _dt(t)
+
+
+def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode, out_cb16=False):
     cin, cout, k = _wdims(w32, layout)
     bsz, _, d1, d2, d3, d4 = x.shape
     g = 2 if symmetric else 1
-    y = torch.empty(bsz, g * cout, d1, d2, d3, d4, device=x.device, dtype=x.dtype)
+    oshape = (bsz, g * cout, d1, d2, d3, d4)
+    if out_cb16:
+        y = _CB16.empty(oshape, k, x.device, x.dtype, cout)
+    else:
+        y = torch.empty(oshape, device=x.device, dtype=x.dtype)
     L = _cabi.lib()
     scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(bsz, cin, cout, d1, d2, d3, d4, k, int(symmetric), mode),
                           device=x.device, dtype=torch.uint8)
@@ -197,46 +228,63 @@ def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode):
         if log:
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ev0.record()
-        _cabi.check(L.ncnet_conv4d_fwd(_ptr(x), _ptr(w32), _ptr(b32), _ptr(y), _ptr(scratch), bsz, cin, cout, d1, d2, d3,
-                                       d4, k, layout, int(symmetric), int(shared_input), int(relu), _dt(x), mode,
-                                       _stream()), "conv4d_fwd")
+        _cabi.check(L.ncnet_conv4d_fwd(x.data_ptr(), _ptr(w32), _ptr(b32), y.data_ptr(), _ptr(scratch), bsz, cin, cout, d1,
+                                       d2, d3, d4, k, layout, int(symmetric), int(shared_input), int(relu), _adt(x),
+                                       _adt(y), mode, _stream()), "conv4d_fwd")
         if log:
             ev1.record()
             EVENT_LOG.append(("conv4d_fwd_16_16", ev0, ev1))
-    _count(2)
+    _count(2 if isinstance(x, _CB16) else 3 if mode == CONV_TC16 else 2)
     return y
 
 
-def _conv_dgrad(gy, w32, mask, layout, symmetric, shared_input, mode):
+def _conv_dgrad(gy, w32, mask, layout, symmetric, shared_input, mode, out_cb16=False):
     cin, cout, k = _wdims(w32, layout)
     bsz, _, d1, d2, d3, d4 = gy.shape
     gin = 1 if (shared_input or not symmetric) else 2
-    gx = torch.empty(bsz, gin * cin, d1, d2, d3, d4, device=gy.device, dtype=gy.dtype)
+    oshape = (bsz, gin * cin, d1, d2, d3, d4)
+    if out_cb16:
+        gx = _CB16.empty(oshape, k, gy.device, gy.dtype, cin)
+    else:
+        gx = torch.empty(oshape, device=gy.device, dtype=gy.dtype)
     L = _cabi.lib()
     scratch = torch.empty(L.ncnet_conv4d_scratch_bytes(bsz, cin, cout, d1, d2, d3, d4, k, int(symmetric), mode),
                           device=gy.device, dtype=torch.uint8)
     with torch.cuda.device(gy.device):
-        _cabi.check(L.ncnet_conv4d_dgrad(_ptr(gy), _ptr(w32), _ptr(mask), _ptr(gx), _ptr(scratch), bsz, cin, cout, d1, d2,
-                                         d3, d4, k, layout, int(symmetric), int(shared_input), _dt(gy), mode, _stream()),
-                    "conv4d_dgrad")
-    _count(2)
+        _cabi.check(L.ncnet_conv4d_dgrad(gy.data_ptr(), _ptr(w32), None if mask is None else mask.data_ptr(),
+                                         gx.data_ptr(), _ptr(scratch), bsz, cin, cout, d1, d2, d3, d4, k, layout,
+                                         int(symmetric), int(shared_input), _adt(gy), 0 if mask is None else _adt(mask),
+                                         _adt(gx), mode, _stream()), "conv4d_dgrad")
+    _count(2 if isinstance(gy, _CB16) else 3 if mode == CONV_TC16 else 2)
     return gx
 
 
 def _conv_wgrad(x, gy, w_like, want_bias, layout, symmetric, shared_input, mode):
     cin, cout, k = _wdims(w_like, layout)
     bsz, _, d1, d2, d3, d4 = x.shape
-    gw = torch.empty(w_like.shape, device=x.device, dtype=torch.float32)
-    gb = torch.empty(cout, device=x.device, dtype=torch.float32) if want_bias else None
+    dev = x.device
+    gw = torch.empty(w_like.shape, device=dev, dtype=torch.float32)
+    gb = torch.empty(cout, device=dev, dtype=torch.float32) if want_bias else None
     L = _cabi.lib()
     nbytes = L.ncnet_conv4d_wgrad_scratch_bytes(bsz, cin, cout, d1, d2, d3, d4, k, int(symmetric), mode)
-    scratch = torch.empty(nbytes, device=x.device, dtype=torch.uint8)
-    with torch.cuda.device(x.device):
-        _cabi.check(L.ncnet_conv4d_wgrad(_ptr(x), _ptr(gy), _ptr(gw), _ptr(gb), _ptr(scratch), bsz, cin, cout, d1, d2, d3,
-                                         d4, k, layout, int(symmetric), int(shared_input), _dt(x), mode, _stream()),
-                    "conv4d_wgrad")
+    scratch = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    with torch.cuda.device(dev):
+        _cabi.check(L.ncnet_conv4d_wgrad(x.data_ptr(), gy.data_ptr(), _ptr(gw), _ptr(gb), _ptr(scratch), bsz, cin, cout, d1,
+                                         d2, d3, d4, k, layout, int(symmetric), int(shared_input), _adt(x), _adt(gy), mode,
+                                         _stream()), "conv4d_wgrad")
     _count(4 if want_bias else 3)
     return gw, gb
+
+
+def cb16_unpack(t: "_CB16", per_group: int) -> torch.Tensor:
+    """CB16 handle -> planar tensor of its shape (tests, and the rare input-gradient path)."""
+    bsz, ch, d1, d2, d3, d4 = t.shape
+    out = torch.empty(t.shape, device=t.device, dtype=t.dtype)
+    with torch.cuda.device(t.device):
+        _cabi.check(_cabi.lib().ncnet_cb16_unpack(t.data_ptr(), _ptr(out), bsz * (ch // per_group), per_group, d1, d2, d3, d4,
+                                                  t.k, _dt(out), _stream()), "cb16_unpack")
+    _count(1)
+    return out
 
 
 class _Conv4dFn(torch.autograd.Function):
@@ -276,35 +324,52 @@ def conv4d(data: torch.Tensor, filters: torch.Tensor, bias: Optional[torch.Tenso
     return _Conv4dFn.apply(data, filters, bias, layout, default_conv_mode() if mode is None else mode)
 
 
+def _stack_can_chain(kernel_sizes, chans, d3, d4, mode) -> bool:
+    """True when every layer of the stack can hand its activations to the next one in CB16
+    (tensor-core mode, one kernel size, <= 16 channels per group)."""
+    if mode != CONV_TC16 or len(set(kernel_sizes)) != 1 or len(kernel_sizes) < 2:
+        return False
+    L = _cabi.lib()
+    cin = 1
+    for cout in chans:
+        if not L.ncnet_conv4d_tc_supported(cin, cout, kernel_sizes[0], d3, d4):
+            return False
+        cin = cout
+    return True
+
+
 class _NeighConsensusFn(torch.autograd.Function):
     """The whole [Conv4d + ReLU] x L stack, both symmetric branches per launch, ReLU fused into the
     conv epilogue and ReLU-backward fused into the dgrad epilogue (reference lib/model.py:143-153).
-    Returns [B, G*Clast, ...] (G=2 branches when symmetric; the caller sums them)."""
+    In tensor-core mode the hidden activations (and their gradients) stay in the CB16 layout between
+    launches.  Returns [B, G*Clast, ...] (G=2 branches when symmetric; the caller sums them)."""
 
     @staticmethod
     def forward(ctx, x, symmetric, mode, *wb):
         n_layers = len(wb) // 2
         xc = x.contiguous()
+        w32s = [wb[2 * l].detach().float().contiguous() for l in range(n_layers)]
+        b32s = [wb[2 * l + 1].detach().float().contiguous() for l in range(n_layers)]
+        chain = _stack_can_chain([w.shape[0] for w in w32s], [w.shape[1] for w in w32s], xc.shape[4], xc.shape[5], mode)
         acts = [xc]
-        w32s = []
         cur = xc
         for l in range(n_layers):
-            w32 = wb[2 * l].detach().float().contiguous()
-            b32 = wb[2 * l + 1].detach().float().contiguous()
-            w32s.append(w32)
-            cur = _conv_fwd(cur, w32, b32, W_KOIKKK, symmetric, l == 0, True, mode)
+            cur = _conv_fwd(cur, w32s[l], b32s[l], W_KOIKKK, symmetric, l == 0, True, mode,
+                            out_cb16=chain and l < n_layers - 1)
             acts.append(cur)
-        ctx.symmetric, ctx.mode, ctx.n_layers = symmetric, mode, n_layers
+        ctx.symmetric, ctx.mode, ctx.n_layers, ctx.chain = symmetric, mode, n_layers, chain
         ctx.wdtype = wb[0].dtype
-        ctx.save_for_backward(*acts, *w32s)
+        ctx.meta = [(a.shape, a.k, a.dtype) if isinstance(a, _CB16) else None for a in acts]
+        ctx.save_for_backward(*[a.buf if isinstance(a, _CB16) else a for a in acts], *w32s)
         return cur
 
     @staticmethod
     def backward(ctx, g):
         n = ctx.n_layers
         saved = ctx.saved_tensors
-        acts, w32s = saved[: n + 1], saved[n + 1:]
-        sym, mode = ctx.symmetric, ctx.mode
+        acts = [(_CB16(t, *m) if m is not None else t) for t, m in zip(saved[: n + 1], ctx.meta)]
+        w32s = saved[n + 1:]
+        sym, mode, chain = ctx.symmetric, ctx.mode, ctx.chain
         out = acts[n]
         bsz = out.shape[0]
         g = g.contiguous()
@@ -321,8 +386,10 @@ class _NeighConsensusFn(torch.autograd.Function):
             gw, gb = _conv_wgrad(acts[l], gz, w32s[l], True, W_KOIKKK, sym, l == 0, mode)
             grads[2 * l], grads[2 * l + 1] = gw.to(ctx.wdtype), gb.to(ctx.wdtype)
             if l > 0:
-                gz = _conv_dgrad(gz, w32s[l], acts[l], W_KOIKKK, sym, False, mode)
+                gz = _conv_dgrad(gz, w32s[l], acts[l], W_KOIKKK, sym, False, mode, out_cb16=chain)
             elif ctx.needs_input_grad[0]:
+                if isinstance(gz, _CB16):       # merged 2*Cout -> Cin gradient runs on the CUDA-core kernel (planar)
+                    gz = cb16_unpack(gz, w32s[0].shape[1])
                 gx = _conv_dgrad(gz, w32s[0], None, W_KOIKKK, sym, True, mode)
         return (gx, None, None, *grads)
 

@@ -34,7 +34,7 @@ def test_argument_validation_without_gpu():
     assert lib.ncnet_mutual_matching_fwd(None, None, None, 1, 4, 4, 1, 0, None) != 0
     assert b"null" in lib.ncnet_last_error()
     one = ctypes.c_void_p(16)
-    rc = lib.ncnet_conv4d_fwd(one, one, None, one, one, 1, 1, 1, 4, 4, 4, 4, 4, 0, 0, 1, 0, 0, 0, None)
+    rc = lib.ncnet_conv4d_fwd(one, one, None, one, one, 1, 1, 1, 4, 4, 4, 4, 4, 0, 0, 1, 0, 0, 0, 0, None)
     assert rc != 0 and b"even kernel" in lib.ncnet_last_error()
     rc = lib.ncnet_maxpool4d_fwd(one, one, one, one, one, one, 5, 4, 4, 4, 2, 8, 0, None)
     assert rc != 0 and b"divisible" in lib.ncnet_last_error()
