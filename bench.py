@@ -244,21 +244,31 @@ def run_ours(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = t.item()
 
-    # dominant kernel: the 16->16 Conv4d forward launches (both symmetric branches per launch)
-    fat = [a.elapsed_time(b) for tag, a, b in ev if tag == "conv4d_fwd_16_16"]
+    # the two heaviest kernels: 16->16 Conv4d forward (+ identical dgrad) and 16->16 weight gradient,
+    # both symmetric branches per launch.  `roofline` is the one with the larger share of the step.
     per_rank_b = hi - lo
     flop_fat = 2.0 * per_rank_b * FS ** 4 * 16 * 16 * 5 ** 4 * 2          # dense convention, 2 branches
     pk, pk_kind = peaks()
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
-    roof = None
-    if fat:
-        avg_ms = sum(fat) / len(fat)
+    mode_name = "fp32 CUDA-core" if mode == 0 else "fp16 operands / fp32 accumulate, tcgen05"
+
+    def roof_for(tag, label):
+        ts = [a.elapsed_time(b) for t, a, b in ev if t == tag]
+        if not ts:
+            return None
+        avg_ms = sum(ts) / len(ts)
         ach = flop_fat / (avg_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
-                "traffic": None, "kernel": "conv4d_fwd 16->16 k=5 (layer 2, both branches, B=%d)" % per_rank_b,
-                "avg_launch_ms": avg_ms, "launches_timed": len(fat), "peak_source": pk_kind + " bf16 sustained",
-                "flop_convention": "2*B*N^4*Cin*Cout*k^4 dense (zero-padding taps counted)",
-                "mode": "fp32 CUDA-core" if mode == 0 else "fp16 operands / fp32 accumulate tcgen05"}
+        return {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+                "traffic": None, "kernel": label + " 16->16 k=5 (layer 2, both branches, B=%d)" % per_rank_b,
+                "avg_launch_ms": avg_ms, "launches_timed": len(ts), "total_ms_in_region": sum(ts),
+                "peak_source": pk_kind + " bf16 sustained",
+                "flop_convention": "2*B*N^4*Cin*Cout*k^4 dense (zero-padding taps counted)", "mode": mode_name}
+
+    r_fwd = roof_for("conv4d_fwd_16_16", "conv4d_fwd")
+    r_wg = roof_for("conv4d_wgrad_16_16", "conv4d_wgrad")
+    cands = [r for r in (r_fwd, r_wg) if r]
+    roof = max(cands, key=lambda r: r["total_ms_in_region"]) if cands else None
+    roof_other = [r for r in cands if r is not roof]
 
     # ---- end to end: pinned host features in, loss out, every step ----------------------------
     barrier()
@@ -282,11 +292,12 @@ def run_ours(args):
         line = {
             "metric": METRIC, "value": evals * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-            "scaling": "strong", "vs_baseline": None, "dtype": "f32" if mode == 0 else "f16 operands, f32 accumulate",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32" if mode == 0 else "f16 (tensor-core operands; f32 accumulate, f32 weights/loss/optimizer)",
             "data": "synthetic", "config": workload_config(world),
             "e2e": {"value": evals * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "last_loss": loss_host},
             "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+            "roofline_other": roof_other[0] if roof_other else None,
         }
         if world == 1 and not args.no_cpu_baseline:
             base = cpu_training_step_rate(pairs=2, steps=1, warmup=0, budget_s=60.0)

@@ -21,8 +21,9 @@ EVENT_LOG = None
 
 
 def default_conv_mode() -> int:
-    """NCNET_CONV_MODE=fp32|tc16 selects the Conv4d back end (default fp32 until told otherwise)."""
-    return CONV_TC16 if os.environ.get("NCNET_CONV_MODE", "fp32").lower() in ("tc16", "tc", "1") else CONV_FP32
+    """NCNET_CONV_MODE selects the Conv4d back end: "tc16" (default; tcgen05 tensor cores, fp16 operands,
+    fp32 accumulation, <= 1e-3 normalised error per layer) or "fp32" (CUDA-core fp32 FMA, parity mode)."""
+    return CONV_FP32 if os.environ.get("NCNET_CONV_MODE", "tc16").lower() in ("fp32", "f32", "0") else CONV_TC16
 
 
 def _dt(t: torch.Tensor) -> int:
@@ -268,10 +269,17 @@ def _conv_wgrad(x, gy, w_like, want_bias, layout, symmetric, shared_input, mode)
     L = _cabi.lib()
     nbytes = L.ncnet_conv4d_wgrad_scratch_bytes(bsz, cin, cout, d1, d2, d3, d4, k, int(symmetric), mode)
     scratch = torch.empty(nbytes, device=dev, dtype=torch.uint8)
+    log = EVENT_LOG is not None and cin == 16 and cout == 16
     with torch.cuda.device(dev):
+        if log:
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
         _cabi.check(L.ncnet_conv4d_wgrad(x.data_ptr(), gy.data_ptr(), _ptr(gw), _ptr(gb), _ptr(scratch), bsz, cin, cout, d1,
                                          d2, d3, d4, k, layout, int(symmetric), int(shared_input), _adt(x), _adt(gy), mode,
                                          _stream()), "conv4d_wgrad")
+        if log:
+            ev1.record()
+            EVENT_LOG.append(("conv4d_wgrad_16_16", ev0, ev1))
     _count(4 if want_bias else 3)
     return gw, gb
 

@@ -5,6 +5,9 @@ import numpy as np
 import pytest
 import torch
 
+# the parity tests use the fp32 CUDA-core Conv4d unless a test asks for the tensor-core mode explicitly
+os.environ.setdefault("NCNET_CONV_MODE", "fp32")
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
