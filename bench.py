@@ -149,7 +149,7 @@ def run_reference(args):
         "e2e": {"value": base["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def workload_config(world: int, note: str = ""):
@@ -302,12 +302,25 @@ def run_ours(args):
         if world == 1 and not args.no_cpu_baseline:
             base = cpu_training_step_rate(pairs=2, steps=1, warmup=0, budget_s=60.0)
             line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
+def _emit(line: dict) -> None:
+    """The JSON line goes to the process's ORIGINAL stdout; everything else (NCCL banners, warnings) was
+    re-routed to stderr in main(), so stdout carries exactly one line."""
+    os.write(_REAL_STDOUT, (json.dumps(line) + "\n").encode())
+
+
+_REAL_STDOUT = 1
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)                      # C-level writers (e.g. "NCCL version ...") now land on stderr
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)

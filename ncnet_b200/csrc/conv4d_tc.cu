@@ -19,8 +19,8 @@
 // 128 B/clk shared-memory read rate at 22 % of the tensor peak.
 //   mode M1 (Cin<=16, Cout>1): channels = input channels, N = (d4, o), K-steps per plane = d3 taps
 //   mode M2 (Cout == 1)      : channels = input channels, N = (d3, d4), one K-step per plane
-//   mode M3 (Cin == 1)       : channels = the k taps along d4 (im2col in the pack kernel),
-//                              N = (d3, o), one K-step per plane
+//   mode M3 (Cin == 1)       : channels = two consecutive d3 taps x the k d4 taps (im2col in the pack
+//                              kernel), N = (d3 pair, o), one K-step per plane
 // Pipeline: one elected lane of warp 0 streams the (d1,d2) planes + their weight slab with
 // cp.async.bulk (TMA engine, mbarrier complete_tx) through a 3-stage ring; one elected lane of warp 1
 // issues tcgen05.mma and commits to the stage's "empty" barrier; warps 2-5 drain TMEM (tcgen05.ld),
@@ -97,12 +97,15 @@ conv4d_tc_kernel(const TcArgs p) {
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     {
-        // zero the activation part of every stage once: the tail behind the copied rows is read by the
-        // last tiles' (discarded) rows and must stay finite
+        // zero, once, the tail of each channel-half buffer behind the rows the bulk copies overwrite: it
+        // is read by the last tiles' (discarded) rows and must stay finite
         const uint4 z = make_uint4(0, 0, 0, 0);
-        for (int s = 0; s < kStages; ++s) {
-            uint4 *d = reinterpret_cast<uint4 *>(stage0 + (size_t)s * p.stage_bytes);
-            for (uint32_t e = threadIdx.x; e < p.data_bytes / 16; e += kTcThreads) d[e] = z;
+        const int copied = min(p.R + p.KS - 1, rows_pad - k0) * p.P;      // positions written by every stage's copy
+        const int tail = p.npos_pad - copied;
+        for (int e = threadIdx.x; e < kStages * 2 * tail; e += kTcThreads) {
+            const int s = e / (2 * tail), r = e - s * 2 * tail;
+            const int half = r / tail, pos = copied + (r - half * tail);
+            reinterpret_cast<uint4 *>(stage0 + (size_t)s * p.stage_bytes)[(size_t)half * p.npos_pad + pos] = z;
         }
         // outbuf starts at the bias
         if (p.CoutPad >= 16) {
@@ -331,6 +334,8 @@ conv4d_tc_kernel(const TcArgs p) {
 //   tap_mode 0: channels = the tensor's C (<= 16) channels
 //   tap_mode 1: C == 1, channel t = x[.., l + t - p]                 (taps along the last axis)
 //   tap_mode 2: C == 1, channel t = x[.., j - t + p, ..]             (taps along the second axis, mirrored)
+//   tap_mode 3: C == 1, half u, channel t = x[.., k + u, l + t - p] seen from the haloed position: two
+//               consecutive d3 taps x all d4 taps in the 16 channels (forward mode M3)
 template <typename T>
 __global__ void __launch_bounds__(256)
 cb16_pack_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1, int d2, int d3, int d4, int pad,
@@ -346,7 +351,16 @@ cb16_pack_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1
         const size_t ijx = pp / ((size_t)P * rows);
         const int k = kk - pad, l = ll - pad;
         __align__(16) __half v[8];
-        if (k >= 0 && k < d3 && l >= 0 && l < d4) {
+        if (tap_mode == 3) {
+            // haloed position (kk,ll), half u: channel t = x[kk - p + u, ll - 2p + t]; evaluated on halo rows too
+            const int ks = k + half;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int lt = l - pad + c;
+                v[c] = __float2half_rn((c < taps && ks >= 0 && ks < d3 && lt >= 0 && lt < d4)
+                                           ? ldf(x + blk * vol + ijx * plane + (size_t)ks * d4 + lt) : 0.f);
+            }
+        } else if (k >= 0 && k < d3 && l >= 0 && l < d4) {
             const size_t pos = ijx * plane + (size_t)k * d4 + l;
             if (tap_mode == 0) {
 #pragma unroll
@@ -461,9 +475,9 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
         } else if (a.mode == 2) {   // N = (t3, t4), single out channel, channel = ci
             t3 = n / k; t4 = n % k; oe = 0; ci = kch;
             ok = n < k * k;
-        } else {                    // N = (t3, o), channel = t4 tap, single in channel
-            t3 = n / a.CoutPad; oe = n % a.CoutPad; t4 = kch; ci = 0;
-            ok = kch < k;
+        } else {                    // N = (t3 pair, o), channel = (t3 parity, t4 tap), single in channel
+            t3 = 2 * (n / a.CoutPad) + half; oe = n % a.CoutPad; t4 = c8; ci = 0;
+            ok = c8 < k;
         }
         float v = 0.f;
         if (ok && t3 < k && t4 < k && oe < a.d.Cout_e && ci < a.d.Cin_e)
@@ -488,15 +502,15 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
     TcPlan pl{};
     pl.ok = false;
     if (Cin_e > 16 || Cout_e > 16 || (k != 3 && k != 5)) return pl;
-    if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = 1; }
+    if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = (k + 1) / 2; pl.KSTEPS = 1; }
     else if (Cout_e == 1)          { pl.mode = 2; pl.CoutPad = 1; pl.NG = k * k; pl.KSTEPS = 1; }
     else                           { pl.mode = 1; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = k; }
-    pl.N = pl.mode == 2 ? ((k * k + 15) / 16) * 16 : k * 16;
+    pl.N = pl.mode == 2 ? ((k * k + 15) / 16) * 16 : pl.NG * 16;
     pl.P = d4 + k - 1;
     const int pad = k / 2;
     const int max_aoff = pl.mode == 1 ? (k - 1) * pl.P : 0;
     // largest epilogue row shift (mode 3 reads the haloed row at column l + pad, hence the extra pad)
-    const int max_shift = pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : (k - 1) * pl.P + pad);
+    const int max_shift = pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : 2 * (pl.NG - 1) * pl.P + pad);
     pl.w_bytes = (uint32_t)pl.KSTEPS * 2u * pl.N * 16u;
     auto fit = [&](int R, TcPlan &o) {
         const int mrows = (R - 1) * o.P + d4 + max_shift;
@@ -554,7 +568,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     if (x_dtype == NCNET_CB16) {
         act = (const __half *)x;
     } else {
-        int rc = cb16_pack(x, x_dtype, sc, B * Gx, d.Cin_e, d1, d2, d3, d4, d.k, pl.mode == 3 ? 1 : 0, st);
+        int rc = cb16_pack(x, x_dtype, sc, B * Gx, d.Cin_e, d1, d2, d3, d4, d.k, pl.mode == 3 ? 3 : 0, st);
         if (rc) return rc;
         act = (const __half *)sc;
         used = align256(cb16_bytes((size_t)B * Gx, d1, d2, d3, d4, d.k));
@@ -587,7 +601,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
         if (gi < pl.NG) {
             if (pl.mode == 1) s = gi;                                   // group = d4 tap
             else if (pl.mode == 2) s = (gi / d.k) * pl.P + (gi % d.k);  // group = (d3, d4)
-            else s = gi * pl.P + pad;                                   // group = d3 tap; the d4 taps sit in the channels of column l + pad
+            else s = 2 * gi * pl.P + pad;                               // group = d3 tap pair; the d4 taps sit in the channels of column l + pad
         }
         a.gshift[gi] = s;
     }

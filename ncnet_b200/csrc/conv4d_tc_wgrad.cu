@@ -210,9 +210,9 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
                         for (int u = 0; u < 8; ++u) {
                             const int n = n0 + u;
                             int o, c, t3, t4, tt2 = t2;
-                            if (p.variant == 2) { t4 = sA; c = av * 8 + c8; t3 = 7 - (n >> 3); o = bv * 8 + (n & 7); }
+                            if (p.variant == 2) { t4 = sA; c = av * 8 + c8; t3 = KS - 1 - (n >> 3); o = bv * 8 + (n & 7); }
                             else if (p.variant == 1) { t3 = sA; t4 = c8; c = 0; o = n; }
-                            else { t4 = sA; c = av * 8 + c8; t3 = 7 - (n >> 3); tt2 = n & 7; o = 0; }
+                            else { t4 = sA; c = av * 8 + c8; t3 = KS - 1 - (n >> 3); tt2 = n & 7; o = 0; }
                             if (t3 < 0 || t3 >= KS || t4 >= KS || tt2 >= KS || c >= p.Cin || o >= p.Cout) continue;
                             dst[(((((size_t)c * KS + t1) * KS + tt2) * KS + t3) * KS + t4) * p.cop + o] = v[u];
                         }
@@ -288,12 +288,12 @@ static WgPlan wg_plan(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, 
         w.cop = ((Cout + 3) / 4) * 4;
     } else {
         // A = X half, groups = d4 shifts; B = G half (V2) or G8 with the d2 taps in its channels (V3),
-        // groups = d3 row shifts in reversed order (group r' <-> tap 7 - r')
+        // only the k useful d3 row shifts, in reversed order (group r' <-> tap k-1-r'): N = 8k
         w.variant = Cout == 1 ? 3 : 2;
-        w.NAv = (Cin + 7) / 8; w.NBv = w.variant == 3 ? 1 : (Cout + 7) / 8; w.N = 64; w.nb_copy = w.NBv;
+        w.NAv = (Cin + 7) / 8; w.NBv = w.variant == 3 ? 1 : (Cout + 7) / 8; w.N = 8 * k; w.nb_copy = w.NBv;
         w.a_sbo = 16u;
         w.b_sbo = (uint32_t)w.P * 16u;
-        w.a_r0 = 0; w.b_r0 = 8 - pad; w.b_start = (uint32_t)(w.P + pad) * 16u;
+        w.a_r0 = 0; w.b_r0 = 8 - pad; w.b_start = (uint32_t)((9 - k) * w.P + pad) * 16u;
         w.npos_a = w.nkb * 16 + 8;
         w.npos_b = w.nkb * 16 + 8 * w.P + pad + 8;
         if (w.npos_b < (w.b_r0 + d3 + 2 * pad) * w.P) w.npos_b = (w.b_r0 + d3 + 2 * pad) * w.P;
