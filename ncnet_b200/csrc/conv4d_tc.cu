@@ -48,6 +48,8 @@ struct TcArgs {
     int R, nchunks;         // output k-rows per CTA, chunks per plane
     int NT, N, NG, KSTEPS;
     int npos_pad;           // positions per channel-half in a smem stage
+    int stages;             // ring depth (2 or 3)
+    uint32_t tmem_cols;     // TMEM columns to allocate (power of two >= NT*N)
     int relu;
     int out_mode;           // 0 planar fp32, 1 planar fp16, 2 CB16
     int mask_mode;          // 0 none, 1 planar fp32, 2 planar fp16, 3 CB16
@@ -60,7 +62,7 @@ struct TcArgs {
 
 using namespace tc;
 
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kTcThreads, 2)
 conv4d_tc_kernel(const TcArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar;
@@ -82,7 +84,7 @@ conv4d_tc_kernel(const TcArgs p) {
     const size_t ij_count = (size_t)p.d1 * p.d2;
 
     uint8_t *stage0 = smem;
-    float *outbuf = reinterpret_cast<float *>(smem + (size_t)kStages * p.stage_bytes);
+    float *outbuf = reinterpret_cast<float *>(smem + (size_t)p.stages * p.stage_bytes);
     const int out_rows = p.NT * 128;
 
     // ---- one-time setup -------------------------------------------------------------------
@@ -92,8 +94,8 @@ conv4d_tc_kernel(const TcArgs p) {
         mbar_init(&accum_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 0) {    // TMEM: all 512 columns (one CTA per SM: the ring + outbuf fill shared memory)
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
+    if (warp == 0) {    // TMEM: NT accumulator tiles (256 columns or fewer lets two CTAs share the SM)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(p.tmem_cols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     {
@@ -102,7 +104,7 @@ conv4d_tc_kernel(const TcArgs p) {
         const uint4 z = make_uint4(0, 0, 0, 0);
         const int copied = min(p.R + p.KS - 1, rows_pad - k0) * p.P;      // positions written by every stage's copy
         const int tail = p.npos_pad - copied;
-        for (int e = threadIdx.x; e < kStages * 2 * tail; e += kTcThreads) {
+        for (int e = threadIdx.x; e < p.stages * 2 * tail; e += kTcThreads) {
             const int s = e / (2 * tail), r = e - s * 2 * tail;
             const int half = r / tail, pos = copied + (r - half * tail);
             reinterpret_cast<uint4 *>(stage0 + (size_t)s * p.stage_bytes)[(size_t)half * p.npos_pad + pos] = z;
@@ -153,7 +155,7 @@ conv4d_tc_kernel(const TcArgs p) {
                     bulk_g2s(sb + p.data_bytes, wsrc, p.w_bytes, &full_bar[stage]);
                 }
                 __syncwarp();
-                if (++stage == kStages) { stage = 0; phase ^= 1; }
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
     } else if (warp == 1) {
@@ -199,7 +201,7 @@ conv4d_tc_kernel(const TcArgs p) {
                 }
                 __syncwarp();
                 first = false;
-                if (++stage == kStages) { stage = 0; phase ^= 1; }
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
         if (elect_one()) { TC_STAMP(1); umma_commit(&accum_bar); }
@@ -323,7 +325,7 @@ conv4d_tc_kernel(const TcArgs p) {
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     if (warp == 0) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
     }
 }
 
@@ -492,7 +494,8 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
 long long *g_tc_debug_buffer = nullptr;     // set through ncnet_debug_set_tc_timing (development only)
 
 struct TcPlan {
-    int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad;
+    int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages;
+    uint32_t tmem_cols;
     uint32_t data_bytes, w_bytes, stage_bytes;
     size_t smem_bytes;
     bool ok;
@@ -512,10 +515,12 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
     // largest epilogue row shift (mode 3 reads the haloed row at column l + pad, hence the extra pad)
     const int max_shift = pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : 2 * (pl.NG - 1) * pl.P + pad);
     pl.w_bytes = (uint32_t)pl.KSTEPS * 2u * pl.N * 16u;
-    auto fit = [&](int R, TcPlan &o) {
+    // budget: one CTA per SM may use all 512 TMEM columns and ~220 KB; two co-resident CTAs (whose
+    // epilogue/prologue then overlap the other's MMA main loop) get 256 columns and ~108 KB each
+    auto fit = [&](int R, int stages, int max_cols, size_t max_smem, TcPlan &o) {
         const int mrows = (R - 1) * o.P + d4 + max_shift;
         const int NT = (mrows + 127) / 128;
-        if (NT * o.N > 512) return false;
+        if (NT * o.N > max_cols) return false;
         int npos = NT * 128 + max_aoff;
         const int need = (R + k - 1) * o.P;
         if (need > npos) npos = need;
@@ -524,19 +529,30 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
         const uint32_t data = 2u * npos * 16u;
         const uint32_t stage = ((data + o.w_bytes + 127) / 128) * 128;
         const size_t outb = o.CoutPad >= 16 ? (size_t)NT * 128 * kOutStride * sizeof(float) : (size_t)NT * 128 * 4 * sizeof(float);
-        const size_t smem = (size_t)kStages * stage + outb;
-        if (smem > 220 * 1024) return false;
+        const size_t smem = (size_t)stages * stage + outb;
+        if (smem > max_smem) return false;
         o.R = R; o.NT = NT; o.npos_pad = npos; o.data_bytes = data; o.stage_bytes = stage; o.smem_bytes = smem;
+        o.stages = stages;
+        const int cols = NT * o.N;
+        o.tmem_cols = cols <= 32 ? 32 : (cols <= 64 ? 64 : (cols <= 128 ? 128 : (cols <= 256 ? 256 : 512)));
         return true;
     };
-    for (int R = d3; R >= 1; --R) {
-        if (!fit(R, pl)) continue;
-        pl.nchunks = (d3 + R - 1) / R;
-        const int balanced = (d3 + pl.nchunks - 1) / pl.nchunks;    // equal chunks; smaller R always fits too
-        if (!fit(balanced, pl)) return pl;
-        pl.ok = true;
-        break;
-    }
+    auto search = [&](int stages, int max_cols, size_t max_smem) {
+        for (int R = d3; R >= 1; --R) {
+            if (!fit(R, stages, max_cols, max_smem, pl)) continue;
+            pl.nchunks = (d3 + R - 1) / R;
+            const int balanced = (d3 + pl.nchunks - 1) / pl.nchunks;    // equal chunks; a smaller R always fits too
+            return fit(balanced, stages, max_cols, max_smem, pl);
+        }
+        return false;
+    };
+    // prefer two CTAs per SM unless that costs more than ~1.6x the plane chunks of the one-CTA plan
+    TcPlan one = pl;
+    bool ok1 = false;
+    { TcPlan keep = pl; ok1 = search(kStages, 512, 220 * 1024); one = pl; pl = keep; }
+    const bool ok2 = search(2, 256, 108 * 1024);
+    if (ok2 && (!ok1 || pl.nchunks <= 2 * one.nchunks)) { pl.ok = true; return pl; }
+    if (ok1) { one.ok = true; return one; }
     return pl;
 }
 
@@ -587,7 +603,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     a.B = B; a.G = d.G_e; a.Gx = Gx; a.Cout = d.Cout_e; a.CoutPad = pl.CoutPad;
     a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = d.k; a.P = pl.P;
     a.R = pl.R; a.nchunks = pl.nchunks; a.NT = pl.NT; a.N = pl.N; a.NG = pl.NG; a.KSTEPS = pl.KSTEPS;
-    a.npos_pad = pl.npos_pad; a.relu = relu;
+    a.npos_pad = pl.npos_pad; a.relu = relu; a.stages = pl.stages; a.tmem_cols = pl.tmem_cols;
     a.out_mode = y_dtype == NCNET_CB16 ? 2 : (y_dtype == NCNET_F16 ? 1 : 0);
     a.mask_mode = !mask ? 0 : (mask_dtype == NCNET_CB16 ? 3 : (mask_dtype == NCNET_F16 ? 2 : 1));
     a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes;

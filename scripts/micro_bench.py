@@ -1,0 +1,73 @@
+"""Config 5 (BASELINE.json): micro-benchmarks of the memory-bound kernels and the Conv4d layers against their rooflines.
+Prints one JSON line per measurement (CUDA events, L2 flushed between iterations for the bandwidth kernels)."""
+import json, os, sys
+import torch
+sys.path.insert(0, ".")
+import ncnet_b200 as nb
+from ncnet_b200 import functional as F_
+from ncnet_b200._cabi import CONV_FP32, CONV_TC16, W_KOIKKK
+
+PEAKS = json.load(open("MEASURED_PEAKS.json")) if os.path.exists("MEASURED_PEAKS.json") else {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}
+dev = torch.device("cuda")
+flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+
+def timeit(fn, iters=10, do_flush=True):
+    for _ in range(3):
+        fn()
+    ts = []
+    for _ in range(iters):
+        if do_flush:
+            flush.fill_(1)
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(); fn(); b.record(); torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def emit(**kw):
+    print(json.dumps(kw), flush=True)
+
+
+with torch.no_grad():
+    # MutualMatching forward: algorithmic bytes = 1 read + 1 write
+    for name, shape, dt in (("PF B=16", (16, 1, 25, 25, 25, 25), torch.float32), ("PF B=64", (64, 1, 25, 25, 25, 25), torch.float32),
+                            ("50^4", (1, 1, 50, 50, 50, 50), torch.float32), ("IL32 pooled fp16", (1, 1, 100, 75, 100, 75), torch.float16),
+                            ("PF B=1", (1, 1, 25, 25, 25, 25), torch.float32)):
+        x = torch.rand(*shape, device=dev).to(dt)
+        ms = timeit(lambda: nb.MutualMatching(x))
+        gbs = 2 * x.numel() * x.element_size() / ms / 1e6
+        emit(kernel="MutualMatching fwd", case=name, ms=ms, achieved_GBs=gbs, frac_of_hbm=gbs / PEAKS["hbm_gbs"], bytes="2*numel*sizeof")
+    # maxpool4d k=2 (InLoc): bytes = input + pooled value + 4 offset bytes
+    for name, shape in (("IL16 fp16", (1, 1, 100, 74, 100, 74)), ("IL32 fp16", (1, 1, 200, 150, 200, 150))):
+        x = torch.rand(*shape, device=dev).half()
+        ms = timeit(lambda: F_.maxpool4d(x, 2, index_dtype=torch.uint8), iters=5)
+        nout = x.numel() // 16
+        gbs = (x.numel() * 2 + nout * (2 + 4)) / ms / 1e6
+        emit(kernel="maxpool4d k=2 (uint8 offsets)", case=name, ms=ms, achieved_GBs=gbs, frac_of_hbm=gbs / PEAKS["hbm_gbs"])
+        ms = timeit(lambda: nb.maxpool4d(x, 2), iters=5)
+        gbs = (x.numel() * 2 + nout * (2 + 32)) / ms / 1e6
+        emit(kernel="maxpool4d k=2 (int64 offsets, reference dtype)", case=name, ms=ms, achieved_GBs=gbs, frac_of_hbm=gbs / PEAKS["hbm_gbs"])
+        del x
+    # corr_to_matches: one read of the volume
+    for name, shape, dt in (("PF B=16", (16, 1, 25, 25, 25, 25), torch.float32), ("IL32 pooled fp16", (1, 1, 100, 75, 100, 75), torch.float16)):
+        x = torch.rand(*shape, device=dev).to(dt)
+        for inv in (False, True):
+            ms = timeit(lambda: nb.corr_to_matches(x, do_softmax=True, invert_matching_direction=inv))
+            gbs = x.numel() * x.element_size() / ms / 1e6
+            emit(kernel="corr_to_matches softmax", case=f"{name} invert={inv}", ms=ms, achieved_GBs=gbs, frac_of_hbm=gbs / PEAKS["hbm_gbs"])
+    # Conv4d layers, forward, both branches, per mode
+    for n in (16, 25, 32):
+        for cin, cout in ((1, 16), (16, 16), (16, 1)):
+            for k in (3, 5):
+                bsz = max(1, (25 ** 4 * 4) // n ** 4)
+                gin = 1 if cin == 1 else 2
+                x = torch.rand(bsz, gin * cin, n, n, n, n, device=dev)
+                w = (torch.rand(k, cout, cin, k, k, k, device=dev) - 0.5) * 0.1
+                b = torch.zeros(cout, device=dev)
+                for mode, mname in ((CONV_TC16, "tc16"), (CONV_FP32, "fp32")):
+                    ms = timeit(lambda: F_._conv_fwd(x, w, b, W_KOIKKK, True, cin == 1, True, mode), iters=3, do_flush=False)
+                    tf = 2.0 * bsz * n ** 4 * cin * cout * k ** 4 * 2 / ms / 1e9
+                    emit(kernel="conv4d fwd (planar in/out, both branches)", case=f"N={n} {cin}->{cout} k={k} B={bsz}", mode=mname, ms=ms,
+                         achieved_TFLOPs=tf, frac_of_bf16_peak=tf / PEAKS["bf16_tflops"])
