@@ -12,8 +12,10 @@ namespace ncnet {
 
 constexpr float kMMEps = 1e-5f;
 constexpr int kMMThreads = 256;
-constexpr int kMMColsPerTile = 256;          // 8 warps x 32 lanes, one column per lane per slot
-constexpr int kMMSlots = kMMColsPerTile / 32;  // columns per lane
+constexpr int kMMSlots = 16;                         // column slots per lane in pass 1
+constexpr int kMMColsPerTile = 32 * kMMSlots;        // 512 columns per CTA tile
+constexpr int kMMBwdSlots = 8;                       // backward keeps the narrower 256-column tile
+constexpr int kMMBwdCols = 32 * kMMBwdSlots;
 
 template <typename T>
 __device__ __forceinline__ float mm_load(const T *x, size_t off, size_t group_stride, int groups) {
@@ -22,88 +24,171 @@ __device__ __forceinline__ float mm_load(const T *x, size_t off, size_t group_st
     return v;
 }
 
-// grid: (col tiles, row strips, B); each warp walks rows warp, warp+8, ... of the strip
-template <typename T>
+// the maximum of a packed key without touching its index half
+__device__ __forceinline__ float key_val_hi(const unsigned long long *keys, size_t i) {
+    return ord2f(reinterpret_cast<const uint32_t *>(keys)[2 * i + 1]);
+}
+
+// Pass 1.  grid: (col tiles of 512, row strips, B); each warp walks rows warp, warp+8, ... of the strip and keeps,
+// per lane, the running (max, first row) of its 16 columns as plain float/int pairs; keys are packed only for the
+// final atomicMax.  VEC = 2: a lane owns pairs of adjacent columns and loads them as one half2 (fp16, even nB).
+// All loads of a row are issued before any use (a predicated-off dependent op between them serialised them once).
+template <typename T, int GROUPS, int VEC>
 __global__ void __launch_bounds__(kMMThreads)
-mm_max_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, int nA, int nB,
-              int rows_per_block, int groups) {
+mm_max_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, int nA, int nB, int rows_per_block) {
+    constexpr int NL = kMMSlots / VEC;                 // loads per lane per row
     const int b = blockIdx.z;
     const int row0 = blockIdx.y * rows_per_block;
     const int col0 = blockIdx.x * kMMColsPerTile;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t mat = (size_t)nA * nB;
-    const T *xb = x + (size_t)b * mat * groups;
+    const T *xb = x + (size_t)b * mat * GROUPS;
     unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
     unsigned long long *colkeys = rowkeys + nA;
 
-    unsigned long long cbest[kMMSlots];
+    float cv[kMMSlots];
+    int ci[kMMSlots];
 #pragma unroll
-    for (int s = 0; s < kMMSlots; ++s) cbest[s] = 0ull;
-
+    for (int s = 0; s < kMMSlots; ++s) { cv[s] = -INFINITY; ci[s] = -1; }
+    const int ncols = min(kMMColsPerTile, nB - col0);
+    // slot s = (load q, element u): column offset q*32*VEC + lane*VEC + u
     const int row_end = min(row0 + rows_per_block, nA);
     for (int a = row0 + warp; a < row_end; a += kMMThreads / 32) {
-        unsigned long long rbest = 0ull;
-        const size_t roff = (size_t)a * nB;
+        const size_t roff = (size_t)a * nB + col0;
+        float v[kMMSlots];
+        if (VEC == 2) {
+            // raw 32-bit loads first (all in flight), conversions afterwards
+            unsigned raw[NL];
+            constexpr unsigned kNegInf2 = 0xFC00FC00u;            // half2(-inf, -inf)
 #pragma unroll
-        for (int s = 0; s < kMMSlots; ++s) {
-            const int c = col0 + s * 32 + lane;
-            if (c < nB) {
-                const float v = mm_load(xb, roff + c, mat, groups);
-                const unsigned long long kr = pack_key(v, (uint32_t)c);
-                const unsigned long long kc = pack_key(v, (uint32_t)a);
-                rbest = kr > rbest ? kr : rbest;
-                cbest[s] = kc > cbest[s] ? kc : cbest[s];
+            for (int q = 0; q < NL; ++q) {
+                const int c = q * 32 * VEC + lane * VEC;
+                raw[q] = (c + 1 < ncols) ? __ldg(reinterpret_cast<const unsigned *>(xb + roff + c)) : kNegInf2;
+            }
+#pragma unroll
+            for (int q = 0; q < NL; ++q) {
+                const __half2 h = *reinterpret_cast<const __half2 *>(&raw[q]);
+                v[q * VEC] = __low2float(h); v[q * VEC + VEC - 1] = __high2float(h);
+            }
+        } else {
+#pragma unroll
+            for (int q = 0; q < NL; ++q) {
+                const int c = q * 32 * VEC + lane * VEC;
+                v[q] = c < ncols ? ldf(xb + roff + c) : -INFINITY;
             }
         }
-        rbest = warp_max_u64(rbest);
-        if (lane == 0 && rbest) atomicMax(rowkeys + a, rbest);
+        if (GROUPS == 2) {                             // second branch, again as one batch of loads
+            float w[kMMSlots];
+#pragma unroll
+            for (int q = 0; q < NL; ++q) {
+                const int c = q * 32 * VEC + lane * VEC;
+#pragma unroll
+                for (int u = 0; u < VEC; ++u) w[q * VEC + u] = (c + u < ncols) ? ldf(xb + mat + roff + c + u) : 0.f;
+            }
+#pragma unroll
+            for (int s = 0; s < kMMSlots; ++s) v[s] = rnd<T>(v[s] + w[s]);
+        }
+        float rv = -INFINITY;
+        int rc = 0x7fffffff;
+#pragma unroll
+        for (int q = 0; q < NL; ++q)
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) {
+                const int s = q * VEC + u;
+                if (v[s] > cv[s]) { cv[s] = v[s]; ci[s] = a; }
+                if (v[s] > rv) { rv = v[s]; rc = col0 + q * 32 * VEC + lane * VEC + u; }
+            }
+        // warp arg-max with first-index tie-break
+        const float m = warp_max(rv);
+        int cand = rv == m ? rc : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, o));
+        if (lane == 0 && cand != 0x7fffffff) atomicMax(rowkeys + a, pack_key(m, (uint32_t)cand));
     }
 
     __shared__ unsigned long long sm[kMMThreads / 32][kMMColsPerTile];
 #pragma unroll
-    for (int s = 0; s < kMMSlots; ++s) sm[warp][s * 32 + lane] = cbest[s];
+    for (int q = 0; q < NL; ++q)
+#pragma unroll
+        for (int u = 0; u < VEC; ++u) {
+            const int s = q * VEC + u;
+            sm[warp][q * 32 * VEC + lane * VEC + u] = ci[s] >= 0 ? pack_key(cv[s], (uint32_t)ci[s]) : 0ull;
+        }
     __syncthreads();
-    const int c = col0 + threadIdx.x;
-    if (c < nB) {
+    for (int cc = threadIdx.x; cc < ncols; cc += kMMThreads) {
         unsigned long long best = 0ull;
 #pragma unroll
         for (int w = 0; w < kMMThreads / 32; ++w) {
-            const unsigned long long k = sm[w][threadIdx.x];
+            const unsigned long long k = sm[w][cc];
             best = k > best ? k : best;
         }
-        if (best) atomicMax(colkeys + c, best);
+        if (best) atomicMax(colkeys + col0 + cc, best);
     }
 }
 
-// elementwise pass: 4 consecutive elements of the flattened matrix per thread
-template <typename T>
+// Pass 2: y = x * ((x * 1/(rowmax+eps)) * (x * 1/(colmax+eps))).  One thread owns kMMApplyVec adjacent columns and
+// walks kMMApplyRows rows: the column reciprocals are computed once per thread, the row reciprocal once per
+// warp-row (lane 0, broadcast), so the inner loop is a load, four multiplies and a store per element.
+// x/(max+eps) is evaluated as x * rcp_rn(max+eps) -- one correctly rounded reciprocal per row/column instead of two
+// IEEE divisions per element (which made this pass ALU-bound); the product is within 1 ulp of the true quotient.
+constexpr int kMMApplyRows = 16;
+
+template <typename T, int GROUPS, int VEC>
 __global__ void __launch_bounds__(256)
 mm_apply_kernel(const T *__restrict__ x, T *__restrict__ y, const unsigned long long *__restrict__ keys,
-                int nA, int nB, int groups) {
-    const int b = blockIdx.y;
+                int nA, int nB) {
+    const int b = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c0 = (blockIdx.x * 32 + lane) * VEC;
+    const int a0 = (blockIdx.y * 8 + warp) * kMMApplyRows;
     const size_t mat = (size_t)nA * nB;
-    const size_t e0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (e0 >= mat) return;
-    const T *xb = x + (size_t)b * mat * groups;
+    const T *xb = x + (size_t)b * mat * GROUPS;
     T *yb = y + (size_t)b * mat;
-    const unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
-    const unsigned long long *colkeys = rowkeys + nA;
-    int a = (int)(e0 / nB), c = (int)(e0 - (size_t)a * nB);
-    float rden = rnd<T>(key_val(rowkeys[a]) + kMMEps);
+    const size_t kb = (size_t)b * (nA + nB);
+    float crcp[VEC];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const size_t e = e0 + i;
-        if (e < mat) {
-            const float v = mm_load(xb, e, mat, groups);
-            const float cden = rnd<T>(key_val(colkeys[c]) + kMMEps);
-            const float qa = rnd<T>(v / rden);      // x / (max over B + eps)   (corr4d_A)
-            const float qb = rnd<T>(v / cden);      // x / (max over A + eps)   (corr4d_B)
-            stf(yb + e, v * rnd<T>(qa * qb));
+    for (int u = 0; u < VEC; ++u)
+        crcp[u] = (c0 + u < nB) ? __frcp_rn(rnd<T>(key_val_hi(keys, kb + nA + c0 + u) + kMMEps)) : 0.f;
+    // row reciprocals of this warp's rows: lane i computes row a0+i, broadcast below
+    float my_rrcp = 0.f;
+    if (lane < kMMApplyRows && a0 + lane < nA) my_rrcp = __frcp_rn(rnd<T>(key_val_hi(keys, kb + a0 + lane) + kMMEps));
+    if (c0 >= nB) {
+        // keep the warp converged for the shuffles below
+    }
+#pragma unroll 4
+    for (int r = 0; r < kMMApplyRows; ++r) {
+        const float rrcp = __shfl_sync(0xffffffffu, my_rrcp, r);
+        const int a = a0 + r;
+        if (a >= nA || c0 >= nB) continue;
+        const size_t off = (size_t)a * nB + c0;
+        float v[VEC];
+        if (VEC == 2 && sizeof(T) == 2 && c0 + 1 < nB) {           // half2 path (nB even: every row start is 4-byte aligned)
+            const __half2 h = *reinterpret_cast<const __half2 *>(xb + off);
+            v[0] = __low2float(h); v[VEC - 1] = __high2float(h);
+            if (GROUPS == 2) {
+                const __half2 g = *reinterpret_cast<const __half2 *>(xb + mat + off);
+                v[0] = rnd<T>(v[0] + __low2float(g)); v[VEC - 1] = rnd<T>(v[VEC - 1] + __high2float(g));
+            }
+        } else {
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) {
+                v[u] = (c0 + u < nB) ? ldf(xb + off + u) : 0.f;
+                if (GROUPS == 2 && c0 + u < nB) v[u] = rnd<T>(v[u] + ldf(xb + mat + off + u));
+            }
         }
-        if (++c == nB) {
-            c = 0;
-            ++a;
-            if (a < nA) rden = rnd<T>(key_val(rowkeys[a]) + kMMEps);
+        float res[VEC];
+#pragma unroll
+        for (int u = 0; u < VEC; ++u) {
+            const float qa = rnd<T>(v[u] * rrcp);      // x / (max over B + eps)   (corr4d_A)
+            const float qb = rnd<T>(v[u] * crcp[u]);   // x / (max over A + eps)   (corr4d_B)
+            res[u] = v[u] * rnd<T>(qa * qb);
+        }
+        if (VEC == 2 && sizeof(T) == 2 && c0 + 1 < nB) {
+            *reinterpret_cast<__half2 *>(yb + off) = __floats2half2_rn(res[0], res[VEC - 1]);
+        } else {
+#pragma unroll
+            for (int u = 0; u < VEC; ++u)
+                if (c0 + u < nB) stf(yb + off + u, res[u]);
         }
     }
 }
@@ -115,7 +200,7 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
                    float *__restrict__ sums, int nA, int nB, int rows_per_block, int groups) {
     const int b = blockIdx.z;
     const int row0 = blockIdx.y * rows_per_block;
-    const int col0 = blockIdx.x * kMMColsPerTile;
+    const int col0 = blockIdx.x * kMMBwdCols;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const size_t mat = (size_t)nA * nB;
     const T *xb = x + (size_t)b * mat * groups;
@@ -125,9 +210,9 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
     float *rsum = sums + (size_t)b * (nA + nB);
     float *csum = rsum + nA;
 
-    float cden[kMMSlots], cacc[kMMSlots];
+    float cden[kMMBwdSlots], cacc[kMMBwdSlots];
 #pragma unroll
-    for (int s = 0; s < kMMSlots; ++s) {
+    for (int s = 0; s < kMMBwdSlots; ++s) {
         const int c = col0 + s * 32 + lane;
         cden[s] = c < nB ? key_val(colkeys[c]) + kMMEps : 1.f;
         cacc[s] = 0.f;
@@ -138,7 +223,7 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
         const size_t roff = (size_t)a * nB;
         float racc = 0.f;
 #pragma unroll
-        for (int s = 0; s < kMMSlots; ++s) {
+        for (int s = 0; s < kMMBwdSlots; ++s) {
             const int c = col0 + s * 32 + lane;
             if (c < nB) {
                 const float v = mm_load(xb, roff + c, mat, groups);
@@ -151,9 +236,9 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
         racc = warp_sum(racc);
         if (lane == 0) atomicAdd(rsum + a, racc);
     }
-    __shared__ float sm[kMMThreads / 32][kMMColsPerTile];
+    __shared__ float sm[kMMThreads / 32][kMMBwdCols];
 #pragma unroll
-    for (int s = 0; s < kMMSlots; ++s) sm[warp][s * 32 + lane] = cacc[s];
+    for (int s = 0; s < kMMBwdSlots; ++s) sm[warp][s * 32 + lane] = cacc[s];
     __syncthreads();
     const int c = col0 + threadIdx.x;
     if (c < nB) {
@@ -207,8 +292,8 @@ mm_bwd_apply_kernel(const T *__restrict__ x, const T *__restrict__ gy, const uns
     }
 }
 
-static int rows_per_block_for(int B, int nA, int nB) {
-    const int col_tiles = (nB + kMMColsPerTile - 1) / kMMColsPerTile;
+static int rows_per_block_for(int B, int nA, int nB, int tile_cols) {
+    const int col_tiles = (nB + tile_cols - 1) / tile_cols;
     // aim for >= 4 blocks per SM; a strip is a multiple of 8 rows (one per warp)
     long long want = 4ll * kNumSMs;
     long long strips = (want + (long long)B * col_tiles - 1) / ((long long)B * col_tiles);
@@ -223,13 +308,22 @@ template <typename T>
 static int mm_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB, int groups, cudaStream_t st) {
     cudaError_t e = cudaMemsetAsync(keys, 0, (size_t)B * (nA + nB) * sizeof(uint64_t), st);
     NC_CHECK(e == cudaSuccess, "mutual_matching: memset keys: %s", cudaGetErrorString(e));
-    const int rpb = rows_per_block_for(B, nA, nB);
+    const int rpb = rows_per_block_for(B, nA, nB, kMMColsPerTile);
     dim3 g1((nB + kMMColsPerTile - 1) / kMMColsPerTile, (nA + rpb - 1) / rpb, B);
-    mm_max_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb, groups);
+    const bool v2 = sizeof(T) == 2 && nB % 2 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 3) == 0;
+#define NC_MM_MAX(G, V) mm_max_kernel<T, G, V><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb)
+    if (groups == 2) { if (v2) NC_MM_MAX(2, 2); else NC_MM_MAX(2, 1); }
+    else             { if (v2) NC_MM_MAX(1, 2); else NC_MM_MAX(1, 1); }
+#undef NC_MM_MAX
     NC_LAUNCH_OK("mm_max_kernel");
-    const size_t mat = (size_t)nA * nB;
-    dim3 g2((unsigned)((mat + 1023) / 1024), B);
-    mm_apply_kernel<T><<<g2, 256, 0, st>>>((const T *)x, (T *)y, (const unsigned long long *)keys, nA, nB, groups);
+    // half2 columns when every row start stays 4-byte aligned (even nB) and the base pointers are
+    const int vec = v2 ? 2 : 1;
+    dim3 g2((nB + 32 * vec - 1) / (32 * vec), (nA + 8 * kMMApplyRows - 1) / (8 * kMMApplyRows), B);
+    NC_CHECK(g2.y <= 65535, "mutual_matching: too many rows");
+#define NC_MM_APPLY(G, V) mm_apply_kernel<T, G, V><<<g2, 256, 0, st>>>((const T *)x, (T *)y, (const unsigned long long *)keys, nA, nB)
+    if (groups == 2) { if (v2) NC_MM_APPLY(2, 2); else NC_MM_APPLY(2, 1); }
+    else             { if (v2) NC_MM_APPLY(1, 2); else NC_MM_APPLY(1, 1); }
+#undef NC_MM_APPLY
     NC_LAUNCH_OK("mm_apply_kernel");
     return 0;
 }
@@ -239,8 +333,8 @@ static int mm_bwd(const void *x, const void *gy, const uint64_t *keys, float *su
                   int groups, cudaStream_t st) {
     cudaError_t e = cudaMemsetAsync(sums, 0, (size_t)B * (nA + nB) * sizeof(float), st);
     NC_CHECK(e == cudaSuccess, "mutual_matching_bwd: memset sums: %s", cudaGetErrorString(e));
-    const int rpb = rows_per_block_for(B, nA, nB);
-    dim3 g1((nB + kMMColsPerTile - 1) / kMMColsPerTile, (nA + rpb - 1) / rpb, B);
+    const int rpb = rows_per_block_for(B, nA, nB, kMMBwdCols);
+    dim3 g1((nB + kMMBwdCols - 1) / kMMBwdCols, (nA + rpb - 1) / rpb, B);
     mm_bwd_sums_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (const T *)gy, (const unsigned long long *)keys,
                                                      sums, nA, nB, rpb, groups);
     NC_LAUNCH_OK("mm_bwd_sums_kernel");

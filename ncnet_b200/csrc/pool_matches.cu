@@ -108,18 +108,29 @@ matches_over_rows_kernel(MatchArgs p) {
     __shared__ float s_m[8][33], s_s[8][33];
     __shared__ unsigned long long s_k[8][33];
     const bool ok = col < nB;
-    // pass 1: running max (+ running sum of exp for the soft-max)
+    // pass 1: running max (+ running sum of exp for the soft-max); 8 independent loads per thread in flight
+    constexpr int U = 8;
     float m = -INFINITY, s = 0.f;
     unsigned long long best = 0ull;
     if (ok)
-        for (int a = ty; a < nA; a += 8) {
-            const float v = ldf(x + (size_t)a * nB + col);
-            if (p.do_softmax) {
-                if (v > m) { s = s * expf(m - v); m = v; }
-                s += expf(v - m);
-            } else {
-                const unsigned long long k = pack_key(v, (uint32_t)a);
-                best = k > best ? k : best;
+        for (int a0 = ty; a0 < nA; a0 += 8 * U) {
+            float v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int a = a0 + 8 * u;
+                v[u] = a < nA ? ldf(x + (size_t)a * nB + col) : -INFINITY;
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int a = a0 + 8 * u;
+                if (a >= nA) break;
+                if (p.do_softmax) {
+                    if (v[u] > m) { s = s * expf(m - v[u]); m = v[u]; }
+                    s += expf(v[u] - m);
+                } else {
+                    const unsigned long long k = pack_key(v[u], (uint32_t)a);
+                    best = k > best ? k : best;
+                }
             }
         }
     float sc = 0.f;
@@ -135,10 +146,21 @@ matches_over_rows_kernel(MatchArgs p) {
         for (int w = 0; w < 8; ++w) S += (s_m[w][tx] == -INFINITY) ? 0.f : s_s[w][tx] * expf(s_m[w][tx] - M);
         // pass 2: arg-max of the soft-max values themselves (ties -> first index)
         if (ok)
-            for (int a = ty; a < nA; a += 8) {
-                const float v = rnd<T>(expf(ldf(x + (size_t)a * nB + col) - M) / S);
-                const unsigned long long k = pack_key(v, (uint32_t)a);
-                best = k > best ? k : best;
+            for (int a0 = ty; a0 < nA; a0 += 8 * U) {
+                float v[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int a = a0 + 8 * u;
+                    v[u] = a < nA ? ldf(x + (size_t)a * nB + col) : -INFINITY;
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const int a = a0 + 8 * u;
+                    if (a >= nA) break;
+                    const float q = rnd<T>(expf(v[u] - M) / S);
+                    const unsigned long long k = pack_key(q, (uint32_t)a);
+                    best = k > best ? k : best;
+                }
             }
     }
     s_k[ty][tx] = best;

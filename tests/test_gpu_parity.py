@@ -56,7 +56,7 @@ def test_mutual_matching_golden(nb, cuda):
     g = load_golden("mutual_matching", cuda)
     x = g["x"].clone().requires_grad_(True)
     y = nb.MutualMatching(x)
-    assert nerr(y, g["y"]) < 3e-7
+    assert nerr(y, g["y"]) < 1e-6
     (gx,) = torch.autograd.grad(y, x, g["grad_y"])
     assert nerr(gx, g["grad_x"]) < 1e-5
 
@@ -175,7 +175,7 @@ def test_mutual_matching_vs_oracle(nb, cuda, shape):
     y = nb.MutualMatching(xg)
     xo = x.clone().requires_grad_(True)
     yo = O.mutual_matching(xo)
-    assert nerr(y, yo) < 3e-7
+    assert nerr(y, yo) < 1e-6
     go = torch.randn_like(yo)
     (gx,) = torch.autograd.grad(y, xg, go.to(cuda))
     (gr,) = torch.autograd.grad(yo, xo, go)
@@ -190,7 +190,7 @@ def test_mutual_matching_symmetry_and_negative(nb, cuda):
     a = nb.MutualMatching(x)
     b = nb.MutualMatching(x.permute(0, 1, 4, 5, 2, 3).contiguous()).permute(0, 1, 4, 5, 2, 3)
     assert torch.equal(a, b)
-    assert nerr(a, O.mutual_matching(x.cpu())) < 3e-7
+    assert nerr(a, O.mutual_matching(x.cpu())) < 1e-6
 
 
 @pytest.mark.parametrize("cin,cout,k,dims,bsz", [
