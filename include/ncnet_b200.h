@@ -71,6 +71,14 @@ int ncnet_corr4d_bwd(const void *grad_out, const void *fa, const void *fb, void 
 size_t ncnet_mutual_matching_keys_bytes(int B, int nA, int nB);
 int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB,
                               int in_groups, int dtype, void *stream);
+/* The two passes of ncnet_mutual_matching_fwd on their own, for volumes sharded into slabs along the first
+ * source axis (BASELINE.json config 4): every rank runs _max on its rows, the per-target halves of `keys`
+ * (entries [nA, nA+nB) of each batch item) are max-reduced across ranks by the caller, then every rank runs
+ * _apply.  Keys compare as unsigned 64-bit integers: larger value wins, then the smaller index. */
+int ncnet_mutual_matching_max(const void *x, uint64_t *keys, int B, int nA, int nB, int in_groups, int dtype,
+                              void *stream);
+int ncnet_mutual_matching_apply(const void *x, const uint64_t *keys, void *y, int B, int nA, int nB, int in_groups,
+                                int dtype, void *stream);
 /* backward: grad_x = d(y)/d(x)^T grad_y incl. the flow through both max reductions.
  * sums: scratch, B*(nA+nB) floats.  x is the forward input (in_groups as in forward;
  * grad_x is [B,nA,nB]: the gradient of the summed volume). */

@@ -304,18 +304,33 @@ static int rows_per_block_for(int B, int nA, int nB, int tile_cols) {
     return rpb;
 }
 
+// which: bit 0 = pass 1 (maxima -> keys), bit 1 = pass 2 (keys -> y)
+template <typename T>
+static int mm_fwd_parts(const void *x, void *y, uint64_t *keys, int B, int nA, int nB, int groups, int which,
+                        cudaStream_t st);
+
 template <typename T>
 static int mm_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB, int groups, cudaStream_t st) {
+    return mm_fwd_parts<T>(x, y, keys, B, nA, nB, groups, 3, st);
+}
+
+template <typename T>
+static int mm_fwd_parts(const void *x, void *y, uint64_t *keys, int B, int nA, int nB, int groups, int which,
+                        cudaStream_t st) {
+    if (which & 1) {
     cudaError_t e = cudaMemsetAsync(keys, 0, (size_t)B * (nA + nB) * sizeof(uint64_t), st);
     NC_CHECK(e == cudaSuccess, "mutual_matching: memset keys: %s", cudaGetErrorString(e));
     const int rpb = rows_per_block_for(B, nA, nB, kMMColsPerTile);
     dim3 g1((nB + kMMColsPerTile - 1) / kMMColsPerTile, (nA + rpb - 1) / rpb, B);
-    const bool v2 = sizeof(T) == 2 && nB % 2 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 3) == 0;
+    const bool v2 = sizeof(T) == 2 && nB % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 3) == 0;
 #define NC_MM_MAX(G, V) mm_max_kernel<T, G, V><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb)
     if (groups == 2) { if (v2) NC_MM_MAX(2, 2); else NC_MM_MAX(2, 1); }
     else             { if (v2) NC_MM_MAX(1, 2); else NC_MM_MAX(1, 1); }
 #undef NC_MM_MAX
     NC_LAUNCH_OK("mm_max_kernel");
+    }
+    if (!(which & 2)) return 0;
+    const bool v2 = sizeof(T) == 2 && nB % 2 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 3) == 0;
     // half2 columns when every row start stays 4-byte aligned (even nB) and the base pointers are
     const int vec = v2 ? 2 : 1;
     dim3 g2((nB + 32 * vec - 1) / (32 * vec), (nA + 8 * kMMApplyRows - 1) / (8 * kMMApplyRows), B);
@@ -363,6 +378,28 @@ extern "C" int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys,
     if (dtype == NCNET_F32) return mm_fwd<float>(x, y, keys, B, nA, nB, in_groups, st);
     if (dtype == NCNET_F16) return mm_fwd<__half>(x, y, keys, B, nA, nB, in_groups, st);
     return fail("mutual_matching_fwd: unsupported dtype %d", dtype);
+}
+
+extern "C" int ncnet_mutual_matching_max(const void *x, uint64_t *keys, int B, int nA, int nB, int in_groups, int dtype,
+                                         void *stream) {
+    NC_CHECK(x && keys, "mutual_matching_max: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "mutual_matching_max: bad shape");
+    NC_CHECK(in_groups == 1 || in_groups == 2, "mutual_matching_max: in_groups must be 1 or 2");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NCNET_F32) return mm_fwd_parts<float>(x, nullptr, keys, B, nA, nB, in_groups, 1, st);
+    if (dtype == NCNET_F16) return mm_fwd_parts<__half>(x, nullptr, keys, B, nA, nB, in_groups, 1, st);
+    return fail("mutual_matching_max: unsupported dtype %d", dtype);
+}
+
+extern "C" int ncnet_mutual_matching_apply(const void *x, const uint64_t *keys, void *y, int B, int nA, int nB,
+                                           int in_groups, int dtype, void *stream) {
+    NC_CHECK(x && keys && y, "mutual_matching_apply: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "mutual_matching_apply: bad shape");
+    NC_CHECK(in_groups == 1 || in_groups == 2, "mutual_matching_apply: in_groups must be 1 or 2");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NCNET_F32) return mm_fwd_parts<float>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, 2, st);
+    if (dtype == NCNET_F16) return mm_fwd_parts<__half>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, 2, st);
+    return fail("mutual_matching_apply: unsupported dtype %d", dtype);
 }
 
 extern "C" int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t *keys, float *sums,

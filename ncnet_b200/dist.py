@@ -118,3 +118,67 @@ def all_reduce_max_(t: torch.Tensor, group=None) -> torch.Tensor:
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX, group=group)
     return t
+
+
+# ------------------------------------------------------------------------------------------- #
+# slab-sharded head on the GPU kernels (BASELINE.json config 4: volumes too large for one GPU)
+# ------------------------------------------------------------------------------------------- #
+_SIGN64 = -(1 << 63)
+
+
+def slab_mutual_matching(x_slab: torch.Tensor, group=None, sum_branches: bool = False) -> torch.Tensor:
+    """MutualMatching (lib/model.py:155-175) of a volume sharded along iA.  ``x_slab``: this rank's rows
+    [B,1|2,rows,fs2,fs3,fs4].  A slab holds whole source rows, so the max over B is local; the max over A of
+    every target cell is an all-reduce(max) over ranks of the per-target key table between the two kernel passes."""
+    from . import _cabi
+    from .functional import _dt, _ptr, _stream, _count
+    x = x_slab.contiguous()
+    b, g, r, f2, f3, f4 = x.shape
+    na, nb = r * f2, f3 * f4
+    lib = _cabi.lib()
+    keys = torch.empty(b, na + nb, device=x.device, dtype=torch.int64)
+    with torch.cuda.device(x.device):
+        _cabi.check(lib.ncnet_mutual_matching_max(_ptr(x), _ptr(keys), b, na, nb, g, _dt(x), _stream()), "mutual_matching_max")
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        # keys order as UNSIGNED 64-bit; flipping the top bit makes the signed max agree
+        colk = (keys[:, na:] ^ _SIGN64).contiguous()
+        dist.all_reduce(colk, op=dist.ReduceOp.MAX, group=group)
+        keys[:, na:] = colk ^ _SIGN64
+    y = torch.empty(b, 1, r, f2, f3, f4, device=x.device, dtype=x.dtype)
+    with torch.cuda.device(x.device):
+        _cabi.check(lib.ncnet_mutual_matching_apply(_ptr(x), _ptr(keys), _ptr(y), b, na, nb, g, _dt(x), _stream()),
+                    "mutual_matching_apply")
+    _count(2)
+    return y
+
+
+def slab_neigh_consensus(x_slab: torch.Tensor, nc, rank: int, world: int, group=None) -> torch.Tensor:
+    """NeighConsensus (lib/model.py:143-153) on a slab: before every Conv4d layer the k//2 boundary rows are
+    exchanged with the neighbouring ranks (point-to-point), the layer runs on the extended slab and the borrowed
+    rows are cropped.  Both symmetric branches stay slab-local (transposed-filter identity).
+    Returns the un-summed branch outputs [B, G*C_last, rows, ...] like ``forward_branches``."""
+    from .functional import _conv_fwd, default_conv_mode, W_KOIKKK
+    ws, bs = nc._params()
+    mode = default_conv_mode()
+    cur = x_slab.contiguous()
+    for l, (w, bvec) in enumerate(zip(ws, bs)):
+        halo = w.shape[0] // 2
+        ext = exchange_halo(cur, halo, rank, world, group)
+        y = _conv_fwd(ext, w.detach().float().contiguous(), bvec.detach().float().contiguous(), W_KOIKKK,
+                      nc.symmetric_mode, l == 0, True, mode)
+        cur = crop_halo(y, halo, rank, world)
+    return cur
+
+
+def slab_match_features(model, feature_A: torch.Tensor, feature_B: torch.Tensor, rank: int, world: int, group=None):
+    """The head of ``ImMatchNet.match_features`` for this rank's rows of the volume: the correlation rows are
+    computed locally from the (replicated) features, so only the halo rows and the target maxima cross NVLink."""
+    lo, hi = slab_bounds(feature_A.shape[2], rank, world)
+    corr = model.FeatureCorrelation(feature_A[:, :, lo:hi].contiguous(), feature_B)
+    corr = slab_mutual_matching(corr, group)
+    br = slab_neigh_consensus(corr, model.NeighConsensus, rank, world, group)
+    if model.NeighConsensus.symmetric_mode and br.shape[1] == 2:
+        return slab_mutual_matching(br, group, sum_branches=True)
+    c = br.shape[1] // 2 if model.NeighConsensus.symmetric_mode else br.shape[1]
+    summed = br[:, :c] + br[:, c:] if model.NeighConsensus.symmetric_mode else br
+    return slab_mutual_matching(summed, group)

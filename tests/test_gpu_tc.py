@@ -145,3 +145,49 @@ def test_tc_mode_routes_wide_layers_to_cuda_cores(F_, cuda):
     a = F_.conv4d(x, w, None, permute_filters=False, mode=_tc())
     b = F_.conv4d(x, w, None, permute_filters=False, mode=0)
     assert torch.equal(a, b)
+
+
+def test_tc_inloc_config_half_precision_relocalisation(F_, cuda, monkeypatch):
+    """BASELINE.json configs[2] in miniature: fp16 features, maxpool4d k=2 relocalisation, NC 3,3 / 16,1 on the
+    tensor-core kernels, corr_to_matches in both directions -- against the fp32 oracle."""
+    import ncnet_b200 as nb
+    monkeypatch.setenv("NCNET_CONV_MODE", "tc16")
+    torch.manual_seed(36)
+    fa = O.feature_l2norm(torch.relu(torch.randn(1, 128, 20, 16)))
+    fb = O.feature_l2norm(torch.relu(torch.randn(1, 128, 16, 20)))
+    onc = O.NeighConsensus([3, 3], [16, 1])
+    ref, rdelta = O.head_forward(fa, fb, onc, relocalization_k_size=2)
+    net = nb.ImMatchNet.__new__(nb.ImMatchNet)
+    torch.nn.Module.__init__(net)
+    net.relocalization_k_size, net.half_precision = 2, True
+    net.FeatureCorrelation = nb.FeatureCorrelation("4D", False)
+    net.NeighConsensus = nb.NeighConsensus(True, [3, 3], [16, 1])
+    net.NeighConsensus.load_state_dict(onc.state_dict())
+    net.NeighConsensus.half()
+    with torch.no_grad():
+        out, delta = net.match_features(fa.half().to(cuda), fb.half().to(cuda))
+    assert out.dtype == torch.float16 and nerr(out.float(), ref) < 5e-3
+    for inv in (False, True):
+        m = nb.corr_to_matches(out, delta4d=delta, k_size=2, do_softmax=True, scale="positive", return_indices=True,
+                               invert_matching_direction=inv)
+        mo = O.corr_to_matches(ref, delta4d=rdelta, k_size=2, do_softmax=True, scale="positive", return_indices=True,
+                               invert_matching_direction=inv)
+        agree = ((m[5].cpu() == mo[5]) & (m[6].cpu() == mo[6]) & (m[7].cpu() == mo[7]) & (m[8].cpu() == mo[8])).float().mean()
+        assert agree > 0.9, float(agree)
+
+
+def test_slab_head_single_rank_equals_whole_volume(F_, cuda):
+    """World size 1 of the slab-sharded head (ncnet_b200.dist) is the ordinary head; the 2-GPU equality run is
+    scripts/slab_check.py under torchrun."""
+    import ncnet_b200 as nb
+    from ncnet_b200 import dist as D
+    torch.manual_seed(37)
+    fa = O.feature_l2norm(torch.relu(torch.randn(1, 32, 8, 7))).to(cuda)
+    fb = O.feature_l2norm(torch.relu(torch.randn(1, 32, 6, 9))).to(cuda)
+    net = nb.ImMatchNet.__new__(nb.ImMatchNet)
+    torch.nn.Module.__init__(net)
+    net.relocalization_k_size, net.half_precision = 0, False
+    net.FeatureCorrelation = nb.FeatureCorrelation("4D", False)
+    net.NeighConsensus = nb.NeighConsensus(True, [3, 3], [16, 1])
+    with torch.no_grad():
+        assert torch.equal(D.slab_match_features(net, fa, fb, 0, 1), net.match_features(fa, fb))
