@@ -59,6 +59,13 @@ int ncnet_feature_l2norm(const void *x, void *y, int B, int C, int HW, int dtype
  * and the roles of A and B exchanged; the Python wrapper does that re-indexing. */
 int ncnet_corr4d_fwd(const void *fa, const void *fb, void *out, int B, int C, int nA, int nB,
                      int dtype, int relu_l2norm, void *stream);
+/* The same product on the tensor cores (tcgen05, fp16 operands, fp32 accumulation in TMEM; <= 1e-3 normalised
+ * error).  scratch: ncnet_corr4d_tc_scratch_bytes(...) bytes (the fp16 operand tiles).  l2norm_inputs != 0 fuses
+ * featureL2Norm (lib/model.py:14-17, applied by the trunk at lib/model.py:85-86) into the operand packing, for
+ * callers that hand over un-normalised trunk outputs. */
+size_t ncnet_corr4d_tc_scratch_bytes(int B, int C, int nA, int nB);
+int ncnet_corr4d_fwd_tc(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB,
+                        int dtype, int relu_l2norm, int l2norm_inputs, void *stream);
 /* gradient of the plain (un-normalised) correlation wrt both feature maps (autograd of lib/model.py:113) */
 int ncnet_corr4d_bwd(const void *grad_out, const void *fa, const void *fb, void *grad_fa, void *grad_fb,
                      int B, int C, int nA, int nB, int dtype, void *stream);

@@ -36,7 +36,7 @@ struct WgArgs {
     int variant, NAv, NBv, N, nb_copy;      // nb_copy: B halves copied per stage
     uint32_t a_sbo, b_sbo;
     int a_r0, b_r0;                         // buffer row at which the haloed X / G plane is placed
-    int npos_a, npos_b, nkb;
+    int npos_a, npos_b, nkb, kb0;           // K blocks [kb0, nkb): blocks that only see halo zeros are skipped
     int S, Cin, Cout, cop;
     uint32_t idesc, tmem_cols;
     uint32_t stage_bytes, a_bytes, b_start;
@@ -155,17 +155,18 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
             if (elect_one()) {
             {   // first K block: clears the accumulators on the CTA's first plane
                 const uint32_t acc = first ? 0u : 1u;
+                const uint32_t ko = (uint32_t)p.kb0 * 16u;
                 {
-                    umma_f16(tmem_base, a_hi | a_lo0, b_hi | b_lo0, p.idesc, acc);
-                    if (two_b) umma_f16(tmem_base + n, a_hi | a_lo0, b_hi | b_lo1, p.idesc, acc);
+                    umma_f16(tmem_base, a_hi | (a_lo0 + ko), b_hi | (b_lo0 + ko), p.idesc, acc);
+                    if (two_b) umma_f16(tmem_base + n, a_hi | (a_lo0 + ko), b_hi | (b_lo1 + ko), p.idesc, acc);
                     if (two_a) {
-                        umma_f16(tmem_base + nb * n, a_hi | a_lo1, b_hi | b_lo0, p.idesc, acc);
-                        if (two_b) umma_f16(tmem_base + (nb + 1) * n, a_hi | a_lo1, b_hi | b_lo1, p.idesc, acc);
+                        umma_f16(tmem_base + nb * n, a_hi | (a_lo1 + ko), b_hi | (b_lo0 + ko), p.idesc, acc);
+                        if (two_b) umma_f16(tmem_base + (nb + 1) * n, a_hi | (a_lo1 + ko), b_hi | (b_lo1 + ko), p.idesc, acc);
                     }
                 }
             }
 #pragma unroll 4
-            for (int kb = 1; kb < p.nkb; ++kb) {
+            for (int kb = p.kb0 + 1; kb < p.nkb; ++kb) {
                 const uint32_t ko = (uint32_t)kb * 16u;                  // 16 positions x 16 B, in 16-byte units
                 {
                     umma_f16(tmem_base, a_hi | (a_lo0 + ko), b_hi | (b_lo0 + ko), p.idesc, 1u);
@@ -262,7 +263,7 @@ cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int
 
 struct WgPlan {
     bool ok;
-    int variant, NAv, NBv, N, nb_copy, P, a_r0, b_r0, npos_a, npos_b, nkb, S, cop;
+    int variant, NAv, NBv, N, nb_copy, P, a_r0, b_r0, npos_a, npos_b, nkb, kb0, S, cop;
     uint32_t a_sbo, b_sbo, a_bytes, stage_bytes, tmem_cols, b_start;
     size_t smem, part_bytes;
 };
@@ -368,7 +369,16 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = k; a.P = w.P;
     a.variant = w.variant; a.NAv = w.NAv; a.NBv = w.NBv; a.N = w.N; a.nb_copy = w.nb_copy;
     a.a_sbo = w.a_sbo; a.b_sbo = w.b_sbo; a.a_r0 = w.a_r0; a.b_r0 = w.b_r0;
-    a.npos_a = w.npos_a; a.npos_b = w.npos_b; a.nkb = w.nkb; a.S = w.S; a.Cin = Cin; a.Cout = Cout; a.cop = w.cop;
+    // K blocks outside [kb0, kb1) multiply nothing but halo zeros (every shifted view of the X side is zero there)
+    {
+        const int pad = k / 2;
+        int lo = pad * w.P + pad - 7;
+        if (lo < 0) lo = 0;
+        const int hi = (pad + d3 - 1) * w.P + pad + d4;
+        a.kb0 = lo / 16;
+        a.nkb = (hi + 15) / 16 < w.nkb ? (hi + 15) / 16 : w.nkb;
+    }
+    a.npos_a = w.npos_a; a.npos_b = w.npos_b; a.S = w.S; a.Cin = Cin; a.Cout = Cout; a.cop = w.cop;
     a.tmem_cols = w.tmem_cols; a.stage_bytes = w.stage_bytes; a.a_bytes = w.a_bytes; a.b_start = w.b_start;
     // D = f32, A = B = f16, both MN-major (bits 15/16), N>>3 at bit 17, M=64 -> 4 at bit 24
     a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);

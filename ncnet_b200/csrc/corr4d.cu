@@ -143,7 +143,26 @@ l2norm_kernel(const T *__restrict__ x, T *__restrict__ y, int C, int HW) {
 
 }  // namespace ncnet
 
+namespace ncnet {
+size_t corr4d_tc_scratch_bytes(int B, int C, int nA, int nB);
+int corr4d_tc_fwd(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB, int dtype,
+                  int relu_l2norm, int l2norm_inputs, cudaStream_t st);
+}  // namespace ncnet
+
 using namespace ncnet;
+
+extern "C" size_t ncnet_corr4d_tc_scratch_bytes(int B, int C, int nA, int nB) {
+    if (B < 1 || C < 1 || nA < 1 || nB < 1) return 0;
+    return corr4d_tc_scratch_bytes(B, C, nA, nB);
+}
+
+extern "C" int ncnet_corr4d_fwd_tc(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB,
+                                   int dtype, int relu_l2norm, int l2norm_inputs, void *stream) {
+    NC_CHECK(fa && fb && out && scratch, "corr4d_fwd_tc: null pointer");
+    NC_CHECK(B > 0 && C > 0 && nA > 0 && nB > 0, "corr4d_fwd_tc: bad shape");
+    NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "corr4d_fwd_tc: unsupported dtype %d", dtype);
+    return corr4d_tc_fwd(fa, fb, out, scratch, B, C, nA, nB, dtype, relu_l2norm, l2norm_inputs, (cudaStream_t)stream);
+}
 
 extern "C" int ncnet_feature_l2norm(const void *x, void *y, int B, int C, int HW, int dtype, void *stream) {
     NC_CHECK(x && y, "feature_l2norm: null pointer");

@@ -1,0 +1,205 @@
+// FeatureCorrelation on the tensor cores (reference lib/model.py:106-118): out[b,a,t] = sum_c fa[b,c,a]*fb[b,c,t].
+//
+// A batched GEMM, M = nA, N = nB, K = C, both operands MN-major (the channel axis is the strided one).  A pack
+// kernel converts each feature map to fp16 (optionally fusing the trunk's featureL2Norm, lib/model.py:85-86) and
+// lays it out as  [b][C/64][n/8][64 c][8 positions]:  the 8 positions are the 16 bytes of a UMMA core-matrix row,
+// 8 consecutive channels are its 8 K rows (LBO = 128 B), position groups are SBO = 1 KB apart, and the
+// (128|256 positions x 64 channels) operand tile of a pipeline stage is ONE contiguous run -> one cp.async.bulk per
+// operand per stage.  fp32 accumulation in TMEM (128 x 256 tile), epilogue: optional ReLU + singleton-dim L2 norm
+// (normalization=True), rows streamed straight to the [B,nA,nB] volume.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace ncnet {
+
+using namespace tc;
+
+constexpr int kCorrThreads = 192;
+constexpr int kCorrStages = 4;
+constexpr int kCorrKB = 64;            // channels per stage
+constexpr int kCorrBM = 128, kCorrBN = 256;
+
+// [B, C, n] (T) -> fp16 [B][KB][npad/8][64][8]; positions >= n and channels >= C are zero.
+template <typename T>
+__global__ void __launch_bounds__(256)
+corr_pack_kernel(const T *__restrict__ f, __half *__restrict__ out, int C, int n, int npad, int kblocks, int l2norm) {
+    const int b = blockIdx.z;
+    const int mg = blockIdx.x * blockDim.x + threadIdx.x;       // group of 8 positions
+    if (mg >= npad / 8) return;
+    const T *fb = f + (size_t)b * C * n;
+    float inv[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) inv[u] = 1.f;
+    if (l2norm) {
+        float ss[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        for (int c = 0; c < C; ++c)
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const int a = mg * 8 + u;
+                const float v = a < n ? ldf(fb + (size_t)c * n + a) : 0.f;
+                ss[u] += v * v;
+            }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) inv[u] = 1.f / sqrtf(ss[u] + 1e-6f);
+    }
+    for (int c = blockIdx.y; c < kblocks * kCorrKB; c += gridDim.y) {
+        __align__(16) __half v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int a = mg * 8 + u;
+            v[u] = __float2half_rn((c < C && a < n) ? ldf(fb + (size_t)c * n + a) * inv[u] : 0.f);
+        }
+        const size_t off = ((((size_t)b * kblocks + c / kCorrKB) * (npad / 8) + mg) * kCorrKB + (c % kCorrKB)) * 8;
+        *reinterpret_cast<uint4 *>(out + off) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
+struct CorrArgs {
+    const __half *pa, *pb;
+    void *out;
+    int nA, nB, npadA, npadB, kblocks;
+    int relu_l2norm, out_f16;
+    uint32_t idesc;
+};
+
+__global__ void __launch_bounds__(kCorrThreads, 1)
+corr4d_tc_kernel(const CorrArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[kCorrStages], empty_bar[kCorrStages], accum_bar;
+    __shared__ uint32_t tmem_base_s;
+    constexpr uint32_t kABytes = kCorrBM / 8 * kCorrKB * 16, kBBytes = kCorrBN / 8 * kCorrKB * 16;   // 16 KB, 32 KB
+    constexpr uint32_t kStage = kABytes + kBBytes;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int nt = blockIdx.x, mt = blockIdx.y, b = blockIdx.z;
+
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < kCorrStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        mbar_init(&accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(256) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    // the last N tile may be narrower than 256 positions (npadB is a multiple of 128)
+    const int n_cols = min(kCorrBN, p.npadB - nt * kCorrBN);
+    const uint32_t b_bytes = (uint32_t)(n_cols / 8) * kCorrKB * 16;
+
+    if (warp == 0) {
+        int stage = 0; uint32_t phase = 0;
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+            mbar_wait(&empty_bar[stage], phase ^ 1);
+            if (elect_one()) {
+                uint8_t *sa = smem + (size_t)stage * kStage;
+                mbar_expect_tx(&full_bar[stage], kABytes + b_bytes);
+                const __half *ga = p.pa + ((((size_t)b * p.kblocks + kb) * (p.npadA / 8) + (size_t)mt * (kCorrBM / 8)) * kCorrKB) * 8;
+                const __half *gb = p.pb + ((((size_t)b * p.kblocks + kb) * (p.npadB / 8) + (size_t)nt * (kCorrBN / 8)) * kCorrKB) * 8;
+                bulk_g2s(sa, ga, kABytes, &full_bar[stage]);
+                bulk_g2s(sa + kABytes, gb, b_bytes, &full_bar[stage]);
+            }
+            __syncwarp();
+            if (++stage == kCorrStages) { stage = 0; phase ^= 1; }
+        }
+    } else if (warp == 1) {
+        int stage = 0; uint32_t phase = 0;
+        // MN-major, no swizzle: LBO = 128 B between groups of 8 channels, SBO = 1 KB between groups of 8 positions
+        const uint64_t hi = ((uint64_t)(((uint32_t)(kCorrKB * 16) >> 4) | (1u << 14))) << 32;
+        const uint32_t lbo_field = (128u >> 4) << 16;
+        const uint32_t idesc = (p.idesc & ~(0x3fu << 17)) | ((uint32_t)(n_cols >> 3) << 17);
+        for (int kb = 0; kb < p.kblocks; ++kb) {
+            mbar_wait(&full_bar[stage], phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (elect_one()) {
+                const uint32_t sa4 = smem_u32(smem + (size_t)stage * kStage) >> 4;
+                const uint32_t sb4 = sa4 + (kABytes >> 4);
+#pragma unroll
+                for (int kk = 0; kk < kCorrKB / 16; ++kk)        // 16 channels = 2 K groups = 256 B further
+                    umma_f16(tmem_base, hi | (uint64_t)(lbo_field | (sa4 + kk * 16)), hi | (uint64_t)(lbo_field | (sb4 + kk * 16)),
+                             idesc, (kb | kk) ? 1u : 0u);
+                umma_commit(&empty_bar[stage]);
+            }
+            __syncwarp();
+            if (++stage == kCorrStages) { stage = 0; phase ^= 1; }
+        }
+        if (elect_one()) umma_commit(&accum_bar);
+        __syncwarp();
+    } else {
+        const int q = warp & 3;
+        mbar_wait(&accum_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const int a = mt * kCorrBM + q * 32 + lane;
+        const size_t row = ((size_t)b * p.nA + a) * p.nB;
+        for (int c0 = 0; c0 < n_cols; c0 += 16) {
+            float v[16];
+            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+            if (a >= p.nA) continue;
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+                const int t = nt * kCorrBN + c0 + u;
+                if (t >= p.nB) break;
+                float x = v[u];
+                if (p.relu_l2norm) {
+                    if (p.out_f16) {
+                        x = rnd<__half>(fmaxf(rnd<__half>(x), 0.f));
+                        x = x / rnd<__half>(sqrtf(rnd<__half>(rnd<__half>(x * x) + 1e-6f)));
+                    } else {
+                        x = fmaxf(x, 0.f);
+                        x = x / sqrtf(x * x + 1e-6f);
+                    }
+                }
+                if (p.out_f16) ((__half *)p.out)[row + t] = __float2half_rn(x);
+                else ((float *)p.out)[row + t] = x;
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+}
+
+static size_t corr_align(size_t v) { return (v + 255) & ~(size_t)255; }
+static int pad128(int n) { return (n + 127) / 128 * 128; }
+
+size_t corr4d_tc_scratch_bytes(int B, int C, int nA, int nB) {
+    const size_t kblocks = (C + kCorrKB - 1) / kCorrKB;
+    return corr_align((size_t)B * kblocks * pad128(nA) * kCorrKB * 2) + corr_align((size_t)B * kblocks * pad128(nB) * kCorrKB * 2) + 256;
+}
+
+template <typename T>
+static int corr_tc_run(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB, int relu_l2norm,
+                       int l2norm_inputs, cudaStream_t st) {
+    const int kblocks = (C + kCorrKB - 1) / kCorrKB;
+    const int npadA = pad128(nA), npadB = pad128(nB);
+    NC_CHECK(B <= 65535, "corr4d(tc): batch too large");
+    __half *pa = (__half *)scratch;
+    __half *pb = (__half *)((uint8_t *)scratch + corr_align((size_t)B * kblocks * npadA * kCorrKB * 2));
+    corr_pack_kernel<T><<<dim3((npadA / 8 + 255) / 256, 64, B), 256, 0, st>>>((const T *)fa, pa, C, nA, npadA, kblocks, l2norm_inputs);
+    NC_LAUNCH_OK("corr_pack_kernel(A)");
+    corr_pack_kernel<T><<<dim3((npadB / 8 + 255) / 256, 64, B), 256, 0, st>>>((const T *)fb, pb, C, nB, npadB, kblocks, l2norm_inputs);
+    NC_LAUNCH_OK("corr_pack_kernel(B)");
+    CorrArgs a{};
+    a.pa = pa; a.pb = pb; a.out = out; a.nA = nA; a.nB = nB; a.npadA = npadA; a.npadB = npadB; a.kblocks = kblocks;
+    a.relu_l2norm = relu_l2norm; a.out_f16 = sizeof(T) == 2;
+    // D = f32, A = B = f16, both MN-major, M = 128; N is patched per tile
+    a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(kCorrBN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    const size_t smem = (size_t)kCorrStages * (kCorrBM + kCorrBN) / 8 * kCorrKB * 16;
+    cudaError_t e = cudaFuncSetAttribute(corr4d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    NC_CHECK(e == cudaSuccess, "corr4d(tc): smem attribute: %s", cudaGetErrorString(e));
+    dim3 grid((npadB + kCorrBN - 1) / kCorrBN, npadA / kCorrBM, B);
+    NC_CHECK(grid.y <= 65535, "corr4d(tc): too many row tiles");
+    corr4d_tc_kernel<<<grid, kCorrThreads, smem, st>>>(a);
+    NC_LAUNCH_OK("corr4d_tc_kernel");
+    return 0;
+}
+
+int corr4d_tc_fwd(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB, int dtype,
+                  int relu_l2norm, int l2norm_inputs, cudaStream_t st) {
+    if (dtype == NCNET_F32) return corr_tc_run<float>(fa, fb, out, scratch, B, C, nA, nB, relu_l2norm, l2norm_inputs, st);
+    return corr_tc_run<__half>(fa, fb, out, scratch, B, C, nA, nB, relu_l2norm, l2norm_inputs, st);
+}
+
+}  // namespace ncnet

@@ -67,10 +67,18 @@ def feature_l2norm(x: torch.Tensor) -> torch.Tensor:
     return y
 
 
-def _corr_fwd_raw(fa: torch.Tensor, fb: torch.Tensor, norm: bool) -> torch.Tensor:
+def _corr_fwd_raw(fa: torch.Tensor, fb: torch.Tensor, norm: bool, tensor_cores: bool = False) -> torch.Tensor:
     b, c = fa.shape[0], fa.shape[1]
     na, nb = fa[0, 0].numel(), fb[0, 0].numel()
     out = torch.empty(b, na, nb, device=fa.device, dtype=fa.dtype)
+    if tensor_cores:
+        L = _cabi.lib()
+        scratch = torch.empty(L.ncnet_corr4d_tc_scratch_bytes(b, c, na, nb), device=fa.device, dtype=torch.uint8)
+        with torch.cuda.device(fa.device):
+            _cabi.check(L.ncnet_corr4d_fwd_tc(_ptr(fa), _ptr(fb), _ptr(out), _ptr(scratch), b, c, na, nb, _dt(fa), int(norm), 0,
+                                              _stream()), "corr4d_fwd_tc")
+        _count(3)
+        return out
     with torch.cuda.device(fa.device):
         _cabi.check(_cabi.lib().ncnet_corr4d_fwd(_ptr(fa), _ptr(fb), _ptr(out), b, c, na, nb, _dt(fa), int(norm),
                                                  _stream()), "corr4d_fwd")
@@ -123,7 +131,7 @@ def feature_correlation(fa: torch.Tensor, fb: torch.Tensor, shape: str = "4D", n
             return m
     else:
         fuse = normalization and shape == "4D"
-        m = _corr_fwd_raw(lhs.contiguous(), rhs.contiguous(), fuse)
+        m = _corr_fwd_raw(lhs.contiguous(), rhs.contiguous(), fuse, tensor_cores=default_conv_mode() == CONV_TC16)
         if normalization and shape == "3D":
             m = feature_l2norm(torch.relu(m.reshape(b, ha * wa, hb, wb)))
             return m

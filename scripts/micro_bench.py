@@ -64,6 +64,18 @@ with torch.no_grad():
             ms = timeit(lambda: nb.corr_to_matches(x, do_softmax=True, invert_matching_direction=inv))
             gbs = x.numel() * x.element_size() / ms / 1e6
             emit(kernel="corr_to_matches softmax", case=f"{name} invert={inv}", ms=ms, achieved_GBs=gbs, frac_of_hbm=gbs / PEAKS["hbm_gbs"])
+    # FeatureCorrelation: tcgen05 GEMM vs the fp32 CUDA-core GEMM
+    for name, b, c, ha, wa, dt in (("PF B=16", 16, 1024, 25, 25, torch.float32), ("IL16 fp16", 1, 1024, 100, 74, torch.float16),
+                                   ("IL32 fp16", 1, 1024, 200, 150, torch.float16)):
+        fa = torch.rand(b, c, ha, wa, device=dev).to(dt); fb = torch.rand(b, c, ha, wa, device=dev).to(dt)
+        for tcm, mname in ((True, "tc16"), (False, "fp32")):
+            if not tcm and ha * wa > 10000:
+                continue
+            ms = timeit(lambda: F_._corr_fwd_raw(fa, fb, False, tensor_cores=tcm), iters=3, do_flush=False)
+            tf = 2.0 * b * (ha * wa) ** 2 * c / ms / 1e9
+            emit(kernel="FeatureCorrelation fwd (incl. operand packing)", case=name, mode=mname, ms=ms, achieved_TFLOPs=tf,
+                 frac_of_bf16_peak=tf / PEAKS["bf16_tflops"])
+        del fa, fb
     # Conv4d layers, forward, both branches, per mode
     for n in (16, 25, 32):
         for cin, cout in ((1, 16), (16, 16), (16, 1)):

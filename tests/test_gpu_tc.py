@@ -191,3 +191,20 @@ def test_slab_head_single_rank_equals_whole_volume(F_, cuda):
     net.NeighConsensus = nb.NeighConsensus(True, [3, 3], [16, 1])
     with torch.no_grad():
         assert torch.equal(D.slab_match_features(net, fa, fb, 0, 1), net.match_features(fa, fb))
+
+
+@pytest.mark.parametrize("shape,dt", [((2, 64, 25, 25, 25, 25), torch.float32), ((1, 96, 9, 13, 20, 7), torch.float32),
+                                       ((1, 128, 40, 30, 33, 28), torch.float16)])
+def test_tc_feature_correlation_vs_oracle(F_, cuda, monkeypatch, shape, dt):
+    """tcgen05 correlation GEMM (operands fp16, fp32 accumulate) against the fp32 oracle, plain and normalised."""
+    import ncnet_b200 as nb
+    monkeypatch.setenv("NCNET_CONV_MODE", "tc16")
+    torch.manual_seed(38)
+    b, c, ha, wa, hb, wb = shape
+    fa = O.feature_l2norm(torch.relu(torch.randn(b, c, ha, wa)))
+    fb = O.feature_l2norm(torch.relu(torch.randn(b, c, hb, wb)))
+    for norm in (False, True):
+        ref = O.feature_correlation(fa, fb, "4D", norm)
+        out = nb.FeatureCorrelation("4D", norm)(fa.to(cuda).to(dt), fb.to(cuda).to(dt))
+        assert out.shape == ref.shape and out.dtype == dt
+        assert nerr(out.float(), ref) < (2e-3 if dt == torch.float16 else 1e-3) * (3 if norm else 1)
