@@ -133,14 +133,16 @@ corr4d_tc_kernel(const CorrArgs p) {
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int a = mt * kCorrBM + q * 32 + lane;
         const size_t row = ((size_t)b * p.nA + a) * p.nB;
+        // rows start 16-byte aligned when nB is a multiple of 8 (fp16) / 4 (fp32) and the base pointer is aligned
+        const bool vec_ok = (p.nB % (p.out_f16 ? 8 : 4)) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0;
         for (int c0 = 0; c0 < n_cols; c0 += 16) {
             float v[16];
             tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
             if (a >= p.nA) continue;
+            const int t0 = nt * kCorrBN + c0;
+            if (t0 >= p.nB) continue;
 #pragma unroll
             for (int u = 0; u < 16; ++u) {
-                const int t = nt * kCorrBN + c0 + u;
-                if (t >= p.nB) break;
                 float x = v[u];
                 if (p.relu_l2norm) {
                     if (p.out_f16) {
@@ -151,8 +153,28 @@ corr4d_tc_kernel(const CorrArgs p) {
                         x = x / sqrtf(x * x + 1e-6f);
                     }
                 }
-                if (p.out_f16) ((__half *)p.out)[row + t] = __float2half_rn(x);
-                else ((float *)p.out)[row + t] = x;
+                v[u] = x;
+            }
+            if (vec_ok && t0 + 16 <= p.nB) {            // whole 16-value chunk in range and 16-byte aligned
+                if (p.out_f16) {
+                    __align__(16) __half h[16];
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) h[u] = __float2half_rn(v[u]);
+                    uint4 *dst = reinterpret_cast<uint4 *>((__half *)p.out + row + t0);
+                    dst[0] = reinterpret_cast<const uint4 *>(h)[0];
+                    dst[1] = reinterpret_cast<const uint4 *>(h)[1];
+                } else {
+                    float4 *dst = reinterpret_cast<float4 *>((float *)p.out + row + t0);
+#pragma unroll
+                    for (int w4 = 0; w4 < 4; ++w4) dst[w4] = make_float4(v[4 * w4], v[4 * w4 + 1], v[4 * w4 + 2], v[4 * w4 + 3]);
+                }
+            } else {
+#pragma unroll
+                for (int u = 0; u < 16; ++u) {
+                    if (t0 + u >= p.nB) break;
+                    if (p.out_f16) ((__half *)p.out)[row + t0 + u] = __float2half_rn(v[u]);
+                    else ((float *)p.out)[row + t0 + u] = v[u];
+                }
             }
         }
     }
