@@ -40,27 +40,42 @@ struct WgArgs {
     int S, Cin, Cout, cop;
     uint32_t idesc, tmem_cols;
     uint32_t stage_bytes, a_bytes, b_start;
+    int stages;                             // ring depth
 };
 
 using namespace tc;
 
-// which (x plane, g plane) pair the CTA's tap pairs with output plane index `pl`; false = skipped
-__device__ __forceinline__ bool wg_pair(const WgArgs &p, int pl, int t1, int t2, int &b, size_t &ij_x, size_t &ij_g) {
+// Work item `pl` of a CTA: which grad plane it stages, which X plane(s), and which of the NAv "A variants" are live.
+//   V2: pl = output plane (i,j); X plane (i+t1-p, j+t2-p); A variants = the channel halves of X (all live)
+//   V1: pl = output plane (i,j); A variant av = X' plane (i+t1-p, j+av-p): one CTA covers every t2, a variant whose
+//       plane falls outside the volume is skipped
+//   V3: pl = X plane (i',j'); grad plane (i'-t1+p, j') whose channels hold the t2 taps; A variants = halves of X
+struct WgItem { int b; size_t ij_g; int xi, xj; uint32_t amask; };
+
+__device__ __forceinline__ bool wg_item(const WgArgs &p, int pl, int t1, int t2, WgItem &it) {
     const int PAD = p.KS / 2;
-    b = pl / (p.d1 * p.d2);
-    const int ij = pl - b * (p.d1 * p.d2);
+    it.b = pl / (p.d1 * p.d2);
+    const int ij = pl - it.b * (p.d1 * p.d2);
     const int i = ij / p.d2, j = ij - i * p.d2;
-    if (p.variant == 3) {       // pl enumerates X planes (i',j'); G8 plane = (i' - t1 + pad, j'), t2 lives in its channels
+    if (p.variant == 3) {
         const int ig = i - t1 + PAD;
         if (ig < 0 || ig >= p.d1) return false;
-        ij_x = (size_t)i * p.d2 + j;
-        ij_g = (size_t)ig * p.d2 + j;
+        it.xi = i; it.xj = j; it.ij_g = (size_t)ig * p.d2 + j; it.amask = (1u << p.NAv) - 1u;
         return true;
     }
-    const int ii = i + t1 - PAD, jj = j + t2 - PAD;
-    if (ii < 0 || ii >= p.d1 || jj < 0 || jj >= p.d2) return false;
-    ij_x = (size_t)ii * p.d2 + jj;
-    ij_g = (size_t)i * p.d2 + j;
+    const int ii = i + t1 - PAD;
+    if (ii < 0 || ii >= p.d1) return false;
+    it.xi = ii; it.ij_g = (size_t)i * p.d2 + j;
+    if (p.variant == 1) {
+        it.xj = j - PAD;                      // A variant av reads plane column xj + av
+        uint32_t m = 0;
+        for (int av = 0; av < p.NAv; ++av) if (it.xj + av >= 0 && it.xj + av < p.d2) m |= 1u << av;
+        it.amask = m;
+        return m != 0;
+    }
+    const int jj = j + t2 - PAD;
+    if (jj < 0 || jj >= p.d2) return false;
+    it.xj = jj; it.amask = (1u << p.NAv) - 1u;
     return true;
 }
 
@@ -73,7 +88,7 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int by = blockIdx.y;
     int t2 = 0;
-    if (p.variant != 3) { t2 = by % p.KS; by /= p.KS; }
+    if (p.variant == 2) { t2 = by % p.KS; by /= p.KS; }
     const int t1 = by % p.KS; by /= p.KS;
     const int g = by;
     const int s = blockIdx.x;
@@ -82,7 +97,7 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
     const int pbeg = s * per, pend = min(nplanes, pbeg + per);
 
     if (warp == 1 && lane == 0) {
-        for (int st = 0; st < kWgStages; ++st) { mbar_init(&full_bar[st], 1); mbar_init(&empty_bar[st], 1); }
+        for (int st = 0; st < p.stages; ++st) { mbar_init(&full_bar[st], 1); mbar_init(&empty_bar[st], 1); }
         mbar_init(&accum_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -93,7 +108,7 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
     {   // zero the whole ring once: halo rows/columns and tails are never written by the row copies
         const uint4 z = make_uint4(0, 0, 0, 0);
         uint4 *d = reinterpret_cast<uint4 *>(smem);
-        const uint32_t n16 = (uint32_t)kWgStages * p.stage_bytes / 16;
+        const uint32_t n16 = (uint32_t)p.stages * p.stage_bytes / 16;
         for (uint32_t e = threadIdx.x; e < n16; e += kWgThreads) d[e] = z;
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     }
@@ -110,78 +125,89 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
         const size_t plane_cb = (size_t)(p.d3 + 2 * (p.KS / 2)) * p.P;
         const size_t ijn = (size_t)p.d1 * p.d2;
         const uint32_t tile = (uint32_t)(plane_cb * 16);
-        const uint32_t tx = (uint32_t)(p.NAv + p.nb_copy) * tile;
         for (int pl = pbeg; pl < pend; ++pl) {
-            int b; size_t ij_x, ij_g;
-            if (!wg_pair(p, pl, t1, t2, b, ij_x, ij_g)) continue;
+            WgItem it;
+            if (!wg_item(p, pl, t1, t2, it)) continue;
             mbar_wait(&empty_bar[stage], phase ^ 1);
             if (elect_one()) {
                 uint8_t *sa = smem + (size_t)stage * p.stage_bytes;
                 uint8_t *sb = sa + p.a_bytes;
-                mbar_expect_tx(&full_bar[stage], tx);
-                const size_t bga = (size_t)b * p.GxA + (p.GxA == 1 ? 0 : g);
-                const size_t bgb = (size_t)b * p.G + g;
-                for (int h = 0; h < p.NAv; ++h)
-                    bulk_g2s(sa + ((size_t)h * p.npos_a + (size_t)p.a_r0 * p.P) * 16,
-                             p.xa + (((bga * 2 + h) * ijn + ij_x) * plane_cb) * 8, tile, &full_bar[stage]);
+                mbar_expect_tx(&full_bar[stage], (uint32_t)(__popc(it.amask) + p.nb_copy) * tile);
+                const size_t bga = (size_t)it.b * p.GxA + (p.GxA == 1 ? 0 : g);
+                const size_t bgb = (size_t)it.b * p.G + g;
+                for (int av = 0; av < p.NAv; ++av) {
+                    if (!((it.amask >> av) & 1u)) continue;
+                    // V1: variant = plane column, always channel half 0;  V2/V3: variant = channel half of one plane
+                    const size_t ijx = (size_t)it.xi * p.d2 + (p.variant == 1 ? it.xj + av : it.xj);
+                    const int half = p.variant == 1 ? 0 : av;
+                    bulk_g2s(sa + ((size_t)av * p.npos_a + (size_t)p.a_r0 * p.P) * 16,
+                             p.xa + (((bga * 2 + half) * ijn + ijx) * plane_cb) * 8, tile, &full_bar[stage]);
+                }
                 for (int h = 0; h < p.nb_copy; ++h)
                     bulk_g2s(sb + ((size_t)h * p.npos_b + (size_t)p.b_r0 * p.P) * 16,
-                             p.gb + (((bgb * 2 + h) * ijn + ij_g) * plane_cb) * 8, tile, &full_bar[stage]);
+                             p.gb + (((bgb * 2 + h) * ijn + it.ij_g) * plane_cb) * 8, tile, &full_bar[stage]);
             }
             __syncwarp();
-            if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
         int stage = 0;
         uint32_t phase = 0;
-        bool first = true;
-        const bool two_a = p.NAv == 2, two_b = p.NBv == 2;
-        const uint32_t nb = (uint32_t)p.NBv;
+        uint32_t inited = 0;                                      // accumulator sets already written once
         const uint32_t lbo_field = (128u >> 4) << 16;                                   // LBO = 128 B (next 8 positions)
         const uint64_t a_hi = ((uint64_t)((p.a_sbo >> 4) | (1u << 14))) << 32;           // SBO + descriptor version 1
         const uint64_t b_hi = ((uint64_t)((p.b_sbo >> 4) | (1u << 14))) << 32;
+        const uint32_t n = (uint32_t)p.N, nbv = (uint32_t)p.NBv;
         for (int pl = pbeg; pl < pend; ++pl) {
-            int b; size_t ij_x, ij_g;
-            if (!wg_pair(p, pl, t1, t2, b, ij_x, ij_g)) continue;
+            WgItem it;
+            if (!wg_item(p, pl, t1, t2, it)) continue;
             mbar_wait(&full_bar[stage], phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            // warp-uniform descriptor arithmetic (only the low word changes); lane 0 issues
+            // warp-uniform descriptor arithmetic (only the low word changes); one elected lane issues
             const uint32_t sa4 = smem_u32(smem + (size_t)stage * p.stage_bytes) >> 4;
             const uint32_t sb4 = sa4 + ((p.a_bytes + p.b_start) >> 4);
-            const uint32_t a_lo0 = lbo_field | sa4, a_lo1 = a_lo0 + (uint32_t)p.npos_a;
-            const uint32_t b_lo0 = lbo_field | sb4, b_lo1 = b_lo0 + (uint32_t)p.npos_b;
-            const uint32_t n = (uint32_t)p.N;
             if (elect_one()) {
-            {   // first K block: clears the accumulators on the CTA's first plane
-                const uint32_t acc = first ? 0u : 1u;
-                const uint32_t ko = (uint32_t)p.kb0 * 16u;
-                {
-                    umma_f16(tmem_base, a_hi | (a_lo0 + ko), b_hi | (b_lo0 + ko), p.idesc, acc);
-                    if (two_b) umma_f16(tmem_base + n, a_hi | (a_lo0 + ko), b_hi | (b_lo1 + ko), p.idesc, acc);
-                    if (two_a) {
-                        umma_f16(tmem_base + nb * n, a_hi | (a_lo1 + ko), b_hi | (b_lo0 + ko), p.idesc, acc);
-                        if (two_b) umma_f16(tmem_base + (nb + 1) * n, a_hi | (a_lo1 + ko), b_hi | (b_lo1 + ko), p.idesc, acc);
-                    }
-                }
-            }
+                if (p.NAv == 2 && p.NBv == 2) {
+                    // 2x2 accumulators: K-block-major in snake order, so consecutive MMAs share one operand descriptor
+                    const uint32_t acc0 = (inited & 1u) ? 1u : 0u;
+                    uint32_t a0 = lbo_field | (sa4 + (uint32_t)p.kb0 * 16u), a1 = a0 + (uint32_t)p.npos_a;
+                    uint32_t b0 = lbo_field | (sb4 + (uint32_t)p.kb0 * 16u), b1 = b0 + (uint32_t)p.npos_b;
+                    umma_f16(tmem_base, a_hi | (uint64_t)a0, b_hi | (uint64_t)b0, p.idesc, acc0);
+                    umma_f16(tmem_base + n, a_hi | (uint64_t)a0, b_hi | (uint64_t)b1, p.idesc, acc0);
+                    umma_f16(tmem_base + 3 * n, a_hi | (uint64_t)a1, b_hi | (uint64_t)b1, p.idesc, acc0);
+                    umma_f16(tmem_base + 2 * n, a_hi | (uint64_t)a1, b_hi | (uint64_t)b0, p.idesc, acc0);
 #pragma unroll 4
-            for (int kb = p.kb0 + 1; kb < p.nkb; ++kb) {
-                const uint32_t ko = (uint32_t)kb * 16u;                  // 16 positions x 16 B, in 16-byte units
-                {
-                    umma_f16(tmem_base, a_hi | (a_lo0 + ko), b_hi | (b_lo0 + ko), p.idesc, 1u);
-                    if (two_b) umma_f16(tmem_base + n, a_hi | (a_lo0 + ko), b_hi | (b_lo1 + ko), p.idesc, 1u);
-                    if (two_a) {
-                        umma_f16(tmem_base + nb * n, a_hi | (a_lo1 + ko), b_hi | (b_lo0 + ko), p.idesc, 1u);
-                        if (two_b) umma_f16(tmem_base + (nb + 1) * n, a_hi | (a_lo1 + ko), b_hi | (b_lo1 + ko), p.idesc, 1u);
+                    for (int kb = p.kb0 + 1; kb < p.nkb; ++kb) {
+                        a0 += 16u; a1 += 16u; b0 += 16u; b1 += 16u;
+                        umma_f16(tmem_base, a_hi | (uint64_t)a0, b_hi | (uint64_t)b0, p.idesc, 1u);
+                        umma_f16(tmem_base + n, a_hi | (uint64_t)a0, b_hi | (uint64_t)b1, p.idesc, 1u);
+                        umma_f16(tmem_base + 3 * n, a_hi | (uint64_t)a1, b_hi | (uint64_t)b1, p.idesc, 1u);
+                        umma_f16(tmem_base + 2 * n, a_hi | (uint64_t)a1, b_hi | (uint64_t)b0, p.idesc, 1u);
+                    }
+                } else
+                // one accumulator set at a time, its K blocks back to back: the inner loop is two adds and one MMA
+                for (int av = 0; av < p.NAv; ++av) {
+                    if (!((it.amask >> av) & 1u)) continue;
+                    const uint32_t a_lo0 = lbo_field | (sa4 + (uint32_t)av * p.npos_a + (uint32_t)p.kb0 * 16u);
+                    const uint32_t acc0 = ((inited >> av) & 1u) ? 1u : 0u;
+                    for (int bv = 0; bv < p.NBv; ++bv) {
+                        const uint32_t d = tmem_base + ((uint32_t)av * nbv + bv) * n;
+                        uint32_t a_lo = a_lo0;
+                        uint32_t b_lo = lbo_field | (sb4 + (uint32_t)bv * p.npos_b + (uint32_t)p.kb0 * 16u);
+                        umma_f16(d, a_hi | (uint64_t)a_lo, b_hi | (uint64_t)b_lo, p.idesc, acc0);
+#pragma unroll 8
+                        for (int kb = p.kb0 + 1; kb < p.nkb; ++kb) {
+                            a_lo += 16u; b_lo += 16u;                    // next 16 positions (16-byte units)
+                            umma_f16(d, a_hi | (uint64_t)a_lo, b_hi | (uint64_t)b_lo, p.idesc, 1u);
+                        }
                     }
                 }
-            }
-            umma_commit(&empty_bar[stage]);
+                umma_commit(&empty_bar[stage]);
             }
             __syncwarp();
-            first = false;
-            if (++stage == kWgStages) { stage = 0; phase ^= 1; }
+            inited |= it.amask;
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
         if (elect_one()) umma_commit(&accum_bar);
         __syncwarp();
@@ -190,17 +216,19 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
         const int q = warp & 3;
         mbar_wait(&accum_bar, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        bool any = false;       // did the issuer touch the accumulators at all? (same walk as the other roles)
-        for (int pl = pbeg; pl < pend && !any; ++pl) {
-            int b; size_t ij_x, ij_g;
-            any = wg_pair(p, pl, t1, t2, b, ij_x, ij_g);
+        uint32_t live = 0;      // accumulator sets the issuer touched (same walk as the other roles)
+        for (int pl = pbeg; pl < pend; ++pl) {
+            WgItem it;
+            if (wg_item(p, pl, t1, t2, it)) live |= it.amask;
+            if (live == (1u << p.NAv) - 1u) break;
         }
-        if (any) {
+        if (live) {
             const int KS = p.KS;
             const size_t per_group = (size_t)p.Cin * KS * KS * KS * KS * p.cop;
             float *dst = p.part + ((size_t)s * p.G + g) * per_group;
             const int m = q * 16 + lane;           // M = 64: rows 16q..16q+15 sit in lanes 0..15 of quadrant q
-            for (int av = 0; av < p.NAv; ++av)
+            for (int av = 0; av < p.NAv; ++av) {
+                if (!((live >> av) & 1u)) continue;
                 for (int bv = 0; bv < p.NBv; ++bv)
                     for (int n0 = 0; n0 < p.N; n0 += 8) {
                         float v[8];
@@ -212,12 +240,13 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
                             const int n = n0 + u;
                             int o, c, t3, t4, tt2 = t2;
                             if (p.variant == 2) { t4 = sA; c = av * 8 + c8; t3 = KS - 1 - (n >> 3); o = bv * 8 + (n & 7); }
-                            else if (p.variant == 1) { t3 = sA; t4 = c8; c = 0; o = n; }
+                            else if (p.variant == 1) { t3 = sA; t4 = c8; c = 0; o = n; tt2 = av; }
                             else { t4 = sA; c = av * 8 + c8; t3 = KS - 1 - (n >> 3); tt2 = n & 7; o = 0; }
                             if (t3 < 0 || t3 >= KS || t4 >= KS || tt2 >= KS || c >= p.Cin || o >= p.Cout) continue;
                             dst[(((((size_t)c * KS + t1) * KS + tt2) * KS + t3) * KS + t4) * p.cop + o] = v[u];
                         }
                     }
+            }
         }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -263,7 +292,7 @@ cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int
 
 struct WgPlan {
     bool ok;
-    int variant, NAv, NBv, N, nb_copy, P, a_r0, b_r0, npos_a, npos_b, nkb, kb0, S, cop;
+    int variant, NAv, NBv, N, nb_copy, P, a_r0, b_r0, npos_a, npos_b, nkb, kb0, S, cop, stages;
     uint32_t a_sbo, b_sbo, a_bytes, stage_bytes, tmem_cols, b_start;
     size_t smem, part_bytes;
 };
@@ -280,10 +309,12 @@ static WgPlan wg_plan(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, 
     w.nkb = (plane_cb + 15) / 16;
     if (Cin == 1 && Cout > 1) {
         // A = X' (d4 taps in the channels of half 0), groups = d3 row shifts; B = G, the two halves are the N groups
-        w.variant = 1; w.NAv = 1; w.NBv = 1; w.N = 16; w.nb_copy = 2;
+        w.variant = 1; w.NAv = k; w.NBv = 1; w.N = 16; w.nb_copy = 2;       // A variants = the k planes j+t2-p
         w.a_sbo = (uint32_t)w.P * 16u;
         w.a_r0 = pad; w.b_r0 = 0; w.b_start = 0;
-        w.npos_a = w.nkb * 16 + 7 * w.P + 8;
+        // the three unused row-shift groups read up to 7 rows past a plane's buffer: into the next variant's buffer or
+        // the grad buffer behind it (finite data, discarded), so no per-buffer margin is reserved for them
+        w.npos_a = w.nkb * 16 + 8;
         if (w.npos_a < (pad + d3 + 2 * pad) * w.P) w.npos_a = (pad + d3 + 2 * pad) * w.P;
         w.npos_b = w.nkb * 16 + 8;
         w.cop = ((Cout + 3) / 4) * 4;
@@ -307,12 +338,14 @@ static WgPlan wg_plan(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, 
     w.a_bytes = (uint32_t)w.NAv * w.npos_a * 16u;
     const uint32_t b_bytes = (uint32_t)w.nb_copy * w.npos_b * 16u;
     w.stage_bytes = ((w.a_bytes + b_bytes + 127) / 128) * 128;
-    w.smem = (size_t)kWgStages * w.stage_bytes;
+    w.stages = kWgStages;
+    if ((size_t)w.stages * w.stage_bytes > 220 * 1024) w.stages = 2;
+    w.smem = (size_t)w.stages * w.stage_bytes;
     if (w.smem > 220 * 1024) return w;
     const int cols = w.NAv * w.NBv * w.N;
     w.tmem_cols = cols <= 32 ? 32 : (cols <= 64 ? 64 : (cols <= 128 ? 128 : (cols <= 256 ? 256 : 512)));
     // slices: enough CTAs for ~4 waves
-    const long long base = (long long)G * k * (w.variant == 3 ? 1 : k);
+    const long long base = (long long)G * k * (w.variant == 2 ? k : 1);
     const long long planes = (long long)B * d1 * d2;
     long long S = (4ll * kNumSMs + base - 1) / base;
     if (S > planes) S = planes;
@@ -380,11 +413,12 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     }
     a.npos_a = w.npos_a; a.npos_b = w.npos_b; a.S = w.S; a.Cin = Cin; a.Cout = Cout; a.cop = w.cop;
     a.tmem_cols = w.tmem_cols; a.stage_bytes = w.stage_bytes; a.a_bytes = w.a_bytes; a.b_start = w.b_start;
+    a.stages = w.stages;
     // D = f32, A = B = f16, both MN-major (bits 15/16), N>>3 at bit 17, M=64 -> 4 at bit 24
     a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
     e = cudaFuncSetAttribute(conv4d_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem);
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): smem attribute: %s", cudaGetErrorString(e));
-    dim3 grid(w.S, G * k * (w.variant == 3 ? 1 : k));
+    dim3 grid(w.S, G * k * (w.variant == 2 ? k : 1));
     conv4d_tc_wgrad_kernel<<<grid, kWgThreads, w.smem, st>>>(a);
     NC_LAUNCH_OK("conv4d_tc_wgrad_kernel");
     if (gy_dtype != NCNET_CB16)
