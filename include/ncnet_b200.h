@@ -107,6 +107,16 @@ int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t 
 int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, int nA, int nB, int in_groups,
                                       int dtype, void *stream);
 
+/* Weak-supervision matching score -- train.py:123-134 with normalization='softmax':
+ *   score = ( mean_{b,t} max_a softmax_a(corr[b,a,t]) + mean_{b,a} max_t softmax_t(corr[b,a,t]) ) / 2
+ * (the reference adds the two score vectors, which needs nA == nB; for nA != nB the two means are taken
+ * separately).  corr: [B,nA,nB].  keys: B*(nA+nB) uint64 and sums: B*(nA+nB) floats are outputs that the backward
+ * pass consumes; score: one float on the device.  _bwd: grad_corr = grad_score[0] * d(score)/d(corr). */
+int ncnet_match_score_fwd(const void *corr, uint64_t *keys, float *sums, float *score, int B, int nA, int nB,
+                          int dtype, void *stream);
+int ncnet_match_score_bwd(const void *corr, const uint64_t *keys, const float *sums, const float *grad_score,
+                          void *grad_corr, int B, int nA, int nB, int dtype, void *stream);
+
 /* conv4d / Conv4d.forward -- lib/conv4d.py:11-51,81-82  (+ fused ReLU, lib/model.py:137-138,
  * + the symmetric second branch of NeighConsensus.forward, lib/model.py:147).
  *

@@ -474,3 +474,167 @@ extern "C" int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, 
     if (dtype == NCNET_F16) return mm_fwd<__half>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, st);
     return fail("mutual_matching_fwd_noalloc: unsupported dtype %d", dtype);
 }
+
+// ---------------------------------------------------------------------------------------------
+// Weak-supervision matching score (reference train.py:123-134, normalization='softmax'), fused.
+//   score = ( mean_{b,t} max_a softmax_a(x[b,a,t]) + mean_{b,a} max_t softmax_t(x[b,a,t]) ) / 2
+// and max softmax = 1 / sum exp(x - max), so the score needs only the row/column maxima (pass 1 above) and the
+// row/column sums of exp(x - max): two reads of the volume instead of four soft-max temporaries, and the
+// gradient is one elementwise pass:  d/dx[a,t] = w_t * ([a = a*_t] - p_col) / S_t + w_a * ([t = t*_a] - p_row) / S_a.
+// ---------------------------------------------------------------------------------------------
+namespace ncnet {
+
+template <typename T>
+__global__ void __launch_bounds__(kMMThreads)
+score_sumexp_kernel(const T *__restrict__ x, const unsigned long long *__restrict__ keys, float *__restrict__ sums,
+                    int nA, int nB, int rows_per_block) {
+    const int b = blockIdx.z;
+    const int row0 = blockIdx.y * rows_per_block;
+    const int col0 = blockIdx.x * kMMBwdCols;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t mat = (size_t)nA * nB;
+    const T *xb = x + (size_t)b * mat;
+    const size_t kb = (size_t)b * (nA + nB);
+    float *rsum = sums + kb, *csum = rsum + nA;
+    float cmax[kMMBwdSlots], cacc[kMMBwdSlots];
+#pragma unroll
+    for (int s = 0; s < kMMBwdSlots; ++s) {
+        const int c = col0 + s * 32 + lane;
+        cmax[s] = c < nB ? key_val_hi(keys, kb + nA + c) : 0.f;
+        cacc[s] = 0.f;
+    }
+    const int row_end = min(row0 + rows_per_block, nA);
+    for (int a = row0 + warp; a < row_end; a += kMMThreads / 32) {
+        const float rmax = key_val_hi(keys, kb + a);
+        const size_t roff = (size_t)a * nB;
+        float v[kMMBwdSlots];
+#pragma unroll
+        for (int s = 0; s < kMMBwdSlots; ++s) {
+            const int c = col0 + s * 32 + lane;
+            v[s] = c < nB ? ldf(xb + roff + c) : -INFINITY;
+        }
+        float racc = 0.f;
+#pragma unroll
+        for (int s = 0; s < kMMBwdSlots; ++s) {
+            if (col0 + s * 32 + lane < nB) {
+                racc += expf(v[s] - rmax);
+                cacc[s] += expf(v[s] - cmax[s]);
+            }
+        }
+        racc = warp_sum(racc);
+        if (lane == 0) atomicAdd(rsum + a, racc);
+    }
+    __shared__ float sm[kMMThreads / 32][kMMBwdCols];
+#pragma unroll
+    for (int s = 0; s < kMMBwdSlots; ++s) sm[warp][s * 32 + lane] = cacc[s];
+    __syncthreads();
+    const int c = col0 + threadIdx.x;
+    if (c < nB) {
+        float t = 0.f;
+#pragma unroll
+        for (int w = 0; w < kMMThreads / 32; ++w) t += sm[w][threadIdx.x];
+        atomicAdd(csum + c, t);
+    }
+}
+
+// score = (sum_rows 1/S / (B*nA) + sum_cols 1/S / (B*nB)) / 2, one block, fixed summation order
+__global__ void __launch_bounds__(1024)
+score_reduce_kernel(const float *__restrict__ sums, float *__restrict__ score, int B, int nA, int nB) {
+    __shared__ double sm[32];
+    const int per = nA + nB;
+    const double wa = 0.5 / ((double)B * nA), wb = 0.5 / ((double)B * nB);
+    double acc = 0.0;
+    for (long long i = threadIdx.x; i < (long long)B * per; i += blockDim.x) {
+        const int r = (int)(i % per);
+        acc += (r < nA ? wa : wb) / (double)sums[i];
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += sm[w];
+        *score = (float)t;
+    }
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+score_bwd_kernel(const T *__restrict__ x, const unsigned long long *__restrict__ keys, const float *__restrict__ sums,
+                 const float *__restrict__ gscore, T *__restrict__ gx, int B, int nA, int nB) {
+    const int b = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c = blockIdx.x * 32 + lane;
+    const int a0 = (blockIdx.y * 8 + warp) * kMMApplyRows;
+    const size_t mat = (size_t)nA * nB;
+    const size_t kb = (size_t)b * (nA + nB);
+    const float g = __ldg(gscore);
+    const float wa = 0.5f * g / ((float)B * nA), wb = 0.5f * g / ((float)B * nB);
+    float cmax = 0.f, cinv = 0.f;
+    int carg = -1;
+    if (c < nB) {
+        const unsigned long long k = keys[kb + nA + c];
+        cmax = key_val(k); carg = (int)key_idx(k); cinv = 1.f / sums[kb + nA + c];
+    }
+    for (int r = 0; r < kMMApplyRows; ++r) {
+        const int a = a0 + r;
+        if (a >= nA) break;
+        const unsigned long long rk = keys[kb + a];
+        const float rmax = key_val(rk), rinv = 1.f / sums[kb + a];
+        const int rarg = (int)key_idx(rk);
+        if (c < nB) {
+            const size_t off = (size_t)b * mat + (size_t)a * nB + c;
+            const float v = ldf(x + off);
+            const float pc = expf(v - cmax) * cinv, pr = expf(v - rmax) * rinv;
+            const float d = wb * ((a == carg ? 1.f : 0.f) - pc) * cinv + wa * ((c == rarg ? 1.f : 0.f) - pr) * rinv;
+            stf(gx + off, d);
+        }
+    }
+}
+
+template <typename T>
+static int score_fwd(const void *x, uint64_t *keys, float *sums, float *score, int B, int nA, int nB, cudaStream_t st) {
+    int rc = mm_fwd_parts<T>(x, nullptr, keys, B, nA, nB, 1, 1, st);      // pass 1: maxima and first arg-maxima
+    if (rc) return rc;
+    cudaError_t e = cudaMemsetAsync(sums, 0, (size_t)B * (nA + nB) * sizeof(float), st);
+    NC_CHECK(e == cudaSuccess, "match_score: memset: %s", cudaGetErrorString(e));
+    const int rpb = rows_per_block_for(B, nA, nB, kMMBwdCols);
+    dim3 g1((nB + kMMBwdCols - 1) / kMMBwdCols, (nA + rpb - 1) / rpb, B);
+    score_sumexp_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (const unsigned long long *)keys, sums, nA, nB, rpb);
+    NC_LAUNCH_OK("score_sumexp_kernel");
+    score_reduce_kernel<<<1, 1024, 0, st>>>(sums, score, B, nA, nB);
+    NC_LAUNCH_OK("score_reduce_kernel");
+    return 0;
+}
+
+}  // namespace ncnet
+
+extern "C" int ncnet_match_score_fwd(const void *corr, uint64_t *keys, float *sums, float *score, int B, int nA, int nB,
+                                     int dtype, void *stream) {
+    NC_CHECK(corr && keys && sums && score, "match_score_fwd: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "match_score_fwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NCNET_F32) return score_fwd<float>(corr, keys, sums, score, B, nA, nB, st);
+    if (dtype == NCNET_F16) return score_fwd<__half>(corr, keys, sums, score, B, nA, nB, st);
+    return fail("match_score_fwd: unsupported dtype %d", dtype);
+}
+
+extern "C" int ncnet_match_score_bwd(const void *corr, const uint64_t *keys, const float *sums, const float *grad_score,
+                                     void *grad_corr, int B, int nA, int nB, int dtype, void *stream) {
+    NC_CHECK(corr && keys && sums && grad_score && grad_corr, "match_score_bwd: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "match_score_bwd: bad shape");
+    cudaStream_t st = (cudaStream_t)stream;
+    dim3 grid((nB + 31) / 32, (nA + 8 * kMMApplyRows - 1) / (8 * kMMApplyRows), B);
+    NC_CHECK(grid.y <= 65535, "match_score_bwd: too many rows");
+    if (dtype == NCNET_F32)
+        score_bwd_kernel<float><<<grid, 256, 0, st>>>((const float *)corr, (const unsigned long long *)keys, sums, grad_score,
+                                                      (float *)grad_corr, B, nA, nB);
+    else if (dtype == NCNET_F16)
+        score_bwd_kernel<__half><<<grid, 256, 0, st>>>((const __half *)corr, (const unsigned long long *)keys, sums, grad_score,
+                                                       (__half *)grad_corr, B, nA, nB);
+    else
+        return fail("match_score_bwd: unsupported dtype %d", dtype);
+    NC_LAUNCH_OK("score_bwd_kernel");
+    return 0;
+}

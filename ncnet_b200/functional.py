@@ -184,6 +184,46 @@ def mutual_matching(corr4d: torch.Tensor, sum_branches: bool = False) -> torch.T
     return _MutualMatchingFn.apply(corr4d)
 
 
+class _MatchScoreFn(torch.autograd.Function):
+    """Soft-max matching score of the weak loss (reference train.py:123-134), fused: maxima, sums of exponentials,
+    one reduction; the backward pass is one elementwise kernel."""
+
+    @staticmethod
+    def forward(ctx, corr4d):
+        b, _, f1, f2, f3, f4 = corr4d.shape
+        x = corr4d.contiguous()
+        na, nb = f1 * f2, f3 * f4
+        keys = torch.empty(b * (na + nb), device=x.device, dtype=torch.int64)
+        sums = torch.empty(b * (na + nb), device=x.device, dtype=torch.float32)
+        score = torch.empty((), device=x.device, dtype=torch.float32)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().ncnet_match_score_fwd(_ptr(x), _ptr(keys), _ptr(sums), _ptr(score), b, na, nb, _dt(x),
+                                                          _stream()), "match_score_fwd")
+        _count(3)
+        ctx.save_for_backward(x, keys, sums)
+        return score.to(x.dtype)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, keys, sums = ctx.saved_tensors
+        b, _, f1, f2, f3, f4 = x.shape
+        gs = g.detach().reshape(1).float().contiguous()
+        gx = torch.empty_like(x)
+        with torch.cuda.device(x.device):
+            _cabi.check(_cabi.lib().ncnet_match_score_bwd(_ptr(x), _ptr(keys), _ptr(sums), _ptr(gs), _ptr(gx), b, f1 * f2,
+                                                          f3 * f4, _dt(x), _stream()), "match_score_bwd")
+        _count(1)
+        return gx
+
+
+def match_score_softmax(corr4d: torch.Tensor) -> torch.Tensor:
+    """mean(max softmax over A + max softmax over B) / 2 of a [B,1,fs1,fs2,fs3,fs4] volume (train.py:123-134)."""
+    _need_cuda(corr4d)
+    if corr4d.dim() != 6 or corr4d.shape[1] != 1:
+        raise RuntimeError(f"match_score: expected [B,1,fs1,fs2,fs3,fs4], got {tuple(corr4d.shape)}")
+    return _MatchScoreFn.apply(corr4d)
+
+
 # ------------------------------------------------------------------------------------------- #
 # Conv4d / NeighConsensus
 # ------------------------------------------------------------------------------------------- #

@@ -1,6 +1,6 @@
 """Weak-supervision loss of the reference's training script (train.py:110-156), restated so that
-``train.py``'s step can be driven on the new head.  The soft-max/max score itself is still
-composed from PyTorch reductions here; SURVEY.md §8(f1) lists its fusion as the next row."""
+``train.py``'s step can be driven on the new head.  For CUDA volumes with the default soft-max normalisation the
+score runs on the fused kernels (ncnet_match_score_fwd/bwd); the other normalisations use PyTorch reductions."""
 from __future__ import annotations
 
 import numpy as np
@@ -9,6 +9,9 @@ import torch
 
 def match_score(corr4d: torch.Tensor, normalization="softmax") -> torch.Tensor:
     """mean over cells of (max over A of norm_A(x) + max over B of norm_B(x)) / 2  (train.py:123-134)."""
+    if normalization == "softmax" and corr4d.is_cuda and corr4d.dim() == 6 and corr4d.shape[1] == 1:
+        from .functional import match_score_softmax
+        return match_score_softmax(corr4d)            # fused kernels (SURVEY.md §8 f1)
     b = corr4d.size(0)
     f1, f2, f3, f4 = corr4d.shape[2:]
     nc_b_avec = corr4d.view(b, f1 * f2, f3, f4)

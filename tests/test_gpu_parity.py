@@ -330,3 +330,19 @@ def test_error_paths(nb, cuda):
         nb.MutualMatching(torch.rand(1, 3, 4, 4, 4, 4, device=cuda))
     with pytest.raises(TypeError):
         nb.MutualMatching(torch.rand(1, 1, 4, 4, 4, 4, device=cuda).double())
+
+
+@pytest.mark.parametrize("shape", [(2, 1, 6, 5, 6, 5), (3, 1, 25, 25, 25, 25), (1, 1, 7, 9, 8, 4)])
+def test_fused_match_score_vs_oracle(nb, cuda, shape):
+    """ncnet_match_score_fwd/bwd against the oracle's soft-max score (train.py:123-134) and its autograd."""
+    from ncnet_b200.functional import match_score_softmax
+    torch.manual_seed(13)
+    x = torch.rand(*shape) * 3
+    xo = x.double().requires_grad_(True)
+    so = O.match_score(xo, "softmax")
+    (go,) = torch.autograd.grad(so, xo)
+    xg = x.to(cuda).requires_grad_(True)
+    sg = match_score_softmax(xg)
+    (gg,) = torch.autograd.grad(sg * 2.5, xg)
+    assert abs(float(sg) - float(so)) < 1e-6 * max(1.0, abs(float(so)))
+    assert nerr(gg, go * 2.5) < 1e-4
