@@ -32,7 +32,7 @@
 namespace ncnet {
 
 constexpr int kTcThreads = 192;
-constexpr int kStages = 3;
+constexpr int kStages = 4;         // ring depth limit (the planner picks 2..4)
 constexpr int kMaxGroups = 32;      // column groups (taps folded into N)
 constexpr int kMaxKSteps = 5;
 constexpr int kOutStride = 20;      // floats per outbuf row (16 channels + pad: conflict-free float4 access)
@@ -58,9 +58,86 @@ struct TcArgs {
     int gshift[kMaxGroups]; // epilogue row shift per column group
     uint32_t stage_bytes, data_bytes, w_bytes;
     long long *dbg;         // development only: per-CTA phase timestamps (8 per CTA) or null
+    int dbg_mode;           // development only: 1 = no weight copies, 2 = no MMAs, 3 = no activation copies (results wrong)
 };
 
 using namespace tc;
+
+// MMA issue loop of one CTA.  NT_C / KS_C > 0: compile-time tile and K-step counts (straight-line issue);
+// 0: run-time counts from the arguments.
+template <int NT_C, int KS_C>
+__device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t *stage0, uint64_t *full_bar, uint64_t *empty_bar,
+                                         uint32_t tmem_base, long long t_start) {
+    constexpr int NTM = NT_C > 0 ? NT_C : 1, KSM = KS_C > 0 ? KS_C : 1;
+    const int NT = NT_C > 0 ? NT_C : p.NT, KSTEPS = KS_C > 0 ? KS_C : p.KSTEPS;
+    const int PAD = p.KS / 2;
+    int stage = 0;
+    uint32_t phase = 0;
+    bool first = true;
+    const uint32_t lbo_a_field = (uint32_t)p.npos_pad << 16, lbo_b_field = (uint32_t)p.N << 16;   // LBO in 16-byte units
+    const uint32_t hi = (128u >> 4) | (1u << 14);                                                 // SBO = 128 B, descriptor version 1
+    const uint32_t b_step = 2u * (uint32_t)p.N;                                                   // 16-byte units per K-step of weights
+    const uint32_t sm4 = smem_u32(stage0) >> 4, stage4 = p.stage_bytes >> 4, data4 = p.data_bytes >> 4;
+    // low descriptor words relative to the stage base: A of (K-step, tile), B of K-step
+    uint32_t a_rel[KSM][NTM], b_rel[KSM], d_col[NTM];
+#pragma unroll
+    for (int ks = 0; ks < KSM; ++ks) {
+        b_rel[ks] = lbo_b_field | (data4 + (uint32_t)ks * b_step);
+#pragma unroll
+        for (int t = 0; t < NTM; ++t) a_rel[ks][t] = lbo_a_field | ((uint32_t)p.aoff[ks] + (uint32_t)t * 128u);
+    }
+#pragma unroll
+    for (int t = 0; t < NTM; ++t) d_col[t] = tmem_base + (uint32_t)(t * p.N);
+    for (int t1 = 0; t1 < p.KS; ++t1) {
+        const int ii = i + t1 - PAD;
+        if (ii < 0 || ii >= p.d1) continue;
+        for (int t2 = 0; t2 < p.KS; ++t2) {
+            const int jj = j + t2 - PAD;
+            if (jj < 0 || jj >= p.d2) continue;
+            mbar_wait(&full_bar[stage], phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (elect_one()) {
+                if (first && p.dbg && blockIdx.x < 3990) p.dbg[blockIdx.x * 8 + 0] = clock64() - t_start;
+                if (p.dbg && blockIdx.x == 2000) p.dbg[32100 + t1 * 5 + t2] = clock64() - t_start;
+                const uint32_t s4 = sm4 + (uint32_t)stage * stage4;      // the address field never carries into LBO (smem < 256 KB)
+                if (NT_C == 0) {
+                    // run-time counts (any NT): descriptor words computed on the fly
+                    for (int ks = 0; ks < KSTEPS; ++ks) {
+                        const uint64_t bdesc = ((uint64_t)hi << 32) | (uint64_t)((lbo_b_field | (data4 + (uint32_t)ks * b_step)) + s4);
+                        const uint32_t a0 = (lbo_a_field | (uint32_t)p.aoff[ks]) + s4;
+                        const uint32_t acc = (first && ks == 0) ? 0u : 1u;
+                        for (int t = 0; t < NT; ++t)
+                            if (p.dbg_mode != 2)
+                                umma_f16(tmem_base + (uint32_t)(t * p.N), ((uint64_t)hi << 32) | (uint64_t)(a0 + (uint32_t)t * 128u), bdesc, p.idesc, acc);
+                    }
+                } else if (first) {
+#pragma unroll
+                    for (int ks = 0; ks < KSM; ++ks) {
+                        const uint64_t bdesc = ((uint64_t)hi << 32) | (uint64_t)(b_rel[ks] + s4);
+#pragma unroll
+                        for (int t = 0; t < NTM; ++t)
+                            if (p.dbg_mode != 2)
+                                umma_f16(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, ks == 0 ? 0u : 1u);
+                    }
+                } else {
+#pragma unroll
+                    for (int ks = 0; ks < KSM; ++ks) {
+                        const uint64_t bdesc = ((uint64_t)hi << 32) | (uint64_t)(b_rel[ks] + s4);
+#pragma unroll
+                        for (int t = 0; t < NTM; ++t)
+                            if (p.dbg_mode != 2)
+                                umma_f16(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, 1u);
+                    }
+                }
+                umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
+                if (p.dbg && blockIdx.x == 2000) p.dbg[32200 + t1 * 5 + t2] = clock64() - t_start;
+            }
+            __syncwarp();
+            first = false;
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+    }
+}
 
 __global__ void __launch_bounds__(kTcThreads, 2)
 conv4d_tc_kernel(const TcArgs p) {
@@ -84,7 +161,10 @@ conv4d_tc_kernel(const TcArgs p) {
     const size_t ij_count = (size_t)p.d1 * p.d2;
 
     uint8_t *stage0 = smem;
-    float *outbuf = reinterpret_cast<float *>(smem + (size_t)p.stages * p.stage_bytes);
+    // The epilogue's output plane ALIASES the stage ring: it is first touched after accum_bar, i.e. after every
+    // staged byte has been consumed, which leaves the whole budget to stages in flight (the main loop is bound by
+    // bulk-copy latency x bytes in flight, not by the tensor pipe).
+    float *outbuf = reinterpret_cast<float *>(smem);
     const int out_rows = p.NT * 128;
 
     // ---- one-time setup -------------------------------------------------------------------
@@ -109,16 +189,6 @@ conv4d_tc_kernel(const TcArgs p) {
             const int half = r / tail, pos = copied + (r - half * tail);
             reinterpret_cast<uint4 *>(stage0 + (size_t)s * p.stage_bytes)[(size_t)half * p.npos_pad + pos] = z;
         }
-        // outbuf starts at the bias
-        if (p.CoutPad >= 16) {
-            for (int e = threadIdx.x; e < out_rows * kOutStride; e += kTcThreads) {
-                const int o = e % kOutStride;
-                outbuf[e] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
-            }
-        } else {
-            const float b0 = p.bias ? __ldg(p.bias) : 0.f;
-            for (int e = threadIdx.x; e < 4 * out_rows; e += kTcThreads) outbuf[e] = e < out_rows ? b0 : 0.f;
-        }
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // generic-proxy zeros -> visible to TMA/UMMA
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -126,17 +196,30 @@ conv4d_tc_kernel(const TcArgs p) {
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
     const long long t_start = clock64();
-#define TC_STAMP(slot) do { if (p.dbg && blockIdx.x < 4096) p.dbg[blockIdx.x * 8 + (slot)] = clock64() - t_start; } while (0)
+#define TC_STAMP(slot) do { if (p.dbg && blockIdx.x < 3990) p.dbg[blockIdx.x * 8 + (slot)] = clock64() - t_start; } while (0)
+    if (p.dbg && blockIdx.x < 3990 && threadIdx.x == 0) {
+        uint32_t smid;
+        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+        p.dbg[blockIdx.x * 8 + 5] = t_start;
+        p.dbg[blockIdx.x * 8 + 6] = smid;
+    }
 
     if (warp == 0) {
-        // ===== producer =====
+        // ===== producer =====  (a lone lane runs ~10 cycles per instruction: everything loop-invariant is hoisted)
         int stage = 0;
         uint32_t phase = 0;
         // the chunk's input rows (haloed coordinates k0 .. k0+R+KS-2), clipped to the plane
         const int rows_in = min(p.R + p.KS - 1, rows_pad - k0);
         const uint32_t half_bytes = (uint32_t)rows_in * p.P * 16u;
-        const uint32_t tx_bytes = 2u * half_bytes + p.w_bytes;
+        const uint32_t tx_bytes = (p.dbg_mode == 3 ? 0u : 2u * half_bytes) + (p.dbg_mode == 1 ? 0u : p.w_bytes);
         const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
+        const size_t plane_halves = plane_cb * 8;
+        const __half *src_base = p.act + (bg * 2 * ij_count * plane_cb + (size_t)k0 * p.P) * 8;
+        const size_t half_off = ij_count * plane_halves;
+        const uint32_t w_halves = p.w_bytes / 2;
+        const __half *w_base = p.wp + (size_t)g * p.KS * p.KS * w_halves;
+        const uint32_t sm0 = smem_u32(stage0), full0 = smem_u32(&full_bar[0]);
+        const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
             if (ii < 0 || ii >= p.d1) continue;
@@ -145,14 +228,15 @@ conv4d_tc_kernel(const TcArgs p) {
                 if (jj < 0 || jj >= p.d2) continue;
                 mbar_wait(&empty_bar[stage], phase ^ 1);
                 if (elect_one()) {
-                    uint8_t *sb = stage0 + (size_t)stage * p.stage_bytes;
-                    mbar_expect_tx(&full_bar[stage], tx_bytes);
-                    const __half *src0 = p.act + (((bg * 2 + 0) * ij_count + (size_t)ii * p.d2 + jj) * plane_cb + (size_t)k0 * p.P) * 8;
-                    const __half *src1 = src0 + ij_count * plane_cb * 8;
-                    bulk_g2s(sb, src0, half_bytes, &full_bar[stage]);
-                    bulk_g2s(sb + (size_t)p.npos_pad * 16, src1, half_bytes, &full_bar[stage]);
-                    const __half *wsrc = p.wp + ((size_t)g * p.KS * p.KS + (size_t)t1 * p.KS + t2) * (p.w_bytes / 2);
-                    bulk_g2s(sb + p.data_bytes, wsrc, p.w_bytes, &full_bar[stage]);
+                    if (p.dbg && blockIdx.x == 2000) p.dbg[32000 + t1 * 5 + t2] = clock64() - t_start;
+                    const uint32_t sb = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(tx_bytes) : "memory");
+                    const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves;
+                    if (p.dbg_mode != 3) {
+                        bulk_g2s_u32(sb, src0, half_bytes, fb);
+                        bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
+                    }
+                    if (p.dbg_mode != 1) bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.KS + t2) * w_halves, p.w_bytes, fb);
                 }
                 __syncwarp();
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -160,50 +244,17 @@ conv4d_tc_kernel(const TcArgs p) {
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
-        int stage = 0;
-        uint32_t phase = 0;
-        bool first = true;
-        const uint32_t lbo_a = (uint32_t)p.npos_pad * 16u;
-        const uint32_t lbo_b = (uint32_t)p.N * 16u;
-        const uint32_t lbo_a_field = (lbo_a >> 4) << 16, lbo_b_field = (lbo_b >> 4) << 16;
-        const uint64_t desc_hi = ((uint64_t)((128u >> 4) | (1u << 14))) << 32;      // SBO = 128 B, descriptor version 1
-        for (int t1 = 0; t1 < p.KS; ++t1) {
-            const int ii = i + t1 - PAD;
-            if (ii < 0 || ii >= p.d1) continue;
-            for (int t2 = 0; t2 < p.KS; ++t2) {
-                const int jj = j + t2 - PAD;
-                if (jj < 0 || jj >= p.d2) continue;
-                mbar_wait(&full_bar[stage], phase);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                if (elect_one()) {
-                    if (first) TC_STAMP(0);
-                    // only the low descriptor word changes from MMA to MMA
-                    const uint32_t sa4 = smem_u32(stage0 + (size_t)stage * p.stage_bytes) >> 4;
-                    const uint32_t sw4 = sa4 + (p.data_bytes >> 4);
-#pragma unroll
-                    for (int ks = 0; ks < kMaxKSteps; ++ks) {
-                        if (ks < p.KSTEPS) {
-                            const uint64_t bdesc = desc_hi | (uint64_t)(lbo_b_field | (sw4 + (uint32_t)ks * 2u * (lbo_b >> 4)));
-                            const uint32_t a_lo0 = lbo_a_field | (sa4 + (uint32_t)p.aoff[ks]);
-                            const uint32_t acc = (first && ks == 0) ? 0u : 1u;
-                            for (int t0 = 0; t0 < p.NT; t0 += 8) {
-#pragma unroll
-                                for (int u = 0; u < 8; ++u) {
-                                    const int t = t0 + u;
-                                    if (t < p.NT)
-                                        umma_f16(tmem_base + (uint32_t)(t * p.N), desc_hi | (uint64_t)(a_lo0 + (uint32_t)t * 128u),
-                                                 bdesc, p.idesc, acc);
-                                }
-                            }
-                        }
-                    }
-                    umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
-                }
-                __syncwarp();
-                first = false;
-                if (++stage == p.stages) { stage = 0; phase ^= 1; }
-            }
-        }
+        // One lane issues every tcgen05.mma; it manages ~1 instruction per 10 cycles, while the tensor pipe can
+        // retire an M128xN80xK16 MMA every 52 cycles.  The hot shapes therefore get a fully unrolled issue body
+        // with the per-MMA descriptor offsets precomputed (one add per MMA); other shapes use the generic loop.
+        bool done = false;
+#define NC_TC_CASE(NT_, KS_) \
+        if (!done && p.NT == NT_ && p.KSTEPS == KS_) { mma_main<NT_, KS_>(p, i, j, stage0, full_bar, empty_bar, tmem_base, t_start); done = true; }
+        NC_TC_CASE(3, 5) NC_TC_CASE(6, 5) NC_TC_CASE(2, 5) NC_TC_CASE(4, 5)
+        NC_TC_CASE(1, 1) NC_TC_CASE(2, 1) NC_TC_CASE(3, 1) NC_TC_CASE(4, 1) NC_TC_CASE(5, 1) NC_TC_CASE(6, 1) NC_TC_CASE(7, 1) NC_TC_CASE(8, 1)
+        NC_TC_CASE(3, 3) NC_TC_CASE(4, 3) NC_TC_CASE(2, 3)
+#undef NC_TC_CASE
+        if (!done) mma_main<0, 0>(p, i, j, stage0, full_bar, empty_bar, tmem_base, t_start);
         if (elect_one()) { TC_STAMP(1); umma_commit(&accum_bar); }
         __syncwarp();
     } else {
@@ -213,6 +264,17 @@ conv4d_tc_kernel(const TcArgs p) {
         mbar_wait(&accum_bar, 0);
         if (et == 0) TC_STAMP(2);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // outbuf starts at the bias (the ring it aliases is idle from here on)
+        if (p.CoutPad >= 16) {
+            for (int e = et; e < out_rows * kOutStride; e += 128) {
+                const int o = e % kOutStride;
+                outbuf[e] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
+            }
+        } else {
+            const float b0 = p.bias ? __ldg(p.bias) : 0.f;
+            for (int e = et; e < 4 * out_rows; e += 128) outbuf[e] = e < out_rows ? b0 : 0.f;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");
         if (p.CoutPad >= 16) {
             // column group gi = 16 out-channels of one folded tap: out[m - shift_gi][o] += D[m][gi*16 + o].
             // Within a group every thread owns a distinct row; groups are separated by a barrier.
@@ -492,6 +554,7 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
 // host side
 // ---------------------------------------------------------------------------------------------
 long long *g_tc_debug_buffer = nullptr;     // set through ncnet_debug_set_tc_timing (development only)
+int g_tc_debug_mode = 0;
 
 struct TcPlan {
     int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages;
@@ -529,7 +592,8 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
         const uint32_t data = 2u * npos * 16u;
         const uint32_t stage = ((data + o.w_bytes + 127) / 128) * 128;
         const size_t outb = o.CoutPad >= 16 ? (size_t)NT * 128 * kOutStride * sizeof(float) : (size_t)NT * 128 * 4 * sizeof(float);
-        const size_t smem = (size_t)stages * stage + outb;
+        size_t smem = (size_t)stages * stage;
+        if (smem < outb) smem = outb;                        // the output plane aliases the ring
         if (smem > max_smem) return false;
         o.R = R; o.NT = NT; o.npos_pad = npos; o.data_bytes = data; o.stage_bytes = stage; o.smem_bytes = smem;
         o.stages = stages;
@@ -546,12 +610,24 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
         }
         return false;
     };
-    // prefer two CTAs per SM unless that costs more than ~1.6x the plane chunks of the one-CTA plan
-    TcPlan one = pl;
-    bool ok1 = false;
-    { TcPlan keep = pl; ok1 = search(kStages, 512, 220 * 1024); one = pl; pl = keep; }
-    const bool ok2 = search(2, 256, 108 * 1024);
-    if (ok2 && (!ok1 || pl.nchunks <= 2 * one.nchunks)) { pl.ok = true; return pl; }
+    // For a budget, take the fewest plane chunks and then the deepest ring that still fits.
+    auto best = [&](int max_cols, size_t max_smem, TcPlan &out) {
+        bool found = false;
+        const TcPlan keep = pl;
+        for (int stages = 2; stages <= kStages; ++stages) {
+            pl = keep;
+            if (!search(stages, max_cols, max_smem)) continue;
+            if (!found || pl.nchunks <= out.nchunks) { out = pl; found = true; }
+        }
+        pl = keep;
+        return found;
+    };
+    // prefer two CTAs per SM (one's epilogue/prologue overlaps the other's main loop) unless that costs more than
+    // twice the plane chunks of the one-CTA plan
+    TcPlan one = pl, two = pl;
+    const bool ok1 = best(512, 220 * 1024, one);
+    const bool ok2 = best(256, 108 * 1024, two);
+    if (ok2 && (!ok1 || two.nchunks <= 2 * one.nchunks)) { two.ok = true; return two; }
     if (ok1) { one.ok = true; return one; }
     return pl;
 }
@@ -608,6 +684,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     a.mask_mode = !mask ? 0 : (mask_dtype == NCNET_CB16 ? 3 : (mask_dtype == NCNET_F16 ? 2 : 1));
     a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes;
     a.dbg = g_tc_debug_buffer;
+    a.dbg_mode = g_tc_debug_mode;
     // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
     a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const int pad = d.k / 2;
@@ -656,3 +733,4 @@ int conv4d_tc_dgrad(const void *gy, int gy_dtype, const float *w, const void *ma
 
 // development hook (not part of include/ncnet_b200.h): device buffer of 4096*8 int64 phase timestamps
 extern "C" void ncnet_debug_set_tc_timing(void *device_buffer) { ncnet::g_tc_debug_buffer = (long long *)device_buffer; }
+extern "C" void ncnet_debug_set_tc_mode(int mode) { ncnet::g_tc_debug_mode = mode; }

@@ -47,6 +47,10 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
 }
+__device__ __forceinline__ void bulk_g2s_u32(uint32_t dst, const void *src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
 // 5-D tensor tile global -> shared (SASS: UTMALDG); out-of-bounds elements arrive as zeros
 __device__ __forceinline__ void tma_tile_5d(void *dst, const CUtensorMap *map, int c0, int c1, int c2, int c3, int c4,
                                             uint64_t *bar) {
