@@ -88,17 +88,15 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
     }
 #pragma unroll
     for (int t = 0; t < NTM; ++t) d_col[t] = tmem_base + (uint32_t)(t * p.N);
-    for (int t1 = 0; t1 < p.KS; ++t1) {
-        const int ii = i + t1 - PAD;
-        if (ii < 0 || ii >= p.d1) continue;
-        for (int t2 = 0; t2 < p.KS; ++t2) {
-            const int jj = j + t2 - PAD;
-            if (jj < 0 || jj >= p.d2) continue;
-            mbar_wait(&full_bar[stage], phase);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            if (elect_one()) {
+    // staged (d1,d2) planes of this CTA (the producer skips the out-of-range ones the same way)
+    const int nplanes = (min(i + PAD, p.d1 - 1) - max(i - PAD, 0) + 1) * (min(j + PAD, p.d2 - 1) - max(j - PAD, 0) + 1);
+    const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+    if (elect_one()) {                      // one lane runs the whole loop: no per-stage election / reconvergence
+        for (int it = 0; it < nplanes; ++it) {
+            {
+                mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 if (first && p.dbg && blockIdx.x < 3990) p.dbg[blockIdx.x * 8 + 0] = clock64() - t_start;
-                if (p.dbg && blockIdx.x == 2000) p.dbg[32100 + t1 * 5 + t2] = clock64() - t_start;
                 const uint32_t s4 = sm4 + (uint32_t)stage * stage4;      // the address field never carries into LBO (smem < 256 KB)
                 if (NT_C == 0) {
                     // run-time counts (any NT): descriptor words computed on the fly
@@ -129,14 +127,15 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
                                 umma_f16(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, 1u);
                     }
                 }
-                umma_commit(&empty_bar[stage]);     // frees the smem slot when these MMAs have read it
-                if (p.dbg && blockIdx.x == 2000) p.dbg[32200 + t1 * 5 + t2] = clock64() - t_start;
+                // frees the smem slot when these MMAs have read it
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                             ::"r"(empty0 + (uint32_t)stage * 8u) : "memory");
             }
-            __syncwarp();
             first = false;
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
     }
+    __syncwarp();
 }
 
 __global__ void __launch_bounds__(kTcThreads, 2)
@@ -220,15 +219,16 @@ conv4d_tc_kernel(const TcArgs p) {
         const __half *w_base = p.wp + (size_t)g * p.KS * p.KS * w_halves;
         const uint32_t sm0 = smem_u32(stage0), full0 = smem_u32(&full_bar[0]);
         const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
+        const uint32_t empty0 = smem_u32(&empty_bar[0]);
+        if (elect_one()) {
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
             if (ii < 0 || ii >= p.d1) continue;
             for (int t2 = 0; t2 < p.KS; ++t2) {
                 const int jj = j + t2 - PAD;
                 if (jj < 0 || jj >= p.d2) continue;
-                mbar_wait(&empty_bar[stage], phase ^ 1);
-                if (elect_one()) {
-                    if (p.dbg && blockIdx.x == 2000) p.dbg[32000 + t1 * 5 + t2] = clock64() - t_start;
+                mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
+                {
                     const uint32_t sb = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
                     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(tx_bytes) : "memory");
                     const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves;
@@ -238,10 +238,11 @@ conv4d_tc_kernel(const TcArgs p) {
                     }
                     if (p.dbg_mode != 1) bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.KS + t2) * w_halves, p.w_bytes, fb);
                 }
-                __syncwarp();
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
+        }
+        __syncwarp();
     } else if (warp == 1) {
         // ===== MMA issuer =====
         // One lane issues every tcgen05.mma; it manages ~1 instruction per 10 cycles, while the tensor pipe can
@@ -264,41 +265,59 @@ conv4d_tc_kernel(const TcArgs p) {
         mbar_wait(&accum_bar, 0);
         if (et == 0) TC_STAMP(2);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        // outbuf starts at the bias (the ring it aliases is idle from here on)
         if (p.CoutPad >= 16) {
-            for (int e = et; e < out_rows * kOutStride; e += 128) {
-                const int o = e % kOutStride;
-                outbuf[e] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
-            }
-        } else {
-            const float b0 = p.bias ? __ldg(p.bias) : 0.f;
-            for (int e = et; e < 4 * out_rows; e += 128) outbuf[e] = e < out_rows ? b0 : 0.f;
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (p.CoutPad >= 16) {
-            // column group gi = 16 out-channels of one folded tap: out[m - shift_gi][o] += D[m][gi*16 + o].
-            // Within a group every thread owns a distinct row; groups are separated by a barrier.
-            for (int t = 0; t < p.NT; ++t) {
-                const int m = t * 128 + q * 32 + lane;
-                for (int gi = 0; gi < p.NG; ++gi) {
-                    float v[16];
-                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.N + gi * 16), v);
-                    const int dest = m - s_gshift[gi];
-                    if (dest >= 0) {
-                        float4 *dst = reinterpret_cast<float4 *>(outbuf + (size_t)dest * kOutStride);
+            // column group gi = 16 out-channels of one folded tap: out[m - shift_gi][o] += D[m][gi*16 + o].  The output
+            // plane aliases the (now idle) ring.  Group 0 has shift 0 and touches every row: it WRITES bias + D, so
+            // no initialisation pass is needed; the other groups accumulate.  Within a group every thread owns
+            // distinct rows (all tiles), so one barrier per group orders the read-modify-writes; the TMEM loads of
+            // two tiles are in flight together.
+            float bv[16];
 #pragma unroll
-                        for (int w4 = 0; w4 < 4; ++w4) {
-                            float4 a = dst[w4];
-                            a.x += v[4 * w4 + 0]; a.y += v[4 * w4 + 1]; a.z += v[4 * w4 + 2]; a.w += v[4 * w4 + 3];
-                            dst[w4] = a;
+            for (int o = 0; o < 16; ++o) bv[o] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
+            const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+            for (int gi = 0; gi < p.NG; ++gi) {
+                const int sh = s_gshift[gi];
+                for (int t = 0; t < p.NT; t += 2) {
+                    const bool two = t + 1 < p.NT;
+                    uint32_t r0[16], r1[16];
+                    tmem_ld16_issue(lane_base + (uint32_t)(t * p.N + gi * 16), r0);
+                    if (two) tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N + gi * 16), r1);
+                    tmem_ld16_wait(r0);
+                    if (two) tmem_ld16_wait(r1);
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        if (h == 1 && !two) break;
+                        const uint32_t(&r)[16] = h ? r1 : r0;
+                        const int dest = (t + h) * 128 + q * 32 + lane - sh;
+                        if (dest >= 0) {
+                            float4 *dst = reinterpret_cast<float4 *>(outbuf + (size_t)dest * kOutStride);
+                            if (gi == 0) {
+#pragma unroll
+                                for (int w4 = 0; w4 < 4; ++w4)
+                                    dst[w4] = make_float4(bv[4 * w4 + 0] + __uint_as_float(r[4 * w4 + 0]), bv[4 * w4 + 1] + __uint_as_float(r[4 * w4 + 1]),
+                                                          bv[4 * w4 + 2] + __uint_as_float(r[4 * w4 + 2]), bv[4 * w4 + 3] + __uint_as_float(r[4 * w4 + 3]));
+                            } else {
+#pragma unroll
+                                for (int w4 = 0; w4 < 4; ++w4) {
+                                    float4 a = dst[w4];
+                                    a.x += __uint_as_float(r[4 * w4 + 0]); a.y += __uint_as_float(r[4 * w4 + 1]);
+                                    a.z += __uint_as_float(r[4 * w4 + 2]); a.w += __uint_as_float(r[4 * w4 + 3]);
+                                    dst[w4] = a;
+                                }
+                            }
                         }
                     }
-                    asm volatile("bar.sync 1, 128;" ::: "memory");
                 }
+                asm volatile("bar.sync 1, 128;" ::: "memory");
             }
         } else {
             // single out-channel: one column per folded (d3,d4) tap.  Each warp accumulates into its
             // own copy of the plane (stride 1), so no cross-warp ordering is needed; the store sums them.
+            {
+                const float b0 = p.bias ? __ldg(p.bias) : 0.f;
+                for (int e = et; e < 4 * out_rows; e += 128) outbuf[e] = e < out_rows ? b0 : 0.f;
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+            }
             float *mine = outbuf + (size_t)q * out_rows;
             for (int t = 0; t < p.NT; ++t) {
                 const int m = t * 128 + q * 32 + lane;
