@@ -290,6 +290,11 @@ cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int
     }
 }
 
+// conv4d_tc_wgrad_pm.cu: full-size tiles for layers with more than 8 channels on both sides
+bool conv4d_tc_wgrad_pm_supported(int d3, int d4, int k);
+int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, float *part, void *pm_scratch, int B, int G, int GxA,
+                           int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int S, int cop, cudaStream_t st);
+
 struct WgPlan {
     bool ok;
     int variant, NAv, NBv, N, nb_copy, P, a_r0, b_r0, npos_a, npos_b, nkb, kb0, S, cop, stages;
@@ -360,8 +365,11 @@ size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, i
     const int G = symmetric ? 2 : 1;
     const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G);
     if (!w.ok) return 0;
-    // CB16 copies of planar operands (worst case both) + the per-slice partial sums
-    return 2 * wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k)) + w.part_bytes + 1024;
+    // CB16 copies of planar operands (worst case both) + the per-slice partial sums (+ the position-major copies
+    // the full-tile kernel reads)
+    const size_t cb = wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));
+    const bool pm = w.variant == 2 && w.NAv == 2 && w.NBv == 2 && conv4d_tc_wgrad_pm_supported(d3, d4, k);
+    return (pm ? 4 : 2) * cb + w.part_bytes + 1024;
 }
 
 // returns 2 when the shape/layout is outside the tensor-core kernel's envelope
@@ -396,6 +404,16 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     cudaError_t e = cudaMemsetAsync(part, 0, w.part_bytes, st);
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): memset: %s", cudaGetErrorString(e));
 
+    bool launched = false;
+    if (w.variant == 2 && w.NAv == 2 && w.NBv == 2 && conv4d_tc_wgrad_pm_supported(d3, d4, k)) {
+        // both sides have more than 8 channels: position-major operands, one M128 MMA per 16 positions
+        const size_t cb = wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));
+        void *pm_scratch = sc + 2 * cb + w.part_bytes;
+        // the partial sums sit right behind the CB16 copies actually made; the PM16 copies go behind the worst case
+        int rc = conv4d_tc_wgrad_pm_run(xa, gbk, part, pm_scratch, B, G, GxA, Cin, Cout, d1, d2, d3, d4, k, w.S, w.cop, st);
+        if (rc == 1) return rc;
+        launched = rc == 0;
+    }
     WgArgs a{};
     a.xa = xa; a.gb = gbk; a.part = part;
     a.B = B; a.G = G; a.GxA = GxA;
@@ -418,9 +436,11 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(64 >> 4) << 24);
     e = cudaFuncSetAttribute(conv4d_tc_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem);
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): smem attribute: %s", cudaGetErrorString(e));
-    dim3 grid(w.S, G * k * (w.variant == 2 ? k : 1));
-    conv4d_tc_wgrad_kernel<<<grid, kWgThreads, w.smem, st>>>(a);
-    NC_LAUNCH_OK("conv4d_tc_wgrad_kernel");
+    if (!launched) {
+        dim3 grid(w.S, G * k * (w.variant == 2 ? k : 1));
+        conv4d_tc_wgrad_kernel<<<grid, kWgThreads, w.smem, st>>>(a);
+        NC_LAUNCH_OK("conv4d_tc_wgrad_kernel");
+    }
     if (gy_dtype != NCNET_CB16)
         return wgrad_finish(part, gw, gb, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, gy_dtype, st);
     int rc = wgrad_finish(part, gw, nullptr, nullptr, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, NCNET_F32, st);

@@ -1,0 +1,277 @@
+// Conv4d weight gradient, 16 -> 16 channel layers, on full-size tensor-core tiles (mode NCNET_CONV_TC16).
+//
+//   dW[o,c,t1,t2,t3,t4] = sum_{b,i,j,k,l} G[b,o,i,j,k,l] * X[b,c,i+t1-p,j+t2-p,k+t3-p,l+t4-p]     (lib/conv4d.py:11-51)
+//
+// conv4d_tc_wgrad.cu reads the channel-blocked layout ([half][position][8 ch]), where one MMA group is 8 channels, so
+// its tiles are M64 x N40 -- four half-rate MMAs (26 cycles each) per 16 positions.  Here both operands are first
+// re-laid-out POSITION-MAJOR ("PM16": [plane][position][16 ch] fp16, 32 B per position, the two 16-byte halves swapped
+// where bit 7 of the byte offset is set = the SWIZZLE_32B pattern).  With SWIZZLE_32B an MN-major "atom" is 16
+// channels x 8 positions, atoms are addressed with one stride (LBO), and a tap shift is exactly such a stride:
+//     A (M = 128): atom a = X shifted by a positions (the d4 taps; 5 of 8 used),        LBO = 32 B
+//     B (N = 16k): atom r = G shifted by r rows      (the d3 taps, reversed order),     LBO = P * 32 B
+//     K = 16 consecutive haloed positions per MMA (two 8-row K atoms, SBO = 256 B)
+// so ONE M128 x N80 x K16 MMA (52 cycles) per 16 positions replaces the four M64 x N40 ones (105 cycles).  The
+// hardware applies the swizzle to absolute shared-memory address bits, so shifted descriptor start addresses read
+// the verbatim-copied image correctly (scripts/umma_sw32_check.cu verifies this on the device).
+// CTA = (group, t1, t2, slice of the (b,i,j) plane list); D[(t4,c)][(r,o)] accumulates in TMEM over the slice and is
+// flushed as per-slice partial sums in the layout unpack_wgrad_kernel reduces.
+#include "conv4d_tc.cuh"
+#include "tc_common.cuh"
+
+namespace ncnet {
+
+using namespace tc;
+
+constexpr int kPmThreads = 192;
+constexpr int kPmStages = 4;
+
+// CB16 [blk][2][ij][npos][8] -> PM16 [blk][ij][npos][16] with the SWIZZLE_32B half swap (npos = haloed plane positions)
+__global__ void __launch_bounds__(256)
+pm16_from_cb16_kernel(const uint4 *__restrict__ cb, uint4 *__restrict__ pm, size_t nblk, size_t ij, int npos) {
+    const size_t per_half = ij * (size_t)npos;
+    const size_t total = nblk * per_half;
+    for (size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < total; e += (size_t)gridDim.x * blockDim.x) {
+        const size_t blk = e / per_half, r = e - blk * per_half;
+        const int pos = (int)(r % npos);
+        const uint4 h0 = cb[(blk * 2 + 0) * per_half + r];
+        const uint4 h1 = cb[(blk * 2 + 1) * per_half + r];
+        const bool swap = (pos >> 2) & 1;
+        pm[e * 2 + 0] = swap ? h1 : h0;
+        pm[e * 2 + 1] = swap ? h0 : h1;
+    }
+}
+
+struct WgPmArgs {
+    const __half *x;    // PM16 [B*GxA][d1*d2][npos][16]
+    const __half *g;    // PM16 [B*G][d1*d2][npos][16]
+    float *part;        // [S][G][Cin][k][k][k][k][cop]
+    int B, G, GxA, d1, d2, KS, N;
+    int nkb, kb0;                   // K blocks [kb0, nkb) of 16 positions
+    int S, Cin, Cout, cop, stages;
+    uint32_t plane_bytes;           // bytes of one haloed PM16 plane
+    uint32_t a_bytes, stage_bytes;  // A buffer / whole stage
+    uint32_t g_off;                 // byte offset of the G plane inside the B buffer (multiple of 256)
+    uint32_t b_rel;                 // byte offset, from the B buffer, of B's K position 0 (atom 0)
+    uint32_t lbo_b;                 // P * 32
+    uint32_t idesc, tmem_cols;
+};
+
+__device__ __forceinline__ bool pm_item(const WgPmArgs &p, int pl, int t1, int t2, int &b, size_t &ij_g, size_t &ij_x) {
+    const int PAD = p.KS / 2;
+    b = pl / (p.d1 * p.d2);
+    const int ij = pl - b * (p.d1 * p.d2);
+    const int i = ij / p.d2, j = ij - i * p.d2;
+    const int ii = i + t1 - PAD, jj = j + t2 - PAD;
+    if (ii < 0 || ii >= p.d1 || jj < 0 || jj >= p.d2) return false;
+    ij_g = (size_t)ij;
+    ij_x = (size_t)ii * p.d2 + jj;
+    return true;
+}
+
+__global__ void __launch_bounds__(kPmThreads, 1)
+conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[kPmStages], empty_bar[kPmStages], accum_bar;
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int by = blockIdx.y;
+    const int t2 = by % p.KS; by /= p.KS;
+    const int t1 = by % p.KS; by /= p.KS;
+    const int g = by;
+    const int s = blockIdx.x;
+    const int nplanes = p.B * p.d1 * p.d2;
+    const int per = (nplanes + p.S - 1) / p.S;
+    const int pbeg = s * per, pend = min(nplanes, pbeg + per);
+
+    if (warp == 1 && lane == 0) {
+        for (int st = 0; st < p.stages; ++st) { mbar_init(&full_bar[st], 1); mbar_init(&empty_bar[st], 1); }
+        mbar_init(&accum_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(p.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {   // zero the ring once: the margins around the planes are read by the shifted views and must stay zero
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        uint4 *d = reinterpret_cast<uint4 *>(smem);
+        const uint32_t n16 = (uint32_t)p.stages * p.stage_bytes / 16;
+        for (uint32_t e = threadIdx.x; e < n16; e += kPmThreads) d[e] = z;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t sm0 = smem_u32(smem), full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+
+    if (warp == 0) {
+        // ===== producer: one lane streams (X plane, G plane) pairs, one bulk copy each =====
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const size_t ijn = (size_t)p.d1 * p.d2;
+            const size_t plane_h = p.plane_bytes / 2;
+            for (int pl = pbeg; pl < pend; ++pl) {
+                int b; size_t ij_g, ij_x;
+                if (!pm_item(p, pl, t1, t2, b, ij_g, ij_x)) continue;
+                mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
+                const uint32_t sa = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(2u * p.plane_bytes) : "memory");
+                const size_t bga = (size_t)b * p.GxA + (p.GxA == 1 ? 0 : g), bgb = (size_t)b * p.G + g;
+                bulk_g2s_u32(sa, p.x + (bga * ijn + ij_x) * plane_h, p.plane_bytes, fb);
+                bulk_g2s_u32(sa + p.a_bytes + p.g_off, p.g + (bgb * ijn + ij_g) * plane_h, p.plane_bytes, fb);
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer: one lane, one M128 x N x K16 MMA per 16 positions =====
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0, acc = 0;
+            // descriptor high word: SBO = 256 B (K atoms), version 1, SWIZZLE_32B (layout type 6 at bits 61-63)
+            const uint64_t hi = (uint64_t)((256u >> 4) | (1u << 14) | (6u << 29)) << 32;
+            const uint32_t lbo_a = (32u >> 4) << 16, lbo_b = (p.lbo_b >> 4) << 16;
+            const int nk = p.nkb - p.kb0;
+            for (int pl = pbeg; pl < pend; ++pl) {
+                int b; size_t ij_g, ij_x;
+                if (!pm_item(p, pl, t1, t2, b, ij_g, ij_x)) continue;
+                mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t sa4 = (sm0 + (uint32_t)stage * p.stage_bytes) >> 4;
+                uint32_t a_lo = lbo_a | (sa4 + (uint32_t)p.kb0 * 32u);                                  // 16 positions = 512 B
+                uint32_t b_lo = lbo_b | (sa4 + ((p.a_bytes + p.b_rel) >> 4) + (uint32_t)p.kb0 * 32u);
+                umma_f16(tmem_base, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, acc);
+                acc = 1u;
+#pragma unroll 8
+                for (int kb = 1; kb < nk; ++kb) {
+                    a_lo += 32u; b_lo += 32u;
+                    umma_f16(tmem_base, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, 1u);
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                             ::"r"(empty0 + (uint32_t)stage * 8u) : "memory");
+                if (++stage == p.stages) { stage = 0; phase ^= 1; }
+            }
+            umma_commit(&accum_bar);
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: flush D[(t4,c)][(r,o)] as this slice's partial sums =====
+        const int q = warp & 3;
+        mbar_wait(&accum_bar, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        bool any = false;       // a slice whose every plane pair is out of range issued no MMA: its partials stay zero
+        for (int pl = pbeg; pl < pend && !any; ++pl) {
+            int b; size_t ij_g, ij_x;
+            any = pm_item(p, pl, t1, t2, b, ij_g, ij_x);
+        }
+        const int KS = p.KS;
+        const int m = q * 32 + lane, t4 = m >> 4, c = m & 15;
+        if (any && q * 2 < KS) {          // warp q holds taps 2q and 2q+1
+            const size_t per_group = (size_t)p.Cin * KS * KS * KS * KS * p.cop;
+            float *dst = p.part + ((size_t)s * p.G + g) * per_group;
+            for (int n0 = 0; n0 < p.N; n0 += 16) {
+                float v[16];
+                tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)n0, v);
+                const int t3 = KS - 1 - (n0 >> 4);
+                if (t4 < KS && c < p.Cin) {
+                    float *row = dst + (((((size_t)c * KS + t1) * KS + t2) * KS + t3) * KS + t4) * p.cop;
+#pragma unroll
+                    for (int o = 0; o < 16; ++o) if (o < p.Cout) row[o] = v[o];
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+    }
+}
+
+struct WgPmPlan {
+    bool ok;
+    int N, nkb, kb0, stages;
+    uint32_t plane_bytes, a_bytes, stage_bytes, g_off, b_rel, lbo_b, tmem_cols;
+    size_t smem;
+};
+
+static WgPmPlan pm_plan(int d3, int d4, int k) {
+    WgPmPlan w{};
+    w.ok = false;
+    if (k != 3 && k != 5) return w;
+    const int pad = k / 2, P = d4 + 2 * pad;
+    const int npos = (d3 + 2 * pad) * P;
+    const int nkb_full = (npos + 15) / 16;
+    // K blocks outside [kb0, nkb) multiply nothing but halo zeros (every used shifted view of X is zero there)
+    int lo = pad * P + pad - 7;
+    if (lo < 0) lo = 0;
+    const int hi = (pad + d3 - 1) * P + pad + d4;
+    w.kb0 = lo / 16;
+    w.nkb = (hi + 15) / 16 < nkb_full ? (hi + 15) / 16 : nkb_full;
+    auto up8 = [](int v) { return (v + 7) / 8 * 8; };
+    const int npos_a = up8(npos > w.nkb * 16 + 8 ? npos : w.nkb * 16 + 8);
+    const int g_off_pos = up8(pad * P - pad);
+    const int reach = w.nkb * 16 + pad * P + pad;
+    const int npos_b = up8(g_off_pos + (npos > reach ? npos : reach));
+    w.plane_bytes = (uint32_t)npos * 32u;
+    w.a_bytes = (uint32_t)npos_a * 32u;
+    w.g_off = (uint32_t)g_off_pos * 32u;
+    w.b_rel = (uint32_t)(g_off_pos - pad * P + pad) * 32u;
+    w.lbo_b = (uint32_t)P * 32u;
+    if ((w.lbo_b >> 4) > 16383u) return w;
+    w.stage_bytes = ((w.a_bytes + (uint32_t)npos_b * 32u + 1023u) / 1024u) * 1024u;
+    int stages = (int)((220u * 1024u) / w.stage_bytes);
+    if (stages > kPmStages) stages = kPmStages;
+    if (stages < 2) return w;
+    w.stages = stages;
+    w.smem = (size_t)stages * w.stage_bytes;
+    w.N = 16 * k;
+    w.tmem_cols = w.N <= 32 ? 32 : (w.N <= 64 ? 64 : 128);
+    w.ok = true;
+    return w;
+}
+
+bool conv4d_tc_wgrad_pm_supported(int d3, int d4, int k) { return pm_plan(d3, d4, k).ok; }
+
+// x_cb / g_cb: CB16 operands; pm_scratch: room for both PM16 copies (same byte counts as the CB16 tensors);
+// part: [S][G][Cin][k][k][k][k][cop], already zeroed.  Returns 2 when the shape is outside the envelope.
+int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, float *part, void *pm_scratch, int B, int G, int GxA,
+                           int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int S, int cop, cudaStream_t st) {
+    const WgPmPlan w = pm_plan(d3, d4, k);
+    if (!w.ok || Cin > 16 || Cout > 16) return 2;
+    const int pad = k / 2;
+    const int npos = (d3 + 2 * pad) * (d4 + 2 * pad);
+    const size_t ij = (size_t)d1 * d2;
+    const size_t xa_bytes = (size_t)B * GxA * ij * npos * 32, gb_bytes = (size_t)B * G * ij * npos * 32;
+    __half *x_pm = (__half *)pm_scratch;
+    __half *g_pm = (__half *)((uint8_t *)pm_scratch + ((xa_bytes + 255) & ~(size_t)255));
+    {
+        const size_t nx = (size_t)B * GxA * ij * npos, ng = (size_t)B * G * ij * npos;
+        const int bx = (int)((nx + 255) / 256 < 148 * 16 ? (nx + 255) / 256 : 148 * 16);
+        const int bg = (int)((ng + 255) / 256 < 148 * 16 ? (ng + 255) / 256 : 148 * 16);
+        pm16_from_cb16_kernel<<<bx, 256, 0, st>>>((const uint4 *)x_cb, (uint4 *)x_pm, (size_t)B * GxA, ij, npos);
+        NC_LAUNCH_OK("pm16_from_cb16_kernel");
+        pm16_from_cb16_kernel<<<bg, 256, 0, st>>>((const uint4 *)g_cb, (uint4 *)g_pm, (size_t)B * G, ij, npos);
+        NC_LAUNCH_OK("pm16_from_cb16_kernel");
+        (void)gb_bytes;
+    }
+    WgPmArgs a{};
+    a.x = x_pm; a.g = g_pm; a.part = part;
+    a.B = B; a.G = G; a.GxA = GxA; a.d1 = d1; a.d2 = d2; a.KS = k; a.N = w.N;
+    a.nkb = w.nkb; a.kb0 = w.kb0; a.S = S; a.Cin = Cin; a.Cout = Cout; a.cop = cop; a.stages = w.stages;
+    a.plane_bytes = w.plane_bytes; a.a_bytes = w.a_bytes; a.stage_bytes = w.stage_bytes;
+    a.g_off = w.g_off; a.b_rel = w.b_rel; a.lbo_b = w.lbo_b; a.tmem_cols = w.tmem_cols;
+    // D = f32, A = B = f16, both MN-major (bits 15/16), N>>3 at bit 17, M = 128 -> 8 at bit 24
+    a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    cudaError_t e = cudaFuncSetAttribute(conv4d_tc_wgrad_pm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem);
+    NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc,pm): smem attribute: %s", cudaGetErrorString(e));
+    dim3 grid(S, G * k * k);
+    conv4d_tc_wgrad_pm_kernel<<<grid, kPmThreads, w.smem, st>>>(a);
+    NC_LAUNCH_OK("conv4d_tc_wgrad_pm_kernel");
+    return 0;
+}
+
+}  // namespace ncnet
