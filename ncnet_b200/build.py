@@ -30,7 +30,8 @@ def _digest() -> str:
     inc = os.path.join(os.path.dirname(HERE), "include", "ncnet_b200.h")
     for p in sorted([os.path.join(CSRC, f) for f in os.listdir(CSRC)] + [inc, __file__]):
         with open(p, "rb") as fh:
-            h.update(p.encode()), h.update(fh.read())
+            # names relative to the package: the digest must not change when the tree is copied elsewhere
+            h.update(os.path.basename(p).encode()), h.update(fh.read())
     return h.hexdigest()
 
 
@@ -45,8 +46,21 @@ def build(force: bool = False, verbose: bool = False) -> str:
     """Compile every .cu under csrc/ into one shared library; returns its path."""
     if not force and up_to_date():
         return LIB
-    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     os.makedirs(OUT_DIR, exist_ok=True)
+    # one builder at a time (ranks of a multi-GPU launch share the tree); the others wait, then find it up to date
+    import fcntl
+    with open(os.path.join(OUT_DIR, "build.lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and up_to_date():
+                return LIB
+            return _build_locked(verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(verbose: bool) -> str:
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
     objs = []
     procs = []
     for src in sources():
@@ -62,10 +76,12 @@ def build(force: bool = False, verbose: bool = False) -> str:
         failed |= p.returncode != 0
     if failed:
         raise RuntimeError("nvcc failed; see output above")
-    cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-lcudart"]
+    tmp = LIB + ".tmp%d" % os.getpid()
+    cmd = [nvcc, "-shared", "-o", tmp] + objs + ["-lcudart"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
         raise RuntimeError("link failed:\n" + r.stdout)
+    os.replace(tmp, LIB)            # a process that already mapped the old file keeps it
     with open(STAMP, "w") as fh:
         fh.write(_digest())
     return LIB
