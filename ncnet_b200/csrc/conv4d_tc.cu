@@ -474,6 +474,62 @@ cb16_pack_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1
     }
 }
 
+// Same mapping for planes whose haloed row fits one warp (P <= 32): one warp per haloed row, lanes along the row, 32-bit
+// index math; the tap modes along the last axis load each element once and exchange it with shuffles.
+template <typename T>
+__global__ void __launch_bounds__(256)
+cb16_pack_rows_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1, int d2, int d3, int d4, int pad,
+                      int tap_mode, int taps) {
+    const unsigned blk = blockIdx.y;
+    const int half = blockIdx.z;
+    const int P = d4 + 2 * pad, rows = d3 + 2 * pad;
+    const unsigned ij = (unsigned)(d1 * d2), nrows = ij * (unsigned)rows;
+    const size_t plane = (size_t)d3 * d4, vol = (size_t)ij * plane;
+    const int lane = threadIdx.x & 31;
+    const unsigned r = blockIdx.x * 8u + (threadIdx.x >> 5);
+    if (r >= nrows) return;
+    const unsigned ijx = r / (unsigned)rows;
+    const int kk = (int)(r - ijx * (unsigned)rows);
+    const int k = kk - pad, l = lane - pad;
+    const bool inside = k >= 0 && k < d3 && l >= 0 && l < d4;
+    __align__(16) __half v[8];
+#pragma unroll
+    for (int c = 0; c < 8; ++c) v[c] = __float2half_rn(0.f);
+    if (tap_mode == 1 || tap_mode == 3) {
+        // lane holds x[row][lane - 2p]; channel c of haloed column ll is the value of lane ll + c
+        const int ks = tap_mode == 3 ? k + half : k;
+        const int col = lane - 2 * pad;
+        float e = 0.f;
+        if (ks >= 0 && ks < d3 && col >= 0 && col < d4) e = ldf(x + (size_t)blk * vol + (size_t)ijx * plane + (size_t)ks * d4 + col);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) {
+            const float o = __shfl_down_sync(0xffffffffu, e, c);
+            if (c < taps && lane + c < 32 && (tap_mode == 3 || inside)) v[c] = __float2half_rn(o);
+        }
+    } else if (inside) {
+        const size_t pos = (size_t)ijx * plane + (size_t)k * d4 + l;
+        if (tap_mode == 0) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int ch = half * 8 + c;
+                if (ch < C) v[c] = __float2half_rn(ldf(x + ((size_t)blk * C + ch) * vol + pos));
+            }
+        } else {
+            const int jx = (int)(ijx % (unsigned)d2);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const int t = half * 8 + c, jt = jx - t + pad;
+                if (t < taps && jt >= 0 && jt < d2)
+                    v[c] = __float2half_rn(ldf(x + (size_t)blk * vol + pos + (ptrdiff_t)(pad - t) * (ptrdiff_t)plane));
+            }
+        }
+    }
+    if (lane < P) {
+        const size_t npad = (size_t)nrows * P;
+        *reinterpret_cast<uint4 *>(cb + (((size_t)blk * 2 + half) * npad + (size_t)r * P + lane) * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
 // CB16 -> planar [nblk, C, vol] (T); interior only
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -503,14 +559,26 @@ int cb16_pack(const void *x, int dtype, void *cb, int nblk, int C, int d1, int d
     NC_CHECK(tap_mode == 0 || C == 1, "cb16_pack: tap modes need a single-channel input");
     const int pad = k / 2;
     const size_t npad = (size_t)d1 * d2 * (d3 + 2 * pad) * (d4 + 2 * pad);
+    // tap modes 1 and 2 put at most k <= 8 taps into the channels: the second channel half is never read
+    const int halves = (tap_mode == 1 || tap_mode == 2) ? 1 : 2;
+    NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "cb16_pack: source dtype %d must be planar fp32/fp16", dtype);
+    if (d4 + 2 * pad <= 32) {
+        const size_t nrows = (size_t)d1 * d2 * (d3 + 2 * pad);
+        NC_CHECK((nrows + 7) / 8 < (1ull << 31), "cb16_pack: too many rows");
+        dim3 grid((unsigned)((nrows + 7) / 8), nblk, halves);
+        if (dtype == NCNET_F32)
+            cb16_pack_rows_kernel<float><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+        else
+            cb16_pack_rows_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+        NC_LAUNCH_OK("cb16_pack_rows_kernel");
+        return 0;
+    }
     const unsigned gx = (unsigned)((npad + 255) / 256 < 8192 ? (npad + 255) / 256 : 8192);
-    dim3 grid(gx, nblk, 2);
+    dim3 grid(gx, nblk, halves);
     if (dtype == NCNET_F32)
         cb16_pack_kernel<float><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
-    else if (dtype == NCNET_F16)
-        cb16_pack_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
     else
-        return fail("cb16_pack: source dtype %d must be planar fp32/fp16", dtype);
+        cb16_pack_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
     NC_LAUNCH_OK("cb16_pack_kernel");
     return 0;
 }
