@@ -77,7 +77,7 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
     const uint32_t lbo_a_field = (uint32_t)p.npos_pad << 16, lbo_b_field = (uint32_t)p.N << 16;   // LBO in 16-byte units
     const uint32_t hi = (128u >> 4) | (1u << 14);                                                 // SBO = 128 B, descriptor version 1
     const uint32_t b_step = 2u * (uint32_t)p.N;                                                   // 16-byte units per K-step of weights
-    const uint32_t sm4 = smem_u32(stage0) >> 4, stage4 = p.stage_bytes >> 4, data4 = p.data_bytes >> 4;
+    const uint32_t sm4 = smem_u32_pinned(stage0) >> 4, stage4 = p.stage_bytes >> 4, data4 = p.data_bytes >> 4;
     // low descriptor words relative to the stage base: A of (K-step, tile), B of K-step
     uint32_t a_rel[KSM][NTM], b_rel[KSM], d_col[NTM];
 #pragma unroll
@@ -90,7 +90,7 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
     for (int t = 0; t < NTM; ++t) d_col[t] = tmem_base + (uint32_t)(t * p.N);
     // staged (d1,d2) planes of this CTA (the producer skips the out-of-range ones the same way)
     const int nplanes = (min(i + PAD, p.d1 - 1) - max(i - PAD, 0) + 1) * (min(j + PAD, p.d2 - 1) - max(j - PAD, 0) + 1);
-    const uint32_t full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+    const uint32_t full0 = smem_u32_pinned(full_bar), empty0 = smem_u32_pinned(empty_bar);
     if (elect_one()) {                      // one lane runs the whole loop: no per-stage election / reconvergence
         for (int it = 0; it < nplanes; ++it) {
             {
@@ -163,7 +163,7 @@ conv4d_tc_kernel(const TcArgs p) {
     // The epilogue's output plane ALIASES the stage ring: it is first touched after accum_bar, i.e. after every
     // staged byte has been consumed, which leaves the whole budget to stages in flight (the main loop is bound by
     // bulk-copy latency x bytes in flight, not by the tensor pipe).
-    float *outbuf = reinterpret_cast<float *>(smem);
+    const uint32_t osm = smem_u32_pinned(smem);       // all epilogue accesses go through this 32-bit shared address
     const int out_rows = p.NT * 128;
 
     // ---- one-time setup -------------------------------------------------------------------
@@ -217,9 +217,9 @@ conv4d_tc_kernel(const TcArgs p) {
         const size_t half_off = ij_count * plane_halves;
         const uint32_t w_halves = p.w_bytes / 2;
         const __half *w_base = p.wp + (size_t)g * p.KS * p.KS * w_halves;
-        const uint32_t sm0 = smem_u32(stage0), full0 = smem_u32(&full_bar[0]);
+        const uint32_t sm0 = smem_u32_pinned(stage0), full0 = smem_u32_pinned(&full_bar[0]);
         const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
-        const uint32_t empty0 = smem_u32(&empty_bar[0]);
+        const uint32_t empty0 = smem_u32_pinned(&empty_bar[0]);
         if (elect_one()) {
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
@@ -262,7 +262,7 @@ conv4d_tc_kernel(const TcArgs p) {
         // ===== epilogue (warps 2..5 <-> TMEM lane quadrants warp%4) =====
         const int q = warp & 3;
         const int et = threadIdx.x - 64;                 // 0..127
-        mbar_wait(&accum_bar, 0);
+        mbar_wait_sleep(&accum_bar, 0, 400);
         if (et == 0) TC_STAMP(2);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         if (p.CoutPad >= 16) {
@@ -275,63 +275,93 @@ conv4d_tc_kernel(const TcArgs p) {
 #pragma unroll
             for (int o = 0; o < 16; ++o) bv[o] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
             const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
-            for (int gi = 0; gi < p.NG; ++gi) {
+            // iteration = (column group, pair of tiles); the TMEM loads of the next iteration are in flight while this
+            // one is accumulated (tcgen05.ld has a few hundred cycles of latency)
+            const int npair = (p.NT + 1) >> 1, nit = p.NG * npair;
+            uint32_t r0[16], r1[16], n0[16], n1[16];
+            tmem_ld16_issue(lane_base, r0);
+            if (p.NT > 1) tmem_ld16_issue(lane_base + (uint32_t)p.N, r1);
+            int gi = 0, t = 0;
+            for (int it = 0; it < nit; ++it) {
+                const bool two = t + 1 < p.NT;
                 const int sh = s_gshift[gi];
-                for (int t = 0; t < p.NT; t += 2) {
-                    const bool two = t + 1 < p.NT;
-                    uint32_t r0[16], r1[16];
-                    tmem_ld16_issue(lane_base + (uint32_t)(t * p.N + gi * 16), r0);
-                    if (two) tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N + gi * 16), r1);
-                    tmem_ld16_wait(r0);
-                    if (two) tmem_ld16_wait(r1);
+                tmem_ld16_wait(r0);
+                if (two) tmem_ld16_wait(r1);
+                int gn = gi, tn = t + 2;
+                if (tn >= p.NT) { tn = 0; ++gn; }
+                if (it + 1 < nit) {
+                    tmem_ld16_issue(lane_base + (uint32_t)(tn * p.N + gn * 16), n0);
+                    if (tn + 1 < p.NT) tmem_ld16_issue(lane_base + (uint32_t)((tn + 1) * p.N + gn * 16), n1);
+                }
 #pragma unroll
-                    for (int h = 0; h < 2; ++h) {
-                        if (h == 1 && !two) break;
-                        const uint32_t(&r)[16] = h ? r1 : r0;
-                        const int dest = (t + h) * 128 + q * 32 + lane - sh;
-                        if (dest >= 0) {
-                            float4 *dst = reinterpret_cast<float4 *>(outbuf + (size_t)dest * kOutStride);
-                            if (gi == 0) {
+                for (int h = 0; h < 2; ++h) {
+                    if (h == 1 && !two) break;
+                    const uint32_t(&r)[16] = h ? r1 : r0;
+                    const int dest = (t + h) * 128 + q * 32 + lane - sh;
+                    if (dest >= 0) {
+                        const uint32_t dst = osm + (uint32_t)dest * (kOutStride * 4u);
+                        if (gi == 0) {
 #pragma unroll
-                                for (int w4 = 0; w4 < 4; ++w4)
-                                    dst[w4] = make_float4(bv[4 * w4 + 0] + __uint_as_float(r[4 * w4 + 0]), bv[4 * w4 + 1] + __uint_as_float(r[4 * w4 + 1]),
-                                                          bv[4 * w4 + 2] + __uint_as_float(r[4 * w4 + 2]), bv[4 * w4 + 3] + __uint_as_float(r[4 * w4 + 3]));
-                            } else {
+                            for (int w4 = 0; w4 < 4; ++w4)
+                                sts_v4(dst + 16u * w4,
+                                       make_float4(bv[4 * w4 + 0] + __uint_as_float(r[4 * w4 + 0]), bv[4 * w4 + 1] + __uint_as_float(r[4 * w4 + 1]),
+                                                   bv[4 * w4 + 2] + __uint_as_float(r[4 * w4 + 2]), bv[4 * w4 + 3] + __uint_as_float(r[4 * w4 + 3])));
+                        } else {
+                            float4 a[4];
 #pragma unroll
-                                for (int w4 = 0; w4 < 4; ++w4) {
-                                    float4 a = dst[w4];
-                                    a.x += __uint_as_float(r[4 * w4 + 0]); a.y += __uint_as_float(r[4 * w4 + 1]);
-                                    a.z += __uint_as_float(r[4 * w4 + 2]); a.w += __uint_as_float(r[4 * w4 + 3]);
-                                    dst[w4] = a;
-                                }
+                            for (int w4 = 0; w4 < 4; ++w4) a[w4] = lds_v4(dst + 16u * w4);
+#pragma unroll
+                            for (int w4 = 0; w4 < 4; ++w4) {
+                                a[w4].x += __uint_as_float(r[4 * w4 + 0]); a[w4].y += __uint_as_float(r[4 * w4 + 1]);
+                                a[w4].z += __uint_as_float(r[4 * w4 + 2]); a[w4].w += __uint_as_float(r[4 * w4 + 3]);
+                                sts_v4(dst + 16u * w4, a[w4]);
                             }
                         }
                     }
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (gn != gi) asm volatile("bar.sync 1, 128;" ::: "memory");       // last tile pair of this group
+                if (it + 1 < nit) {
+                    tmem_ld16_wait(n0);
+                    if (tn + 1 < p.NT) tmem_ld16_wait(n1);
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) { r0[u] = n0[u]; r1[u] = n1[u]; }
+                }
+                gi = gn; t = tn;
             }
         } else {
-            // single out-channel: one column per folded (d3,d4) tap.  Each warp accumulates into its
-            // own copy of the plane (stride 1), so no cross-warp ordering is needed; the store sums them.
-            {
-                const float b0 = p.bias ? __ldg(p.bias) : 0.f;
-                for (int e = et; e < 4 * out_rows; e += 128) outbuf[e] = e < out_rows ? b0 : 0.f;
-                asm volatile("bar.sync 1, 128;" ::: "memory");
-            }
-            float *mine = outbuf + (size_t)q * out_rows;
+            // single out-channel: column c of D holds tap (d3,d4) = (c / k, c % k) of output row m - shift_c.  The
+            // columns are parked in shared memory as planes S[c][row] (lanes = consecutive rows: conflict-free, no
+            // ordering between writers); the store below sums the k*k shifted reads of each output position.
+            const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+            const bool wide = p.NG > 16;
+            // tcgen05.ld has a few hundred cycles of latency: the next tile's loads are in flight while this one is stored
+            uint32_t ra[16], rb[16], na[16], nb[16];
+            tmem_ld16_issue(lane_base, ra);
+            if (wide) tmem_ld16_issue(lane_base + 16u, rb);
             for (int t = 0; t < p.NT; ++t) {
-                const int m = t * 128 + q * 32 + lane;
-                for (int c0 = 0; c0 < p.NG; c0 += 16) {
-                    float v[16];
-                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t * p.N + c0), v);
+                const int row = t * 128 + q * 32 + lane;
+                if (p.dbg && blockIdx.x == 2000 && et == 0) p.dbg[32000 + 3 * t] = clock64() - t_start;
+                tmem_ld16_wait(ra);
+                if (wide) tmem_ld16_wait(rb);
+                if (p.dbg && blockIdx.x == 2000 && et == 0) p.dbg[32001 + 3 * t] = clock64() - t_start;
+                if (t + 1 < p.NT) {
+                    tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N), na);
+                    if (wide) tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N + 16), nb);
+                }
 #pragma unroll
-                    for (int u = 0; u < 16; ++u) {
-                        if (c0 + u < p.NG) {
-                            const int dest = m - s_gshift[c0 + u];
-                            if (dest >= 0) mine[dest] += v[u];
-                        }
-                        __syncwarp();
-                    }
+                for (int u = 0; u < 16; ++u)
+                    if (u < p.NG) sts_f32(osm + (uint32_t)(u * out_rows + row) * 4u, __uint_as_float(ra[u]));
+                if (wide) {
+#pragma unroll
+                    for (int u = 0; u < 16; ++u)
+                        if (16 + u < p.NG) sts_f32(osm + (uint32_t)((16 + u) * out_rows + row) * 4u, __uint_as_float(rb[u]));
+                }
+                if (p.dbg && blockIdx.x == 2000 && et == 0) p.dbg[32002 + 3 * t] = clock64() - t_start;
+                if (t + 1 < p.NT) {
+                    tmem_ld16_wait(na);
+                    if (wide) tmem_ld16_wait(nb);
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) { ra[u] = na[u]; rb[u] = nb[u]; }
                 }
             }
         }
@@ -354,8 +384,8 @@ conv4d_tc_kernel(const TcArgs p) {
                 const size_t goff = ((size_t)half * ij_count * plane_cb + (size_t)kk * p.P + ll) * 8;
                 __align__(16) __half hv[8];
                 if (kr >= 0 && kr < rows_out && lc >= 0 && lc < p.d4) {
-                    const float4 *src = reinterpret_cast<const float4 *>(outbuf + (size_t)(kr * p.P + lc) * kOutStride + half * 8);
-                    const float4 a = src[0], c = src[1];
+                    const uint32_t src = osm + (uint32_t)((kr * p.P + lc) * kOutStride + half * 8) * 4u;
+                    const float4 a = lds_v4(src), c = lds_v4(src + 16u);
                     float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
                     if (p.mask_mode == 3) {
                         const uint4 mraw = *reinterpret_cast<const uint4 *>(mb + goff);
@@ -381,6 +411,7 @@ conv4d_tc_kernel(const TcArgs p) {
             const size_t vol = ij_count * plane_pos;
             const int ew = et >> 5;
             const int npairs = p.Cout * rows_out;
+            const float bias0 = (p.CoutPad < 16 && p.bias) ? __ldg(p.bias) : 0.f;
             for (int pr = ew; pr < npairs; pr += 4) {
                 const int o = pr / rows_out, rr = pr - o * rows_out;
                 const size_t off0 = ((size_t)b * p.G * p.Cout + (size_t)g * p.Cout + o) * vol +
@@ -388,8 +419,23 @@ conv4d_tc_kernel(const TcArgs p) {
                 for (int l = lane; l < p.d4; l += 32) {
                     const int row = rr * p.P + l;
                     float v;
-                    if (p.CoutPad >= 16) v = outbuf[(size_t)row * kOutStride + o];
-                    else v = outbuf[row] + outbuf[out_rows + row] + outbuf[2 * out_rows + row] + outbuf[3 * out_rows + row];
+                    if (p.CoutPad >= 16) v = lds_f32(osm + (uint32_t)(row * kOutStride + o) * 4u);
+                    else {
+                        // sum of the k*k column planes at their tap shifts (d3 * P + d4): independent loads
+                        const uint32_t src = osm + (uint32_t)row * 4u, col = (uint32_t)out_rows * 4u;
+                        float a0 = bias0, a1 = 0.f, a2 = 0.f, a3 = 0.f, a4 = 0.f;
+                        if (p.KS == 5) {
+#pragma unroll
+                            for (int t3 = 0; t3 < 5; ++t3) {
+                                const uint32_t s3 = src + (uint32_t)(t3 * 5) * col + (uint32_t)(t3 * p.P) * 4u;
+                                a0 += lds_f32(s3); a1 += lds_f32(s3 + col + 4u); a2 += lds_f32(s3 + 2u * col + 8u);
+                                a3 += lds_f32(s3 + 3u * col + 12u); a4 += lds_f32(s3 + 4u * col + 16u);
+                            }
+                        } else {
+                            for (int c = 0; c < p.NG; ++c) a0 += lds_f32(src + (uint32_t)c * col + (uint32_t)s_gshift[c] * 4u);
+                        }
+                        v = (a0 + a1) + (a2 + a3) + a4;
+                    }
                     if (p.relu) v = fmaxf(v, 0.f);
                     const size_t off = off0 + l;
                     if (p.mask_mode == 1) { if (!(((const float *)p.mask)[off] > 0.f)) v = 0.f; }
@@ -678,7 +724,7 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
         if (npos > 16383) return false;                      // 14-bit LBO field (16 B units)
         const uint32_t data = 2u * npos * 16u;
         const uint32_t stage = ((data + o.w_bytes + 127) / 128) * 128;
-        const size_t outb = o.CoutPad >= 16 ? (size_t)NT * 128 * kOutStride * sizeof(float) : (size_t)NT * 128 * 4 * sizeof(float);
+        const size_t outb = o.CoutPad >= 16 ? (size_t)NT * 128 * kOutStride * sizeof(float) : (size_t)NT * 128 * o.NG * sizeof(float);
         size_t smem = (size_t)stages * stage;
         if (smem < outb) smem = outb;                        // the output plane aliases the ring
         if (smem > max_smem) return false;

@@ -159,13 +159,14 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
         const uint64_t a_hi = ((uint64_t)((p.a_sbo >> 4) | (1u << 14))) << 32;           // SBO + descriptor version 1
         const uint64_t b_hi = ((uint64_t)((p.b_sbo >> 4) | (1u << 14))) << 32;
         const uint32_t n = (uint32_t)p.N, nbv = (uint32_t)p.NBv;
+        const uint32_t smem0 = smem_u32_pinned(smem);
         for (int pl = pbeg; pl < pend; ++pl) {
             WgItem it;
             if (!wg_item(p, pl, t1, t2, it)) continue;
             mbar_wait(&full_bar[stage], phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             // warp-uniform descriptor arithmetic (only the low word changes); one elected lane issues
-            const uint32_t sa4 = smem_u32(smem + (size_t)stage * p.stage_bytes) >> 4;
+            const uint32_t sa4 = (smem0 + (uint32_t)stage * p.stage_bytes) >> 4;
             const uint32_t sb4 = sa4 + ((p.a_bytes + p.b_start) >> 4);
             if (elect_one()) {
                 if (p.NAv == 2 && p.NBv == 2) {

@@ -104,7 +104,7 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
-    const uint32_t sm0 = smem_u32(smem), full0 = smem_u32(full_bar), empty0 = smem_u32(empty_bar);
+    const uint32_t sm0 = smem_u32_pinned(smem), full0 = smem_u32_pinned(full_bar), empty0 = smem_u32_pinned(empty_bar);
 
     if (warp == 0) {
         // ===== producer: one lane streams (X plane, G plane) pairs, one bulk copy each =====

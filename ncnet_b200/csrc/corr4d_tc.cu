@@ -109,12 +109,13 @@ corr4d_tc_kernel(const CorrArgs p) {
         // MN-major, no swizzle: LBO = 128 B between groups of 8 channels, SBO = 1 KB between groups of 8 positions
         const uint64_t hi = ((uint64_t)(((uint32_t)(kCorrKB * 16) >> 4) | (1u << 14))) << 32;
         const uint32_t lbo_field = (128u >> 4) << 16;
+        const uint32_t smem0 = smem_u32_pinned(smem);
         const uint32_t idesc = (p.idesc & ~(0x3fu << 17)) | ((uint32_t)(n_cols >> 3) << 17);
         for (int kb = 0; kb < p.kblocks; ++kb) {
             mbar_wait(&full_bar[stage], phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             if (elect_one()) {
-                const uint32_t sa4 = smem_u32(smem + (size_t)stage * kStage) >> 4;
+                const uint32_t sa4 = (smem0 + (uint32_t)stage * (uint32_t)kStage) >> 4;
                 const uint32_t sb4 = sa4 + (kABytes >> 4);
 #pragma unroll
                 for (int kk = 0; kk < kCorrKB / 16; ++kk)        // 16 channels = 2 K groups = 256 B further

@@ -9,6 +9,14 @@ namespace tc {
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
+// A shared-window address the compiler must keep in a register: the plain conversion is "pure", so it gets
+// re-materialised (S2UR SR_CgaCtaId + 3 uniform ops, ~60 cycles of latency) next to every use in unrolled code.
+__device__ __forceinline__ uint32_t smem_u32_pinned(const void *p) {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %1;" : "=r"(r) : "r"((uint32_t)__cvta_generic_to_shared(p)));
+    return r;
+}
+
 // true in exactly one lane of a converged warp; ptxas knows code under it runs single-lane, so
 // tcgen05/TMA operands move to uniform registers without a per-value "waterfall" loop
 __device__ __forceinline__ bool elect_one() {
@@ -47,6 +55,36 @@ __device__ __forceinline__ void mbar_wait_u32(uint32_t addr, uint32_t parity) {
     }
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) { mbar_wait_u32(smem_u32(bar), parity); }
+// long waits (an epilogue waiting for a whole main loop): back off between probes -- every probe is a shared-memory
+// pipeline transaction, and four spinning warps slow the co-resident CTA's epilogue loads/stores severalfold
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t *bar, uint32_t parity, unsigned ns) {
+    const uint32_t addr = smem_u32(bar);
+    if (mbar_try(addr, parity)) return;
+    const long long t0 = clock64();
+    for (;;) {
+        __nanosleep(ns);
+        if (mbar_try(addr, parity)) return;
+        if (clock64() - t0 > 8000000000ll) __trap();
+    }
+}
+// Shared-memory accesses by 32-bit shared-window address.  Through a generic pointer the compiler re-derives the
+// window base (S2UR SR_CgaCtaId, ~60 cycles) next to every access of an unrolled epilogue; these forms cost one LDS/STS.
+__device__ __forceinline__ void sts_f32(uint32_t addr, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_v4(uint32_t addr, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ float4 lds_v4(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
 // 1-D bulk copy global -> shared through the TMA engine (SASS: UBLKCP)
 __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"

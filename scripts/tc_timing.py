@@ -8,11 +8,22 @@ B = 4
 x = torch.rand(B, 32, 25, 25, 25, 25, device="cuda")
 w = (torch.rand(5, 16, 16, 5, 5, 5, device="cuda") * 2 - 1) * 0.01
 b = torch.zeros(16, device="cuda")
-x = F_._conv_fwd(x, w, b, W_KOIKKK, True, False, True, CONV_TC16, out_cb16=True) if "cb16" in sys.argv else x
+x = F_._conv_fwd(x, w, b, W_KOIKKK, True, False, True, CONV_TC16, out_cb16=True) if ("cb16" in sys.argv and "thin1" not in sys.argv) else x
 CB = "cb16" in sys.argv
 if CB:
     w = (torch.rand(5, 16, 16, 5, 5, 5, device="cuda") * 2 - 1) * 0.01
-F_._conv_fwd(x, w, b, W_KOIKKK, True, False, True, CONV_TC16, out_cb16=CB)
+THIN = "thin" in sys.argv          # the 16 -> 1 layer (planar output) on the CB16 activations
+if THIN:
+    w = (torch.rand(5, 1, 16, 5, 5, 5, device="cuda") * 2 - 1) * 0.01
+    b = torch.zeros(1, device="cuda")
+    CB = False
+THIN1 = "thin1" in sys.argv        # the 1 -> 16 layer (planar single-channel input, CB16 output)
+if THIN1:
+    x = torch.rand(B, 1, 25, 25, 25, 25, device="cuda")
+    w = (torch.rand(5, 16, 1, 5, 5, 5, device="cuda") * 2 - 1) * 0.01
+    b = torch.zeros(16, device="cuda")
+    CB = True
+F_._conv_fwd(x, w, b, W_KOIKKK, True, THIN1, True, CONV_TC16, out_cb16=CB)
 buf = torch.zeros(4096 * 8, dtype=torch.int64, device="cuda")
 lib = _cabi.lib()
 lib.ncnet_debug_set_tc_timing.argtypes = [ctypes.c_void_p]
@@ -22,7 +33,7 @@ lib.ncnet_debug_set_tc_mode(MODE)
 lib.ncnet_debug_set_tc_timing(buf.data_ptr())
 e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 e0.record()
-F_._conv_fwd(x, w, b, W_KOIKKK, True, False, True, CONV_TC16, out_cb16=CB)
+F_._conv_fwd(x, w, b, W_KOIKKK, True, THIN1, True, CONV_TC16, out_cb16=CB)
 e1.record()
 torch.cuda.synchronize()
 print("mode", MODE, "call ms", e0.elapsed_time(e1))
@@ -59,6 +70,6 @@ print("SMs", len(by_sm), "pipe-occupied fraction (>=1 CTA between first_full and
       " sum(MMA phase)/span", round(tot_mma / tot_span, 3), " sum(CTA life)/span", round(tot_life / tot_span, 3))
 
 flat = buf.cpu().tolist()
-print("CTA 2000 producer issue :", [int(v) for v in flat[32000:32025]])
+print("CTA 2000 stamps :", [int(v) for v in flat[32000:32025]])
 print("CTA 2000 full arrival   :", [int(v) for v in flat[32100:32125]])
 print("CTA 2000 mma issued     :", [int(v) for v in flat[32200:32225]])
