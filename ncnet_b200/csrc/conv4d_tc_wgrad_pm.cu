@@ -17,6 +17,7 @@
 // flushed as per-slice partial sums in the layout unpack_wgrad_kernel reduces.
 #include "conv4d_tc.cuh"
 #include "tc_common.cuh"
+#include <cstdlib>
 
 namespace ncnet {
 
@@ -49,24 +50,37 @@ struct WgPmArgs {
     int nkb, kb0;                   // K blocks [kb0, nkb) of 16 positions
     int S, Cin, Cout, cop, stages;
     uint32_t plane_bytes;           // bytes of one haloed PM16 plane
-    uint32_t a_bytes, stage_bytes;  // A buffer / whole stage
+    int nav, ncls;                  // d2 taps (X plane variants) per CTA, CTA classes per (group, t1) = ceil(k / nav)
+    uint32_t a1_bytes;              // one X plane buffer
+    uint32_t a_bytes, stage_bytes;  // all X buffers of a stage / whole stage
     uint32_t g_off;                 // byte offset of the G plane inside the B buffer (multiple of 256)
     uint32_t b_rel;                 // byte offset, from the B buffer, of B's K position 0 (atom 0)
     uint32_t lbo_b;                 // P * 32
     uint32_t idesc, tmem_cols;
 };
 
-__device__ __forceinline__ bool pm_item(const WgPmArgs &p, int pl, int t1, int t2, int &b, size_t &ij_g, size_t &ij_x) {
-    const int PAD = p.KS / 2;
-    b = pl / (p.d1 * p.d2);
-    const int ij = pl - b * (p.d1 * p.d2);
-    const int i = ij / p.d2, j = ij - i * p.d2;
-    const int ii = i + t1 - PAD, jj = j + t2 - PAD;
-    if (ii < 0 || ii >= p.d1 || jj < 0 || jj >= p.d2) return false;
-    ij_g = (size_t)ij;
-    ij_x = (size_t)ii * p.d2 + jj;
-    return true;
-}
+// Walk over the CTA's output planes (b,i,j) without divisions in the loop (a lone lane runs ~10 cycles per instruction;
+// two integer divisions per item cost as much as ten MMAs).
+struct PmWalk {
+    int b, i, j;
+    __device__ __forceinline__ void start(const WgPmArgs &p, int pl) {
+        b = pl / (p.d1 * p.d2);
+        const int ij = pl - b * (p.d1 * p.d2);
+        i = ij / p.d2; j = ij - i * p.d2;
+    }
+    __device__ __forceinline__ void next(const WgPmArgs &p) {
+        if (++j == p.d2) { j = 0; if (++i == p.d1) { i = 0; ++b; } }
+    }
+    // mask of the CTA's d2 taps t2a+v whose X plane (i+t1-p, j+t2a+v-p) exists (0: nothing to do)
+    __device__ __forceinline__ uint32_t mask(const WgPmArgs &p, int t1, int t2a, int nv) const {
+        const int PAD = p.KS / 2;
+        const int ii = i + t1 - PAD, jj = j + t2a - PAD;
+        if (ii < 0 || ii >= p.d1) return 0u;
+        uint32_t m = 0;
+        for (int v = 0; v < nv; ++v) if (jj + v >= 0 && jj + v < p.d2) m |= 1u << v;
+        return m;
+    }
+};
 
 __global__ void __launch_bounds__(kPmThreads, 1)
 conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
@@ -75,11 +89,14 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
     __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int by = blockIdx.y;
-    const int t2 = by % p.KS; by /= p.KS;
+    // grid.x = (group, t1, tap class), grid.y = slice: the CTAs that run together walk the SAME planes with different
+    // taps, so every plane is fetched from HBM once and then served by L2 (slice-major order re-read it per tap: 20 GB)
+    int by = blockIdx.x;
+    const int cls = by % p.ncls; by /= p.ncls;
     const int t1 = by % p.KS; by /= p.KS;
+    const int t2a = cls * p.nav, nv = min(p.nav, p.KS - t2a);
     const int g = by;
-    const int s = blockIdx.x;
+    const int s = blockIdx.y;
     const int nplanes = p.B * p.d1 * p.d2;
     const int per = (nplanes + p.S - 1) / p.S;
     const int pbeg = s * per, pend = min(nplanes, pbeg + per);
@@ -113,14 +130,22 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
             uint32_t phase = 0;
             const size_t ijn = (size_t)p.d1 * p.d2;
             const size_t plane_h = p.plane_bytes / 2;
-            for (int pl = pbeg; pl < pend; ++pl) {
-                int b; size_t ij_g, ij_x;
-                if (!pm_item(p, pl, t1, t2, b, ij_g, ij_x)) continue;
+            PmWalk w;
+            w.start(p, pbeg);
+            const int PAD = p.KS / 2;
+            for (int pl = pbeg; pl < pend; ++pl, w.next(p)) {
+                const uint32_t mask = w.mask(p, t1, t2a, nv);
+                if (!mask) continue;
+                const int b = w.b;
+                const size_t ij_g = (size_t)w.i * p.d2 + w.j;
+                const long long ij_x = (long long)(w.i + t1 - PAD) * p.d2 + (w.j + t2a - PAD);
                 mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
                 const uint32_t sa = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
-                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(2u * p.plane_bytes) : "memory");
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"((uint32_t)(__popc(mask) + 1) * p.plane_bytes) : "memory");
                 const size_t bga = (size_t)b * p.GxA + (p.GxA == 1 ? 0 : g), bgb = (size_t)b * p.G + g;
-                bulk_g2s_u32(sa, p.x + (bga * ijn + ij_x) * plane_h, p.plane_bytes, fb);
+                for (int v = 0; v < nv; ++v)
+                    if ((mask >> v) & 1u)
+                        bulk_g2s_u32(sa + (uint32_t)v * p.a1_bytes, p.x + ((long long)(bga * ijn) + ij_x + v) * (long long)plane_h, p.plane_bytes, fb);
                 bulk_g2s_u32(sa + p.a_bytes + p.g_off, p.g + (bgb * ijn + ij_g) * plane_h, p.plane_bytes, fb);
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -130,26 +155,45 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
         // ===== MMA issuer: one lane, one M128 x N x K16 MMA per 16 positions =====
         if (elect_one()) {
             int stage = 0;
-            uint32_t phase = 0, acc = 0;
+            uint32_t phase = 0, inited = 0;
             // descriptor high word: SBO = 256 B (K atoms), version 1, SWIZZLE_32B (layout type 6 at bits 61-63)
             const uint64_t hi = (uint64_t)((256u >> 4) | (1u << 14) | (6u << 29)) << 32;
             const uint32_t lbo_a = (32u >> 4) << 16, lbo_b = (p.lbo_b >> 4) << 16;
             const int nk = p.nkb - p.kb0;
-            for (int pl = pbeg; pl < pend; ++pl) {
-                int b; size_t ij_g, ij_x;
-                if (!pm_item(p, pl, t1, t2, b, ij_g, ij_x)) continue;
+            const uint32_t a1 = p.a1_bytes >> 4, n = (uint32_t)p.N;
+            PmWalk w;
+            w.start(p, pbeg);
+            for (int pl = pbeg; pl < pend; ++pl, w.next(p)) {
+                const uint32_t mask = w.mask(p, t1, t2a, nv);
+                if (!mask) continue;
                 mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t sa4 = (sm0 + (uint32_t)stage * p.stage_bytes) >> 4;
                 uint32_t a_lo = lbo_a | (sa4 + (uint32_t)p.kb0 * 32u);                                  // 16 positions = 512 B
                 uint32_t b_lo = lbo_b | (sa4 + ((p.a_bytes + p.b_rel) >> 4) + (uint32_t)p.kb0 * 32u);
-                umma_f16(tmem_base, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, acc);
-                acc = 1u;
+                if (mask == 3u) {
+                    // both d2 taps: K-block-major, the two MMAs of a block share the grad descriptor
+                    const uint32_t acc0 = inited & 1u, acc1 = (inited >> 1) & 1u;
+                    umma_f16(tmem_base, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, acc0);
+                    umma_f16(tmem_base + n, hi | (uint64_t)(a_lo + a1), hi | (uint64_t)b_lo, p.idesc, acc1);
+#pragma unroll 4
+                    for (int kb = 1; kb < nk; ++kb) {
+                        a_lo += 32u; b_lo += 32u;
+                        umma_f16(tmem_base, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, 1u);
+                        umma_f16(tmem_base + n, hi | (uint64_t)(a_lo + a1), hi | (uint64_t)b_lo, p.idesc, 1u);
+                    }
+                } else {
+                    const uint32_t v = mask >> 1;            // the single live variant (mask is 1 or 2)
+                    const uint32_t d = tmem_base + v * n;
+                    a_lo += v * a1;
+                    umma_f16(d, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, (inited >> v) & 1u);
 #pragma unroll 8
-                for (int kb = 1; kb < nk; ++kb) {
-                    a_lo += 32u; b_lo += 32u;
-                    umma_f16(tmem_base, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, 1u);
+                    for (int kb = 1; kb < nk; ++kb) {
+                        a_lo += 32u; b_lo += 32u;
+                        umma_f16(d, hi | (uint64_t)a_lo, hi | (uint64_t)b_lo, p.idesc, 1u);
+                    }
                 }
+                inited |= mask;
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
                              ::"r"(empty0 + (uint32_t)stage * 8u) : "memory");
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -162,24 +206,28 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
         const int q = warp & 3;
         mbar_wait(&accum_bar, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        bool any = false;       // a slice whose every plane pair is out of range issued no MMA: its partials stay zero
-        for (int pl = pbeg; pl < pend && !any; ++pl) {
-            int b; size_t ij_g, ij_x;
-            any = pm_item(p, pl, t1, t2, b, ij_g, ij_x);
+        uint32_t live = 0;      // accumulators the issuer wrote (same walk); untouched ones hold garbage, their partials stay zero
+        {
+            PmWalk w;
+            w.start(p, pbeg);
+            for (int pl = pbeg; pl < pend && live != (1u << nv) - 1u; ++pl, w.next(p)) live |= w.mask(p, t1, t2a, nv);
         }
         const int KS = p.KS;
         const int m = q * 32 + lane, t4 = m >> 4, c = m & 15;
-        if (any && q * 2 < KS) {          // warp q holds taps 2q and 2q+1
+        if (q * 2 < KS) {          // warp q holds taps 2q and 2q+1
             const size_t per_group = (size_t)p.Cin * KS * KS * KS * KS * p.cop;
             float *dst = p.part + ((size_t)s * p.G + g) * per_group;
-            for (int n0 = 0; n0 < p.N; n0 += 16) {
-                float v[16];
-                tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)n0, v);
-                const int t3 = KS - 1 - (n0 >> 4);
-                if (t4 < KS && c < p.Cin) {
-                    float *row = dst + (((((size_t)c * KS + t1) * KS + t2) * KS + t3) * KS + t4) * p.cop;
+            for (int v = 0; v < nv; ++v) {
+                if (!((live >> v) & 1u)) continue;
+                for (int n0 = 0; n0 < p.N; n0 += 16) {
+                    float val[16];
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(v * p.N + n0), val);
+                    const int t3 = KS - 1 - (n0 >> 4);
+                    if (t4 < KS && c < p.Cin) {
+                        float *row = dst + (((((size_t)c * KS + t1) * KS + (t2a + v)) * KS + t3) * KS + t4) * p.cop;
 #pragma unroll
-                    for (int o = 0; o < 16; ++o) if (o < p.Cout) row[o] = v[o];
+                        for (int o = 0; o < 16; ++o) if (o < p.Cout) row[o] = val[o];
+                    }
                 }
             }
         }
@@ -193,8 +241,8 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
 
 struct WgPmPlan {
     bool ok;
-    int N, nkb, kb0, stages;
-    uint32_t plane_bytes, a_bytes, stage_bytes, g_off, b_rel, lbo_b, tmem_cols;
+    int N, nkb, kb0, stages, nav, ncls;
+    uint32_t plane_bytes, a1_bytes, a_bytes, stage_bytes, g_off, b_rel, lbo_b, tmem_cols;
     size_t smem;
 };
 
@@ -217,19 +265,28 @@ static WgPmPlan pm_plan(int d3, int d4, int k) {
     const int reach = w.nkb * 16 + pad * P + pad;
     const int npos_b = up8(g_off_pos + (npos > reach ? npos : reach));
     w.plane_bytes = (uint32_t)npos * 32u;
-    w.a_bytes = (uint32_t)npos_a * 32u;
+    w.a1_bytes = (uint32_t)npos_a * 32u;
     w.g_off = (uint32_t)g_off_pos * 32u;
     w.b_rel = (uint32_t)(g_off_pos - pad * P + pad) * 32u;
     w.lbo_b = (uint32_t)P * 32u;
     if ((w.lbo_b >> 4) > 16383u) return w;
-    w.stage_bytes = ((w.a_bytes + (uint32_t)npos_b * 32u + 1023u) / 1024u) * 1024u;
-    int stages = (int)((220u * 1024u) / w.stage_bytes);
-    if (stages > kPmStages) stages = kPmStages;
-    if (stages < 2) return w;
-    w.stages = stages;
-    w.smem = (size_t)stages * w.stage_bytes;
+    // two d2 taps per CTA (one grad plane staged per two X planes: the kernel is close to the L2->shared ceiling) when a
+    // 2-deep ring of such stages fits; else one tap and a deeper ring
     w.N = 16 * k;
-    w.tmem_cols = w.N <= 32 ? 32 : (w.N <= 64 ? 64 : 128);
+    const char *env = getenv("NCNET_WG_NAV");      // development knob
+    for (w.nav = (env && env[0] == '1') ? 1 : 2; w.nav >= 1; --w.nav) {
+        w.a_bytes = (uint32_t)w.nav * w.a1_bytes;
+        w.stage_bytes = ((w.a_bytes + (uint32_t)npos_b * 32u + 1023u) / 1024u) * 1024u;
+        int stages = (int)((220u * 1024u) / w.stage_bytes);
+        if (stages > kPmStages) stages = kPmStages;
+        w.stages = stages;
+        if (stages >= 2 && w.nav * w.N <= 512) break;
+    }
+    if (w.nav < 1) return w;
+    w.ncls = (k + w.nav - 1) / w.nav;
+    w.smem = (size_t)w.stages * w.stage_bytes;
+    const int cols = w.nav * w.N;
+    w.tmem_cols = cols <= 32 ? 32 : (cols <= 64 ? 64 : (cols <= 128 ? 128 : (cols <= 256 ? 256 : 512)));
     w.ok = true;
     return w;
 }
@@ -262,13 +319,14 @@ int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, float *part, 
     a.x = x_pm; a.g = g_pm; a.part = part;
     a.B = B; a.G = G; a.GxA = GxA; a.d1 = d1; a.d2 = d2; a.KS = k; a.N = w.N;
     a.nkb = w.nkb; a.kb0 = w.kb0; a.S = S; a.Cin = Cin; a.Cout = Cout; a.cop = cop; a.stages = w.stages;
-    a.plane_bytes = w.plane_bytes; a.a_bytes = w.a_bytes; a.stage_bytes = w.stage_bytes;
+    a.plane_bytes = w.plane_bytes; a.a1_bytes = w.a1_bytes; a.a_bytes = w.a_bytes; a.stage_bytes = w.stage_bytes;
+    a.nav = w.nav; a.ncls = w.ncls;
     a.g_off = w.g_off; a.b_rel = w.b_rel; a.lbo_b = w.lbo_b; a.tmem_cols = w.tmem_cols;
     // D = f32, A = B = f16, both MN-major (bits 15/16), N>>3 at bit 17, M = 128 -> 8 at bit 24
     a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     cudaError_t e = cudaFuncSetAttribute(conv4d_tc_wgrad_pm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)w.smem);
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc,pm): smem attribute: %s", cudaGetErrorString(e));
-    dim3 grid(S, G * k * k);
+    dim3 grid(G * k * w.ncls, S);
     conv4d_tc_wgrad_pm_kernel<<<grid, kPmThreads, w.smem, st>>>(a);
     NC_LAUNCH_OK("conv4d_tc_wgrad_pm_kernel");
     return 0;
