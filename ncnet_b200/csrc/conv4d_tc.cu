@@ -57,6 +57,7 @@ struct TcArgs {
     int aoff[kMaxKSteps];   // A row offset (positions) per K-step
     int gshift[kMaxGroups]; // epilogue row shift per column group
     uint32_t stage_bytes, data_bytes, w_bytes;
+    uint32_t mask_off;      // CB16 mask: byte offset of its staging area in dynamic smem (0 = read it from global)
     long long *dbg;         // development only: per-CTA phase timestamps (8 per CTA) or null
     int dbg_mode;           // development only: 1 = no weight copies, 2 = no MMAs, 3 = no activation copies (results wrong)
 };
@@ -141,7 +142,7 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
 __global__ void __launch_bounds__(kTcThreads, 2)
 conv4d_tc_kernel(const TcArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar;
+    __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar, mask_bar;
     __shared__ uint32_t tmem_base_s;
     __shared__ int s_gshift[kMaxGroups];
 
@@ -171,6 +172,7 @@ conv4d_tc_kernel(const TcArgs p) {
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
         mbar_init(&accum_bar, 1);
+        mbar_init(&mask_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {    // TMEM: NT accumulator tiles (256 columns or fewer lets two CTAs share the SM)
@@ -221,6 +223,15 @@ conv4d_tc_kernel(const TcArgs p) {
         const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
         const uint32_t empty0 = smem_u32_pinned(&empty_bar[0]);
         if (elect_one()) {
+        if (p.mask_mode == 3 && p.mask_off) {
+            // the ReLU mask of this chunk's output rows (dgrad): staged now, read by the epilogue from shared memory
+            const uint32_t mbytes = (uint32_t)rows_out * p.P * 16u, mb = smem_u32(&mask_bar);
+            const __half *msrc = (const __half *)p.mask +
+                ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8 + (size_t)(k0 + PAD) * p.P * 8;
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mb), "r"(2u * mbytes) : "memory");
+            bulk_g2s_u32(sm0 + p.mask_off, msrc, mbytes, mb);
+            bulk_g2s_u32(sm0 + p.mask_off + mbytes, msrc + ij_count * plane_cb * 8, mbytes, mb);
+        }
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
             if (ii < 0 || ii >= p.d1) continue;
@@ -377,6 +388,9 @@ conv4d_tc_kernel(const TcArgs p) {
             const size_t base_off = ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8;
             __half *ob = (__half *)p.out + base_off;
             const __half *mb = (const __half *)p.mask + base_off;
+            const bool smem_mask = p.mask_mode == 3 && p.mask_off;
+            const uint32_t mbytes = (uint32_t)rows_out * p.P * 16u;
+            if (smem_mask) mbar_wait(&mask_bar, 0);
             for (int e = et; e < 2 * npos; e += 128) {
                 const int half = e / npos, pp = e - half * npos;
                 const int kk = ra + pp / p.P, ll = pp % p.P;
@@ -388,7 +402,8 @@ conv4d_tc_kernel(const TcArgs p) {
                     const float4 a = lds_v4(src), c = lds_v4(src + 16u);
                     float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
                     if (p.mask_mode == 3) {
-                        const uint4 mraw = *reinterpret_cast<const uint4 *>(mb + goff);
+                        const uint4 mraw = smem_mask ? lds_u4(osm + p.mask_off + (uint32_t)half * mbytes + (uint32_t)(kr * p.P + ll) * 16u)
+                                                     : *reinterpret_cast<const uint4 *>(mb + goff);
                         const __half *mh = reinterpret_cast<const __half *>(&mraw);
 #pragma unroll
                         for (int c8 = 0; c8 < 8; ++c8) if (!(__half2float(mh[c8]) > 0.f)) v[c8] = 0.f;
@@ -576,6 +591,63 @@ cb16_pack_rows_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, i
     }
 }
 
+// Rows wider than a warp: the same warp-per-row mapping walked in 32-column segments, direct (L1-served) tap loads.
+template <typename T>
+__global__ void __launch_bounds__(256)
+cb16_pack_wide_rows_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1, int d2, int d3, int d4, int pad,
+                      int tap_mode, int taps) {
+    const unsigned blk = blockIdx.y;
+    const int half = blockIdx.z;
+    const int P = d4 + 2 * pad, rows = d3 + 2 * pad;
+    const unsigned ij = (unsigned)(d1 * d2), nrows = ij * (unsigned)rows;
+    const size_t plane = (size_t)d3 * d4, vol = (size_t)ij * plane;
+    const int lane = threadIdx.x & 31;
+    const unsigned r = blockIdx.x * 8u + (threadIdx.x >> 5);
+    if (r >= nrows) return;
+    const unsigned ijx = r / (unsigned)rows;
+    const int kk = (int)(r - ijx * (unsigned)rows);
+    const int k = kk - pad;
+    const size_t npad = (size_t)nrows * P;
+    __half *dst = cb + (((size_t)blk * 2 + half) * npad + (size_t)r * P) * 8;
+    for (int ll0 = 0; ll0 < P; ll0 += 32) {
+        const int ll = ll0 + lane, l = ll - pad;
+        const bool inside = k >= 0 && k < d3 && l >= 0 && l < d4;
+        __align__(16) __half v[8];
+#pragma unroll
+        for (int c = 0; c < 8; ++c) v[c] = __float2half_rn(0.f);
+        if (tap_mode == 1 || tap_mode == 3) {
+            const int ks = tap_mode == 3 ? k + half : k;
+            const bool row_ok = ks >= 0 && ks < d3;
+            const T *xr = x + (size_t)blk * vol + (size_t)ijx * plane + (size_t)(row_ok ? ks : 0) * d4;
+            if (row_ok && (tap_mode == 3 || inside)) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int col = ll - 2 * pad + c;
+                    if (c < taps && col >= 0 && col < d4) v[c] = __float2half_rn(ldf(xr + col));
+                }
+            }
+        } else if (inside) {
+            const size_t pos = (size_t)ijx * plane + (size_t)k * d4 + l;
+            if (tap_mode == 0) {
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int ch = half * 8 + c;
+                    if (ch < C) v[c] = __float2half_rn(ldf(x + ((size_t)blk * C + ch) * vol + pos));
+                }
+            } else {
+                const int jx = (int)(ijx % (unsigned)d2);
+#pragma unroll
+                for (int c = 0; c < 8; ++c) {
+                    const int t = half * 8 + c, jt = jx - t + pad;
+                    if (t < taps && jt >= 0 && jt < d2)
+                        v[c] = __float2half_rn(ldf(x + (size_t)blk * vol + pos + (ptrdiff_t)(pad - t) * (ptrdiff_t)plane));
+                }
+            }
+        }
+        if (ll < P) *reinterpret_cast<uint4 *>(dst + (size_t)ll * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
 // CB16 -> planar [nblk, C, vol] (T); interior only
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -608,14 +680,17 @@ int cb16_pack(const void *x, int dtype, void *cb, int nblk, int C, int d1, int d
     // tap modes 1 and 2 put at most k <= 8 taps into the channels: the second channel half is never read
     const int halves = (tap_mode == 1 || tap_mode == 2) ? 1 : 2;
     NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "cb16_pack: source dtype %d must be planar fp32/fp16", dtype);
-    if (d4 + 2 * pad <= 32) {
-        const size_t nrows = (size_t)d1 * d2 * (d3 + 2 * pad);
-        NC_CHECK((nrows + 7) / 8 < (1ull << 31), "cb16_pack: too many rows");
+    const size_t nrows = (size_t)d1 * d2 * (d3 + 2 * pad);
+    if ((nrows + 7) / 8 < (1ull << 31)) {
         dim3 grid((unsigned)((nrows + 7) / 8), nblk, halves);
-        if (dtype == NCNET_F32)
-            cb16_pack_rows_kernel<float><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
-        else
-            cb16_pack_rows_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+        const bool narrow = d4 + 2 * pad <= 32;
+        if (dtype == NCNET_F32) {
+            if (narrow) cb16_pack_rows_kernel<float><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+            else cb16_pack_wide_rows_kernel<float><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+        } else {
+            if (narrow) cb16_pack_rows_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+            else cb16_pack_wide_rows_kernel<__half><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, C, d1, d2, d3, d4, pad, tap_mode, k);
+        }
         NC_LAUNCH_OK("cb16_pack_rows_kernel");
         return 0;
     }
@@ -692,12 +767,12 @@ int g_tc_debug_mode = 0;
 struct TcPlan {
     int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages;
     uint32_t tmem_cols;
-    uint32_t data_bytes, w_bytes, stage_bytes;
+    uint32_t data_bytes, w_bytes, stage_bytes, mask_off;
     size_t smem_bytes;
     bool ok;
 };
 
-static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
+static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask = false) {
     TcPlan pl{};
     pl.ok = false;
     if (Cin_e > 16 || Cout_e > 16 || (k != 3 && k != 5)) return pl;
@@ -727,6 +802,12 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4) {
         const size_t outb = o.CoutPad >= 16 ? (size_t)NT * 128 * kOutStride * sizeof(float) : (size_t)NT * 128 * o.NG * sizeof(float);
         size_t smem = (size_t)stages * stage;
         if (smem < outb) smem = outb;                        // the output plane aliases the ring
+        smem = (smem + 127) / 128 * 128;
+        o.mask_off = 0;
+        if (cb_mask) {                                       // staging area for the chunk's CB16 ReLU mask
+            o.mask_off = (uint32_t)smem;
+            smem += ((size_t)2 * R * o.P * 16 + 127) / 128 * 128;
+        }
         if (smem > max_smem) return false;
         o.R = R; o.NT = NT; o.npos_pad = npos; o.data_bytes = data; o.stage_bytes = stage; o.smem_bytes = smem;
         o.stages = stages;
@@ -782,7 +863,7 @@ bool conv4d_tc_supports(int Cin_e, int Cout_e, int k, int d3, int d4) { return t
 static int run_tc(const void *x, int x_dtype, const float *w, const float *bias, const void *mask, int mask_dtype, void *y,
                   int y_dtype, void *scratch, PackDesc d, int B, int Gx, int d1, int d2, int d3, int d4, int relu,
                   cudaStream_t st) {
-    const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4);
+    const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4, mask && mask_dtype == NCNET_CB16);
     if (!pl.ok) return 2;
     if (x_dtype == NCNET_CB16 && pl.mode == 3) return 2;        // the tap im2col needs the planar single-channel input
     if (y_dtype == NCNET_CB16 && pl.CoutPad < 16) return 2;
@@ -815,7 +896,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     a.npos_pad = pl.npos_pad; a.relu = relu; a.stages = pl.stages; a.tmem_cols = pl.tmem_cols;
     a.out_mode = y_dtype == NCNET_CB16 ? 2 : (y_dtype == NCNET_F16 ? 1 : 0);
     a.mask_mode = !mask ? 0 : (mask_dtype == NCNET_CB16 ? 3 : (mask_dtype == NCNET_F16 ? 2 : 1));
-    a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes;
+    a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes; a.mask_off = pl.mask_off;
     a.dbg = g_tc_debug_buffer;
     a.dbg_mode = g_tc_debug_mode;
     // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
