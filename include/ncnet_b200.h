@@ -157,6 +157,9 @@ int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, fl
  * entirely on the tensor-core kernels in TC16 mode (forward, dgrad and wgrad), i.e. can take and
  * produce CB16 activations; otherwise TC16 mode routes it to the CUDA-core kernels (planar only). */
 int ncnet_conv4d_tc_supported(int Cin, int Cout, int k, int d3, int d4);
+/* Forward only (inference): 1 when ncnet_conv4d_fwd can take and produce NCNET_CB16 for this layer shape, even if the
+ * tensor-core dgrad / wgrad envelope (whole planes staged in shared memory) does not cover it. */
+int ncnet_conv4d_tc_fwd_supported(int Cin, int Cout, int k, int d3, int d4);
 
 /* CB16 helpers: byte size of a tensor of `nblk` 16-channel blocks; conversion from / to the planar
  * reference layout [nblk, C, d1,d2,d3,d4] (C <= 16, dtype NCNET_F32/F16). */

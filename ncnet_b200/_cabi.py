@@ -43,6 +43,7 @@ SIGNATURES = {
     "ncnet_conv4d_wgrad_scratch_bytes": (_sz, [_i] * 10),
     "ncnet_conv4d_wgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 14 + [_p]),
     "ncnet_conv4d_tc_supported": (_i, [_i] * 5),
+    "ncnet_conv4d_tc_fwd_supported": (_i, [_i] * 5),
     "ncnet_cb16_bytes": (_sz, [_i] * 6),
     "ncnet_cb16_pack": (_i, [_p, _p] + [_i] * 8 + [_p]),
     "ncnet_cb16_unpack": (_i, [_p, _p] + [_i] * 8 + [_p]),

@@ -120,6 +120,11 @@ extern "C" int ncnet_conv4d_tc_supported(int Cin, int Cout, int k, int d3, int d
     return fwd && bwd && wg ? 1 : 0;
 }
 
+extern "C" int ncnet_conv4d_tc_fwd_supported(int Cin, int Cout, int k, int d3, int d4) {
+    if (Cin < 1 || Cout < 1 || (k != 3 && k != 5) || d3 < 1 || d4 < 1) return 0;
+    return conv4d_tc_supports(Cin, Cout, k, d3, d4) ? 1 : 0;
+}
+
 extern "C" size_t ncnet_cb16_bytes(int nblk, int d1, int d2, int d3, int d4, int k) {
     return cb16_bytes((size_t)nblk, d1, d2, d3, d4, k);
 }

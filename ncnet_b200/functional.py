@@ -380,15 +380,16 @@ def conv4d(data: torch.Tensor, filters: torch.Tensor, bias: Optional[torch.Tenso
     return _Conv4dFn.apply(data, filters, bias, layout, default_conv_mode() if mode is None else mode)
 
 
-def _stack_can_chain(kernel_sizes, chans, d3, d4, mode) -> bool:
+def _stack_can_chain(kernel_sizes, chans, d3, d4, mode, need_backward=True) -> bool:
     """True when every layer of the stack can hand its activations to the next one in CB16
-    (tensor-core mode, one kernel size, <= 16 channels per group)."""
+    (tensor-core mode, one kernel size, <= 16 channels per group).  Inference only needs the forward envelope."""
     if mode != CONV_TC16 or len(set(kernel_sizes)) != 1 or len(kernel_sizes) < 2:
         return False
     L = _cabi.lib()
+    ok = L.ncnet_conv4d_tc_supported if need_backward else L.ncnet_conv4d_tc_fwd_supported
     cin = 1
     for cout in chans:
-        if not L.ncnet_conv4d_tc_supported(cin, cout, kernel_sizes[0], d3, d4):
+        if not ok(cin, cout, kernel_sizes[0], d3, d4):
             return False
         cin = cout
     return True
@@ -401,12 +402,13 @@ class _NeighConsensusFn(torch.autograd.Function):
     launches.  Returns [B, G*Clast, ...] (G=2 branches when symmetric; the caller sums them)."""
 
     @staticmethod
-    def forward(ctx, x, symmetric, mode, *wb):
+    def forward(ctx, x, symmetric, mode, train, *wb):
         n_layers = len(wb) // 2
         xc = x.contiguous()
         w32s = [wb[2 * l].detach().float().contiguous() for l in range(n_layers)]
         b32s = [wb[2 * l + 1].detach().float().contiguous() for l in range(n_layers)]
-        chain = _stack_can_chain([w.shape[0] for w in w32s], [w.shape[1] for w in w32s], xc.shape[4], xc.shape[5], mode)
+        chain = _stack_can_chain([w.shape[0] for w in w32s], [w.shape[1] for w in w32s], xc.shape[4], xc.shape[5], mode,
+                                 need_backward=train)
         acts = [xc]
         cur = xc
         for l in range(n_layers):
@@ -447,7 +449,7 @@ class _NeighConsensusFn(torch.autograd.Function):
                 if isinstance(gz, _CB16):       # merged 2*Cout -> Cin gradient runs on the CUDA-core kernel (planar)
                     gz = cb16_unpack(gz, w32s[0].shape[1])
                 gx = _conv_dgrad(gz, w32s[0], None, W_KOIKKK, sym, True, mode)
-        return (gx, None, None, *grads)
+        return (gx, None, None, None, *grads)
 
 
 def neigh_consensus_branches(x: torch.Tensor, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor],
@@ -457,7 +459,9 @@ def neigh_consensus_branches(x: torch.Tensor, weights: Sequence[torch.Tensor], b
     wb = []
     for w, b in zip(weights, biases):
         wb += [w, b]
-    return _NeighConsensusFn.apply(x, bool(symmetric), default_conv_mode() if mode is None else mode, *wb)
+    # inference (no gradient will be asked for) only needs the forward envelope to keep the activations in CB16
+    train = torch.is_grad_enabled() and any(t.requires_grad for t in (x, *wb))
+    return _NeighConsensusFn.apply(x, bool(symmetric), default_conv_mode() if mode is None else mode, train, *wb)
 
 
 # ------------------------------------------------------------------------------------------- #
