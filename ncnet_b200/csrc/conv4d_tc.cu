@@ -20,7 +20,10 @@
 //   mode M1 (Cin<=16, Cout>1): channels = input channels, N = (d4, o), K-steps per plane = d3 taps
 //   mode M2 (Cout == 1)      : channels = input channels, N = (d3, d4), one K-step per plane
 //   mode M3 (Cin == 1)       : channels = two consecutive d3 taps x the k d4 taps (im2col in the pack
-//                              kernel), N = (d3 pair, o), one K-step per plane
+//                              kernel), N = (d3 pair, o), one K-step per plane   (kept for comparison: NCNET_TC_M3=1)
+//   mode M4 (Cin == 1)       : channels = the (d2,d4) taps, 16 per channel block (k=5: 25 taps in 2 blocks; k=3: 9 in 1),
+//                              so a staged plane carries every d2 tap: 5x2 stages per output plane instead of 25;
+//                              K-steps = d3 taps (row-shifted views), N = 16 out-channels, no shifted-sum epilogue
 // Pipeline: one elected lane of warp 0 streams the (d1,d2) planes + their weight slab with
 // cp.async.bulk (TMA engine, mbarrier complete_tx) through a 3-stage ring; one elected lane of warp 1
 // issues tcgen05.mma and commits to the stage's "empty" barrier; warps 2-5 drain TMEM (tcgen05.ld),
@@ -28,6 +31,7 @@
 #include "conv4d_tc.cuh"
 #include "conv4d_common.cuh"
 #include "tc_common.cuh"
+#include <cstdlib>
 
 namespace ncnet {
 
@@ -47,6 +51,7 @@ struct TcArgs {
     int d1, d2, d3, d4, KS, P;
     int R, nchunks;         // output k-rows per CTA, chunks per plane
     int NT, N, NG, KSTEPS;
+    int inner, m4;          // inner stage loop: the k d2 taps, or (mode M4) the channel blocks of the (d2,d4) taps
     int npos_pad;           // positions per channel-half in a smem stage
     int stages;             // ring depth (2 or 3)
     uint32_t tmem_cols;     // TMEM columns to allocate (power of two >= NT*N)
@@ -90,7 +95,8 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
 #pragma unroll
     for (int t = 0; t < NTM; ++t) d_col[t] = tmem_base + (uint32_t)(t * p.N);
     // staged (d1,d2) planes of this CTA (the producer skips the out-of-range ones the same way)
-    const int nplanes = (min(i + PAD, p.d1 - 1) - max(i - PAD, 0) + 1) * (min(j + PAD, p.d2 - 1) - max(j - PAD, 0) + 1);
+    const int nplanes = (min(i + PAD, p.d1 - 1) - max(i - PAD, 0) + 1) *
+                        (p.m4 ? p.inner : min(j + PAD, p.d2 - 1) - max(j - PAD, 0) + 1);
     const uint32_t full0 = smem_u32_pinned(full_bar), empty0 = smem_u32_pinned(empty_bar);
     if (elect_one()) {                      // one lane runs the whole loop: no per-stage election / reconvergence
         for (int it = 0; it < nplanes; ++it) {
@@ -215,10 +221,12 @@ conv4d_tc_kernel(const TcArgs p) {
         const uint32_t tx_bytes = (p.dbg_mode == 3 ? 0u : 2u * half_bytes) + (p.dbg_mode == 1 ? 0u : p.w_bytes);
         const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
         const size_t plane_halves = plane_cb * 8;
-        const __half *src_base = p.act + (bg * 2 * ij_count * plane_cb + (size_t)k0 * p.P) * 8;
+        // mode M4: the inner index selects the channel block (tensor block bg*inner + t2) of the SAME plane column j
+        const size_t blk_halves = 2 * ij_count * plane_halves;
+        const __half *src_base = p.act + (size_t)(p.m4 ? bg * p.inner : bg) * blk_halves + (size_t)k0 * p.P * 8;
         const size_t half_off = ij_count * plane_halves;
         const uint32_t w_halves = p.w_bytes / 2;
-        const __half *w_base = p.wp + (size_t)g * p.KS * p.KS * w_halves;
+        const __half *w_base = p.wp + (size_t)g * p.KS * p.inner * w_halves;
         const uint32_t sm0 = smem_u32_pinned(stage0), full0 = smem_u32_pinned(&full_bar[0]);
         const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
         const uint32_t empty0 = smem_u32_pinned(&empty_bar[0]);
@@ -235,19 +243,19 @@ conv4d_tc_kernel(const TcArgs p) {
         for (int t1 = 0; t1 < p.KS; ++t1) {
             const int ii = i + t1 - PAD;
             if (ii < 0 || ii >= p.d1) continue;
-            for (int t2 = 0; t2 < p.KS; ++t2) {
-                const int jj = j + t2 - PAD;
+            for (int t2 = 0; t2 < p.inner; ++t2) {
+                const int jj = p.m4 ? j : j + t2 - PAD;
                 if (jj < 0 || jj >= p.d2) continue;
                 mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
                 {
                     const uint32_t sb = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
                     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(tx_bytes) : "memory");
-                    const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves;
+                    const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves + (p.m4 ? (size_t)t2 * blk_halves : 0);
                     if (p.dbg_mode != 3) {
                         bulk_g2s_u32(sb, src0, half_bytes, fb);
                         bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
                     }
-                    if (p.dbg_mode != 1) bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.KS + t2) * w_halves, p.w_bytes, fb);
+                    if (p.dbg_mode != 1) bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.inner + t2) * w_halves, p.w_bytes, fb);
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -648,6 +656,111 @@ cb16_pack_wide_rows_kernel(const T *__restrict__ x, __half *__restrict__ cb, int
     }
 }
 
+// tap_mode 4 (forward mode M4): single-channel planar [nblk, vol] -> nblk*ngrp CB16 blocks.  Channel c of block
+// (blk, gr) at haloed position (i, j, kk, ll) is the (d2,d4) tap (t2,t4) = divmod(gr*16 + c, k):
+//     x[blk, i, j + t2 - p, kk - p, ll + t4 - p]          (zero outside the volume or for gr*16 + c >= k*k),
+// i.e. the d4 tap is taken relative to the column index ll itself, so a row-shifted view (the d3 taps) of this
+// plane lines up with the output position (kr, lc) at row kr + t3, column lc.  One warp per haloed row.
+template <typename T, int k>
+__global__ void __launch_bounds__(256)
+cb16_pack_taps2d_kernel(const T *__restrict__ x, __half *__restrict__ cb, int d1, int d2, int d3, int d4) {
+    constexpr int pad = k / 2, ngrp = (k * k + 15) / 16;          // compile-time: the tap divisions below fold away
+    const unsigned blk_out = blockIdx.y;
+    const unsigned blk = blk_out / (unsigned)ngrp;
+    const int gr = (int)(blk_out - blk * (unsigned)ngrp), half = blockIdx.z;
+    const int P = d4 + 2 * pad, rows = d3 + 2 * pad;
+    const unsigned ij = (unsigned)(d1 * d2), nrows = ij * (unsigned)rows;
+    const size_t plane = (size_t)d3 * d4, vol = (size_t)ij * plane;
+    const int lane = threadIdx.x & 31;
+    const unsigned r = blockIdx.x * 8u + (threadIdx.x >> 5);
+    if (r >= nrows) return;
+    const unsigned ijx = r / (unsigned)rows;
+    const int kk = (int)(r - ijx * (unsigned)rows), kq = kk - pad;
+    const int jx = (int)(ijx % (unsigned)d2);
+    __half *dst = cb + (((size_t)blk_out * 2 + half) * ((size_t)nrows * P) + (size_t)r * P) * 8;
+    const bool row_ok = kq >= 0 && kq < d3;
+    const T *xrow = x + (size_t)blk * vol + (size_t)ijx * plane + (size_t)(row_ok ? kq : 0) * d4;
+    // the 8 channels of this thread: tap offsets and plane pointers are the same for every column of the row
+    int lt0[8];
+    const T *src[8];
+#pragma unroll
+    for (int c8 = 0; c8 < 8; ++c8) {
+        const int c = gr * 16 + half * 8 + c8;
+        const int t2 = c / k, t4 = c - t2 * k;
+        const int jt = jx + t2 - pad;
+        const bool ok = row_ok && c < k * k && jt >= 0 && jt < d2;
+        lt0[c8] = ok ? t4 - pad : -(1 << 20);                      // pushes the column out of range when the tap is invalid
+        src[c8] = xrow + (ok ? (ptrdiff_t)(t2 - pad) * (ptrdiff_t)plane : 0);
+    }
+    for (int ll = lane; ll < P; ll += 32) {
+        __align__(16) __half v[8];
+#pragma unroll
+        for (int c8 = 0; c8 < 8; ++c8) {
+            const int lt = ll + lt0[c8];
+            v[c8] = __float2half_rn((lt >= 0 && lt < d4) ? ldf(src[c8] + lt) : 0.f);
+        }
+        *reinterpret_cast<uint4 *>(dst + (size_t)ll * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
+// Narrow rows (P <= 32) of tap_mode 4: block = one (i,j) plane of one (output block, channel half); the eight
+// channels' (d2,d4) taps are compile-time (BASE = first tap of this channel octet), each source row segment is loaded
+// once per d2 tap and handed to the channels with shuffles.
+template <typename T, int k, int BASE>
+__device__ __forceinline__ void taps2d_rows(const T *__restrict__ xp, __half *__restrict__ dst, int jx, int d2, int d3, int d4,
+                                            size_t plane, int warp, int lane) {
+    constexpr int pad = k / 2, T2A = BASE / k;
+    const int P = d4 + 2 * pad, rows = d3 + 2 * pad;
+    const int col = lane - pad;
+    const bool col_ok = col >= 0 && col < d4;
+    for (int kk = warp; kk < rows; kk += 8) {
+        const int kq = kk - pad;
+        const bool row_ok = kq >= 0 && kq < d3;
+        float e[3];
+#pragma unroll
+        for (int u = 0; u < 3; ++u) {
+            const int jt = jx + T2A + u - pad;
+            e[u] = (row_ok && col_ok && T2A + u < k && jt >= 0 && jt < d2)
+                       ? ldf(xp + (ptrdiff_t)(T2A + u - pad) * (ptrdiff_t)plane + (size_t)kq * d4 + col) : 0.f;
+        }
+        __align__(16) __half v[8];
+#pragma unroll
+        for (int c8 = 0; c8 < 8; ++c8) {
+            constexpr int dummy = 0; (void)dummy;
+            const int c = BASE + c8;                     // compile-time after unrolling
+            const int t2 = c / k, t4 = c - t2 * k;
+            float o = 0.f;
+            if (c < k * k) {
+                const int srcl = lane + t4;              // column (lane + t4 - p) is held by lane (lane + t4)
+                const float got = __shfl_sync(0xffffffffu, e[t2 - T2A], srcl & 31);
+                o = srcl < 32 ? got : 0.f;
+            }
+            v[c8] = __float2half_rn(o);
+        }
+        if (lane < P) *reinterpret_cast<uint4 *>(dst + ((size_t)kk * P + lane) * 8) = *reinterpret_cast<const uint4 *>(v);
+    }
+}
+
+template <typename T, int k>
+__global__ void __launch_bounds__(256)
+cb16_pack_taps2d_narrow_kernel(const T *__restrict__ x, __half *__restrict__ cb, int d1, int d2, int d3, int d4) {
+    constexpr int pad = k / 2, ngrp = (k * k + 15) / 16;
+    const int jx = blockIdx.x, ix = blockIdx.y;
+    const unsigned z = blockIdx.z, blk_out = z >> 1, half = z & 1u;
+    const unsigned blk = blk_out / ngrp, gr = blk_out - blk * ngrp;
+    const int P = d4 + 2 * pad, rows = d3 + 2 * pad;
+    const size_t ij = (size_t)d1 * d2, plane = (size_t)d3 * d4;
+    const size_t ijx = (size_t)ix * d2 + jx;
+    const T *xp = x + ((size_t)blk * ij + ijx) * plane;
+    __half *dst = cb + ((((size_t)blk_out * 2 + half) * ij + ijx) * rows * P) * 8;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int base = (int)(gr * 16 + half * 8);
+    if (base == 0) taps2d_rows<T, k, 0>(xp, dst, jx, d2, d3, d4, plane, warp, lane);
+    else if (base == 8) taps2d_rows<T, k, 8>(xp, dst, jx, d2, d3, d4, plane, warp, lane);
+    else if (base == 16) taps2d_rows<T, k, 16>(xp, dst, jx, d2, d3, d4, plane, warp, lane);
+    else taps2d_rows<T, k, 24>(xp, dst, jx, d2, d3, d4, plane, warp, lane);
+}
+
 // CB16 -> planar [nblk, C, vol] (T); interior only
 template <typename T>
 __global__ void __launch_bounds__(256)
@@ -676,6 +789,34 @@ int cb16_pack(const void *x, int dtype, void *cb, int nblk, int C, int d1, int d
     NC_CHECK(nblk > 0 && nblk <= 65535 && C >= 1 && C <= 16, "cb16_pack: bad shape (blocks %d, channels %d)", nblk, C);
     NC_CHECK(tap_mode == 0 || C == 1, "cb16_pack: tap modes need a single-channel input");
     const int pad = k / 2;
+    if (tap_mode == 4) {
+        const int ngrp = (k * k + 15) / 16;
+        const size_t nrows4 = (size_t)d1 * d2 * (d3 + 2 * pad);
+        NC_CHECK((nrows4 + 7) / 8 < (1ull << 31) && (long long)nblk * ngrp <= 65535, "cb16_pack: grid too large");
+        NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "cb16_pack: source dtype %d must be planar fp32/fp16", dtype);
+        if (d4 + 2 * pad <= 32 && d1 <= 65535 && (long long)nblk * ngrp * 2 <= 65535) {
+            dim3 g2(d2, d1, nblk * ngrp * 2);
+            if (dtype == NCNET_F32) {
+                if (k == 5) cb16_pack_taps2d_narrow_kernel<float, 5><<<g2, 256, 0, st>>>((const float *)x, (__half *)cb, d1, d2, d3, d4);
+                else cb16_pack_taps2d_narrow_kernel<float, 3><<<g2, 256, 0, st>>>((const float *)x, (__half *)cb, d1, d2, d3, d4);
+            } else {
+                if (k == 5) cb16_pack_taps2d_narrow_kernel<__half, 5><<<g2, 256, 0, st>>>((const __half *)x, (__half *)cb, d1, d2, d3, d4);
+                else cb16_pack_taps2d_narrow_kernel<__half, 3><<<g2, 256, 0, st>>>((const __half *)x, (__half *)cb, d1, d2, d3, d4);
+            }
+            NC_LAUNCH_OK("cb16_pack_taps2d_narrow_kernel");
+            return 0;
+        }
+        dim3 grid((unsigned)((nrows4 + 7) / 8), nblk * ngrp, 2);
+        if (dtype == NCNET_F32) {
+            if (k == 5) cb16_pack_taps2d_kernel<float, 5><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, d1, d2, d3, d4);
+            else cb16_pack_taps2d_kernel<float, 3><<<grid, 256, 0, st>>>((const float *)x, (__half *)cb, d1, d2, d3, d4);
+        } else {
+            if (k == 5) cb16_pack_taps2d_kernel<__half, 5><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, d1, d2, d3, d4);
+            else cb16_pack_taps2d_kernel<__half, 3><<<grid, 256, 0, st>>>((const __half *)x, (__half *)cb, d1, d2, d3, d4);
+        }
+        NC_LAUNCH_OK("cb16_pack_taps2d_kernel");
+        return 0;
+    }
     const size_t npad = (size_t)d1 * d2 * (d3 + 2 * pad) * (d4 + 2 * pad);
     // tap modes 1 and 2 put at most k <= 8 taps into the channels: the second channel half is never read
     const int halves = (tap_mode == 1 || tap_mode == 2) ? 1 : 2;
@@ -721,14 +862,14 @@ int cb16_unpack(const void *cb, void *x, int dtype, int nblk, int C, int d1, int
 
 struct TcPackW {
     PackDesc d;
-    int mode;       // 1,2,3
-    int KSTEPS, N, CoutPad;
+    int mode;       // 1,2,3,4
+    int KSTEPS, N, CoutPad, inner;
 };
 
-// -> [G][k*k][KSTEPS][2][N][8] fp16
+// -> [G][k*inner][KSTEPS][2][N][8] fp16   (inner = k d2 taps; mode 4: channel blocks of the (d2,d4) taps)
 __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict__ wp, TcPackW a) {
     const int k = a.d.k;
-    const long long total = (long long)a.d.G_e * k * k * a.KSTEPS * 2 * a.N * 8;
+    const long long total = (long long)a.d.G_e * k * a.inner * a.KSTEPS * 2 * a.N * 8;
     for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
          idx += (long long)gridDim.x * blockDim.x) {
         long long r = idx;
@@ -736,13 +877,17 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
         const int n = (int)(r % a.N); r /= a.N;
         const int half = (int)(r % 2); r /= 2;
         const int ks = (int)(r % a.KSTEPS); r /= a.KSTEPS;
-        const int t2 = (int)(r % k); r /= k;
+        int t2 = (int)(r % a.inner); r /= a.inner;
         const int t1 = (int)(r % k); r /= k;
         const int g = (int)r;
         const int kch = half * 8 + c8;
         int oe, ci, t3, t4;
         bool ok = true;
-        if (a.mode == 1) {          // N = (t4, o), K-step = t3, channel = ci
+        if (a.mode == 4) {          // N = o, K-step = t3, channel = (t2,t4) tap of block t2
+            const int c = t2 * 16 + kch;
+            ok = c < k * k;
+            t2 = c / k; t4 = c - t2 * k; t3 = ks; oe = n; ci = 0;
+        } else if (a.mode == 1) {          // N = (t4, o), K-step = t3, channel = ci
             t3 = ks; t4 = n / a.CoutPad; oe = n % a.CoutPad; ci = kch;
         } else if (a.mode == 2) {   // N = (t3, t4), single out channel, channel = ci
             t3 = n / k; t4 = n % k; oe = 0; ci = kch;
@@ -765,7 +910,7 @@ long long *g_tc_debug_buffer = nullptr;     // set through ncnet_debug_set_tc_ti
 int g_tc_debug_mode = 0;
 
 struct TcPlan {
-    int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages;
+    int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages, inner;
     uint32_t tmem_cols;
     uint32_t data_bytes, w_bytes, stage_bytes, mask_off;
     size_t smem_bytes;
@@ -776,15 +921,18 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask
     TcPlan pl{};
     pl.ok = false;
     if (Cin_e > 16 || Cout_e > 16 || (k != 3 && k != 5)) return pl;
-    if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = (k + 1) / 2; pl.KSTEPS = 1; }
+    pl.inner = k;
+    static const bool force_m3 = [] { const char *e = getenv("NCNET_TC_M3"); return e && e[0] == '1'; }();   // development knob
+    if (Cin_e == 1 && Cout_e > 1 && !force_m3) { pl.mode = 4; pl.CoutPad = 16; pl.NG = 1; pl.KSTEPS = k; pl.inner = (k * k + 15) / 16; }
+    else if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = (k + 1) / 2; pl.KSTEPS = 1; }
     else if (Cout_e == 1)          { pl.mode = 2; pl.CoutPad = 1; pl.NG = k * k; pl.KSTEPS = 1; }
     else                           { pl.mode = 1; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = k; }
     pl.N = pl.mode == 2 ? ((k * k + 15) / 16) * 16 : pl.NG * 16;
     pl.P = d4 + k - 1;
     const int pad = k / 2;
-    const int max_aoff = pl.mode == 1 ? (k - 1) * pl.P : 0;
+    const int max_aoff = (pl.mode == 1 || pl.mode == 4) ? (k - 1) * pl.P : 0;
     // largest epilogue row shift (mode 3 reads the haloed row at column l + pad, hence the extra pad)
-    const int max_shift = pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : 2 * (pl.NG - 1) * pl.P + pad);
+    const int max_shift = pl.mode == 4 ? 0 : pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : 2 * (pl.NG - 1) * pl.P + pad);
     pl.w_bytes = (uint32_t)pl.KSTEPS * 2u * pl.N * 16u;
     // budget: one CTA per SM may use all 512 TMEM columns and ~220 KB; two co-resident CTAs (whose
     // epilogue/prologue then overlap the other's MMA main loop) get 256 columns and ~108 KB each
@@ -852,7 +1000,7 @@ size_t conv4d_tc_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3,
     const int G = symmetric ? 2 : 1;
     (void)Cin; (void)Cout;
     // a CB16 copy of a planar input (up to G blocks per batch item) + the re-laid-out weights
-    const size_t act = cb16_bytes((size_t)B * G, d1, d2, d3, d4, k);
+    const size_t act = cb16_bytes((size_t)B * G * 2, d1, d2, d3, d4, k);     // mode M4 packs up to 2 channel blocks per input
     const size_t wts = (size_t)G * k * k * k * 2 * 96 * 16;
     return align256(act) + align256(wts) + 512;
 }
@@ -865,7 +1013,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
                   cudaStream_t st) {
     const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4, mask && mask_dtype == NCNET_CB16);
     if (!pl.ok) return 2;
-    if (x_dtype == NCNET_CB16 && pl.mode == 3) return 2;        // the tap im2col needs the planar single-channel input
+    if (x_dtype == NCNET_CB16 && (pl.mode == 3 || pl.mode == 4)) return 2;   // the tap im2col needs the planar single-channel input
     if (y_dtype == NCNET_CB16 && pl.CoutPad < 16) return 2;
     if (mask && ((mask_dtype == NCNET_CB16) != (y_dtype == NCNET_CB16))) return 2;
     uint8_t *sc = (uint8_t *)scratch;
@@ -874,16 +1022,16 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     if (x_dtype == NCNET_CB16) {
         act = (const __half *)x;
     } else {
-        int rc = cb16_pack(x, x_dtype, sc, B * Gx, d.Cin_e, d1, d2, d3, d4, d.k, pl.mode == 3 ? 3 : 0, st);
+        int rc = cb16_pack(x, x_dtype, sc, B * Gx, d.Cin_e, d1, d2, d3, d4, d.k, pl.mode == 3 ? 3 : (pl.mode == 4 ? 4 : 0), st);
         if (rc) return rc;
         act = (const __half *)sc;
-        used = align256(cb16_bytes((size_t)B * Gx, d1, d2, d3, d4, d.k));
+        used = align256(cb16_bytes((size_t)B * Gx * (pl.mode == 4 ? pl.inner : 1), d1, d2, d3, d4, d.k));
     }
     __half *wp = (__half *)(sc + used);
     {
         TcPackW a{};
-        a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad;
-        const long long total = (long long)d.G_e * d.k * d.k * pl.KSTEPS * 2 * pl.N * 8;
+        a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad; a.inner = pl.inner;
+        const long long total = (long long)d.G_e * d.k * pl.inner * pl.KSTEPS * 2 * pl.N * 8;
         const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
         pack_w_tc_kernel<<<blocks, 256, 0, st>>>(w, wp, a);
         NC_LAUNCH_OK("pack_w_tc_kernel");
@@ -893,6 +1041,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     a.B = B; a.G = d.G_e; a.Gx = Gx; a.Cout = d.Cout_e; a.CoutPad = pl.CoutPad;
     a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = d.k; a.P = pl.P;
     a.R = pl.R; a.nchunks = pl.nchunks; a.NT = pl.NT; a.N = pl.N; a.NG = pl.NG; a.KSTEPS = pl.KSTEPS;
+    a.inner = pl.inner; a.m4 = pl.mode == 4;
     a.npos_pad = pl.npos_pad; a.relu = relu; a.stages = pl.stages; a.tmem_cols = pl.tmem_cols;
     a.out_mode = y_dtype == NCNET_CB16 ? 2 : (y_dtype == NCNET_F16 ? 1 : 0);
     a.mask_mode = !mask ? 0 : (mask_dtype == NCNET_CB16 ? 3 : (mask_dtype == NCNET_F16 ? 2 : 1));
@@ -902,11 +1051,12 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
     a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const int pad = d.k / 2;
-    for (int ks = 0; ks < kMaxKSteps; ++ks) a.aoff[ks] = (pl.mode == 1 && ks < d.k) ? ks * pl.P : 0;
+    for (int ks = 0; ks < kMaxKSteps; ++ks) a.aoff[ks] = ((pl.mode == 1 || pl.mode == 4) && ks < d.k) ? ks * pl.P : 0;
     for (int gi = 0; gi < kMaxGroups; ++gi) {
         int s = 0;
         if (gi < pl.NG) {
-            if (pl.mode == 1) s = gi;                                   // group = d4 tap
+            if (pl.mode == 4) s = 0;                                    // one group, taps are in the channels / K-steps
+            else if (pl.mode == 1) s = gi;                              // group = d4 tap
             else if (pl.mode == 2) s = (gi / d.k) * pl.P + (gi % d.k);  // group = (d3, d4)
             else s = 2 * gi * pl.P + pad;                               // group = d3 tap pair; the d4 taps sit in the channels of column l + pad
         }
