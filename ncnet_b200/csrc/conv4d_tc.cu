@@ -51,6 +51,7 @@ struct TcArgs {
     int d1, d2, d3, d4, KS, P;
     int R, nchunks;         // output k-rows per CTA, chunks per plane
     int NT, N, NG, KSTEPS;
+    int OG;                 // branch groups side by side in N (1, or 2 for mode M4 on a shared input)
     int inner, m4;          // inner stage loop: the k d2 taps, or (mode M4) the channel blocks of the (d2,d4) taps
     int npos_pad;           // positions per channel-half in a smem stage
     int stages;             // ring depth (2 or 3)
@@ -284,6 +285,11 @@ conv4d_tc_kernel(const TcArgs p) {
         mbar_wait_sleep(&accum_bar, 0, 400);
         if (et == 0) TC_STAMP(2);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        // OG > 1 (mode M4 on a shared input): the N columns hold OG branch groups of 16 out-channels side by side;
+        // each is drained and stored as its own output group
+        for (int og = 0; og < p.OG; ++og) {
+        const int go = g * p.OG + og, Gt = p.G * p.OG;
+        if (og) asm volatile("bar.sync 1, 128;" ::: "memory");       // the previous group's store has read the plane
         if (p.CoutPad >= 16) {
             // column group gi = 16 out-channels of one folded tap: out[m - shift_gi][o] += D[m][gi*16 + o].  The output
             // plane aliases the (now idle) ring.  Group 0 has shift 0 and touches every row: it WRITES bias + D, so
@@ -293,7 +299,7 @@ conv4d_tc_kernel(const TcArgs p) {
             float bv[16];
 #pragma unroll
             for (int o = 0; o < 16; ++o) bv[o] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
-            const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+            const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(og * 16);
             // iteration = (column group, pair of tiles); the TMEM loads of the next iteration are in flight while this
             // one is accumulated (tcgen05.ld has a few hundred cycles of latency)
             const int npair = (p.NT + 1) >> 1, nit = p.NG * npair;
@@ -393,7 +399,7 @@ conv4d_tc_kernel(const TcArgs p) {
             const int ra = chunk == 0 ? 0 : k0 + PAD;
             const int rb = chunk == p.nchunks - 1 ? rows_pad : k0 + PAD + rows_out;
             const int npos = (rb - ra) * p.P;
-            const size_t base_off = ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8;
+            const size_t base_off = ((((size_t)b * Gt + go) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8;
             __half *ob = (__half *)p.out + base_off;
             const __half *mb = (const __half *)p.mask + base_off;
             const bool smem_mask = p.mask_mode == 3 && p.mask_off;
@@ -437,7 +443,7 @@ conv4d_tc_kernel(const TcArgs p) {
             const float bias0 = (p.CoutPad < 16 && p.bias) ? __ldg(p.bias) : 0.f;
             for (int pr = ew; pr < npairs; pr += 4) {
                 const int o = pr / rows_out, rr = pr - o * rows_out;
-                const size_t off0 = ((size_t)b * p.G * p.Cout + (size_t)g * p.Cout + o) * vol +
+                const size_t off0 = ((size_t)b * Gt * p.Cout + (size_t)go * p.Cout + o) * vol +
                                     ((size_t)i * p.d2 + j) * plane_pos + (size_t)(k0 + rr) * p.d4;
                 for (int l = lane; l < p.d4; l += 32) {
                     const int row = rr * p.P + l;
@@ -468,6 +474,7 @@ conv4d_tc_kernel(const TcArgs p) {
                 }
             }
         }
+        }   // og
     }
 
     if (threadIdx.x == 64) TC_STAMP(4);
@@ -863,13 +870,13 @@ int cb16_unpack(const void *cb, void *x, int dtype, int nblk, int C, int d1, int
 struct TcPackW {
     PackDesc d;
     int mode;       // 1,2,3,4
-    int KSTEPS, N, CoutPad, inner;
+    int KSTEPS, N, CoutPad, inner, OG;
 };
 
 // -> [G][k*inner][KSTEPS][2][N][8] fp16   (inner = k d2 taps; mode 4: channel blocks of the (d2,d4) taps)
 __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict__ wp, TcPackW a) {
     const int k = a.d.k;
-    const long long total = (long long)a.d.G_e * k * a.inner * a.KSTEPS * 2 * a.N * 8;
+    const long long total = (long long)(a.d.G_e / a.OG) * k * a.inner * a.KSTEPS * 2 * a.N * 8;
     for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
          idx += (long long)gridDim.x * blockDim.x) {
         long long r = idx;
@@ -879,14 +886,15 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
         const int ks = (int)(r % a.KSTEPS); r /= a.KSTEPS;
         int t2 = (int)(r % a.inner); r /= a.inner;
         const int t1 = (int)(r % k); r /= k;
-        const int g = (int)r;
+        int g = (int)r;
         const int kch = half * 8 + c8;
         int oe, ci, t3, t4;
         bool ok = true;
-        if (a.mode == 4) {          // N = o, K-step = t3, channel = (t2,t4) tap of block t2
+        if (a.mode == 4) {          // N = (branch group when merged, o), K-step = t3, channel = (t2,t4) tap of block t2
             const int c = t2 * 16 + kch;
             ok = c < k * k;
-            t2 = c / k; t4 = c - t2 * k; t3 = ks; oe = n; ci = 0;
+            t2 = c / k; t4 = c - t2 * k; t3 = ks; oe = n % 16; ci = 0;
+            g = g * a.OG + n / 16;
         } else if (a.mode == 1) {          // N = (t4, o), K-step = t3, channel = ci
             t3 = ks; t4 = n / a.CoutPad; oe = n % a.CoutPad; ci = kch;
         } else if (a.mode == 2) {   // N = (t3, t4), single out channel, channel = ci
@@ -910,14 +918,14 @@ long long *g_tc_debug_buffer = nullptr;     // set through ncnet_debug_set_tc_ti
 int g_tc_debug_mode = 0;
 
 struct TcPlan {
-    int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages, inner;
+    int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages, inner, OG;
     uint32_t tmem_cols;
     uint32_t data_bytes, w_bytes, stage_bytes, mask_off;
     size_t smem_bytes;
     bool ok;
 };
 
-static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask = false) {
+static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask = false, int og = 1) {
     TcPlan pl{};
     pl.ok = false;
     if (Cin_e > 16 || Cout_e > 16 || (k != 3 && k != 5)) return pl;
@@ -928,6 +936,8 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask
     else if (Cout_e == 1)          { pl.mode = 2; pl.CoutPad = 1; pl.NG = k * k; pl.KSTEPS = 1; }
     else                           { pl.mode = 1; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = k; }
     pl.N = pl.mode == 2 ? ((k * k + 15) / 16) * 16 : pl.NG * 16;
+    pl.OG = pl.mode == 4 ? og : 1;
+    pl.N *= pl.OG;
     pl.P = d4 + k - 1;
     const int pad = k / 2;
     const int max_aoff = (pl.mode == 1 || pl.mode == 4) ? (k - 1) * pl.P : 0;
@@ -1011,7 +1021,9 @@ bool conv4d_tc_supports(int Cin_e, int Cout_e, int k, int d3, int d4) { return t
 static int run_tc(const void *x, int x_dtype, const float *w, const float *bias, const void *mask, int mask_dtype, void *y,
                   int y_dtype, void *scratch, PackDesc d, int B, int Gx, int d1, int d2, int d3, int d4, int relu,
                   cudaStream_t st) {
-    const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4, mask && mask_dtype == NCNET_CB16);
+    // both branch groups read the same single-channel input: their out-channels sit side by side in N
+    const int og = (d.G_e == 2 && Gx == 1 && d.Cin_e == 1 && !d.dgrad && !mask) ? 2 : 1;
+    const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4, mask && mask_dtype == NCNET_CB16, og);
     if (!pl.ok) return 2;
     if (x_dtype == NCNET_CB16 && (pl.mode == 3 || pl.mode == 4)) return 2;   // the tap im2col needs the planar single-channel input
     if (y_dtype == NCNET_CB16 && pl.CoutPad < 16) return 2;
@@ -1030,15 +1042,15 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     __half *wp = (__half *)(sc + used);
     {
         TcPackW a{};
-        a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad; a.inner = pl.inner;
-        const long long total = (long long)d.G_e * d.k * pl.inner * pl.KSTEPS * 2 * pl.N * 8;
+        a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad; a.inner = pl.inner; a.OG = pl.OG;
+        const long long total = (long long)(d.G_e / pl.OG) * d.k * pl.inner * pl.KSTEPS * 2 * pl.N * 8;
         const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
         pack_w_tc_kernel<<<blocks, 256, 0, st>>>(w, wp, a);
         NC_LAUNCH_OK("pack_w_tc_kernel");
     }
     TcArgs a{};
     a.act = act; a.wp = wp; a.bias = bias; a.mask = mask; a.out = y;
-    a.B = B; a.G = d.G_e; a.Gx = Gx; a.Cout = d.Cout_e; a.CoutPad = pl.CoutPad;
+    a.B = B; a.G = d.G_e / pl.OG; a.OG = pl.OG; a.Gx = Gx; a.Cout = d.Cout_e; a.CoutPad = pl.CoutPad;
     a.d1 = d1; a.d2 = d2; a.d3 = d3; a.d4 = d4; a.KS = d.k; a.P = pl.P;
     a.R = pl.R; a.nchunks = pl.nchunks; a.NT = pl.NT; a.N = pl.N; a.NG = pl.NG; a.KSTEPS = pl.KSTEPS;
     a.inner = pl.inner; a.m4 = pl.mode == 4;
@@ -1064,7 +1076,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     }
     cudaError_t e = cudaFuncSetAttribute(conv4d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes);
     NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
-    const long long ctas = (long long)B * d.G_e * d1 * d2 * pl.nchunks;
+    const long long ctas = (long long)B * (d.G_e / pl.OG) * d1 * d2 * pl.nchunks;
     NC_CHECK(ctas < (1ll << 31), "conv4d(tc): grid too large");
     conv4d_tc_kernel<<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a);
     NC_LAUNCH_OK("conv4d_tc_kernel");
