@@ -296,6 +296,12 @@ bool conv4d_tc_wgrad_pm_supported(int d3, int d4, int k);
 int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, float *part, void *pm_scratch, int B, int G, int GxA,
                            int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int S, int cop, cudaStream_t st);
 
+// conv4d_tc_wgrad_thin.cu: M128 tiles for the single-channel layers (Cin == 1 or Cout == 1)
+bool conv4d_tc_wgrad_thin_supported(int d3, int d4, int k);
+int conv4d_tc_wgrad_thin_run(const __half *w16_cb, const void *one, int one_dtype, float *part, void *scratch, int cin1,
+                             int B, int G, int Gt, int C16, int d1, int d2, int d3, int d4, int k, int S, int cop,
+                             cudaStream_t st);
+
 struct WgPlan {
     bool ok;
     int variant, NAv, NBv, N, nb_copy, P, a_r0, b_r0, npos_a, npos_b, nkb, kb0, S, cop, stages;
@@ -379,7 +385,8 @@ size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, i
     // the full-tile kernel reads)
     const size_t cb = wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));
     const bool pm = w.variant == 2 && w.NAv == 2 && w.NBv == 2 && conv4d_tc_wgrad_pm_supported(d3, d4, k);
-    return (pm ? 4 : 2) * cb + w.part_bytes + 1024;
+    const bool thin = w.variant != 2 && conv4d_tc_wgrad_thin_supported(d3, d4, k);
+    return (pm ? 4 : (thin ? 5 : 2)) * cb + w.part_bytes + 1024;
 }
 
 // returns 2 when the shape/layout is outside the tensor-core kernel's envelope
@@ -396,14 +403,19 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     uint8_t *sc = (uint8_t *)scratch;
     size_t used = 0;
     const __half *xa, *gbk;
-    if (x_dtype == NCNET_CB16) xa = (const __half *)x;
+    // single-channel layers: the single-channel tensor is tap-packed by the thin kernel's own pack
+    const bool thin = w.variant != 2 && (w.variant == 1 || GxA == G) && conv4d_tc_wgrad_thin_supported(d3, d4, k);
+    xa = gbk = nullptr;
+    if (thin && w.variant == 1) {
+    } else if (x_dtype == NCNET_CB16) xa = (const __half *)x;
     else {
         int rc = cb16_pack(x, x_dtype, sc + used, B * GxA, Cin, d1, d2, d3, d4, k, w.variant == 1 ? 1 : 0, st);
         if (rc) return rc;
         xa = (const __half *)(sc + used);
         used += wg_align(cb16_bytes((size_t)B * GxA, d1, d2, d3, d4, k));
     }
-    if (gy_dtype == NCNET_CB16) gbk = (const __half *)gy;
+    if (thin && w.variant == 3) {
+    } else if (gy_dtype == NCNET_CB16) gbk = (const __half *)gy;
     else {
         int rc = cb16_pack(gy, gy_dtype, sc + used, B * G, Cout, d1, d2, d3, d4, k, w.variant == 3 ? 2 : 0, st);
         if (rc) return rc;
@@ -415,6 +427,15 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): memset: %s", cudaGetErrorString(e));
 
     bool launched = false;
+    if (thin) {
+        const size_t cb = wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));
+        void *pm_scratch = sc + 2 * cb + w.part_bytes;
+        int rc = w.variant == 1
+            ? conv4d_tc_wgrad_thin_run(gbk, x, x_dtype, part, pm_scratch, 1, B, G, GxA, Cout, d1, d2, d3, d4, k, w.S, w.cop, st)
+            : conv4d_tc_wgrad_thin_run(xa, gy, gy_dtype, part, pm_scratch, 0, B, G, G, Cin, d1, d2, d3, d4, k, w.S, w.cop, st);
+        if (rc) return rc == 2 ? fail("conv4d_wgrad(tc,thin): plan failed after the capability check") : rc;
+        launched = true;
+    }
     if (w.variant == 2 && w.NAv == 2 && w.NBv == 2 && conv4d_tc_wgrad_pm_supported(d3, d4, k)) {
         // both sides have more than 8 channels: position-major operands, one M128 MMA per 16 positions
         const size_t cb = wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));

@@ -42,6 +42,13 @@ pm16_from_cb16_kernel(const uint4 *__restrict__ cb, uint4 *__restrict__ pm, size
     }
 }
 
+// shared with conv4d_tc_wgrad_thin.cu
+void pm16_from_cb16(const __half *cb, __half *pm, size_t nblk, size_t ij, int npos, cudaStream_t st) {
+    const size_t n = nblk * ij * (size_t)npos;
+    const int blocks = (int)((n + 255) / 256 < 148 * 16 ? (n + 255) / 256 : 148 * 16);
+    pm16_from_cb16_kernel<<<blocks, 256, 0, st>>>((const uint4 *)cb, (uint4 *)pm, nblk, ij, npos);
+}
+
 struct WgPmArgs {
     const __half *x;    // PM16 [B*GxA][d1*d2][npos][16]
     const __half *g;    // PM16 [B*G][d1*d2][npos][16]
