@@ -36,6 +36,12 @@ extern "C" {
  * it; a tensor [B, G*C] (C<=16 per group) has B*G blocks.  Lets a stack of layers hand activations
  * from one tensor-core launch to the next without layout passes (sizes: ncnet_cb16_bytes). */
 #define NCNET_CB16 2
+/* A CB16 tensor immediately followed (at the next multiple of 256 bytes after its ncnet_cb16_bytes) by its
+ * position-major twin: [blocks][d1*d2][(d3+2p)*(d4+2p)][16] fp16, the two 16-byte halves of a position swapped where
+ * bit 7 of the in-plane byte offset is set.  ncnet_conv4d_fwd / _dgrad write both when asked for this output type;
+ * ncnet_conv4d_wgrad then reads the twin directly instead of converting (training stacks); every other use reads
+ * the CB16 part.  Buffer size: 2 * ((ncnet_cb16_bytes + 255) & ~255). */
+#define NCNET_CB16PM 3
 
 /* weight layouts accepted by the Conv4d entry points */
 #define NCNET_W_OIKKKK 0 /* [Cout,Cin,k,k,k,k]   (lib/conv4d.py:16-18, permute_filters=True) */

@@ -14,7 +14,7 @@ from . import build as _build
 _lock = threading.Lock()
 _lib = None
 
-F32, F16, CB16 = 0, 1, 2
+F32, F16, CB16, CB16PM = 0, 1, 2, 3
 W_OIKKKK, W_KOIKKK = 0, 1
 CONV_FP32, CONV_TC16 = 0, 1
 

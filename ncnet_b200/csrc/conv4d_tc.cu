@@ -63,6 +63,7 @@ struct TcArgs {
     int aoff[kMaxKSteps];   // A row offset (positions) per K-step
     int gshift[kMaxGroups]; // epilogue row shift per column group
     uint32_t stage_bytes, data_bytes, w_bytes;
+    __half *out_pm;         // optional position-major twin of a CB16 output (NCNET_CB16PM) or null
     uint32_t mask_off;      // CB16 mask: byte offset of its staging area in dynamic smem (0 = read it from global)
     long long *dbg;         // development only: per-CTA phase timestamps (8 per CTA) or null
     int dbg_mode;           // development only: 1 = no weight copies, 2 = no MMAs, 3 = no activation copies (results wrong)
@@ -433,6 +434,12 @@ conv4d_tc_kernel(const TcArgs p) {
                     for (int c8 = 0; c8 < 8; ++c8) hv[c8] = __float2half_rn(0.f);
                 }
                 *reinterpret_cast<uint4 *>(ob + goff) = *reinterpret_cast<const uint4 *>(hv);
+                if (p.out_pm) {      // position-major twin: 32 B per position, halves swapped by bit 7 of the in-plane offset
+                    const int pos = kk * p.P + ll;
+                    const size_t pm_off = ((((size_t)b * Gt + go) * ij_count + (size_t)i * p.d2 + j) * plane_cb + pos) * 16 +
+                                          (size_t)((half ^ ((pos >> 2) & 1)) * 8);
+                    *reinterpret_cast<uint4 *>(p.out_pm + pm_off) = *reinterpret_cast<const uint4 *>(hv);
+                }
             }
         } else {
             // ---- planar store: one warp per (channel, output row), lanes along l ----------------------
@@ -1021,6 +1028,14 @@ bool conv4d_tc_supports(int Cin_e, int Cout_e, int k, int d3, int d4) { return t
 static int run_tc(const void *x, int x_dtype, const float *w, const float *bias, const void *mask, int mask_dtype, void *y,
                   int y_dtype, void *scratch, PackDesc d, int B, int Gx, int d1, int d2, int d3, int d4, int relu,
                   cudaStream_t st) {
+    // NCNET_CB16PM = CB16 followed by its position-major twin: read as CB16, written as both
+    __half *out_pm = nullptr;
+    if (x_dtype == NCNET_CB16PM) x_dtype = NCNET_CB16;
+    if (mask_dtype == NCNET_CB16PM) mask_dtype = NCNET_CB16;
+    if (y_dtype == NCNET_CB16PM) {
+        y_dtype = NCNET_CB16;
+        out_pm = (__half *)((uint8_t *)y + align256(cb16_bytes((size_t)B * d.G_e, d1, d2, d3, d4, d.k)));
+    }
     // both branch groups read the same single-channel input: their out-channels sit side by side in N
     const int og = (d.G_e == 2 && Gx == 1 && d.Cin_e == 1 && !d.dgrad && !mask) ? 2 : 1;
     const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4, mask && mask_dtype == NCNET_CB16, og);
@@ -1058,6 +1073,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     a.out_mode = y_dtype == NCNET_CB16 ? 2 : (y_dtype == NCNET_F16 ? 1 : 0);
     a.mask_mode = !mask ? 0 : (mask_dtype == NCNET_CB16 ? 3 : (mask_dtype == NCNET_F16 ? 2 : 1));
     a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes; a.mask_off = pl.mask_off;
+    a.out_pm = out_pm;
     a.dbg = g_tc_debug_buffer;
     a.dbg_mode = g_tc_debug_mode;
     // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24

@@ -293,12 +293,13 @@ cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int
 
 // conv4d_tc_wgrad_pm.cu: full-size tiles for layers with more than 8 channels on both sides
 bool conv4d_tc_wgrad_pm_supported(int d3, int d4, int k);
-int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, float *part, void *pm_scratch, int B, int G, int GxA,
-                           int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int S, int cop, cudaStream_t st);
+int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, const __half *x_pm_in, const __half *g_pm_in, float *part,
+                           void *pm_scratch, int B, int G, int GxA, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                           int S, int cop, cudaStream_t st);
 
 // conv4d_tc_wgrad_thin.cu: M128 tiles for the single-channel layers (Cin == 1 or Cout == 1)
 bool conv4d_tc_wgrad_thin_supported(int d3, int d4, int k);
-int conv4d_tc_wgrad_thin_run(const __half *w16_cb, const void *one, int one_dtype, float *part, void *scratch, int cin1,
+int conv4d_tc_wgrad_thin_run(const __half *w16_cb, const __half *w16_pm_in, const void *one, int one_dtype, float *part, void *scratch, int cin1,
                              int B, int G, int Gt, int C16, int d1, int d2, int d3, int d4, int k, int S, int cop,
                              cudaStream_t st);
 
@@ -397,6 +398,16 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     const int GxA = (G == 2 && !shared_input) ? 2 : 1;
     const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G);
     if (!w.ok) return 2;
+    // NCNET_CB16PM: the position-major twin sits behind the CB16 tensor
+    const __half *x_pm = nullptr, *g_pm = nullptr;
+    if (x_dtype == NCNET_CB16PM) {
+        x_dtype = NCNET_CB16;
+        x_pm = (const __half *)((const uint8_t *)x + wg_align(cb16_bytes((size_t)B * GxA, d1, d2, d3, d4, k)));
+    }
+    if (gy_dtype == NCNET_CB16PM) {
+        gy_dtype = NCNET_CB16;
+        g_pm = (const __half *)((const uint8_t *)gy + wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k)));
+    }
     if (w.variant == 1 && x_dtype == NCNET_CB16) return 2;      // the tap im2col needs the planar single-channel tensors
     if (w.variant == 3 && gy_dtype == NCNET_CB16) return 2;
     const size_t vol = (size_t)d1 * d2 * d3 * d4;
@@ -431,8 +442,8 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
         const size_t cb = wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));
         void *pm_scratch = sc + 2 * cb + w.part_bytes;
         int rc = w.variant == 1
-            ? conv4d_tc_wgrad_thin_run(gbk, x, x_dtype, part, pm_scratch, 1, B, G, GxA, Cout, d1, d2, d3, d4, k, w.S, w.cop, st)
-            : conv4d_tc_wgrad_thin_run(xa, gy, gy_dtype, part, pm_scratch, 0, B, G, G, Cin, d1, d2, d3, d4, k, w.S, w.cop, st);
+            ? conv4d_tc_wgrad_thin_run(gbk, g_pm, x, x_dtype, part, pm_scratch, 1, B, G, GxA, Cout, d1, d2, d3, d4, k, w.S, w.cop, st)
+            : conv4d_tc_wgrad_thin_run(xa, x_pm, gy, gy_dtype, part, pm_scratch, 0, B, G, G, Cin, d1, d2, d3, d4, k, w.S, w.cop, st);
         if (rc) return rc == 2 ? fail("conv4d_wgrad(tc,thin): plan failed after the capability check") : rc;
         launched = true;
     }
@@ -441,7 +452,7 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
         const size_t cb = wg_align(cb16_bytes((size_t)B * G, d1, d2, d3, d4, k));
         void *pm_scratch = sc + 2 * cb + w.part_bytes;
         // the partial sums sit right behind the CB16 copies actually made; the PM16 copies go behind the worst case
-        int rc = conv4d_tc_wgrad_pm_run(xa, gbk, part, pm_scratch, B, G, GxA, Cin, Cout, d1, d2, d3, d4, k, w.S, w.cop, st);
+        int rc = conv4d_tc_wgrad_pm_run(xa, gbk, x_pm, g_pm, part, pm_scratch, B, G, GxA, Cin, Cout, d1, d2, d3, d4, k, w.S, w.cop, st);
         if (rc == 1) return rc;
         launched = rc == 0;
     }

@@ -302,26 +302,30 @@ bool conv4d_tc_wgrad_pm_supported(int d3, int d4, int k) { return pm_plan(d3, d4
 
 // x_cb / g_cb: CB16 operands; pm_scratch: room for both PM16 copies (same byte counts as the CB16 tensors);
 // part: [S][G][Cin][k][k][k][k][cop], already zeroed.  Returns 2 when the shape is outside the envelope.
-int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, float *part, void *pm_scratch, int B, int G, int GxA,
-                           int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int S, int cop, cudaStream_t st) {
+int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, const __half *x_pm_in, const __half *g_pm_in, float *part,
+                           void *pm_scratch, int B, int G, int GxA, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
+                           int S, int cop, cudaStream_t st) {
     const WgPmPlan w = pm_plan(d3, d4, k);
     if (!w.ok || Cin > 16 || Cout > 16) return 2;
     const int pad = k / 2;
     const int npos = (d3 + 2 * pad) * (d4 + 2 * pad);
     const size_t ij = (size_t)d1 * d2;
     const size_t xa_bytes = (size_t)B * GxA * ij * npos * 32, gb_bytes = (size_t)B * G * ij * npos * 32;
-    __half *x_pm = (__half *)pm_scratch;
-    __half *g_pm = (__half *)((uint8_t *)pm_scratch + ((xa_bytes + 255) & ~(size_t)255));
-    {
-        const size_t nx = (size_t)B * GxA * ij * npos, ng = (size_t)B * G * ij * npos;
-        const int bx = (int)((nx + 255) / 256 < 148 * 16 ? (nx + 255) / 256 : 148 * 16);
-        const int bg = (int)((ng + 255) / 256 < 148 * 16 ? (ng + 255) / 256 : 148 * 16);
-        pm16_from_cb16_kernel<<<bx, 256, 0, st>>>((const uint4 *)x_cb, (uint4 *)x_pm, (size_t)B * GxA, ij, npos);
+    // operands that already come with their position-major twin (NCNET_CB16PM) skip the conversion pass
+    const __half *x_pm = x_pm_in, *g_pm = g_pm_in;
+    if (!x_pm) {
+        __half *dst = (__half *)pm_scratch;
+        pm16_from_cb16(x_cb, dst, (size_t)B * GxA, ij, npos, st);
         NC_LAUNCH_OK("pm16_from_cb16_kernel");
-        pm16_from_cb16_kernel<<<bg, 256, 0, st>>>((const uint4 *)g_cb, (uint4 *)g_pm, (size_t)B * G, ij, npos);
-        NC_LAUNCH_OK("pm16_from_cb16_kernel");
-        (void)gb_bytes;
+        x_pm = dst;
     }
+    if (!g_pm) {
+        __half *dst = (__half *)((uint8_t *)pm_scratch + ((xa_bytes + 255) & ~(size_t)255));
+        pm16_from_cb16(g_cb, dst, (size_t)B * G, ij, npos, st);
+        NC_LAUNCH_OK("pm16_from_cb16_kernel");
+        g_pm = dst;
+    }
+    (void)gb_bytes;
     WgPmArgs a{};
     a.x = x_pm; a.g = g_pm; a.part = part;
     a.B = B; a.G = G; a.GxA = GxA; a.d1 = d1; a.d2 = d2; a.KS = k; a.N = w.N;

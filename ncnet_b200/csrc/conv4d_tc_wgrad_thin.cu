@@ -300,7 +300,7 @@ void pm16_from_cb16(const __half *cb, __half *pm, size_t nblk, size_t ij, int np
 // w16_cb: the 16-channel tensor in CB16 ([B*G] blocks);  one: the single-channel tensor, planar [B*Gt, vol] (dtype);
 // cin1 = 1: Cin == 1 (w16 = grad_y, one = x);  0: Cout == 1 (w16 = x, one = grad_y).  scratch: room for the PM16 copy
 // of w16 (same bytes as its CB16 form) + the tap blocks (2x that for k = 5).  part: zeroed partial sums.
-int conv4d_tc_wgrad_thin_run(const __half *w16_cb, const void *one, int one_dtype, float *part, void *scratch, int cin1,
+int conv4d_tc_wgrad_thin_run(const __half *w16_cb, const __half *w16_pm_in, const void *one, int one_dtype, float *part, void *scratch, int cin1,
                              int B, int G, int Gt, int C16, int d1, int d2, int d3, int d4, int k, int S, int cop,
                              cudaStream_t st) {
     const WgThinPlan w = thin_plan(d3, d4, k);
@@ -310,9 +310,13 @@ int conv4d_tc_wgrad_thin_run(const __half *w16_cb, const void *one, int one_dtyp
     const int npos = (d3 + 2 * pad) * (d4 + 2 * pad);
     const size_t ij = (size_t)d1 * d2;
     const size_t w16_bytes = ((size_t)B * G * ij * npos * 32 + 255) & ~(size_t)255;
-    __half *w16_pm = (__half *)scratch;
+    const __half *w16_pm = w16_pm_in;         // NCNET_CB16PM operands bring their position-major twin
     __half *t2_pm = (__half *)((uint8_t *)scratch + w16_bytes);
-    pm16_from_cb16(w16_cb, w16_pm, (size_t)B * G, ij, npos, st);
+    if (!w16_pm) {
+        pm16_from_cb16(w16_cb, (__half *)scratch, (size_t)B * G, ij, npos, st);
+        NC_LAUNCH_OK("pm16_from_cb16_kernel");
+        w16_pm = (const __half *)scratch;
+    }
     {
         const long long zb = (long long)B * Gt * w.ngrp * 2;
         NC_CHECK(zb <= 65535 && d1 <= 65535, "conv4d_wgrad(tc,thin): grid too large");

@@ -235,18 +235,22 @@ def _wdims(w: torch.Tensor, layout: int) -> Tuple[int, int, int]:
 
 class _CB16:
     """Handle of a channel-blocked, zero-haloed fp16 activation tensor (include/ncnet_b200.h: NCNET_CB16).
-    ``buf`` is a flat uint8 torch tensor owned by PyTorch; ``shape`` is the planar shape it stands for."""
-    __slots__ = ("buf", "shape", "k", "dtype")
+    ``buf`` is a flat uint8 torch tensor owned by PyTorch; ``shape`` is the planar shape it stands for.  ``pm``: the
+    buffer also holds the position-major twin behind the CB16 part (NCNET_CB16PM), which the weight-gradient kernels
+    read without a conversion pass."""
+    __slots__ = ("buf", "shape", "k", "dtype", "pm")
 
-    def __init__(self, buf, shape, k, dtype):
-        self.buf, self.shape, self.k, self.dtype = buf, tuple(shape), k, dtype
+    def __init__(self, buf, shape, k, dtype, pm=False):
+        self.buf, self.shape, self.k, self.dtype, self.pm = buf, tuple(shape), k, dtype, pm
 
     @staticmethod
-    def empty(shape, k, device, dtype, per_group):
+    def empty(shape, k, device, dtype, per_group, pm=False):
         bsz, ch, d1, d2, d3, d4 = shape
         nblk = bsz * (ch // per_group)
         nbytes = _cabi.lib().ncnet_cb16_bytes(nblk, d1, d2, d3, d4, k)
-        return _CB16(torch.empty(nbytes, device=device, dtype=torch.uint8), shape, k, dtype)
+        if pm:
+            nbytes = 2 * ((nbytes + 255) & ~255)
+        return _CB16(torch.empty(nbytes, device=device, dtype=torch.uint8), shape, k, dtype, pm)
 
     @property
     def device(self):
@@ -257,16 +261,18 @@ class _CB16:
 
 
 def _adt(t) -> int:
-    return _cabi.CB16 if isinstance(t, _CB16) else _dt(t)
+    if isinstance(t, _CB16):
+        return _cabi.CB16PM if t.pm else _cabi.CB16
+    return _dt(t)
 
 
-def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode, out_cb16=False):
+def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode, out_cb16=False, out_pm=False):
     cin, cout, k = _wdims(w32, layout)
     bsz, _, d1, d2, d3, d4 = x.shape
     g = 2 if symmetric else 1
     oshape = (bsz, g * cout, d1, d2, d3, d4)
     if out_cb16:
-        y = _CB16.empty(oshape, k, x.device, x.dtype, cout)
+        y = _CB16.empty(oshape, k, x.device, x.dtype, cout, pm=out_pm)
     else:
         y = torch.empty(oshape, device=x.device, dtype=x.dtype)
     L = _cabi.lib()
@@ -287,13 +293,13 @@ def _conv_fwd(x, w32, b32, layout, symmetric, shared_input, relu, mode, out_cb16
     return y
 
 
-def _conv_dgrad(gy, w32, mask, layout, symmetric, shared_input, mode, out_cb16=False):
+def _conv_dgrad(gy, w32, mask, layout, symmetric, shared_input, mode, out_cb16=False, out_pm=False):
     cin, cout, k = _wdims(w32, layout)
     bsz, _, d1, d2, d3, d4 = gy.shape
     gin = 1 if (shared_input or not symmetric) else 2
     oshape = (bsz, gin * cin, d1, d2, d3, d4)
     if out_cb16:
-        gx = _CB16.empty(oshape, k, gy.device, gy.dtype, cin)
+        gx = _CB16.empty(oshape, k, gy.device, gy.dtype, cin, pm=out_pm)
     else:
         gx = torch.empty(oshape, device=gy.device, dtype=gy.dtype)
     L = _cabi.lib()
@@ -413,11 +419,11 @@ class _NeighConsensusFn(torch.autograd.Function):
         cur = xc
         for l in range(n_layers):
             cur = _conv_fwd(cur, w32s[l], b32s[l], W_KOIKKK, symmetric, l == 0, True, mode,
-                            out_cb16=chain and l < n_layers - 1)
+                            out_cb16=chain and l < n_layers - 1, out_pm=train)   # training: + position-major twin for wgrad
             acts.append(cur)
         ctx.symmetric, ctx.mode, ctx.n_layers, ctx.chain = symmetric, mode, n_layers, chain
         ctx.wdtype = wb[0].dtype
-        ctx.meta = [(a.shape, a.k, a.dtype) if isinstance(a, _CB16) else None for a in acts]
+        ctx.meta = [(a.shape, a.k, a.dtype, a.pm) if isinstance(a, _CB16) else None for a in acts]
         ctx.save_for_backward(*[a.buf if isinstance(a, _CB16) else a for a in acts], *w32s)
         return cur
 
@@ -444,7 +450,7 @@ class _NeighConsensusFn(torch.autograd.Function):
             gw, gb = _conv_wgrad(acts[l], gz, w32s[l], True, W_KOIKKK, sym, l == 0, mode)
             grads[2 * l], grads[2 * l + 1] = gw.to(ctx.wdtype), gb.to(ctx.wdtype)
             if l > 0:
-                gz = _conv_dgrad(gz, w32s[l], acts[l], W_KOIKKK, sym, False, mode, out_cb16=chain)
+                gz = _conv_dgrad(gz, w32s[l], acts[l], W_KOIKKK, sym, False, mode, out_cb16=chain, out_pm=chain)
             elif ctx.needs_input_grad[0]:
                 if isinstance(gz, _CB16):       # merged 2*Cout -> Cin gradient runs on the CUDA-core kernel (planar)
                     gz = cb16_unpack(gz, w32s[0].shape[1])
