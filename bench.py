@@ -252,6 +252,10 @@ def run_ours(args):
     peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
     mode_name = "fp32 CUDA-core" if mode == 0 else "fp16 operands / fp32 accumulate, tcgen05"
 
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch of the two kernels at the 1-GPU batch, from the
+    # `ncu --set full` capture summarised in profiles/r1_tc16_conv_kernels_ncu_full_summary.csv (TC16 mode only)
+    ncu_traffic = {"conv4d_fwd": 0.539e9 + 1.022e9, "conv4d_wgrad": 2.621e9 + 0.041e9} if (mode != 0 and per_rank_b == 16) else {}
+
     def roof_for(tag, label):
         ts = [a.elapsed_time(b) for t, a, b in ev if t == tag]
         if not ts:
@@ -259,7 +263,7 @@ def run_ours(args):
         avg_ms = sum(ts) / len(ts)
         ach = flop_fat / (avg_ms * 1e-3) / 1e12
         return {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
-                "traffic": None, "kernel": label + " 16->16 k=5 (layer 2, both branches, B=%d)" % per_rank_b,
+                "traffic": ncu_traffic.get(label), "kernel": label + " 16->16 k=5 (layer 2, both branches, B=%d)" % per_rank_b,
                 "avg_launch_ms": avg_ms, "launches_timed": len(ts), "total_ms_in_region": sum(ts),
                 "peak_source": pk_kind + " bf16 sustained",
                 "flop_convention": "2*B*N^4*Cin*Cout*k^4 dense (zero-padding taps counted)", "mode": mode_name}
