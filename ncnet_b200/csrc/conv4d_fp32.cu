@@ -416,9 +416,13 @@ bias_grad_kernel(const T *__restrict__ gy, float *__restrict__ db, int Cout, int
     const T *src = gy + (size_t)chan * vol;
     const size_t per = (vol + chunks - 1) / chunks;
     const size_t beg = (size_t)blockIdx.x * per, end = min(vol, beg + per);
-    float a = 0.f;
-    for (size_t e = beg + threadIdx.x; e < end; e += blockDim.x) a += ldf(src + e);
-    a = warp_sum(a);
+    float a = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;       // four loads in flight per thread
+    size_t e = beg + threadIdx.x;
+    for (; e + 3 * blockDim.x < end; e += 4 * blockDim.x) {
+        a += ldf(src + e); a1 += ldf(src + e + blockDim.x); a2 += ldf(src + e + 2 * blockDim.x); a3 += ldf(src + e + 3 * blockDim.x);
+    }
+    for (; e < end; e += blockDim.x) a += ldf(src + e);
+    a = warp_sum((a + a1) + (a2 + a3));
     __shared__ float sm[8];
     if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = a;
     __syncthreads();
@@ -600,7 +604,10 @@ int wgrad_finish(const float *part, float *gw, float *gb, const void *gy, int S,
     if (gb) {
         cudaError_t e = cudaMemsetAsync(gb, 0, Cout * sizeof(float), st);
         NC_CHECK(e == cudaSuccess, "wgrad: memset bias: %s", cudaGetErrorString(e));
-        int chunks = (int)((vol + 65535) / 65536);
+        // enough blocks to fill the GPU at small batches (a few channels x 6 chunks left 140 SMs idle)
+        int chunks = (int)((16 * kNumSMs + (size_t)B * G * Cout - 1) / ((size_t)B * G * Cout));
+        const int max_chunks = (int)((vol + 2047) / 2048);
+        if (chunks > max_chunks) chunks = max_chunks;
         if (chunks < 1) chunks = 1;
         NC_CHECK(B * G * Cout <= 65535, "wgrad: too many channels for bias grid");
         if (dtype == NCNET_F32)

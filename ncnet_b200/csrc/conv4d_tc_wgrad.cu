@@ -270,7 +270,15 @@ cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int
     const size_t per = (npad + chunks - 1) / chunks;
     const size_t beg = (size_t)blockIdx.x * per, end = beg + per < npad ? beg + per : npad;
     float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    for (size_t e = beg + threadIdx.x; e < end; e += blockDim.x) {
+    size_t e = beg + threadIdx.x;
+    for (; e + blockDim.x < end; e += 2 * blockDim.x) {       // two 16-byte loads in flight per thread
+        const uint4 r0 = *reinterpret_cast<const uint4 *>(src + e * 8);
+        const uint4 r1 = *reinterpret_cast<const uint4 *>(src + (e + blockDim.x) * 8);
+        const __half *h0 = reinterpret_cast<const __half *>(&r0), *h1 = reinterpret_cast<const __half *>(&r1);
+#pragma unroll
+        for (int c = 0; c < 8; ++c) acc[c] += __half2float(h0[c]) + __half2float(h1[c]);
+    }
+    for (; e < end; e += blockDim.x) {
         const uint4 raw = *reinterpret_cast<const uint4 *>(src + e * 8);
         const __half *h = reinterpret_cast<const __half *>(&raw);
 #pragma unroll
@@ -491,7 +499,9 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): memset bias: %s", cudaGetErrorString(e));
     const int pad = k / 2;
     const size_t npad = (size_t)d1 * d2 * (d3 + 2 * pad) * (d4 + 2 * pad);
-    int chunks = (int)((npad + 65535) / 65536);
+    int chunks = (int)((16 * kNumSMs + (size_t)B * G * 2 - 1) / ((size_t)B * G * 2));     // fill the GPU at small batches
+    const int max_chunks = (int)((npad + 2047) / 2048);
+    if (chunks > max_chunks) chunks = max_chunks;
     if (chunks < 1) chunks = 1;
     NC_CHECK(B * G * 2 <= 65535, "conv4d_wgrad(tc): too many blocks for the bias grid");
     cb16_bias_grad_kernel<<<dim3(chunks, B * G * 2), 256, 0, st>>>(gbk, gb, Cout, npad, chunks);
