@@ -51,6 +51,7 @@ struct TcArgs {
     int d1, d2, d3, d4, KS, P;
     int R, nchunks;         // output k-rows per CTA, chunks per plane
     int NT, N, NG, KSTEPS;
+    int pair;               // 1: CTA pairs (cluster of 2, tcgen05 cta_group::2): the two plane chunks share one M256 MMA stream
     int OG;                 // branch groups side by side in N (1, or 2 for mode M4 on a shared input)
     int inner, m4;          // inner stage loop: the k d2 taps, or (mode M4) the channel blocks of the (d2,d4) taps
     int npos_pad;           // positions per channel-half in a smem stage
@@ -73,18 +74,38 @@ using namespace tc;
 
 // MMA issue loop of one CTA.  NT_C / KS_C > 0: compile-time tile and K-step counts (straight-line issue);
 // 0: run-time counts from the arguments.
-template <int NT_C, int KS_C>
+// PAIR: issued by the leader CTA of a pair with cta_group::2 (M = 256: this CTA's 128 rows + the peer's, each CTA holds
+// half of the N weight columns); waits for the peer's stage too and commits to both CTAs' barriers.
+template <bool PAIR>
+__device__ __forceinline__ void umma_issue(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+    if (PAIR)
+        asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                     ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
+    else
+        umma_f16(d, a, b, idesc, acc);
+}
+template <bool PAIR>
+__device__ __forceinline__ void umma_commit_to(uint32_t bar) {
+    if (PAIR)
+        asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                     ::"r"(bar), "h"((uint16_t)3) : "memory");
+    else
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+
+template <int NT_C, int KS_C, bool PAIR = false>
 __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t *stage0, uint64_t *full_bar, uint64_t *empty_bar,
-                                         uint32_t tmem_base, long long t_start) {
+                                         uint64_t *peer_full, uint32_t tmem_base, long long t_start) {
     constexpr int NTM = NT_C > 0 ? NT_C : 1, KSM = KS_C > 0 ? KS_C : 1;
     const int NT = NT_C > 0 ? NT_C : p.NT, KSTEPS = KS_C > 0 ? KS_C : p.KSTEPS;
     const int PAD = p.KS / 2;
     int stage = 0;
     uint32_t phase = 0;
     bool first = true;
-    const uint32_t lbo_a_field = (uint32_t)p.npos_pad << 16, lbo_b_field = (uint32_t)p.N << 16;   // LBO in 16-byte units
+    const uint32_t nloc = PAIR ? (uint32_t)p.N / 2u : (uint32_t)p.N;                              // weight columns held by this CTA
+    const uint32_t lbo_a_field = (uint32_t)p.npos_pad << 16, lbo_b_field = nloc << 16;            // LBO in 16-byte units
     const uint32_t hi = (128u >> 4) | (1u << 14);                                                 // SBO = 128 B, descriptor version 1
-    const uint32_t b_step = 2u * (uint32_t)p.N;                                                   // 16-byte units per K-step of weights
+    const uint32_t b_step = 2u * nloc;                                                            // 16-byte units per K-step of weights
     const uint32_t sm4 = smem_u32_pinned(stage0) >> 4, stage4 = p.stage_bytes >> 4, data4 = p.data_bytes >> 4;
     // low descriptor words relative to the stage base: A of (K-step, tile), B of K-step
     uint32_t a_rel[KSM][NTM], b_rel[KSM], d_col[NTM];
@@ -100,10 +121,12 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
     const int nplanes = (min(i + PAD, p.d1 - 1) - max(i - PAD, 0) + 1) *
                         (p.m4 ? p.inner : min(j + PAD, p.d2 - 1) - max(j - PAD, 0) + 1);
     const uint32_t full0 = smem_u32_pinned(full_bar), empty0 = smem_u32_pinned(empty_bar);
+    const uint32_t peer0 = smem_u32_pinned(peer_full);
     if (elect_one()) {                      // one lane runs the whole loop: no per-stage election / reconvergence
         for (int it = 0; it < nplanes; ++it) {
             {
                 mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+                if (PAIR) mbar_wait_u32(peer0 + (uint32_t)stage * 8u, phase);       // the peer CTA's stage has landed too
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 if (first && p.dbg && blockIdx.x < 3990) p.dbg[blockIdx.x * 8 + 0] = clock64() - t_start;
                 const uint32_t s4 = sm4 + (uint32_t)stage * stage4;      // the address field never carries into LBO (smem < 256 KB)
@@ -115,7 +138,7 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
                         const uint32_t acc = (first && ks == 0) ? 0u : 1u;
                         for (int t = 0; t < NT; ++t)
                             if (p.dbg_mode != 2)
-                                umma_f16(tmem_base + (uint32_t)(t * p.N), ((uint64_t)hi << 32) | (uint64_t)(a0 + (uint32_t)t * 128u), bdesc, p.idesc, acc);
+                                umma_issue<PAIR>(tmem_base + (uint32_t)(t * p.N), ((uint64_t)hi << 32) | (uint64_t)(a0 + (uint32_t)t * 128u), bdesc, p.idesc, acc);
                     }
                 } else if (first) {
 #pragma unroll
@@ -124,7 +147,7 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
 #pragma unroll
                         for (int t = 0; t < NTM; ++t)
                             if (p.dbg_mode != 2)
-                                umma_f16(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, ks == 0 ? 0u : 1u);
+                                umma_issue<PAIR>(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, ks == 0 ? 0u : 1u);
                     }
                 } else {
 #pragma unroll
@@ -133,12 +156,11 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
 #pragma unroll
                         for (int t = 0; t < NTM; ++t)
                             if (p.dbg_mode != 2)
-                                umma_f16(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, 1u);
+                                umma_issue<PAIR>(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, 1u);
                     }
                 }
                 // frees the smem slot when these MMAs have read it
-                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
-                             ::"r"(empty0 + (uint32_t)stage * 8u) : "memory");
+                umma_commit_to<PAIR>(empty0 + (uint32_t)stage * 8u);
             }
             first = false;
             if (++stage == p.stages) { stage = 0; phase ^= 1; }
@@ -147,14 +169,19 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
     __syncwarp();
 }
 
+// PAIR = true is a separate instantiation: a kernel that contains cta_group::2 / cluster instructions can only be launched
+// as a cluster, so the plain launches use the PAIR = false code.
+template <bool PAIR>
 __global__ void __launch_bounds__(kTcThreads, 2)
 conv4d_tc_kernel(const TcArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], accum_bar, mask_bar;
+    __shared__ __align__(8) uint64_t full_bar[kStages], empty_bar[kStages], peer_full[kStages], accum_bar, mask_bar;
     __shared__ uint32_t tmem_base_s;
     __shared__ int s_gshift[kMaxGroups];
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t cta_rank = 0;          // position in the CTA pair (= chunk parity: the pair is the two chunks of one plane)
+    if (PAIR) asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
     int bx = blockIdx.x;
     const int chunk = bx % p.nchunks; bx /= p.nchunks;
     const int j = bx % p.d2; bx /= p.d2;
@@ -178,14 +205,19 @@ conv4d_tc_kernel(const TcArgs p) {
     // ---- one-time setup -------------------------------------------------------------------
     if (threadIdx.x < kMaxGroups) s_gshift[threadIdx.x] = p.gshift[threadIdx.x];
     if (warp == 1 && lane == 0) {
-        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < kStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&peer_full[s], 1); }
         mbar_init(&accum_bar, 1);
         mbar_init(&mask_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {    // TMEM: NT accumulator tiles (256 columns or fewer lets two CTAs share the SM)
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(p.tmem_cols) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        if (PAIR) {
+            asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(p.tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+        } else {
+            asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(p.tmem_cols) : "memory");
+            asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+        }
     }
     {
         // zero, once, the tail of each channel-half buffer behind the rows the bulk copies overwrite: it
@@ -202,6 +234,10 @@ conv4d_tc_kernel(const TcArgs p) {
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (PAIR) {       // the peer's barriers must be initialised before remote arrives / multicast commits reach them
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
     const long long t_start = clock64();
@@ -220,7 +256,8 @@ conv4d_tc_kernel(const TcArgs p) {
         // the chunk's input rows (haloed coordinates k0 .. k0+R+KS-2), clipped to the plane
         const int rows_in = min(p.R + p.KS - 1, rows_pad - k0);
         const uint32_t half_bytes = (uint32_t)rows_in * p.P * 16u;
-        const uint32_t tx_bytes = (p.dbg_mode == 3 ? 0u : 2u * half_bytes) + (p.dbg_mode == 1 ? 0u : p.w_bytes);
+        const uint32_t wb = PAIR ? p.w_bytes / 2u : p.w_bytes;       // a pair's CTAs each hold half of the weight columns
+        const uint32_t tx_bytes = (p.dbg_mode == 3 ? 0u : 2u * half_bytes) + (p.dbg_mode == 1 ? 0u : wb);
         const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
         const size_t plane_halves = plane_cb * 8;
         // mode M4: the inner index selects the channel block (tensor block bg*inner + t2) of the SAME plane column j
@@ -257,7 +294,7 @@ conv4d_tc_kernel(const TcArgs p) {
                         bulk_g2s_u32(sb, src0, half_bytes, fb);
                         bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
                     }
-                    if (p.dbg_mode != 1) bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.inner + t2) * w_halves, p.w_bytes, fb);
+                    if (p.dbg_mode != 1) bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.inner + t2) * w_halves + (size_t)cta_rank * (wb / 2u), wb, fb);
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -270,14 +307,39 @@ conv4d_tc_kernel(const TcArgs p) {
         // retire an M128xN80xK16 MMA every 52 cycles.  The hot shapes therefore get a fully unrolled issue body
         // with the per-MMA descriptor offsets precomputed (one add per MMA); other shapes use the generic loop.
         bool done = false;
+        if (PAIR) {
+            done = true;
+            if (cta_rank == 0) {
+                if (p.NT == 3 && p.KSTEPS == 5) mma_main<3, 5, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start);
+                else mma_main<0, 0, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start);
+                if (elect_one()) { TC_STAMP(1); umma_commit_to<true>(smem_u32(&accum_bar)); }
+            } else if (elect_one()) {
+                // peer CTA: no MMAs of its own; tell the leader when each of this CTA's stages has landed
+                const int PADp = p.KS / 2;
+                const int nplanes = (min(i + PADp, p.d1 - 1) - max(i - PADp, 0) + 1) * (min(j + PADp, p.d2 - 1) - max(j - PADp, 0) + 1);
+                const uint32_t full0 = smem_u32_pinned(full_bar);
+                uint32_t remote0;
+                asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote0) : "r"(smem_u32(peer_full)), "r"(0));
+                int stage = 0;
+                uint32_t phase = 0;
+                for (int it = 0; it < nplanes; ++it) {
+                    mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+                    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote0 + (uint32_t)stage * 8u) : "memory");
+                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                }
+            }
+            __syncwarp();
+        }
 #define NC_TC_CASE(NT_, KS_) \
-        if (!done && p.NT == NT_ && p.KSTEPS == KS_) { mma_main<NT_, KS_>(p, i, j, stage0, full_bar, empty_bar, tmem_base, t_start); done = true; }
+        if (!done && p.NT == NT_ && p.KSTEPS == KS_) { mma_main<NT_, KS_>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start); done = true; }
         NC_TC_CASE(3, 5) NC_TC_CASE(6, 5) NC_TC_CASE(2, 5) NC_TC_CASE(4, 5)
         NC_TC_CASE(1, 1) NC_TC_CASE(2, 1) NC_TC_CASE(3, 1) NC_TC_CASE(4, 1) NC_TC_CASE(5, 1) NC_TC_CASE(6, 1) NC_TC_CASE(7, 1) NC_TC_CASE(8, 1)
         NC_TC_CASE(3, 3) NC_TC_CASE(4, 3) NC_TC_CASE(2, 3)
 #undef NC_TC_CASE
-        if (!done) mma_main<0, 0>(p, i, j, stage0, full_bar, empty_bar, tmem_base, t_start);
+        if (!PAIR) {
+        if (!done) mma_main<0, 0>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start);
         if (elect_one()) { TC_STAMP(1); umma_commit(&accum_bar); }
+        }
         __syncwarp();
     } else {
         // ===== epilogue (warps 2..5 <-> TMEM lane quadrants warp%4) =====
@@ -488,8 +550,13 @@ conv4d_tc_kernel(const TcArgs p) {
     // ---- teardown ------------------------------------------------------------------------------
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
+    if (PAIR) {       // neither CTA of a pair may leave (or free TMEM) while the other can still be read by the shared MMAs
+        asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+        asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    }
     if (warp == 0) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+        if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
+        else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(p.tmem_cols) : "memory");
     }
 }
 
@@ -878,6 +945,7 @@ struct TcPackW {
     PackDesc d;
     int mode;       // 1,2,3,4
     int KSTEPS, N, CoutPad, inner, OG;
+    int pairsplit;  // 1: per (d1,d2) slab the N columns are split in two contiguous halves [rank][K-step][2][N/2][8] (CTA pairs)
 };
 
 // -> [G][k*inner][KSTEPS][2][N][8] fp16   (inner = k d2 taps; mode 4: channel blocks of the (d2,d4) taps)
@@ -888,9 +956,18 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
          idx += (long long)gridDim.x * blockDim.x) {
         long long r = idx;
         const int c8 = (int)(r % 8); r /= 8;
-        const int n = (int)(r % a.N); r /= a.N;
-        const int half = (int)(r % 2); r /= 2;
-        const int ks = (int)(r % a.KSTEPS); r /= a.KSTEPS;
+        int n, half, ks;
+        if (a.pairsplit) {
+            const int nh = a.N / 2;
+            n = (int)(r % nh); r /= nh;
+            half = (int)(r % 2); r /= 2;
+            ks = (int)(r % a.KSTEPS); r /= a.KSTEPS;
+            n += (int)(r % 2) * nh; r /= 2;
+        } else {
+            n = (int)(r % a.N); r /= a.N;
+            half = (int)(r % 2); r /= 2;
+            ks = (int)(r % a.KSTEPS); r /= a.KSTEPS;
+        }
         int t2 = (int)(r % a.inner); r /= a.inner;
         const int t1 = (int)(r % k); r /= k;
         int g = (int)r;
@@ -1043,6 +1120,9 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     if (x_dtype == NCNET_CB16 && (pl.mode == 3 || pl.mode == 4)) return 2;   // the tap im2col needs the planar single-channel input
     if (y_dtype == NCNET_CB16 && pl.CoutPad < 16) return 2;
     if (mask && ((mask_dtype == NCNET_CB16) != (y_dtype == NCNET_CB16))) return 2;
+    // CTA pairs for the many-channel layers: the two chunks of a plane run as one cluster, one M256 MMA stream
+    static const bool pair_off = [] { const char *e = getenv("NCNET_TC_PAIR"); return e && e[0] == '0'; }();
+    const int pair = (!pair_off && pl.mode == 1 && pl.nchunks == 2 && pl.tmem_cols <= 256 && (pl.N / 2) % 8 == 0) ? 1 : 0;
     uint8_t *sc = (uint8_t *)scratch;
     const __half *act;
     size_t used = 0;
@@ -1058,6 +1138,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     {
         TcPackW a{};
         a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad; a.inner = pl.inner; a.OG = pl.OG;
+        a.pairsplit = pair;
         const long long total = (long long)(d.G_e / pl.OG) * d.k * pl.inner * pl.KSTEPS * 2 * pl.N * 8;
         const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
         pack_w_tc_kernel<<<blocks, 256, 0, st>>>(w, wp, a);
@@ -1077,7 +1158,8 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     a.dbg = g_tc_debug_buffer;
     a.dbg_mode = g_tc_debug_mode;
     // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
-    a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)((pair ? 256 : 128) >> 4) << 24);
+    a.pair = pair;
     const int pad = d.k / 2;
     for (int ks = 0; ks < kMaxKSteps; ++ks) a.aoff[ks] = ((pl.mode == 1 || pl.mode == 4) && ks < d.k) ? ks * pl.P : 0;
     for (int gi = 0; gi < kMaxGroups; ++gi) {
@@ -1090,11 +1172,23 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
         }
         a.gshift[gi] = s;
     }
-    cudaError_t e = cudaFuncSetAttribute(conv4d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes);
+    cudaError_t e = pair ? cudaFuncSetAttribute(conv4d_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes)
+                         : cudaFuncSetAttribute(conv4d_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pl.smem_bytes);
     NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
     const long long ctas = (long long)B * (d.G_e / pl.OG) * d1 * d2 * pl.nchunks;
     NC_CHECK(ctas < (1ll << 31), "conv4d(tc): grid too large");
-    conv4d_tc_kernel<<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a);
+    if (pair) {
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = pl.smem_bytes; cfg.stream = st;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr; cfg.numAttrs = 1;
+        e = cudaLaunchKernelEx(&cfg, conv4d_tc_kernel<true>, a);
+        NC_CHECK(e == cudaSuccess, "conv4d(tc): cluster launch: %s", cudaGetErrorString(e));
+    } else {
+        conv4d_tc_kernel<false><<<(unsigned)ctas, kTcThreads, pl.smem_bytes, st>>>(a);
+    }
     NC_LAUNCH_OK("conv4d_tc_kernel");
     return 0;
 }

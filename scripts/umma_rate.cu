@@ -101,6 +101,68 @@ __global__ void __launch_bounds__(128) rate_kernel(const RateArgs p) {
     if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tb), "r"(p.tmem_cols) : "memory");
 }
 
+
+// ---- CTA pair (cta_group::2): M = 256 across two SMs, each CTA supplies its 128 rows of A and HALF of B ----
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128) rate2_kernel(const RateArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t bar;
+    __shared__ uint32_t tmem_base_s;
+    for (int e = threadIdx.x; e < 96 * 1024 / 16; e += blockDim.x) reinterpret_cast<uint4 *>(smem)[e] = make_uint4(0, 0, 0, 0);
+    const int warp = threadIdx.x >> 5;
+    uint32_t rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(rank));
+    if (threadIdx.x == 0) { mbar_init(&bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(p.tmem_cols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tb = tmem_base_s;
+    long long best = 1ll << 60;
+    for (int rep = 0; rep < 3; ++rep) {
+        const long long t0 = clock64();
+        if (warp == 1 && rank == 0) {
+            if (elect_one()) {
+                const uint32_t sa4 = smem_u32(smem) >> 4, sb4 = (smem_u32(smem) + 64 * 1024) >> 4;
+                uint64_t av[8], bv[8];
+                uint32_t dv[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    const uint32_t c = (uint32_t)(u % p.cyc);
+                    av[u] = p.adesc | (uint64_t)(sa4 + c * p.a_step);
+                    bv[u] = p.bdesc | (uint64_t)(sb4 + c * p.b_step);
+                    dv[u] = tb + (uint32_t)((u % p.nacc) * p.N);
+                }
+                for (int it = 0; it < p.iters; it += 8) {
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, 1, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, q;\n\t}"
+                                     ::"r"(dv[u]), "l"(av[u]), "l"(bv[u]), "r"(p.idesc) : "memory");
+                }
+                asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                             ::"r"(smem_u32(&bar)), "h"((uint16_t)3) : "memory");
+            }
+            __syncwarp();
+        }
+        if (warp == 1) {
+            mbar_wait(&bar, rep & 1);
+            const long long dt = clock64() - t0;
+            if (dt < best) best = dt;
+        }
+    }
+    if (warp == 1 && (threadIdx.x & 31) == 0) p.out[blockIdx.x] = best;
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tb), "r"(p.tmem_cols) : "memory");
+}
+
 static uint64_t desc_hi(uint32_t lbo, uint32_t sbo, int layout) {
     uint64_t d = 0;
     d |= (uint64_t)((lbo >> 4) & 0x3fff) << 16;
@@ -150,5 +212,30 @@ int main() {
         printf("%-28s %4d %4d %10.1f %8.1f\n", c.name, c.M, c.N, s / grid / a.iters, c.M * c.N / 256.0);
         fflush(stdout);
     }
+
+    // CTA pairs: N is the TOTAL N of the M256 MMA, each CTA's B descriptor addresses its own N/2 columns
+    cudaFuncSetAttribute(rate2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
+    for (int per_sm = 1; per_sm <= 2; ++per_sm)
+        for (int N : {80, 160, 256}) {
+            RateArgs a{};
+            a.idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
+            a.adesc = desc_hi(8192, 128, 0);
+            a.bdesc = desc_hi((uint32_t)(N / 2) * 16, 128, 0);
+            a.a_step = 29; a.b_step = 0; a.cyc = 5; a.iters = 2048; a.N = N;
+            a.tmem_cols = per_sm == 2 ? 256 : 512;
+            a.nacc = (a.tmem_cols - 16) / N; if (a.nacc > 3) a.nacc = 3; if (a.nacc < 1) a.nacc = 1;
+            a.out = out;
+            const int grid = 148 * per_sm;
+            rate2_kernel<<<grid, 128, 96 * 1024>>>(a);
+            cudaError_t e = cudaDeviceSynchronize();
+            if (e != cudaSuccess) { printf("pair N=%d: ERROR %s\n", N, cudaGetErrorString(e)); return 1; }
+            std::vector<long long> h(grid);
+            cudaMemcpy(h.data(), out, grid * sizeof(long long), cudaMemcpyDeviceToHost);
+            double sum = 0; int cnt = 0;
+            for (int i = 0; i < grid; i += 2) { sum += (double)h[i]; ++cnt; }       // leaders
+            printf("%-28s %4d %4d %10.1f %8.1f\n", per_sm == 2 ? "cta_group::2 Kmaj 2pair/2sm" : "cta_group::2 Kmaj none", 256, N,
+                   sum / cnt / a.iters, 128 * N / 256.0);
+            fflush(stdout);
+        }
     return 0;
 }
