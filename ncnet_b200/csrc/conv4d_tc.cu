@@ -51,6 +51,8 @@ struct TcArgs {
     int d1, d2, d3, d4, KS, P;
     int R, nchunks;         // output k-rows per CTA, chunks per plane
     int NT, N, NG, KSTEPS;
+    int ntiles;             // persistent kernel: number of (b, group, iA, jA) planes
+    uint32_t out_off, mask_stride;   // persistent kernel: smem offset of the output plane; bytes between its two mask buffers
     int pair;               // 1: CTA pairs (cluster of 2, tcgen05 cta_group::2): the two plane chunks share one M256 MMA stream
     int OG;                 // branch groups side by side in N (1, or 2 for mode M4 on a shared input)
     int inner, m4;          // inner stage loop: the k d2 taps, or (mode M4) the channel blocks of the (d2,d4) taps
@@ -95,12 +97,10 @@ __device__ __forceinline__ void umma_commit_to(uint32_t bar) {
 
 template <int NT_C, int KS_C, bool PAIR = false>
 __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t *stage0, uint64_t *full_bar, uint64_t *empty_bar,
-                                         uint64_t *peer_full, uint32_t tmem_base, long long t_start) {
+                                         uint64_t *peer_full, uint32_t tmem_base, long long t_start, int &stage, uint32_t &phase) {
     constexpr int NTM = NT_C > 0 ? NT_C : 1, KSM = KS_C > 0 ? KS_C : 1;
     const int NT = NT_C > 0 ? NT_C : p.NT, KSTEPS = KS_C > 0 ? KS_C : p.KSTEPS;
     const int PAD = p.KS / 2;
-    int stage = 0;
-    uint32_t phase = 0;
     bool first = true;
     const uint32_t nloc = PAIR ? (uint32_t)p.N / 2u : (uint32_t)p.N;                              // weight columns held by this CTA
     const uint32_t lbo_a_field = (uint32_t)p.npos_pad << 16, lbo_b_field = nloc << 16;            // LBO in 16-byte units
@@ -307,11 +307,13 @@ conv4d_tc_kernel(const TcArgs p) {
         // retire an M128xN80xK16 MMA every 52 cycles.  The hot shapes therefore get a fully unrolled issue body
         // with the per-MMA descriptor offsets precomputed (one add per MMA); other shapes use the generic loop.
         bool done = false;
+        int mstage = 0;
+        uint32_t mphase = 0;
         if (PAIR) {
             done = true;
             if (cta_rank == 0) {
-                if (p.NT == 3 && p.KSTEPS == 5) mma_main<3, 5, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start);
-                else mma_main<0, 0, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start);
+                if (p.NT == 3 && p.KSTEPS == 5) mma_main<3, 5, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase);
+                else mma_main<0, 0, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase);
                 if (elect_one()) { TC_STAMP(1); umma_commit_to<true>(smem_u32(&accum_bar)); }
             } else if (elect_one()) {
                 // peer CTA: no MMAs of its own; tell the leader when each of this CTA's stages has landed
@@ -331,13 +333,13 @@ conv4d_tc_kernel(const TcArgs p) {
             __syncwarp();
         }
 #define NC_TC_CASE(NT_, KS_) \
-        if (!done && p.NT == NT_ && p.KSTEPS == KS_) { mma_main<NT_, KS_>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start); done = true; }
+        if (!done && p.NT == NT_ && p.KSTEPS == KS_) { mma_main<NT_, KS_>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase); done = true; }
         NC_TC_CASE(3, 5) NC_TC_CASE(6, 5) NC_TC_CASE(2, 5) NC_TC_CASE(4, 5)
         NC_TC_CASE(1, 1) NC_TC_CASE(2, 1) NC_TC_CASE(3, 1) NC_TC_CASE(4, 1) NC_TC_CASE(5, 1) NC_TC_CASE(6, 1) NC_TC_CASE(7, 1) NC_TC_CASE(8, 1)
         NC_TC_CASE(3, 3) NC_TC_CASE(4, 3) NC_TC_CASE(2, 3)
 #undef NC_TC_CASE
         if (!PAIR) {
-        if (!done) mma_main<0, 0>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start);
+        if (!done) mma_main<0, 0>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase);
         if (elect_one()) { TC_STAMP(1); umma_commit(&accum_bar); }
         }
         __syncwarp();
@@ -560,6 +562,308 @@ conv4d_tc_kernel(const TcArgs p) {
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Persistent, TMEM-double-buffered variant for the many-channel layers (mode M1, CB16 output, CTA pairs).
+//
+// One CTA pair per SM pair walks the plane list.  The 512 TMEM columns hold TWO accumulator sets, so the leader's MMA
+// stream runs on while the epilogue warps drain, shift-sum and store the previous plane: the tensor pipe no longer
+// idles during prologue/epilogue (which was ~25 % of a CTA's life in the one-plane-per-CTA kernel), barriers and TMEM
+// are set up once, and the stage ring (which no longer doubles as the output plane) keeps streaming across planes.
+//   warp 0: producer (both CTAs)        warp 1: MMA issuer (leader) / stage relay (peer)        warps 2-5: epilogue
+//   barriers: full/empty per stage, peer_full per stage (leader), acc_full[2] (multicast commit), acc_empty[2] (leader,
+//   one arrive per CTA after its TMEM reads), mask_full[2] / mask_empty[2] (dgrad ReLU mask staging)
+// ---------------------------------------------------------------------------------------------
+constexpr int kPStages = 8;
+
+__device__ __forceinline__ void tile_coords(const TcArgs &p, int tile, int &b, int &g, int &i, int &j) {
+    j = tile % p.d2; tile /= p.d2;
+    i = tile % p.d1; tile /= p.d1;
+    g = tile % p.G;
+    b = tile / p.G;
+}
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv4d_tc_persist_kernel(const TcArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[kPStages], empty_bar[kPStages], peer_full[kPStages];
+    __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2], mask_full[2], mask_empty[2];
+    __shared__ uint32_t tmem_base_s;
+    __shared__ int s_gshift[kMaxGroups];
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t cta_rank;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
+    const int chunk = (int)cta_rank;                     // the pair = the two row chunks of a plane
+    const int cluster_id = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
+    const int PAD = p.KS / 2;
+    const int k0 = chunk * p.R;
+    const int rows_out = min(p.R, p.d3 - k0);
+    const int rows_pad = p.d3 + 2 * PAD;
+    const size_t plane_cb = (size_t)rows_pad * p.P;
+    const size_t ij_count = (size_t)p.d1 * p.d2;
+    const bool has_mask = p.mask_mode == 3;
+    const uint32_t mbytes = (uint32_t)rows_out * p.P * 16u;
+
+    if (threadIdx.x < kMaxGroups) s_gshift[threadIdx.x] = p.gshift[threadIdx.x];
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&peer_full[s], 1); }
+        for (int s = 0; s < 2; ++s) {
+            mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 2);
+            mbar_init(&mask_full[s], 1); mbar_init(&mask_empty[s], 1);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    {   // zero, once, the tail of each channel-half buffer behind the rows the bulk copies overwrite (read by the last
+        // tiles' discarded rows; must stay finite).  The chunk, hence the tail, is the same for every plane of this CTA.
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        const int copied = min(p.R + p.KS - 1, rows_pad - k0) * p.P;
+        const int tail = p.npos_pad - copied;
+        for (int e = threadIdx.x; e < p.stages * 2 * tail; e += kTcThreads) {
+            const int s = e / (2 * tail), r = e - s * 2 * tail;
+            const int half = r / tail, pos = copied + (r - half * tail);
+            reinterpret_cast<uint4 *>(smem + (size_t)s * p.stage_bytes)[(size_t)half * p.npos_pad + pos] = z;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t sm0 = smem_u32_pinned(smem);
+
+
+    if (warp == 0) {
+        // ===== producer: streams every plane's (d1,d2) stages, then that plane's ReLU-mask chunk =====
+        if (elect_one()) {
+            int stage = 0;
+            uint32_t phase = 0;
+            const int rows_in = min(p.R + p.KS - 1, rows_pad - k0);
+            const uint32_t half_bytes = (uint32_t)rows_in * p.P * 16u;
+            const uint32_t wb = p.w_bytes / 2u;                      // this CTA's half of the weight columns
+            const uint32_t tx_bytes = 2u * half_bytes + wb;
+            const size_t plane_halves = plane_cb * 8;
+            const size_t blk_halves = 2 * ij_count * plane_halves, half_off = ij_count * plane_halves;
+            const uint32_t w_halves = p.w_bytes / 2;
+            const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
+            const uint32_t full0 = smem_u32_pinned(full_bar), empty0 = smem_u32_pinned(empty_bar);
+            const uint32_t mfull0 = smem_u32_pinned(mask_full), mempty0 = smem_u32_pinned(mask_empty);
+            int n = 0;
+            for (int tile = cluster_id; tile < p.ntiles; tile += nclusters, ++n) {
+                int b, g, i, j;
+                tile_coords(p, tile, b, g, i, j);
+                const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
+                const __half *src_base = p.act + bg * blk_halves + (size_t)k0 * p.P * 8;
+                const __half *w_base = p.wp + (size_t)g * p.KS * p.KS * w_halves + (size_t)cta_rank * (wb / 2u);
+                for (int t1 = 0; t1 < p.KS; ++t1) {
+                    const int ii = i + t1 - PAD;
+                    if (ii < 0 || ii >= p.d1) continue;
+                    for (int t2 = 0; t2 < p.KS; ++t2) {
+                        const int jj = j + t2 - PAD;
+                        if (jj < 0 || jj >= p.d2) continue;
+                        mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
+                        const uint32_t sb = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
+                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(tx_bytes) : "memory");
+                        const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves;
+                        bulk_g2s_u32(sb, src0, half_bytes, fb);
+                        bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
+                        bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.KS + t2) * w_halves, wb, fb);
+                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                    }
+                }
+                if (has_mask) {
+                    // after the plane's stages: waiting for the mask buffer (free once the epilogue of plane n-2 has
+                    // stored) must not hold back the stage stream
+                    const uint32_t mb = (uint32_t)(n & 1);
+                    mbar_wait_u32(mempty0 + mb * 8u, (((uint32_t)n >> 1) & 1u) ^ 1u);
+                    const uint32_t mf = mfull0 + mb * 8u, dst = sm0 + p.mask_off + mb * p.mask_stride;
+                    const __half *msrc = (const __half *)p.mask +
+                        ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8 + (size_t)(k0 + PAD) * p.P * 8;
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mf), "r"(2u * mbytes) : "memory");
+                    bulk_g2s_u32(dst, msrc, mbytes, mf);
+                    bulk_g2s_u32(dst + mbytes, msrc + ij_count * plane_cb * 8, mbytes, mf);
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (cta_rank == 0) {
+            // ===== MMA issuer (leader): accumulator set n&1; waits until BOTH CTAs' epilogues have drained it =====
+            int stage = 0;
+            uint32_t phase = 0;
+            const uint32_t aempty0 = smem_u32_pinned(acc_empty), afull0 = smem_u32_pinned(acc_full);
+            int n = 0;
+            for (int tile = cluster_id; tile < p.ntiles; tile += nclusters, ++n) {
+                int b, g, i, j;
+                tile_coords(p, tile, b, g, i, j);
+                const uint32_t buf = (uint32_t)(n & 1);
+                mbar_wait_u32(aempty0 + buf * 8u, (((uint32_t)n >> 1) & 1u) ^ 1u);
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint32_t tb = tmem_base + buf * 256u;
+                if (p.NT == 3 && p.KSTEPS == 5) mma_main<3, 5, true>(p, i, j, smem, full_bar, empty_bar, peer_full, tb, 0, stage, phase);
+                else mma_main<0, 0, true>(p, i, j, smem, full_bar, empty_bar, peer_full, tb, 0, stage, phase);
+                if (elect_one()) umma_commit_to<true>(afull0 + buf * 8u);
+                __syncwarp();
+            }
+        } else if (elect_one()) {
+            // ===== stage relay (peer): tells the leader when each of this CTA's stages has landed =====
+            const uint32_t full0 = smem_u32_pinned(full_bar);
+            uint32_t remote0;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote0) : "r"(smem_u32(peer_full)), "r"(0));
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int tile = cluster_id; tile < p.ntiles; tile += nclusters) {
+                int b, g, i, j;
+                tile_coords(p, tile, b, g, i, j);
+                const int nplanes = (min(i + PAD, p.d1 - 1) - max(i - PAD, 0) + 1) * (min(j + PAD, p.d2 - 1) - max(j - PAD, 0) + 1);
+                for (int it = 0; it < nplanes; ++it) {
+                    mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+                    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote0 + (uint32_t)stage * 8u) : "memory");
+                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                }
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue (warps 2..5 <-> TMEM lane quadrants warp%4): drains set n&1 while the issuer fills the other =====
+        const int q = warp & 3;
+        const int et = threadIdx.x - 64;                 // 0..127
+        const uint32_t osm = sm0 + p.out_off;
+        const uint32_t afull0 = smem_u32_pinned(acc_full), mfull0 = smem_u32_pinned(mask_full);
+        uint32_t aempty_leader;                          // the leader's acc_empty[0] as a cluster address
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(aempty_leader) : "r"(smem_u32(acc_empty)), "r"(0));
+        float bv[16];
+#pragma unroll
+        for (int o = 0; o < 16; ++o) bv[o] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
+        const int ra = chunk == 0 ? 0 : k0 + PAD;
+        const int rb = chunk == p.nchunks - 1 ? rows_pad : k0 + PAD + rows_out;
+        const int npos = (rb - ra) * p.P;
+        int n = 0;
+        for (int tile = cluster_id; tile < p.ntiles; tile += nclusters, ++n) {
+            int b, g, i, j;
+            tile_coords(p, tile, b, g, i, j);
+            const uint32_t buf = (uint32_t)(n & 1), par = ((uint32_t)n >> 1) & 1u;
+            mbar_wait_sleep(&acc_full[buf], par, 200);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            // shifted sums: out[m - shift_gi][o] (+)= D[m][gi*16 + o]; group 0 writes bias + D, the others accumulate
+            const uint32_t lane_base = tmem_base + buf * 256u + ((uint32_t)(q * 32) << 16);
+            const int npair = (p.NT + 1) >> 1, nit = p.NG * npair;
+            uint32_t r0[16], r1[16], n0[16], n1[16];
+            tmem_ld16_issue(lane_base, r0);
+            if (p.NT > 1) tmem_ld16_issue(lane_base + (uint32_t)p.N, r1);
+            int gi = 0, t = 0;
+            for (int it = 0; it < nit; ++it) {
+                const bool two = t + 1 < p.NT;
+                const int sh = s_gshift[gi];
+                tmem_ld16_wait(r0);
+                if (two) tmem_ld16_wait(r1);
+                int gn = gi, tn = t + 2;
+                if (tn >= p.NT) { tn = 0; ++gn; }
+                if (it + 1 < nit) {
+                    tmem_ld16_issue(lane_base + (uint32_t)(tn * p.N + gn * 16), n0);
+                    if (tn + 1 < p.NT) tmem_ld16_issue(lane_base + (uint32_t)((tn + 1) * p.N + gn * 16), n1);
+                }
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    if (h == 1 && !two) break;
+                    const uint32_t(&r)[16] = h ? r1 : r0;
+                    const int dest = (t + h) * 128 + q * 32 + lane - sh;
+                    if (dest >= 0) {
+                        const uint32_t dst = osm + (uint32_t)dest * (kOutStride * 4u);
+                        if (gi == 0) {
+#pragma unroll
+                            for (int w4 = 0; w4 < 4; ++w4)
+                                sts_v4(dst + 16u * w4,
+                                       make_float4(bv[4 * w4 + 0] + __uint_as_float(r[4 * w4 + 0]), bv[4 * w4 + 1] + __uint_as_float(r[4 * w4 + 1]),
+                                                   bv[4 * w4 + 2] + __uint_as_float(r[4 * w4 + 2]), bv[4 * w4 + 3] + __uint_as_float(r[4 * w4 + 3])));
+                        } else {
+                            float4 a[4];
+#pragma unroll
+                            for (int w4 = 0; w4 < 4; ++w4) a[w4] = lds_v4(dst + 16u * w4);
+#pragma unroll
+                            for (int w4 = 0; w4 < 4; ++w4) {
+                                a[w4].x += __uint_as_float(r[4 * w4 + 0]); a[w4].y += __uint_as_float(r[4 * w4 + 1]);
+                                a[w4].z += __uint_as_float(r[4 * w4 + 2]); a[w4].w += __uint_as_float(r[4 * w4 + 3]);
+                                sts_v4(dst + 16u * w4, a[w4]);
+                            }
+                        }
+                    }
+                }
+                if (it + 1 < nit) {
+                    tmem_ld16_wait(n0);
+                    if (tn + 1 < p.NT) tmem_ld16_wait(n1);
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) { r0[u] = n0[u]; r1[u] = n1[u]; }
+                }
+                if (gn != gi) {
+                    if (it + 1 == nit) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");   // all TMEM reads done
+                    asm volatile("bar.sync 1, 128;" ::: "memory");       // last tile pair of this group
+                }
+                gi = gn; t = tn;
+            }
+            // this CTA's half of accumulator set `buf` is drained: one arrive per CTA on the LEADER's barrier
+            if (et == 0)
+                asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(aempty_leader + buf * 8u) : "memory");
+            // ---- store: CB16 (+ position-major twin), this chunk's rows of the haloed plane, halo written as zeros ----
+            const uint32_t mb = buf;
+            if (has_mask) mbar_wait_u32(mfull0 + mb * 8u, par);
+            const uint32_t msm = sm0 + p.mask_off + mb * p.mask_stride;
+            const size_t base_off = ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8;
+            __half *ob = (__half *)p.out + base_off;
+            for (int e = et; e < 2 * npos; e += 128) {
+                const int half = e / npos, pp = e - half * npos;
+                const int kk = ra + pp / p.P, ll = pp % p.P;
+                const int kr = kk - PAD - k0, lc = ll - PAD;
+                const size_t goff = ((size_t)half * ij_count * plane_cb + (size_t)kk * p.P + ll) * 8;
+                __align__(16) __half hv[8];
+                if (kr >= 0 && kr < rows_out && lc >= 0 && lc < p.d4) {
+                    const uint32_t src = osm + (uint32_t)((kr * p.P + lc) * kOutStride + half * 8) * 4u;
+                    const float4 a = lds_v4(src), c = lds_v4(src + 16u);
+                    float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+                    if (has_mask) {
+                        const uint4 mraw = lds_u4(msm + (uint32_t)half * mbytes + (uint32_t)(kr * p.P + ll) * 16u);
+                        const __half *mh = reinterpret_cast<const __half *>(&mraw);
+#pragma unroll
+                        for (int c8 = 0; c8 < 8; ++c8) if (!(__half2float(mh[c8]) > 0.f)) v[c8] = 0.f;
+                    }
+#pragma unroll
+                    for (int c8 = 0; c8 < 8; ++c8) {
+                        float x = v[c8];
+                        if (p.relu) x = fmaxf(x, 0.f);
+                        hv[c8] = __float2half_rn((half * 8 + c8) < p.Cout ? x : 0.f);
+                    }
+                } else {
+#pragma unroll
+                    for (int c8 = 0; c8 < 8; ++c8) hv[c8] = __float2half_rn(0.f);
+                }
+                *reinterpret_cast<uint4 *>(ob + goff) = *reinterpret_cast<const uint4 *>(hv);
+                if (p.out_pm) {
+                    const int pos = kk * p.P + ll;
+                    const size_t pm_off = ((((size_t)b * p.G + g) * ij_count + (size_t)i * p.d2 + j) * plane_cb + pos) * 16 +
+                                          (size_t)((half ^ ((pos >> 2) & 1)) * 8);
+                    *reinterpret_cast<uint4 *>(p.out_pm + pm_off) = *reinterpret_cast<const uint4 *>(hv);
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");       // the output plane and the mask buffer are free again
+            if (has_mask && et == 0) {
+                const uint32_t me = smem_u32(&mask_empty[mb]);
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(me) : "memory");
+            }
+        }
+    }
+    // ---- teardown: neither CTA may leave while the other's MMAs / remote arrives can still touch it ----
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+}
 // ---------------------------------------------------------------------------------------------
 // CB16 packing
 // ---------------------------------------------------------------------------------------------
@@ -1177,6 +1481,40 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
     const long long ctas = (long long)B * (d.G_e / pl.OG) * d1 * d2 * pl.nchunks;
     NC_CHECK(ctas < (1ll << 31), "conv4d(tc): grid too large");
+    // persistent, TMEM-double-buffered pair kernel for CB16 -> CB16 layers
+    // (opt-in: measured 3.95 ms against 3.71 ms for the two-CTAs-per-SM pair kernel on the 16->16 layer at B = 16 -- with
+    // one pair per SM pair the main loop needs 33 B/clk/SM of L2->shared traffic, above the ~26 B/clk the chip delivers)
+    static const bool persist_on = [] { const char *e = getenv("NCNET_TC_PERSIST"); return e && e[0] == '1'; }();
+    if (pair && persist_on && a.out_mode == 2 && (a.mask_mode == 0 || a.mask_mode == 3) && !a.dbg && pl.NT * pl.N <= 256 &&
+        pl.stages <= kPStages) {
+        const uint32_t stage_p = ((pl.data_bytes + pl.w_bytes / 2u + 127u) / 128u) * 128u;
+        const uint32_t outb = (((uint32_t)pl.NT * 128u * kOutStride * 4u) + 127u) / 128u * 128u;
+        const uint32_t maskb = a.mask_mode == 3 ? (((uint32_t)2 * pl.R * pl.P * 16u + 127u) / 128u * 128u) : 0u;
+        const uint32_t budget = 220u * 1024u;
+        int stages_p = (int)((budget - outb - 2u * maskb) / stage_p);
+        if (stages_p > kPStages) stages_p = kPStages;
+        if (stages_p >= 3) {
+            TcArgs q = a;
+            q.stages = stages_p; q.stage_bytes = stage_p;
+            q.out_off = (uint32_t)stages_p * stage_p;
+            q.mask_off = q.out_off + outb; q.mask_stride = maskb;
+            q.ntiles = B * a.G * d1 * d2;
+            const size_t smem_p = (size_t)q.mask_off + 2u * maskb;
+            e = cudaFuncSetAttribute(conv4d_tc_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p);
+            NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
+            const int nclusters = q.ntiles < kNumSMs / 2 ? q.ntiles : kNumSMs / 2;
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3((unsigned)(2 * nclusters)); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = smem_p; cfg.stream = st;
+            cudaLaunchAttribute attr[1];
+            attr[0].id = cudaLaunchAttributeClusterDimension;
+            attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+            cfg.attrs = attr; cfg.numAttrs = 1;
+            e = cudaLaunchKernelEx(&cfg, conv4d_tc_persist_kernel, q);
+            NC_CHECK(e == cudaSuccess, "conv4d(tc): persistent cluster launch: %s", cudaGetErrorString(e));
+            NC_LAUNCH_OK("conv4d_tc_persist_kernel");
+            return 0;
+        }
+    }
     if (pair) {
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = pl.smem_bytes; cfg.stream = st;
