@@ -40,7 +40,8 @@ def test_tc_conv4d_golden(F_, cuda, tag):
 
 @pytest.mark.parametrize("cin,cout,k,dims,bsz", [
     (16, 16, 5, (6, 7, 25, 25), 2), (1, 16, 5, (7, 6, 12, 13), 2), (16, 1, 5, (6, 6, 11, 9), 1),
-    (16, 16, 3, (5, 6, 20, 37), 1), (10, 10, 3, (5, 5, 8, 9), 2), (1, 16, 3, (5, 6, 50, 37), 1)])
+    (16, 16, 3, (5, 6, 20, 37), 1), (10, 10, 3, (5, 5, 8, 9), 2), (1, 16, 3, (5, 6, 50, 37), 1),
+    (16, 1, 3, (5, 5, 9, 10), 2), (1, 12, 3, (6, 5, 10, 9), 2), (12, 1, 5, (5, 6, 25, 25), 1)])
 def test_tc_conv4d_vs_oracle(F_, cuda, cin, cout, k, dims, bsz):
     torch.manual_seed(31)
     x = torch.rand(bsz, cin, *dims)
@@ -55,6 +56,26 @@ def test_tc_conv4d_vs_oracle(F_, cuda, cin, cout, k, dims, bsz):
     assert nerr(y, yo) < 1e-3
     gx, gw, gb = torch.autograd.grad(y, (xg, wg, bg), gy.to(cuda))
     assert nerr(gx, rx) < 1e-3 and nerr(gw, rw) < 1e-3 and nerr(gb, rb) < 1e-3
+
+
+@pytest.mark.parametrize("cin,cout,k", [(1, 16, 5), (16, 1, 5), (16, 16, 5)])
+def test_tc_conv4d_half_tensors_vs_oracle(F_, cuda, cin, cout, k):
+    """fp16 activations (the InLoc storage type) through the tensor-core forward / dgrad / wgrad kernels."""
+    torch.manual_seed(39)
+    dims, bsz = (5, 6, 12, 11), 2
+    x = torch.rand(bsz, cin, *dims).half().float()
+    layer = O.Conv4d(cin, cout, k)
+    w, b = layer.weight.detach(), layer.bias.detach()
+    xo, wo, bo = x.clone().requires_grad_(True), w.clone().requires_grad_(True), b.clone().requires_grad_(True)
+    yo = O.conv4d(xo, wo, bo, permute_filters=False)
+    gy = torch.randn_like(yo).half().float()
+    rx, rw, rb = torch.autograd.grad(yo, (xo, wo, bo), gy)
+    xg = x.half().to(cuda).requires_grad_(True)
+    wg, bg = (t.to(cuda).requires_grad_(True) for t in (w, b))
+    y = F_.conv4d(xg, wg, bg, permute_filters=False, mode=_tc())
+    assert y.dtype == torch.float16 and nerr(y.float(), yo) < 3e-3
+    gx, gw, gb = torch.autograd.grad(y, (xg, wg, bg), gy.half().to(cuda))
+    assert nerr(gx.float(), rx) < 3e-3 and nerr(gw.float(), rw) < 3e-3 and nerr(gb.float(), rb) < 3e-3
 
 
 def test_cb16_roundtrip_and_halo(F_, cuda):
