@@ -155,7 +155,7 @@ mm_apply_kernel(const T *__restrict__ x, T *__restrict__ y, const unsigned long 
     if (c0 >= nB) {
         // keep the warp converged for the shuffles below
     }
-#pragma unroll 4
+#pragma unroll
     for (int r = 0; r < kMMApplyRows; ++r) {
         const float rrcp = __shfl_sync(0xffffffffu, my_rrcp, r);
         const int a = a0 + r;
