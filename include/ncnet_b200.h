@@ -93,8 +93,11 @@ int ncnet_mutual_matching_max(const void *x, uint64_t *keys, int B, int nA, int 
 int ncnet_mutual_matching_apply(const void *x, const uint64_t *keys, void *y, int B, int nA, int nB, int in_groups,
                                 int dtype, void *stream);
 /* backward: grad_x = d(y)/d(x)^T grad_y incl. the flow through both max reductions.
- * sums: scratch, B*(nA+nB) floats.  x is the forward input (in_groups as in forward;
- * grad_x is [B,nA,nB]: the gradient of the summed volume). */
+ * sums: scratch of ncnet_mutual_matching_sums_bytes(B,nA,nB) bytes (the reduced row/column sums followed by
+ * per-CTA partial sums: the sums are formed in a fixed order, without floating-point atomics, so two runs give
+ * the same bits).  x is the forward input (in_groups as in forward; grad_x is [B,nA,nB]: the gradient of the
+ * summed volume). */
+size_t ncnet_mutual_matching_sums_bytes(int B, int nA, int nB);
 int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t *keys, float *sums,
                               void *grad_x, int B, int nA, int nB, int in_groups, int dtype, void *stream);
 
@@ -116,8 +119,9 @@ int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, int nA, int
 /* Weak-supervision matching score -- train.py:123-134 with normalization='softmax':
  *   score = ( mean_{b,t} max_a softmax_a(corr[b,a,t]) + mean_{b,a} max_t softmax_t(corr[b,a,t]) ) / 2
  * (the reference adds the two score vectors, which needs nA == nB; for nA != nB the two means are taken
- * separately).  corr: [B,nA,nB].  keys: B*(nA+nB) uint64 and sums: B*(nA+nB) floats are outputs that the backward
- * pass consumes; score: one float on the device.  _bwd: grad_corr = grad_score[0] * d(score)/d(corr). */
+ * separately).  corr: [B,nA,nB].  keys: B*(nA+nB) uint64 and sums: ncnet_mutual_matching_sums_bytes(B,nA,nB) bytes
+ * (its first B*(nA+nB) floats are the row/column sums of exponentials) are outputs that the backward pass
+ * consumes; score: one float on the device.  _bwd: grad_corr = grad_score[0] * d(score)/d(corr). */
 int ncnet_match_score_fwd(const void *corr, uint64_t *keys, float *sums, float *score, int B, int nA, int nB,
                           int dtype, void *stream);
 int ncnet_match_score_bwd(const void *corr, const uint64_t *keys, const float *sums, const float *grad_score,

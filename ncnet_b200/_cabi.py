@@ -30,6 +30,7 @@ SIGNATURES = {
     "ncnet_corr4d_fwd_tc": (_i, [_p, _p, _p, _p] + [_i] * 7 + [_p]),
     "ncnet_corr4d_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_keys_bytes": (_sz, [_i, _i, _i]),
+    "ncnet_mutual_matching_sums_bytes": (_sz, [_i, _i, _i]),
     "ncnet_mutual_matching_fwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_max": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_apply": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),

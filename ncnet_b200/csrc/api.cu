@@ -89,9 +89,10 @@ extern "C" size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int
     size_t a = conv4d_fp32_wgrad_scratch_bytes(B, Cin, Cout, d1, d2, d3, d4, k, symmetric);
     if (mode == NCNET_CONV_TC16) {
         size_t b = conv4d_tc_wgrad_scratch_bytes(B, Cin, Cout, d1, d2, d3, d4, k, symmetric);
-        return a > b ? a : b;
+        a = a > b ? a : b;
     }
-    return a;
+    if (a == 0) return 0;
+    return a + bias_partial_bytes(B, symmetric ? 2 : 1, Cout);       // head of the scratch: bias-gradient partial sums
 }
 
 extern "C" int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, float *grad_bias,
@@ -101,15 +102,17 @@ extern "C" int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad
     NC_CHECK(x && grad_y && grad_weight && scratch, "conv4d_wgrad: null pointer");
     if (check_conv("conv4d_wgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, NCNET_F32, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
+    float *bias_part = (float *)scratch;
+    scratch = (uint8_t *)scratch + bias_partial_bytes(B, symmetric ? 2 : 1, Cout);
     if (mode == NCNET_CONV_TC16) {
-        const int rc = conv4d_tc_wgrad(x, x_dtype, grad_y, gy_dtype, grad_weight, grad_bias, scratch, B, Cin, Cout, d1, d2,
-                                       d3, d4, k, w_layout, symmetric, shared_input, st);
+        const int rc = conv4d_tc_wgrad(x, x_dtype, grad_y, gy_dtype, grad_weight, grad_bias, scratch, bias_part, B, Cin, Cout,
+                                       d1, d2, d3, d4, k, w_layout, symmetric, shared_input, st);
         if (rc != 2) return rc;      // 2: outside the tensor-core kernel's envelope -> CUDA-core kernel
     }
     NC_CHECK(planar(x_dtype) && x_dtype == gy_dtype,
              "conv4d_wgrad: this shape runs on the CUDA-core kernel, which needs planar tensors of one dtype");
-    return conv4d_fp32_wgrad(x, grad_y, grad_weight, grad_bias, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout,
-                             symmetric, shared_input, x_dtype, st);
+    return conv4d_fp32_wgrad(x, grad_y, grad_weight, grad_bias, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k,
+                             w_layout, symmetric, shared_input, x_dtype, st);
 }
 
 extern "C" int ncnet_conv4d_tc_supported(int Cin, int Cout, int k, int d3, int d4) {

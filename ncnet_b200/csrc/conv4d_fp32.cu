@@ -429,8 +429,26 @@ bias_grad_kernel(const T *__restrict__ gy, float *__restrict__ db, int Cout, int
     if (threadIdx.x == 0) {
         float t = 0.f;
         for (int w = 0; w < 8; ++w) t += sm[w];
-        atomicAdd(db + o, t);
+        // partial of (chunk, b, g) for channel o:  part[(chunk*B*G + bg)*Cout + o]
+        db[((size_t)blockIdx.x * (gridDim.y / Cout) + chan / Cout) * Cout + o] = t;
     }
+}
+
+// db[o] = sum over entries of part[e*W + o], one warp per channel, fixed order
+__global__ void bias_reduce_kernel(const float *__restrict__ part, float *__restrict__ db, int Cout, int entries, int W) {
+    const int o = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (o >= Cout) return;
+    float t = 0.f;
+    for (int e = lane; e < entries; e += 32) t += part[(size_t)e * W + o];
+    t = warp_sum(t);
+    if (lane == 0) db[o] = t;
+}
+
+int bias_reduce(const float *part, float *db, int Cout, int entries, int W, cudaStream_t st) {
+    NC_CHECK(Cout <= 32, "bias gradient: more than 32 output channels");
+    bias_reduce_kernel<<<1, 32 * Cout, 0, st>>>(part, db, Cout, entries, W);
+    NC_LAUNCH_OK("bias_reduce_kernel");
+    return 0;
 }
 
 template <typename T>
@@ -596,32 +614,31 @@ static int launch_wgrad(WgradArgs a, const WgradPlan &w, cudaStream_t st) {
 }
 
 // shared tail of both wgrad back ends: slice partials -> reference layout (+ bias gradient)
-int wgrad_finish(const float *part, float *gw, float *gb, const void *gy, int S, int G, int B, int Cin, int Cout, int k,
-                 int cop, int w_layout, size_t vol, int dtype, cudaStream_t st) {
+int wgrad_finish(const float *part, float *gw, float *gb, float *bias_part, const void *gy, int S, int G, int B, int Cin,
+                 int Cout, int k, int cop, int w_layout, size_t vol, int dtype, cudaStream_t st) {
     const int total = Cout * Cin * k * k * k * k;
     unpack_wgrad_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, gw, S, G, Cin, Cout, k, cop, w_layout);
     NC_LAUNCH_OK("unpack_wgrad_kernel");
     if (gb) {
-        cudaError_t e = cudaMemsetAsync(gb, 0, Cout * sizeof(float), st);
-        NC_CHECK(e == cudaSuccess, "wgrad: memset bias: %s", cudaGetErrorString(e));
         // enough blocks to fill the GPU at small batches (a few channels x 6 chunks left 140 SMs idle)
-        int chunks = (int)((16 * kNumSMs + (size_t)B * G * Cout - 1) / ((size_t)B * G * Cout));
+        int chunks = (int)((kBiasTargetCtas + (size_t)B * G * Cout - 1) / ((size_t)B * G * Cout));
         const int max_chunks = (int)((vol + 2047) / 2048);
         if (chunks > max_chunks) chunks = max_chunks;
         if (chunks < 1) chunks = 1;
         NC_CHECK(B * G * Cout <= 65535, "wgrad: too many channels for bias grid");
         if (dtype == NCNET_F32)
-            bias_grad_kernel<float><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const float *)gy, gb, Cout, G, vol, chunks);
+            bias_grad_kernel<float><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const float *)gy, bias_part, Cout, G, vol, chunks);
         else
-            bias_grad_kernel<__half><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const __half *)gy, gb, Cout, G, vol, chunks);
+            bias_grad_kernel<__half><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const __half *)gy, bias_part, Cout, G, vol, chunks);
         NC_LAUNCH_OK("bias_grad_kernel");
+        return bias_reduce(bias_part, gb, Cout, chunks * B * G, Cout, st);
     }
     return 0;
 }
 
 template <typename T>
-static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout,
-                     int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
+static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, int B, int Cin,
+                     int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
                      cudaStream_t st) {
     const int G = symmetric ? 2 : 1;
     NC_CHECK(Cout <= 16, "conv4d_wgrad: Cout=%d > 16 not supported", Cout);
@@ -637,17 +654,17 @@ static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *
     int rc = (k == 3) ? launch_wgrad<3, T>(a, w, st) : (k == 5 ? launch_wgrad<5, T>(a, w, st)
                                                               : fail("conv4d_wgrad: kernel size %d not supported", k));
     if (rc) return rc;
-    return wgrad_finish((const float *)scratch, gw, gb, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout,
+    return wgrad_finish((const float *)scratch, gw, gb, bias_part, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout,
                         (size_t)d1 * d2 * d3 * d4, sizeof(T) == 4 ? NCNET_F32 : NCNET_F16, st);
 }
 
-int conv4d_fp32_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, int B, int Cin, int Cout,
-                      int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input, int dtype,
-                      cudaStream_t st) {
+int conv4d_fp32_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, int B, int Cin,
+                      int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
+                      int dtype, cudaStream_t st) {
     if (dtype == NCNET_F32)
-        return run_wgrad<float>(x, gy, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+        return run_wgrad<float>(x, gy, gw, gb, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
                                 shared_input, st);
-    return run_wgrad<__half>(x, gy, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+    return run_wgrad<__half>(x, gy, gw, gb, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
                              shared_input, st);
 }
 

@@ -258,10 +258,11 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
 }
 
 // conv4d_fp32.cu: reduces the per-slice partial sums into the reference layout and sums the bias gradient
-int wgrad_finish(const float *part, float *gw, float *gb, const void *gy, int S, int G, int B, int Cin, int Cout, int k,
-                 int cop, int w_layout, size_t vol, int dtype, cudaStream_t st);
+int wgrad_finish(const float *part, float *gw, float *gb, float *bias_part, const void *gy, int S, int G, int B, int Cin,
+                 int Cout, int k, int cop, int w_layout, size_t vol, int dtype, cudaStream_t st);
 
-// bias gradient from a CB16 grad_y: db[o] += sum over blocks and positions (halo is zero)
+// bias gradient from a CB16 grad_y, stage 1: db[(chunk*nblk + blk)*16 + o] = partial sum over the chunk's positions
+// (halo is zero); stage 2 is bias_reduce (conv4d_fp32.cu)
 __global__ void __launch_bounds__(256)
 cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int Cout, size_t npad, int chunks) {
     const size_t blkhalf = blockIdx.y;            // (block, half)
@@ -295,7 +296,7 @@ cb16_bias_grad_kernel(const __half *__restrict__ gy, float *__restrict__ db, int
         float t = 0.f;
         for (int w8 = 0; w8 < 8; ++w8) t += sm[w8][threadIdx.x];
         const int o = half * 8 + threadIdx.x;
-        if (o < Cout) atomicAdd(db + o, t);
+        db[((size_t)blockIdx.x * (gridDim.y >> 1) + (blkhalf >> 1)) * 16 + o] = t;
     }
 }
 
@@ -399,9 +400,9 @@ size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, i
 }
 
 // returns 2 when the shape/layout is outside the tensor-core kernel's envelope
-static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch, int B,
-                  int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
-                  cudaStream_t st) {
+static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch,
+                  float *bias_part, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
+                  int symmetric, int shared_input, cudaStream_t st) {
     const int G = symmetric ? 2 : 1;
     const int GxA = (G == 2 && !shared_input) ? 2 : 1;
     const WgPlan w = wg_plan(B, Cin, Cout, d1, d2, d3, d4, k, G);
@@ -492,27 +493,25 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
         NC_LAUNCH_OK("conv4d_tc_wgrad_kernel");
     }
     if (gy_dtype != NCNET_CB16)
-        return wgrad_finish(part, gw, gb, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, gy_dtype, st);
-    int rc = wgrad_finish(part, gw, nullptr, nullptr, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, NCNET_F32, st);
+        return wgrad_finish(part, gw, gb, bias_part, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, gy_dtype, st);
+    int rc = wgrad_finish(part, gw, nullptr, nullptr, nullptr, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, NCNET_F32, st);
     if (rc || !gb) return rc;
-    e = cudaMemsetAsync(gb, 0, Cout * sizeof(float), st);
-    NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc): memset bias: %s", cudaGetErrorString(e));
     const int pad = k / 2;
     const size_t npad = (size_t)d1 * d2 * (d3 + 2 * pad) * (d4 + 2 * pad);
-    int chunks = (int)((16 * kNumSMs + (size_t)B * G * 2 - 1) / ((size_t)B * G * 2));     // fill the GPU at small batches
+    int chunks = (int)((kBiasTargetCtas + (size_t)B * G * 2 - 1) / ((size_t)B * G * 2));     // fill the GPU at small batches
     const int max_chunks = (int)((npad + 2047) / 2048);
     if (chunks > max_chunks) chunks = max_chunks;
     if (chunks < 1) chunks = 1;
     NC_CHECK(B * G * 2 <= 65535, "conv4d_wgrad(tc): too many blocks for the bias grid");
-    cb16_bias_grad_kernel<<<dim3(chunks, B * G * 2), 256, 0, st>>>(gbk, gb, Cout, npad, chunks);
+    cb16_bias_grad_kernel<<<dim3(chunks, B * G * 2), 256, 0, st>>>(gbk, bias_part, Cout, npad, chunks);
     NC_LAUNCH_OK("cb16_bias_grad_kernel");
-    return 0;
+    return bias_reduce(bias_part, gb, Cout, chunks * B * G, 16, st);
 }
 
-int conv4d_tc_wgrad(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch, int B,
-                    int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric,
-                    int shared_input, cudaStream_t st) {
-    return wg_run(x, x_dtype, gy, gy_dtype, gw, gb, scratch, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+int conv4d_tc_wgrad(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch,
+                    float *bias_part, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
+                    int symmetric, int shared_input, cudaStream_t st) {
+    return wg_run(x, x_dtype, gy, gy_dtype, gw, gb, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
                   shared_input, st);
 }
 

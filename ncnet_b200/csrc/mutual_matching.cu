@@ -193,11 +193,34 @@ mm_apply_kernel(const T *__restrict__ x, T *__restrict__ y, const unsigned long 
     }
 }
 
-// backward pass 1: Sr[a] = sum_b g*y, Sc[b] = sum_a g*y  (y recomputed in fp32)
+// Row / column sums without floating-point atomics (their arrival order would make the result differ from run to
+// run).  The sum kernels run on a (column tile, row strip, batch) grid; every CTA owns one (tile, strip) cell and
+// writes its partial row sums to rpart[b][tile][a] and its partial column sums to cpart[b][strip][c].  Every entry
+// is written exactly once, so the buffers need no clearing, and the consumers add the partials in index order.
+// Layout of the `sums` scratch (floats): [B*(nA+nB)] reduced sums | rpart | cpart.
+struct MMSumLayout {
+    int rpb, col_tiles, strips;
+    size_t rpart_off, cpart_off, total;
+};
+
+static int rows_per_block_for(int B, int nA, int nB, int tile_cols);
+
+static MMSumLayout mm_sum_layout(int B, int nA, int nB) {
+    MMSumLayout L;
+    L.rpb = rows_per_block_for(B, nA, nB, kMMBwdCols);
+    L.col_tiles = (nB + kMMBwdCols - 1) / kMMBwdCols;
+    L.strips = (nA + L.rpb - 1) / L.rpb;
+    L.rpart_off = (size_t)B * ((size_t)nA + nB);
+    L.cpart_off = L.rpart_off + (size_t)B * L.col_tiles * nA;
+    L.total = L.cpart_off + (size_t)B * L.strips * nB;
+    return L;
+}
+
+// backward pass 1: partial sums of Sr[a] = sum_b g*y, Sc[b] = sum_a g*y  (y recomputed in fp32)
 template <typename T>
 __global__ void __launch_bounds__(kMMThreads)
 mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsigned long long *__restrict__ keys,
-                   float *__restrict__ sums, int nA, int nB, int rows_per_block, int groups) {
+                   float *__restrict__ rpart, float *__restrict__ cpart, int nA, int nB, int rows_per_block, int groups) {
     const int b = blockIdx.z;
     const int row0 = blockIdx.y * rows_per_block;
     const int col0 = blockIdx.x * kMMBwdCols;
@@ -207,8 +230,8 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
     const T *gb = gy + (size_t)b * mat;
     const unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
     const unsigned long long *colkeys = rowkeys + nA;
-    float *rsum = sums + (size_t)b * (nA + nB);
-    float *csum = rsum + nA;
+    float *rsum = rpart + ((size_t)b * gridDim.x + blockIdx.x) * nA;
+    float *csum = cpart + ((size_t)b * gridDim.y + blockIdx.y) * nB;
 
     float cden[kMMBwdSlots], cacc[kMMBwdSlots];
 #pragma unroll
@@ -234,7 +257,7 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
             }
         }
         racc = warp_sum(racc);
-        if (lane == 0) atomicAdd(rsum + a, racc);
+        if (lane == 0) rsum[a] = racc;
     }
     __shared__ float sm[kMMThreads / 32][kMMBwdCols];
 #pragma unroll
@@ -245,7 +268,7 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < kMMThreads / 32; ++w) t += sm[w][threadIdx.x];
-        atomicAdd(csum + c, t);
+        csum[c] = t;
     }
 }
 
@@ -253,7 +276,8 @@ mm_bwd_sums_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsi
 template <typename T>
 __global__ void __launch_bounds__(256)
 mm_bwd_apply_kernel(const T *__restrict__ x, const T *__restrict__ gy, const unsigned long long *__restrict__ keys,
-                    const float *__restrict__ sums, T *__restrict__ gx, int nA, int nB, int groups) {
+                    const float *__restrict__ rpart, const float *__restrict__ cpart, int col_tiles, int strips,
+                    T *__restrict__ gx, int nA, int nB, int groups) {
     const int b = blockIdx.y;
     const size_t mat = (size_t)nA * nB;
     const size_t e0 = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
@@ -263,8 +287,8 @@ mm_bwd_apply_kernel(const T *__restrict__ x, const T *__restrict__ gy, const uns
     T *ob = gx + (size_t)b * mat;
     const unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
     const unsigned long long *colkeys = rowkeys + nA;
-    const float *rsum = sums + (size_t)b * (nA + nB);
-    const float *csum = rsum + nA;
+    const float *rsum = rpart + (size_t)b * col_tiles * nA;     // [col_tiles][nA] partials of this batch item
+    const float *csum = cpart + (size_t)b * strips * nB;        // [strips][nB]
     int a = (int)(e0 / nB), c = (int)(e0 - (size_t)a * nB);
     unsigned long long rk = rowkeys[a];
 #pragma unroll
@@ -280,8 +304,17 @@ mm_bwd_apply_kernel(const T *__restrict__ x, const T *__restrict__ gy, const uns
             // y = v*(qa*qb):  d/dv through the three occurrences of v
             float d = g * (qa * qb) + (g * v * qb) / rden + (g * v * qa) / cden;
             // flow through the maxima lands on their (first) arg-max element
-            if ((int)key_idx(rk) == c) d -= rsum[a] / rden;
-            if ((int)key_idx(ck) == a) d -= csum[c] / cden;
+            // (one element per row and per column: the partial sums are added here, in index order)
+            if ((int)key_idx(rk) == c) {
+                float t = 0.f;
+                for (int q = 0; q < col_tiles; ++q) t += rsum[(size_t)q * nA + a];
+                d -= t / rden;
+            }
+            if ((int)key_idx(ck) == a) {
+                float t = 0.f;
+                for (int q = 0; q < strips; ++q) t += csum[(size_t)q * nB + c];
+                d -= t / cden;
+            }
             stf(ob + e, d);
         }
         if (++c == nB) {
@@ -346,16 +379,16 @@ static int mm_fwd_parts(const void *x, void *y, uint64_t *keys, int B, int nA, i
 template <typename T>
 static int mm_bwd(const void *x, const void *gy, const uint64_t *keys, float *sums, void *gx, int B, int nA, int nB,
                   int groups, cudaStream_t st) {
-    cudaError_t e = cudaMemsetAsync(sums, 0, (size_t)B * (nA + nB) * sizeof(float), st);
-    NC_CHECK(e == cudaSuccess, "mutual_matching_bwd: memset sums: %s", cudaGetErrorString(e));
-    const int rpb = rows_per_block_for(B, nA, nB, kMMBwdCols);
-    dim3 g1((nB + kMMBwdCols - 1) / kMMBwdCols, (nA + rpb - 1) / rpb, B);
+    const MMSumLayout L = mm_sum_layout(B, nA, nB);
+    NC_CHECK(L.strips <= 65535, "mutual_matching_bwd: too many row strips");
+    dim3 g1(L.col_tiles, L.strips, B);
     mm_bwd_sums_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (const T *)gy, (const unsigned long long *)keys,
-                                                     sums, nA, nB, rpb, groups);
+                                                     sums + L.rpart_off, sums + L.cpart_off, nA, nB, L.rpb, groups);
     NC_LAUNCH_OK("mm_bwd_sums_kernel");
     const size_t mat = (size_t)nA * nB;
     dim3 g2((unsigned)((mat + 1023) / 1024), B);
-    mm_bwd_apply_kernel<T><<<g2, 256, 0, st>>>((const T *)x, (const T *)gy, (const unsigned long long *)keys, sums,
+    mm_bwd_apply_kernel<T><<<g2, 256, 0, st>>>((const T *)x, (const T *)gy, (const unsigned long long *)keys,
+                                               sums + L.rpart_off, sums + L.cpart_off, L.col_tiles, L.strips,
                                                (T *)gx, nA, nB, groups);
     NC_LAUNCH_OK("mm_bwd_apply_kernel");
     return 0;
@@ -367,6 +400,11 @@ using namespace ncnet;
 
 extern "C" size_t ncnet_mutual_matching_keys_bytes(int B, int nA, int nB) {
     return (size_t)B * ((size_t)nA + nB) * sizeof(uint64_t);
+}
+
+extern "C" size_t ncnet_mutual_matching_sums_bytes(int B, int nA, int nB) {
+    if (B <= 0 || nA <= 0 || nB <= 0) return 0;
+    return mm_sum_layout(B, nA, nB).total * sizeof(float);
 }
 
 extern "C" int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB,
@@ -486,8 +524,8 @@ namespace ncnet {
 
 template <typename T>
 __global__ void __launch_bounds__(kMMThreads)
-score_sumexp_kernel(const T *__restrict__ x, const unsigned long long *__restrict__ keys, float *__restrict__ sums,
-                    int nA, int nB, int rows_per_block) {
+score_sumexp_kernel(const T *__restrict__ x, const unsigned long long *__restrict__ keys, float *__restrict__ rpart,
+                    float *__restrict__ cpart, int nA, int nB, int rows_per_block) {
     const int b = blockIdx.z;
     const int row0 = blockIdx.y * rows_per_block;
     const int col0 = blockIdx.x * kMMBwdCols;
@@ -495,7 +533,8 @@ score_sumexp_kernel(const T *__restrict__ x, const unsigned long long *__restric
     const size_t mat = (size_t)nA * nB;
     const T *xb = x + (size_t)b * mat;
     const size_t kb = (size_t)b * (nA + nB);
-    float *rsum = sums + kb, *csum = rsum + nA;
+    float *rsum = rpart + ((size_t)b * gridDim.x + blockIdx.x) * nA;
+    float *csum = cpart + ((size_t)b * gridDim.y + blockIdx.y) * nB;
     float cmax[kMMBwdSlots], cacc[kMMBwdSlots];
 #pragma unroll
     for (int s = 0; s < kMMBwdSlots; ++s) {
@@ -522,7 +561,7 @@ score_sumexp_kernel(const T *__restrict__ x, const unsigned long long *__restric
             }
         }
         racc = warp_sum(racc);
-        if (lane == 0) atomicAdd(rsum + a, racc);
+        if (lane == 0) rsum[a] = racc;
     }
     __shared__ float sm[kMMThreads / 32][kMMBwdCols];
 #pragma unroll
@@ -533,8 +572,27 @@ score_sumexp_kernel(const T *__restrict__ x, const unsigned long long *__restric
         float t = 0.f;
 #pragma unroll
         for (int w = 0; w < kMMThreads / 32; ++w) t += sm[w][threadIdx.x];
-        atomicAdd(csum + c, t);
+        csum[c] = t;
     }
+}
+
+// partial sums -> sums[b][0..nA) (rows) and sums[b][nA..nA+nB) (columns), added in index order
+__global__ void __launch_bounds__(256)
+score_sums_reduce_kernel(float *__restrict__ sums, const float *__restrict__ rpart, const float *__restrict__ cpart,
+                         int B, int nA, int nB, int col_tiles, int strips) {
+    const int per = nA + nB;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)B * per) return;
+    const int b = (int)(i / per), r = (int)(i - (long long)b * per);
+    float t = 0.f;
+    if (r < nA) {
+        const float *p = rpart + (size_t)b * col_tiles * nA + r;
+        for (int q = 0; q < col_tiles; ++q) t += p[(size_t)q * nA];
+    } else {
+        const float *p = cpart + (size_t)b * strips * nB + (r - nA);
+        for (int q = 0; q < strips; ++q) t += p[(size_t)q * nB];
+    }
+    sums[i] = t;
 }
 
 // score = (sum_rows 1/S / (B*nA) + sum_cols 1/S / (B*nB)) / 2, one block, fixed summation order
@@ -597,12 +655,16 @@ template <typename T>
 static int score_fwd(const void *x, uint64_t *keys, float *sums, float *score, int B, int nA, int nB, cudaStream_t st) {
     int rc = mm_fwd_parts<T>(x, nullptr, keys, B, nA, nB, 1, 1, st);      // pass 1: maxima and first arg-maxima
     if (rc) return rc;
-    cudaError_t e = cudaMemsetAsync(sums, 0, (size_t)B * (nA + nB) * sizeof(float), st);
-    NC_CHECK(e == cudaSuccess, "match_score: memset: %s", cudaGetErrorString(e));
-    const int rpb = rows_per_block_for(B, nA, nB, kMMBwdCols);
-    dim3 g1((nB + kMMBwdCols - 1) / kMMBwdCols, (nA + rpb - 1) / rpb, B);
-    score_sumexp_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (const unsigned long long *)keys, sums, nA, nB, rpb);
+    const MMSumLayout L = mm_sum_layout(B, nA, nB);
+    NC_CHECK(L.strips <= 65535, "match_score: too many row strips");
+    dim3 g1(L.col_tiles, L.strips, B);
+    score_sumexp_kernel<T><<<g1, kMMThreads, 0, st>>>((const T *)x, (const unsigned long long *)keys, sums + L.rpart_off,
+                                                      sums + L.cpart_off, nA, nB, L.rpb);
     NC_LAUNCH_OK("score_sumexp_kernel");
+    const long long nsum = (long long)B * (nA + nB);
+    score_sums_reduce_kernel<<<(unsigned)((nsum + 255) / 256), 256, 0, st>>>(sums, sums + L.rpart_off, sums + L.cpart_off, B,
+                                                                             nA, nB, L.col_tiles, L.strips);
+    NC_LAUNCH_OK("score_sums_reduce_kernel");
     score_reduce_kernel<<<1, 1024, 0, st>>>(sums, score, B, nA, nB);
     NC_LAUNCH_OK("score_reduce_kernel");
     return 0;

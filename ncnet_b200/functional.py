@@ -167,7 +167,7 @@ class _MutualMatchingFn(torch.autograd.Function):
         na, nb = f1 * f2, f3 * f4
         gy = gy.contiguous()
         gx = torch.empty(b, 1, f1, f2, f3, f4, device=xc.device, dtype=xc.dtype)
-        sums = torch.empty(b * (na + nb), device=xc.device, dtype=torch.float32)
+        sums = torch.empty(_cabi.lib().ncnet_mutual_matching_sums_bytes(b, na, nb) // 4, device=xc.device, dtype=torch.float32)
         with torch.cuda.device(xc.device):
             _cabi.check(_cabi.lib().ncnet_mutual_matching_bwd(_ptr(xc), _ptr(gy), _ptr(keys), _ptr(sums), _ptr(gx), b,
                                                               na, nb, g, _dt(xc), _stream()), "mutual_matching_bwd")
@@ -194,7 +194,7 @@ class _MatchScoreFn(torch.autograd.Function):
         x = corr4d.contiguous()
         na, nb = f1 * f2, f3 * f4
         keys = torch.empty(b * (na + nb), device=x.device, dtype=torch.int64)
-        sums = torch.empty(b * (na + nb), device=x.device, dtype=torch.float32)
+        sums = torch.empty(_cabi.lib().ncnet_mutual_matching_sums_bytes(b, na, nb) // 4, device=x.device, dtype=torch.float32)
         score = torch.empty((), device=x.device, dtype=torch.float32)
         with torch.cuda.device(x.device):
             _cabi.check(_cabi.lib().ncnet_match_score_fwd(_ptr(x), _ptr(keys), _ptr(sums), _ptr(score), b, na, nb, _dt(x),
