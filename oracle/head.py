@@ -2,7 +2,7 @@
 
 TEST INFRASTRUCTURE ONLY -- never imported by ``ncnet_b200``.  Plain PyTorch on
 CPU tensors, fp32 or fp64, written from the algorithm's definition and pinned
-against the reference's own modules by ``oracle/check_against_reference.py``
+against the reference's own modules by ``oracle/make_golden.py``
 (run in the build container where ``/root/reference`` exists) and by the golden
 fixtures under ``tests/golden`` that script family generates.
 

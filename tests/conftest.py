@@ -45,3 +45,18 @@ def cuda():
     if not torch.cuda.is_available():
         pytest.skip("no CUDA device")
     return torch.device("cuda:0")
+
+
+def make_head(nb, kernel_sizes, channels, state_dict=None, reloc=0, half=False):
+    """An ImMatchNet without its trunk (no torchvision download): the matching head the GPU tests drive through
+    ``match_features``.  The real constructor is exercised by tests/test_gpu_model.py."""
+    net = nb.ImMatchNet.__new__(nb.ImMatchNet)
+    torch.nn.Module.__init__(net)
+    net.relocalization_k_size, net.half_precision = reloc, half
+    net.FeatureCorrelation = nb.FeatureCorrelation("4D", False)
+    net.NeighConsensus = nb.NeighConsensus(True, list(kernel_sizes), list(channels))
+    if state_dict is not None:
+        net.NeighConsensus.load_state_dict(state_dict)
+    if half:
+        net.NeighConsensus.half()
+    return net
