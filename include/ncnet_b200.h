@@ -207,6 +207,38 @@ int ncnet_corr_to_matches(const void *corr, int B, int fs1, int fs2, int fs3, in
                           float *xA, float *yA, float *xB, float *yB, float *score,
                           int64_t *iA, int64_t *jA, int64_t *iB, int64_t *jB, int dtype, void *stream);
 
+/* InLoc match post-processing -- eval_inloc.py:151-203, on the device instead of numpy on the host.
+ * Input: the (xA,yA,xB,yB,score) columns of corr_to_matches for one direction (n1 matches) and optionally the
+ * other (n2 matches) -- the reference concatenates them in this order.  n2 == 0 (second-direction pointers and
+ * scratch may be NULL) is the reference's single-direction branch: nothing is removed, the order is kept, the
+ * coordinates are recentred.  Otherwise duplicate (xA,yA,xB,yB) columns are removed keeping the highest score (the reference sorts by descending score
+ * and lets np.unique keep the first occurrence); the survivors come out in np.unique's order (lexicographic in
+ * xA,yA,xB,yB), recentred as  v*(n-1)/n + 0.5/n  with n = recentre_* (the reference's fs*k_size per axis; 0 = leave
+ * the coordinate alone), as rows [xA,yA,xB,yB,score] of out[(n1+n2),5]; unused rows are zero; *count (device int) =
+ * number of rows written.  scratch: ncnet_matches_unique_scratch_bytes(n1+n2) bytes.  The duplicate search compares
+ * all pairs (at most 2^20 matches). */
+size_t ncnet_matches_unique_scratch_bytes(int n);
+int ncnet_matches_sort_unique(const float *xA, const float *yA, const float *xB, const float *yB, const float *score,
+                              int n1, const float *xA2, const float *yA2, const float *xB2, const float *yB2,
+                              const float *score2, int n2, int recentre_yA, int recentre_xA, int recentre_yB,
+                              int recentre_xB, float *out, int *count, void *scratch, void *stream);
+
+/* PointsToUnitCoords / PointsToPixelCoords -- lib/point_tnf.py:151-167 (normalize_axis / unnormalize_axis, :6-10).
+ * points,out: [B,2,N] (row 0 = x scaled by the image width, row 1 = y by the height); im_size: [B,im_stride] fp32
+ * rows (h, w, ...).  to_unit != 0: pixel -> [-1,1]; 0: the inverse. */
+int ncnet_points_axis_transform(const float *points, const float *im_size, int im_stride, float *out, int B, int N,
+                                int to_unit, void *stream);
+/* bilinearInterpPointTnf -- lib/point_tnf.py:96-148.  matches xA,yA,xB,yB: [B,fs*fs] (corr_to_matches, B->A
+ * direction: xB,yB is the regular target grid); grid: the fs values np.linspace(-1,1,fs) as fp32;
+ * target_points_norm,out: [B,2,N].  Like the reference the neighbour look-ups address the flattened match arrays
+ * without a batch offset (the evaluation uses batch 1). */
+int ncnet_bilinear_point_tnf(const float *xA, const float *yA, const float *xB, const float *yB, const float *grid,
+                             int fs, const float *target_points_norm, float *out, int B, int N, void *stream);
+/* pck -- lib/eval_util.py:12-25.  source_points, warped_points: [B,2,N] (invalid source points are -1 and trail the
+ * valid ones); L_pck: [B]; out[b] = fraction of the valid points with distance <= L_pck[b]*alpha. */
+int ncnet_pck(const float *source_points, const float *warped_points, const float *L_pck, float alpha, float *out,
+              int B, int N, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -50,6 +50,11 @@ SIGNATURES = {
     "ncnet_cb16_unpack": (_i, [_p, _p] + [_i] * 8 + [_p]),
     "ncnet_relu_mask_bcast": (_i, [_p, _p, _p, _i, _i, _ll, _i, _p]),
     "ncnet_maxpool4d_fwd": (_i, [_p] * 6 + [_i] * 7 + [_p]),
+    "ncnet_matches_unique_scratch_bytes": (_sz, [_i]),
+    "ncnet_matches_sort_unique": (_i, [_p] * 5 + [_i] + [_p] * 5 + [_i] * 5 + [_p] * 4),
+    "ncnet_points_axis_transform": (_i, [_p, _p, _i, _p, _i, _i, _i, _p]),
+    "ncnet_bilinear_point_tnf": (_i, [_p] * 5 + [_i, _p, _p, _i, _i, _p]),
+    "ncnet_pck": (_i, [_p, _p, _p, C.c_float, _p, _i, _i, _p]),
     "ncnet_corr_to_matches": (_i, [_p] + [_i] * 8 + [_p] * 4 + [_i] + [_p] * 4 + [_p] * 9 + [_i, _p]),
 }
 

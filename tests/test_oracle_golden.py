@@ -101,3 +101,30 @@ def test_head_and_weak_loss():
     assert nerr(O.head_forward(g["fa"], g["fb"], nc), g["head_pos"]) < 1e-5
     loss = O.weak_loss(g["fa"], g["fb"], nc)
     assert abs(float(loss) - float(g["loss"])) < 5e-8
+
+
+def test_post_oracle_reproduces_reference_point_transfer_and_pck():
+    """oracle/post.py against the reference's own bilinearInterpPointTnf / PointsTo*Coords / pck outputs."""
+    from oracle import post as P
+    g = load_golden("point_tnf")
+    tpn = P.points_to_unit_coords(g["target_points"], g["target_im_size"])
+    assert torch.equal(tpn, g["target_points_norm"])
+    wpn = P.bilinear_interp_point_tnf((g["xA"], g["yA"], g["xB"], g["yB"]), tpn)
+    assert torch.equal(wpn, g["warped_points_norm"])
+    assert torch.equal(P.points_to_pixel_coords(wpn, g["source_im_size"]), g["warped_points"])
+    assert torch.equal(P.pck(g["source_points"], g["warped_points"], g["L_pck"]), g["pck"])
+    assert torch.equal(P.pck(g["source_points"], g["warped_points"], g["L_pck"], 0.05), g["pck05"])
+
+
+def test_inloc_postprocess_oracle_removes_duplicates_keeping_best_score():
+    from oracle import post as P
+    torch.manual_seed(5)
+    corr = torch.rand(1, 1, 4, 5, 6, 3)
+    corr[0, 0, 1, 2, 3, 1] = 5.0                       # a mutual best match: found in both directions
+    a = O.corr_to_matches(corr, do_softmax=True, scale="positive")
+    b = O.corr_to_matches(corr, do_softmax=True, scale="positive", invert_matching_direction=True)
+    rows = P.inloc_postprocess(a, b, (4, 5, 6, 3), 1)
+    assert rows.shape[1] == 5 and rows.shape[0] < 18 + 20
+    assert len({tuple(r[:4]) for r in rows}) == rows.shape[0]
+    coords = [tuple(r[:4]) for r in rows]
+    assert coords == sorted(coords)                    # np.unique order: lexicographic in (xA, yA, xB, yB)
