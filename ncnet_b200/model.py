@@ -3,7 +3,7 @@ and state_dict keys; the matching head runs on this library's CUDA kernels, the 
 stays on stock PyTorch/cuDNN (BASELINE.json north_star)."""
 from __future__ import annotations
 
-import warnings
+import os
 from collections import OrderedDict
 
 import torch
@@ -23,20 +23,20 @@ class FeatureExtraction(torch.nn.Module):
     so ``ImMatchNet`` is self-contained.  Only its trailing L2 normalisation runs on our kernel."""
 
     def __init__(self, train_fe=False, feature_extraction_cnn='resnet101', feature_extraction_model_file='',
-                 normalization=True, last_layer='', use_cuda=True):
+                 normalization=True, last_layer='', use_cuda=True, pretrained=None):
+        """``pretrained`` (not in the reference): None = ImageNet weights as the reference's ``pretrained=True``
+        (lib/model.py:39: torchvision's IMAGENET1K_V1 set) unless NCNET_TRUNK_WEIGHTS=random is set; False = random
+        initialisation (what ``ImMatchNet`` passes when a checkpoint will overwrite the trunk anyway).  A failed
+        download raises: a silently random trunk trains and evaluates to garbage."""
         super().__init__()
         import torchvision.models as models
         self.normalization = normalization
         self.feature_extraction_cnn = feature_extraction_cnn
+        if pretrained is None:
+            pretrained = os.environ.get("NCNET_TRUNK_WEIGHTS", "imagenet").lower() != "random"
 
         def make(name):
-            ctor = getattr(models, name)
-            try:
-                return ctor(weights="DEFAULT")
-            except Exception as exc:                       # no network / no cached weights
-                warnings.warn(f"FeatureExtraction: pretrained {name} weights unavailable ({type(exc).__name__}); "
-                              "using random initialisation")
-                return ctor(weights=None)
+            return getattr(models, name)(weights="IMAGENET1K_V1" if pretrained else None)
 
         if feature_extraction_cnn == 'vgg':
             names = ['conv1_1', 'relu1_1', 'conv1_2', 'relu1_2', 'pool1', 'conv2_1', 'relu2_1', 'conv2_2', 'relu2_2',
@@ -172,7 +172,8 @@ class ImMatchNet(nn.Module):
                                                    feature_extraction_model_file=feature_extraction_model_file,
                                                    last_layer=feature_extraction_last_layer,
                                                    normalization=normalize_features,
-                                                   use_cuda=self.use_cuda)
+                                                   use_cuda=self.use_cuda,
+                                                   pretrained=False if (checkpoint is not None and checkpoint != '') else None)
         self.FeatureCorrelation = FeatureCorrelation(shape='4D', normalization=False)
         self.NeighConsensus = NeighConsensus(use_cuda=self.use_cuda, kernel_sizes=ncons_kernel_sizes,
                                              channels=ncons_channels)

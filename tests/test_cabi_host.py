@@ -87,3 +87,31 @@ def test_axis_helpers():
     n = nb.normalize_axis(x, 25)
     assert torch.allclose(n, torch.tensor([-1.0, 0.0, 1.0]))
     assert torch.allclose(nb.unnormalize_axis(n, 25), x)
+
+
+def test_lib_shim_resolves_head_modules_to_this_library(tmp_path, monkeypatch):
+    """ncnet_b200/dropin/lib: `from lib.model import ImMatchNet` (train.py:15) gives this library's class while the
+    reference's other lib.* modules keep resolving to the reference checkout."""
+    import importlib
+    import sys
+    fake = tmp_path / "ref" / "lib"
+    fake.mkdir(parents=True)
+    (fake / "torch_util.py").write_text("def str_to_bool(v):\n    return v == 'True'\n")
+    (fake / "model.py").write_text("raise ImportError('the reference head must not be imported')\n")
+    dropin = os.path.join(ROOT, "ncnet_b200", "dropin")
+    monkeypatch.setenv("NCNET_REFERENCE_ROOT", str(tmp_path / "ref"))
+    monkeypatch.syspath_prepend(dropin)
+    for name in [m for m in sys.modules if m == "lib" or m.startswith("lib.")]:
+        monkeypatch.delitem(sys.modules, name)
+    lib = importlib.import_module("lib")
+    assert os.path.dirname(lib.__file__) == os.path.join(dropin, "lib")
+    import ncnet_b200
+    from lib.conv4d import Conv4d, conv4d
+    from lib.eval_util import pck_metric
+    from lib.model import ImMatchNet, MutualMatching
+    from lib.point_tnf import bilinearInterpPointTnf, corr_to_matches, normalize_axis
+    from lib.torch_util import str_to_bool
+    assert ImMatchNet is ncnet_b200.ImMatchNet and Conv4d is ncnet_b200.Conv4d and corr_to_matches is ncnet_b200.corr_to_matches
+    assert str_to_bool("True") and callable(pck_metric) and callable(bilinearInterpPointTnf) and callable(MutualMatching)
+    for name in [m for m in sys.modules if m == "lib" or m.startswith("lib.")]:
+        monkeypatch.delitem(sys.modules, name)
