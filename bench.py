@@ -35,13 +35,26 @@ GLOBAL_BATCH, CHANNELS, FS = 16, 1024, 25
 KERNELS, NC_CHANNELS = [5, 5, 5], [16, 16, 1]
 
 
-def synthetic_features(seed: int = 0):
-    """featureL2Norm(relu(randn)): what the frozen ResNet-101 trunk hands to the head."""
+def synthetic_pairs(batch: int, channels: int, fs: int, seed: int = 0, planted: bool = True):
+    """Synthetic trunk outputs for `batch` image pairs: post-ReLU, L2-normalised over channels, like what the frozen
+    ResNet-101 hands to the head.  planted: the target map of pair b is the source map of pair b moved by a
+    random shift of up to 3 cells plus noise, so positive pairs hold real correspondences and the rolled negatives
+    (target b with source b+1) do not -- the weak loss then has a signal to train on instead of the difference of two
+    statistically identical scores."""
     g = torch.Generator().manual_seed(seed)
-    def one():
-        f = torch.relu(torch.randn(GLOBAL_BATCH, CHANNELS, FS, FS, generator=g))
-        return f / (f.pow(2).sum(1, keepdim=True) + 1e-6).sqrt()
-    return one(), one()
+    a = torch.relu(torch.randn(batch, channels, fs, fs, generator=g))
+    if planted:
+        sh = torch.randint(-3, 4, (batch, 2), generator=g)
+        b = torch.stack([torch.roll(a[i], (int(sh[i, 0]), int(sh[i, 1])), dims=(1, 2)) for i in range(batch)])
+        b = torch.relu(b + 0.5 * torch.randn(batch, channels, fs, fs, generator=g))
+    else:
+        b = torch.relu(torch.randn(batch, channels, fs, fs, generator=g))
+    norm = lambda f: f / (f.pow(2).sum(1, keepdim=True) + 1e-6).sqrt()
+    return norm(a), norm(b)
+
+
+def synthetic_features(seed: int = 0):
+    return synthetic_pairs(GLOBAL_BATCH, CHANNELS, FS, seed)
 
 
 def peaks():

@@ -60,3 +60,19 @@ def make_head(nb, kernel_sizes, channels, state_dict=None, reloc=0, half=False):
     if half:
         net.NeighConsensus.half()
     return net
+
+
+def record(key, values):
+    """When NCNET_PARITY_REPORT names a file, the parity tests also write what they measured into it (JSON, one entry
+    per key) -- that is how profiles/r2_parity_tc16.json is produced on the B200."""
+    path = os.environ.get("NCNET_PARITY_REPORT")
+    if not path:
+        return
+    import json
+    data = {}
+    if os.path.exists(path):
+        with open(path) as fh:
+            data = json.load(fh)
+    data[key] = values
+    with open(path, "w") as fh:
+        json.dump(data, fh, indent=1, sort_keys=True)
