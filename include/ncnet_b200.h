@@ -121,11 +121,14 @@ int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, int nA, int
  * (the reference adds the two score vectors, which needs nA == nB; for nA != nB the two means are taken
  * separately).  corr: [B,nA,nB].  keys: B*(nA+nB) uint64 and sums: ncnet_mutual_matching_sums_bytes(B,nA,nB) bytes
  * (its first B*(nA+nB) floats are the row/column sums of exponentials) are outputs that the backward pass
- * consumes; score: one float on the device.  _bwd: grad_corr = grad_score[0] * d(score)/d(corr). */
-int ncnet_match_score_fwd(const void *corr, uint64_t *keys, float *sums, float *score, int B, int nA, int nB,
-                          int dtype, void *stream);
-int ncnet_match_score_bwd(const void *corr, const uint64_t *keys, const float *sums, const float *grad_score,
-                          void *grad_corr, int B, int nA, int nB, int dtype, void *stream);
+ * consumes; score: one float on the device.  _bwd: grad_corr = grad_score[0] * d(score)/d(corr).
+ * item_weight (device, B floats, may be NULL): the mean over the batch becomes sum_b item_weight[b] * score_b.  With
+ * the positive pairs and the rolled negative pairs of train.py:135-139 stacked into one batch of 2B and weights
+ * (-1/B, ..., +1/B, ...) the result is the weak loss itself (score_neg - score_pos) from ONE pass of the head. */
+int ncnet_match_score_fwd(const void *corr, uint64_t *keys, float *sums, const float *item_weight, float *score, int B,
+                          int nA, int nB, int dtype, void *stream);
+int ncnet_match_score_bwd(const void *corr, const uint64_t *keys, const float *sums, const float *item_weight,
+                          const float *grad_score, void *grad_corr, int B, int nA, int nB, int dtype, void *stream);
 
 /* conv4d / Conv4d.forward -- lib/conv4d.py:11-51,81-82  (+ fused ReLU, lib/model.py:137-138,
  * + the symmetric second branch of NeighConsensus.forward, lib/model.py:147).

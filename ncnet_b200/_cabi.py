@@ -36,8 +36,8 @@ SIGNATURES = {
     "ncnet_mutual_matching_apply": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_fwd_noalloc": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
-    "ncnet_match_score_fwd": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _p]),
-    "ncnet_match_score_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
+    "ncnet_match_score_fwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
+    "ncnet_match_score_bwd": (_i, [_p, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "ncnet_conv4d_scratch_bytes": (_sz, [_i] * 10),
     "ncnet_conv4d_fwd": (_i, [_p, _p, _p, _p, _p] + [_i] * 15 + [_p]),
     "ncnet_conv4d_dgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 15 + [_p]),

@@ -597,14 +597,20 @@ score_sums_reduce_kernel(float *__restrict__ sums, const float *__restrict__ rpa
 
 // score = (sum_rows 1/S / (B*nA) + sum_cols 1/S / (B*nB)) / 2, one block, fixed summation order
 __global__ void __launch_bounds__(1024)
-score_reduce_kernel(const float *__restrict__ sums, float *__restrict__ score, int B, int nA, int nB) {
+score_reduce_kernel(const float *__restrict__ sums, const float *__restrict__ item_weight, float *__restrict__ score,
+                    int B, int nA, int nB) {
     __shared__ double sm[32];
     const int per = nA + nB;
     const double wa = 0.5 / ((double)B * nA), wb = 0.5 / ((double)B * nB);
     double acc = 0.0;
     for (long long i = threadIdx.x; i < (long long)B * per; i += blockDim.x) {
         const int r = (int)(i % per);
-        acc += (r < nA ? wa : wb) / (double)sums[i];
+        if (item_weight) {        // weighted sum over batch items instead of the mean
+            const double w = (double)item_weight[i / per];
+            acc += w * (r < nA ? 0.5 / nA : 0.5 / nB) / (double)sums[i];
+        } else {
+            acc += (r < nA ? wa : wb) / (double)sums[i];
+        }
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
@@ -620,7 +626,8 @@ score_reduce_kernel(const float *__restrict__ sums, float *__restrict__ score, i
 template <typename T>
 __global__ void __launch_bounds__(256)
 score_bwd_kernel(const T *__restrict__ x, const unsigned long long *__restrict__ keys, const float *__restrict__ sums,
-                 const float *__restrict__ gscore, T *__restrict__ gx, int B, int nA, int nB) {
+                 const float *__restrict__ gscore, const float *__restrict__ item_weight, T *__restrict__ gx, int B, int nA,
+                 int nB) {
     const int b = blockIdx.z;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int c = blockIdx.x * 32 + lane;
@@ -628,7 +635,11 @@ score_bwd_kernel(const T *__restrict__ x, const unsigned long long *__restrict__
     const size_t mat = (size_t)nA * nB;
     const size_t kb = (size_t)b * (nA + nB);
     const float g = __ldg(gscore);
-    const float wa = 0.5f * g / ((float)B * nA), wb = 0.5f * g / ((float)B * nB);
+    float wa = 0.5f * g / ((float)B * nA), wb = 0.5f * g / ((float)B * nB);
+    if (item_weight) {
+        const float w = __ldg(item_weight + b);
+        wa = 0.5f * g * w / (float)nA; wb = 0.5f * g * w / (float)nB;
+    }
     float cmax = 0.f, cinv = 0.f;
     int carg = -1;
     if (c < nB) {
@@ -652,7 +663,8 @@ score_bwd_kernel(const T *__restrict__ x, const unsigned long long *__restrict__
 }
 
 template <typename T>
-static int score_fwd(const void *x, uint64_t *keys, float *sums, float *score, int B, int nA, int nB, cudaStream_t st) {
+static int score_fwd(const void *x, uint64_t *keys, float *sums, const float *item_weight, float *score, int B, int nA, int nB,
+                     cudaStream_t st) {
     int rc = mm_fwd_parts<T>(x, nullptr, keys, B, nA, nB, 1, 1, st);      // pass 1: maxima and first arg-maxima
     if (rc) return rc;
     const MMSumLayout L = mm_sum_layout(B, nA, nB);
@@ -665,35 +677,36 @@ static int score_fwd(const void *x, uint64_t *keys, float *sums, float *score, i
     score_sums_reduce_kernel<<<(unsigned)((nsum + 255) / 256), 256, 0, st>>>(sums, sums + L.rpart_off, sums + L.cpart_off, B,
                                                                              nA, nB, L.col_tiles, L.strips);
     NC_LAUNCH_OK("score_sums_reduce_kernel");
-    score_reduce_kernel<<<1, 1024, 0, st>>>(sums, score, B, nA, nB);
+    score_reduce_kernel<<<1, 1024, 0, st>>>(sums, item_weight, score, B, nA, nB);
     NC_LAUNCH_OK("score_reduce_kernel");
     return 0;
 }
 
 }  // namespace ncnet
 
-extern "C" int ncnet_match_score_fwd(const void *corr, uint64_t *keys, float *sums, float *score, int B, int nA, int nB,
-                                     int dtype, void *stream) {
+extern "C" int ncnet_match_score_fwd(const void *corr, uint64_t *keys, float *sums, const float *item_weight, float *score,
+                                     int B, int nA, int nB, int dtype, void *stream) {
     NC_CHECK(corr && keys && sums && score, "match_score_fwd: null pointer");
     NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "match_score_fwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
-    if (dtype == NCNET_F32) return score_fwd<float>(corr, keys, sums, score, B, nA, nB, st);
-    if (dtype == NCNET_F16) return score_fwd<__half>(corr, keys, sums, score, B, nA, nB, st);
+    if (dtype == NCNET_F32) return score_fwd<float>(corr, keys, sums, item_weight, score, B, nA, nB, st);
+    if (dtype == NCNET_F16) return score_fwd<__half>(corr, keys, sums, item_weight, score, B, nA, nB, st);
     return fail("match_score_fwd: unsupported dtype %d", dtype);
 }
 
-extern "C" int ncnet_match_score_bwd(const void *corr, const uint64_t *keys, const float *sums, const float *grad_score,
-                                     void *grad_corr, int B, int nA, int nB, int dtype, void *stream) {
+extern "C" int ncnet_match_score_bwd(const void *corr, const uint64_t *keys, const float *sums, const float *item_weight,
+                                     const float *grad_score, void *grad_corr, int B, int nA, int nB, int dtype,
+                                     void *stream) {
     NC_CHECK(corr && keys && sums && grad_score && grad_corr, "match_score_bwd: null pointer");
     NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "match_score_bwd: bad shape");
     cudaStream_t st = (cudaStream_t)stream;
     dim3 grid((nB + 31) / 32, (nA + 8 * kMMApplyRows - 1) / (8 * kMMApplyRows), B);
     NC_CHECK(grid.y <= 65535, "match_score_bwd: too many rows");
     if (dtype == NCNET_F32)
-        score_bwd_kernel<float><<<grid, 256, 0, st>>>((const float *)corr, (const unsigned long long *)keys, sums, grad_score,
+        score_bwd_kernel<float><<<grid, 256, 0, st>>>((const float *)corr, (const unsigned long long *)keys, sums, grad_score, item_weight,
                                                       (float *)grad_corr, B, nA, nB);
     else if (dtype == NCNET_F16)
-        score_bwd_kernel<__half><<<grid, 256, 0, st>>>((const __half *)corr, (const unsigned long long *)keys, sums, grad_score,
+        score_bwd_kernel<__half><<<grid, 256, 0, st>>>((const __half *)corr, (const unsigned long long *)keys, sums, grad_score, item_weight,
                                                        (__half *)grad_corr, B, nA, nB);
     else
         return fail("match_score_bwd: unsupported dtype %d", dtype);

@@ -189,39 +189,45 @@ class _MatchScoreFn(torch.autograd.Function):
     one reduction; the backward pass is one elementwise kernel."""
 
     @staticmethod
-    def forward(ctx, corr4d):
+    def forward(ctx, corr4d, item_weight=None):
         b, _, f1, f2, f3, f4 = corr4d.shape
         x = corr4d.contiguous()
+        wt = None if item_weight is None else item_weight.detach().to(device=x.device, dtype=torch.float32).contiguous()
+        if wt is not None and wt.numel() != b:
+            raise RuntimeError(f"match_score: {wt.numel()} item weights for a batch of {b}")
         na, nb = f1 * f2, f3 * f4
         keys = torch.empty(b * (na + nb), device=x.device, dtype=torch.int64)
         sums = torch.empty(_cabi.lib().ncnet_mutual_matching_sums_bytes(b, na, nb) // 4, device=x.device, dtype=torch.float32)
         score = torch.empty((), device=x.device, dtype=torch.float32)
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().ncnet_match_score_fwd(_ptr(x), _ptr(keys), _ptr(sums), _ptr(score), b, na, nb, _dt(x),
-                                                          _stream()), "match_score_fwd")
-        _count(3)
-        ctx.save_for_backward(x, keys, sums)
+            _cabi.check(_cabi.lib().ncnet_match_score_fwd(_ptr(x), _ptr(keys), _ptr(sums), _ptr(wt), _ptr(score), b, na, nb,
+                                                          _dt(x), _stream()), "match_score_fwd")
+        _count(4)
+        ctx.has_weight = wt is not None
+        ctx.save_for_backward(x, keys, sums, *([wt] if wt is not None else []))
         return score.to(x.dtype)
 
     @staticmethod
     def backward(ctx, g):
-        x, keys, sums = ctx.saved_tensors
+        x, keys, sums = ctx.saved_tensors[:3]
+        wt = ctx.saved_tensors[3] if ctx.has_weight else None
         b, _, f1, f2, f3, f4 = x.shape
         gs = g.detach().reshape(1).float().contiguous()
         gx = torch.empty_like(x)
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().ncnet_match_score_bwd(_ptr(x), _ptr(keys), _ptr(sums), _ptr(gs), _ptr(gx), b, f1 * f2,
-                                                          f3 * f4, _dt(x), _stream()), "match_score_bwd")
+            _cabi.check(_cabi.lib().ncnet_match_score_bwd(_ptr(x), _ptr(keys), _ptr(sums), _ptr(wt), _ptr(gs), _ptr(gx), b,
+                                                          f1 * f2, f3 * f4, _dt(x), _stream()), "match_score_bwd")
         _count(1)
-        return gx
+        return gx, None
 
 
-def match_score_softmax(corr4d: torch.Tensor) -> torch.Tensor:
-    """mean(max softmax over A + max softmax over B) / 2 of a [B,1,fs1,fs2,fs3,fs4] volume (train.py:123-134)."""
+def match_score_softmax(corr4d: torch.Tensor, item_weight: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """mean(max softmax over A + max softmax over B) / 2 of a [B,1,fs1,fs2,fs3,fs4] volume (train.py:123-134).
+    ``item_weight`` [B]: weighted sum over the batch items instead of their mean (see include/ncnet_b200.h)."""
     _need_cuda(corr4d)
     if corr4d.dim() != 6 or corr4d.shape[1] != 1:
         raise RuntimeError(f"match_score: expected [B,1,fs1,fs2,fs3,fs4], got {tuple(corr4d.shape)}")
-    return _MatchScoreFn.apply(corr4d)
+    return _MatchScoreFn.apply(corr4d, item_weight)
 
 
 # ------------------------------------------------------------------------------------------- #

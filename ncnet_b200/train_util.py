@@ -40,7 +40,26 @@ def weak_loss(model, batch, normalization="softmax", alpha=30):
 
 def weak_loss_from_features(model, feature_A, feature_B, normalization="softmax"):
     """weak_loss with the trunk factored out: the negative pass pairs target b with source b+1
-    (rolling the images rolls their features).  Used by the head-only bench and tests."""
+    (rolling the images rolls their features).  Used by the tests."""
     score_pos = match_score(model.match_features(feature_A, feature_B), normalization)
     score_neg = match_score(model.match_features(torch.roll(feature_A, shifts=-1, dims=0), feature_B), normalization)
     return score_neg - score_pos
+
+
+_WEIGHT_CACHE = {}
+
+
+def weak_loss_stacked(model, source_pos, source_neg, target, world_batch=None):
+    """The same weak loss (train.py:135-139, soft-max normalisation) from ONE pass of the head: the B positive pairs
+    (source_pos[b], target[b]) and the B negative pairs (source_neg[b], target[b]) are stacked into a batch of 2B and the
+    fused score kernel sums them with weights -1/B and +1/B.  Same 2B pair evaluations as two calls of the model, half
+    the kernel launches, twice the work per launch.  ``source_neg`` is the globally rolled source batch sliced like
+    ``source_pos`` (ncnet_b200.dist.shard_pairs)."""
+    from .functional import match_score_softmax
+    b = source_pos.shape[0]
+    key = (b, str(source_pos.device))
+    w = _WEIGHT_CACHE.get(key)
+    if w is None:
+        w = _WEIGHT_CACHE[key] = torch.cat([torch.full((b,), -1.0 / b), torch.full((b,), 1.0 / b)]).to(source_pos.device)
+    corr = model.match_features(torch.cat([source_pos, source_neg], 0), torch.cat([target, target], 0))
+    return match_score_softmax(corr, w)
