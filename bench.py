@@ -180,12 +180,33 @@ def workload_config(world: int, note: str = ""):
 # --------------------------------------------------------------------------------------------- #
 # our arm
 # --------------------------------------------------------------------------------------------- #
+def valid_tap_fraction(n: int, k: int) -> float:
+    """Share of the k^4 taps that fall inside an n^4 volume, averaged over the output cells (the rest multiply the
+    zero padding; the kernels skip whole out-of-range (d1,d2) planes, the dense FLOP convention counts them)."""
+    p = k // 2
+    per_dim = (n * k - 2 * sum(range(1, p + 1))) / (n * k)
+    return per_dim ** 4
+
+
+def ncu_traffic(label: str, batch: int):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the tracked `ncu --set full` summary of this build
+    (profiles/r2_ncu_traffic.json, written by scripts/ncu_summarise.py); None when no capture matches the batch."""
+    p = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
+    if not os.path.exists(p):
+        return None
+    with open(p) as fh:
+        d = json.load(fh).get(label)
+    if not d or d.get("batch") != batch:
+        return None
+    return d["dram_read_bytes"] + d["dram_write_bytes"]
+
+
 def run_ours(args):
     import torch.distributed as dist
     import ncnet_b200 as nb
     from ncnet_b200 import functional as F_
     from ncnet_b200.dist import GradBucket, shard_range
-    from ncnet_b200.train_util import match_score
+    from ncnet_b200.train_util import weak_loss_of_stacked
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -201,95 +222,122 @@ def run_ours(args):
     mode = F_.default_conv_mode()
     fa_h, fb_h = synthetic_features()
     lo, hi = shard_range(GLOBAL_BATCH, rank, world)
+    b = hi - lo
     # this rank's positives and negatives (negative source = source (b+1) mod 16 of the GLOBAL batch)
     src_h = fa_h[lo:hi].contiguous().pin_memory()
     neg_h = torch.roll(fa_h, -1, 0)[lo:hi].contiguous().pin_memory()
     tgt_h = fb_h[lo:hi].contiguous().pin_memory()
-    src, neg, tgt = src_h.to(dev), neg_h.to(dev), tgt_h.to(dev)
+    # static device inputs of the step: positives and negatives stacked (2b pairs per pass of the head)
+    src2 = torch.empty(2 * b, CHANNELS, FS, FS, device=dev)
+    tgt2 = torch.empty(2 * b, CHANNELS, FS, FS, device=dev)
 
-    torch.manual_seed(0)
-    net = nb.ImMatchNet.__new__(nb.ImMatchNet)          # head only: no trunk download/instantiation
-    torch.nn.Module.__init__(net)
-    net.relocalization_k_size, net.half_precision = 0, False
-    net.FeatureCorrelation = nb.FeatureCorrelation("4D", False)
-    net.NeighConsensus = nb.NeighConsensus(True, KERNELS, NC_CHANNELS)
+    def load_inputs(a, n, t):
+        src2[:b].copy_(a, non_blocking=True), src2[b:].copy_(n, non_blocking=True)
+        tgt2[:b].copy_(t, non_blocking=True), tgt2[b:].copy_(t, non_blocking=True)
+
+    load_inputs(src_h, neg_h, tgt_h)
+
+    def make_net():
+        torch.manual_seed(0)
+        net = nb.ImMatchNet.__new__(nb.ImMatchNet)          # head only: no trunk download/instantiation
+        torch.nn.Module.__init__(net)
+        net.relocalization_k_size, net.half_precision = 0, False
+        net.FeatureCorrelation = nb.FeatureCorrelation("4D", False)
+        net.NeighConsensus = nb.NeighConsensus(True, KERNELS, NC_CHANNELS)
+        return net
+
+    net = make_net()
     params = list(net.NeighConsensus.parameters())
-    opt = torch.optim.Adam(params, lr=5e-4)
+    use_graph = os.environ.get("NCNET_BENCH_GRAPH", "1") != "0"
+    opt = torch.optim.Adam(params, lr=5e-4, capturable=use_graph)
     bucket = GradBucket(params)
-
-    def step(a, n, t):
-        opt.zero_grad(set_to_none=True)
-        loss = match_score(net.match_features(n, t)) - match_score(net.match_features(a, t))
-        loss.backward()
-        bucket.all_reduce_mean()
-        opt.step()
-        return loss
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
-        step(src, neg, tgt)
+    # ---- before anything is timed: the sharded gradient must equal the single-GPU gradient ------------------
+    shard_check = None
+    if world > 1:
+        loss = weak_loss_of_stacked(net, src2, tgt2)
+        loss.backward()
+        bucket.all_reduce_mean()
+        g_sharded = torch.cat([p.grad.reshape(-1) for p in params]).clone()
+        net.zero_grad(set_to_none=True)
+        if rank == 0:
+            fa_d, fb_d = fa_h.to(dev), fb_h.to(dev)
+            full_loss = weak_loss_of_stacked(net, torch.cat([fa_d, torch.roll(fa_d, -1, 0)]), torch.cat([fb_d, fb_d]))
+            full_loss.backward()
+            g_full = torch.cat([p.grad.reshape(-1) for p in params])
+            shard_check = ((g_sharded - g_full).abs().max() / g_full.abs().max()).item()
+            net.zero_grad(set_to_none=True)
+            del fa_d, fb_d, g_full
+            assert shard_check < 1e-3, f"sharded gradient differs from the unsharded one: nerr {shard_check:.3e}"
+        barrier()
+
+    def step_body():
+        opt.zero_grad(set_to_none=True)
+        loss = weak_loss_of_stacked(net, src2, tgt2)
+        loss.backward()
+        bucket.all_reduce_mean()
+        opt.step()
+        return loss
+
+    # ---- warm-up (eager): also measures the launches per step ------------------------------------------------
+    l0 = F_.LAUNCHES["n"]
+    first_loss = None
+    for w in range(args.warmup):
+        loss = step_body()
+        if w == 0:
+            first_loss = loss.detach().clone()
+    launches_per_step = (F_.LAUNCHES["n"] - l0) // max(args.warmup, 1)
+    barrier()
+
+    graph, static_loss, graph_note = None, None, "off (NCNET_BENCH_GRAPH=0)"
+    if use_graph:
+        try:
+            graph = torch.cuda.CUDAGraph()
+            opt.zero_grad(set_to_none=True)
+            with torch.cuda.graph(graph):
+                static_loss = step_body()
+            graph_note = "whole step (forward, backward, gradient all-reduce, Adam) replayed as one CUDA graph"
+        except Exception as exc:                     # capture unsupported on this stack: time the eager step instead
+            graph, graph_note = None, f"capture failed ({type(exc).__name__}: {exc}); eager"
+            torch.cuda.synchronize()
+    barrier()
+
+    def step():
+        if graph is not None:
+            graph.replay()
+            return static_loss
+        return step_body()
+
+    step()                                           # first replay outside the timed region
     barrier()
 
     # ---- timed region: device-resident inputs -------------------------------------------------
-    F_.EVENT_LOG = []
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    launches0 = F_.LAUNCHES["n"]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record()
     for _ in range(args.steps):
-        step(src, neg, tgt)
+        step()
     e1.record()
     barrier()
     ms = e0.elapsed_time(e1)
     clocks = sampler.stop() if rank == 0 else None
-    launches = F_.LAUNCHES["n"] - launches0
-    ev = F_.EVENT_LOG
-    F_.EVENT_LOG = None
     t = torch.tensor([ms], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms = t.item()
 
-    # the two heaviest kernels: 16->16 Conv4d forward (+ identical dgrad) and 16->16 weight gradient,
-    # both symmetric branches per launch.  `roofline` is the one with the larger share of the step.
-    per_rank_b = hi - lo
-    flop_fat = 2.0 * per_rank_b * FS ** 4 * 16 * 16 * 5 ** 4 * 2          # dense convention, 2 branches
-    pk, pk_kind = peaks()
-    peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
-    mode_name = "fp32 CUDA-core" if mode == 0 else "fp16 operands / fp32 accumulate, tcgen05"
-
-    # dram__bytes_read.sum + dram__bytes_write.sum per launch of the two kernels at the 1-GPU batch, from the
-    # `ncu --set full` capture summarised in profiles/r1_tc16_conv_kernels_ncu_full_summary.csv (TC16 mode only)
-    ncu_traffic = {"conv4d_fwd": 0.539e9 + 1.022e9, "conv4d_wgrad": 2.621e9 + 0.041e9} if (mode != 0 and per_rank_b == 16) else {}
-
-    def roof_for(tag, label):
-        ts = [a.elapsed_time(b) for t, a, b in ev if t == tag]
-        if not ts:
-            return None
-        avg_ms = sum(ts) / len(ts)
-        ach = flop_fat / (avg_ms * 1e-3) / 1e12
-        return {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
-                "traffic": ncu_traffic.get(label), "kernel": label + " 16->16 k=5 (layer 2, both branches, B=%d)" % per_rank_b,
-                "avg_launch_ms": avg_ms, "launches_timed": len(ts), "total_ms_in_region": sum(ts),
-                "peak_source": pk_kind + " bf16 sustained",
-                "flop_convention": "2*B*N^4*Cin*Cout*k^4 dense (zero-padding taps counted)", "mode": mode_name}
-
-    r_fwd = roof_for("conv4d_fwd_16_16", "conv4d_fwd")
-    r_wg = roof_for("conv4d_wgrad_16_16", "conv4d_wgrad")
-    cands = [r for r in (r_fwd, r_wg) if r]
-    roof = max(cands, key=lambda r: r["total_ms_in_region"]) if cands else None
-    roof_other = [r for r in cands if r is not roof]
-
     # ---- end to end: pinned host features in, loss out, every step ----------------------------
     # The uploads run on a copy stream, one step ahead (what a pinned-memory loader does), so the PCIe transfer of
-    # step s+1 overlaps the kernels of step s; every step still takes its inputs from host memory inside the region.
+    # step s+1 overlaps the kernels of step s; every step still takes its inputs from host memory inside the region
+    # and copies them into the step's static input buffers on the compute stream.
     copy_stream = torch.cuda.Stream(device=dev)
 
     def upload():
@@ -302,16 +350,18 @@ def run_ours(args):
     barrier()
     t0 = time.perf_counter()
     nxt = upload()
+    loss_host = float("nan")
     for s in range(args.steps):
         (a, n, tt), done = nxt
         cur = torch.cuda.current_stream()
         cur.wait_event(done)
         for x in (a, n, tt):
             x.record_stream(cur)
+        load_inputs(a, n, tt)
         if s + 1 < args.steps:
             nxt = upload()
-        loss = step(a, n, tt)
-        loss_host = loss.item()
+        loss_host = step().item()
+        assert loss_host == loss_host and abs(loss_host) < 10.0, f"training diverged: loss {loss_host} at e2e step {s}"
     barrier()
     e2e_s = time.perf_counter() - t0
     t = torch.tensor([e2e_s], device=dev, dtype=torch.float64)
@@ -320,18 +370,72 @@ def run_ours(args):
     e2e_s = t.item()
     h2d = (src_h.numel() + neg_h.numel() + tgt_h.numel()) * 4
 
+    # ---- the two heaviest kernels, timed with CUDA events around their launches --------------------------------
+    # 16->16 Conv4d forward (+ the identical dgrad) and 16->16 weight gradient, both symmetric branches per launch.
+    # Events cannot bracket a kernel inside a graph replay, so the same step runs eagerly `steps` more times right here.
+    F_.EVENT_LOG = []
+    for _ in range(args.steps):
+        step_body()
+    torch.cuda.synchronize()
+    ev = F_.EVENT_LOG
+    F_.EVENT_LOG = None
+    last_loss_t = step().detach().float()
+    last = torch.stack([last_loss_t.reshape(()), first_loss.float().reshape(())])
+    if world > 1:
+        dist.all_reduce(last, op=dist.ReduceOp.AVG)
+    global_last_loss, global_first_loss = last[0].item(), last[1].item()
+
+    pairs_per_launch = 2 * b
+    flop_fat = 2.0 * pairs_per_launch * FS ** 4 * 16 * 16 * 5 ** 4 * 2          # dense convention, 2 branches
+    pk, pk_kind = peaks()
+    peak_tf = pk.get("bf16_tflops_sustained", pk["bf16_tflops"])
+    peak_burst = pk.get("bf16_tflops", peak_tf)
+    mode_name = "fp32 CUDA-core" if mode == 0 else "fp16 operands / fp32 accumulate, tcgen05"
+    vfrac = valid_tap_fraction(FS, 5)
+
+    def roof_for(tag, label):
+        ts = [a.elapsed_time(b_) for t_, a, b_ in ev if t_ == tag]
+        if not ts:
+            return None
+        avg_ms = sum(ts) / len(ts)
+        ach = flop_fat / (avg_ms * 1e-3) / 1e12
+        return {"bound": "tensor", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s", "frac": ach / peak_tf,
+                "traffic": ncu_traffic(label, pairs_per_launch) if mode != 0 else None,
+                "kernel": label + " 16->16 k=5 (layer 2, both branches, %d pairs per launch)" % pairs_per_launch,
+                "avg_launch_ms": avg_ms, "launches_timed": len(ts), "total_ms_in_region": sum(ts),
+                "peak_source": pk_kind + " bf16 sustained (cuBLAS back to back, 1237 MHz median under its power cap)",
+                "frac_of_burst_peak": ach / peak_burst, "burst_peak": peak_burst,
+                "achieved_executed_taps": ach * vfrac, "valid_tap_fraction": vfrac,
+                "flop_convention": "2*B*N^4*Cin*Cout*k^4 dense (zero-padding taps counted); achieved_executed_taps "
+                                   "counts only taps inside the volume",
+                "timing": "CUDA events around each launch in %d eager steps run right after the timed graph replays" % args.steps,
+                "mode": mode_name}
+
+    r_fwd = roof_for("conv4d_fwd_16_16", "conv4d_fwd")
+    r_wg = roof_for("conv4d_wgrad_16_16", "conv4d_wgrad")
+    cands = [r for r in (r_fwd, r_wg) if r]
+    roof = max(cands, key=lambda r: r["total_ms_in_region"]) if cands else None
+    roof_other = [r for r in cands if r is not roof]
+
     if rank == 0:
         evals = 2 * GLOBAL_BATCH
+        cfg = workload_config(world)
+        cfg["launch"] = graph_note
+        cfg["pairs_per_head_pass"] = "%d (positives and rolled negatives stacked)" % pairs_per_launch
         line = {
             "metric": METRIC, "value": evals * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32" if mode == 0 else "f16 (tensor-core operands; f32 accumulate, f32 weights/loss/optimizer)",
-            "data": "synthetic", "config": workload_config(world),
+            "data": "synthetic (planted correspondences)", "config": cfg,
             "e2e": {"value": evals * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "last_loss": loss_host},
-            "gpu_launches": launches, "clocks": clocks, "roofline": roof,
+            "gpu_launches": launches_per_step * args.steps, "launches_per_step": launches_per_step,
+            "loss": {"first_step_global": global_first_loss, "last_step_global": global_last_loss,
+                     "sharded_vs_unsharded_grad_nerr": shard_check},
+            "clocks": clocks, "roofline": roof,
             "roofline_other": roof_other[0] if roof_other else None,
         }
+        assert all(v == v and abs(v) < 10.0 for v in (global_first_loss, global_last_loss)), "non-finite loss"
         if world == 1 and not args.no_cpu_baseline:
             base = cpu_training_step_rate(pairs=2, steps=1, warmup=0, budget_s=60.0)
             line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -49,17 +49,22 @@ def weak_loss_from_features(model, feature_A, feature_B, normalization="softmax"
 _WEIGHT_CACHE = {}
 
 
-def weak_loss_stacked(model, source_pos, source_neg, target, world_batch=None):
+def weak_loss_stacked(model, source_pos, source_neg, target):
     """The same weak loss (train.py:135-139, soft-max normalisation) from ONE pass of the head: the B positive pairs
     (source_pos[b], target[b]) and the B negative pairs (source_neg[b], target[b]) are stacked into a batch of 2B and the
     fused score kernel sums them with weights -1/B and +1/B.  Same 2B pair evaluations as two calls of the model, half
     the kernel launches, twice the work per launch.  ``source_neg`` is the globally rolled source batch sliced like
     ``source_pos`` (ncnet_b200.dist.shard_pairs)."""
+    return weak_loss_of_stacked(model, torch.cat([source_pos, source_neg], 0), torch.cat([target, target], 0))
+
+
+def weak_loss_of_stacked(model, source2, target2):
+    """``weak_loss_stacked`` for inputs that are already stacked: the first half of the batch holds the positive
+    pairs, the second half the negative ones."""
     from .functional import match_score_softmax
-    b = source_pos.shape[0]
-    key = (b, str(source_pos.device))
+    b = source2.shape[0] // 2
+    key = (b, str(source2.device))
     w = _WEIGHT_CACHE.get(key)
     if w is None:
-        w = _WEIGHT_CACHE[key] = torch.cat([torch.full((b,), -1.0 / b), torch.full((b,), 1.0 / b)]).to(source_pos.device)
-    corr = model.match_features(torch.cat([source_pos, source_neg], 0), torch.cat([target, target], 0))
-    return match_score_softmax(corr, w)
+        w = _WEIGHT_CACHE[key] = torch.cat([torch.full((b,), -1.0 / b), torch.full((b,), 1.0 / b)]).to(source2.device)
+    return match_score_softmax(model.match_features(source2, target2), w)

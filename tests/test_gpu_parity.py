@@ -346,3 +346,21 @@ def test_fused_match_score_vs_oracle(nb, cuda, shape):
     (gg,) = torch.autograd.grad(sg * 2.5, xg)
     assert abs(float(sg) - float(so)) < 1e-6 * max(1.0, abs(float(so)))
     assert nerr(gg, go * 2.5) < 1e-4
+
+
+def test_stacked_weak_loss_equals_two_pass_loss(nb, cuda):
+    """One pass of the head over [positives; rolled negatives] with per-item score weights (what bench.py times) gives
+    the loss and the gradients of the reference's two passes (train.py:135-139)."""
+    from ncnet_b200.train_util import weak_loss_from_features, weak_loss_stacked
+    from conftest import make_head
+    torch.manual_seed(61)
+    fa = O.feature_l2norm(torch.relu(torch.randn(3, 32, 7, 6))).to(cuda)
+    fb = O.feature_l2norm(torch.relu(torch.randn(3, 32, 6, 7))).to(cuda)
+    net = make_head(nb, [3, 3], [16, 1])
+    l2 = weak_loss_from_features(net, fa, fb)
+    g2 = torch.autograd.grad(l2, list(net.NeighConsensus.parameters()))
+    l1 = weak_loss_stacked(net, fa, torch.roll(fa, -1, 0), fb)
+    g1 = torch.autograd.grad(l1, list(net.NeighConsensus.parameters()))
+    assert abs(float(l1) - float(l2)) < 1e-7 + 1e-5 * abs(float(l2))
+    for a, b in zip(g1, g2):
+        assert nerr(a, b) < 1e-4
