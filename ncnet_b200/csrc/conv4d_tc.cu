@@ -19,8 +19,6 @@
 // 128 B/clk shared-memory read rate at 22 % of the tensor peak.
 //   mode M1 (Cin<=16, Cout>1): channels = input channels, N = (d4, o), K-steps per plane = d3 taps
 //   mode M2 (Cout == 1)      : channels = input channels, N = (d3, d4), one K-step per plane
-//   mode M3 (Cin == 1)       : channels = two consecutive d3 taps x the k d4 taps (im2col in the pack
-//                              kernel), N = (d3 pair, o), one K-step per plane   (kept for comparison: NCNET_TC_M3=1)
 //   mode M4 (Cin == 1)       : channels = the (d2,d4) taps, 16 per channel block (k=5: 25 taps in 2 blocks; k=3: 9 in 1),
 //                              so a staged plane carries every d2 tap: 5x2 stages per output plane instead of 25;
 //                              K-steps = d3 taps (row-shifted views), N = 16 out-channels, no shifted-sum epilogue
@@ -51,8 +49,6 @@ struct TcArgs {
     int d1, d2, d3, d4, KS, P;
     int R, nchunks;         // output k-rows per CTA, chunks per plane
     int NT, N, NG, KSTEPS;
-    int ntiles;             // persistent kernel: number of (b, group, iA, jA) planes
-    uint32_t out_off, mask_stride;   // persistent kernel: smem offset of the output plane; bytes between its two mask buffers
     int pair;               // 1: CTA pairs (cluster of 2, tcgen05 cta_group::2): the two plane chunks share one M256 MMA stream
     int OG;                 // branch groups side by side in N (1, or 2 for mode M4 on a shared input)
     int inner, m4;          // inner stage loop: the k d2 taps, or (mode M4) the channel blocks of the (d2,d4) taps
@@ -68,8 +64,6 @@ struct TcArgs {
     uint32_t stage_bytes, data_bytes, w_bytes;
     __half *out_pm;         // optional position-major twin of a CB16 output (NCNET_CB16PM) or null
     uint32_t mask_off;      // CB16 mask: byte offset of its staging area in dynamic smem (0 = read it from global)
-    long long *dbg;         // development only: per-CTA phase timestamps (8 per CTA) or null
-    int dbg_mode;           // development only: 1 = no weight copies, 2 = no MMAs, 3 = no activation copies (results wrong)
 };
 
 using namespace tc;
@@ -97,7 +91,7 @@ __device__ __forceinline__ void umma_commit_to(uint32_t bar) {
 
 template <int NT_C, int KS_C, bool PAIR = false>
 __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t *stage0, uint64_t *full_bar, uint64_t *empty_bar,
-                                         uint64_t *peer_full, uint32_t tmem_base, long long t_start, int &stage, uint32_t &phase) {
+                                         uint64_t *peer_full, uint32_t tmem_base, int &stage, uint32_t &phase) {
     constexpr int NTM = NT_C > 0 ? NT_C : 1, KSM = KS_C > 0 ? KS_C : 1;
     const int NT = NT_C > 0 ? NT_C : p.NT, KSTEPS = KS_C > 0 ? KS_C : p.KSTEPS;
     const int PAD = p.KS / 2;
@@ -128,7 +122,6 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
                 mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
                 if (PAIR) mbar_wait_u32(peer0 + (uint32_t)stage * 8u, phase);       // the peer CTA's stage has landed too
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                if (first && p.dbg && blockIdx.x < 3990) p.dbg[blockIdx.x * 8 + 0] = clock64() - t_start;
                 const uint32_t s4 = sm4 + (uint32_t)stage * stage4;      // the address field never carries into LBO (smem < 256 KB)
                 if (NT_C == 0) {
                     // run-time counts (any NT): descriptor words computed on the fly
@@ -137,7 +130,6 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
                         const uint32_t a0 = (lbo_a_field | (uint32_t)p.aoff[ks]) + s4;
                         const uint32_t acc = (first && ks == 0) ? 0u : 1u;
                         for (int t = 0; t < NT; ++t)
-                            if (p.dbg_mode != 2)
                                 umma_issue<PAIR>(tmem_base + (uint32_t)(t * p.N), ((uint64_t)hi << 32) | (uint64_t)(a0 + (uint32_t)t * 128u), bdesc, p.idesc, acc);
                     }
                 } else if (first) {
@@ -146,7 +138,6 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
                         const uint64_t bdesc = ((uint64_t)hi << 32) | (uint64_t)(b_rel[ks] + s4);
 #pragma unroll
                         for (int t = 0; t < NTM; ++t)
-                            if (p.dbg_mode != 2)
                                 umma_issue<PAIR>(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, ks == 0 ? 0u : 1u);
                     }
                 } else {
@@ -155,7 +146,6 @@ __device__ __forceinline__ void mma_main(const TcArgs &p, int i, int j, uint8_t 
                         const uint64_t bdesc = ((uint64_t)hi << 32) | (uint64_t)(b_rel[ks] + s4);
 #pragma unroll
                         for (int t = 0; t < NTM; ++t)
-                            if (p.dbg_mode != 2)
                                 umma_issue<PAIR>(d_col[t], ((uint64_t)hi << 32) | (uint64_t)(a_rel[ks][t] + s4), bdesc, p.idesc, 1u);
                     }
                 }
@@ -240,14 +230,6 @@ conv4d_tc_kernel(const TcArgs p) {
     }
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
-    const long long t_start = clock64();
-#define TC_STAMP(slot) do { if (p.dbg && blockIdx.x < 3990) p.dbg[blockIdx.x * 8 + (slot)] = clock64() - t_start; } while (0)
-    if (p.dbg && blockIdx.x < 3990 && threadIdx.x == 0) {
-        uint32_t smid;
-        asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
-        p.dbg[blockIdx.x * 8 + 5] = t_start;
-        p.dbg[blockIdx.x * 8 + 6] = smid;
-    }
 
     if (warp == 0) {
         // ===== producer =====  (a lone lane runs ~10 cycles per instruction: everything loop-invariant is hoisted)
@@ -257,7 +239,7 @@ conv4d_tc_kernel(const TcArgs p) {
         const int rows_in = min(p.R + p.KS - 1, rows_pad - k0);
         const uint32_t half_bytes = (uint32_t)rows_in * p.P * 16u;
         const uint32_t wb = PAIR ? p.w_bytes / 2u : p.w_bytes;       // a pair's CTAs each hold half of the weight columns
-        const uint32_t tx_bytes = (p.dbg_mode == 3 ? 0u : 2u * half_bytes) + (p.dbg_mode == 1 ? 0u : wb);
+        const uint32_t tx_bytes = 2u * half_bytes + wb;
         const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
         const size_t plane_halves = plane_cb * 8;
         // mode M4: the inner index selects the channel block (tensor block bg*inner + t2) of the SAME plane column j
@@ -290,11 +272,9 @@ conv4d_tc_kernel(const TcArgs p) {
                     const uint32_t sb = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
                     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(tx_bytes) : "memory");
                     const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves + (p.m4 ? (size_t)t2 * blk_halves : 0);
-                    if (p.dbg_mode != 3) {
-                        bulk_g2s_u32(sb, src0, half_bytes, fb);
-                        bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
-                    }
-                    if (p.dbg_mode != 1) bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.inner + t2) * w_halves + (size_t)cta_rank * (wb / 2u), wb, fb);
+                    bulk_g2s_u32(sb, src0, half_bytes, fb);
+                    bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
+                    bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.inner + t2) * w_halves + (size_t)cta_rank * (wb / 2u), wb, fb);
                 }
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
@@ -312,9 +292,9 @@ conv4d_tc_kernel(const TcArgs p) {
         if (PAIR) {
             done = true;
             if (cta_rank == 0) {
-                if (p.NT == 3 && p.KSTEPS == 5) mma_main<3, 5, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase);
-                else mma_main<0, 0, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase);
-                if (elect_one()) { TC_STAMP(1); umma_commit_to<true>(smem_u32(&accum_bar)); }
+                if (p.NT == 3 && p.KSTEPS == 5) mma_main<3, 5, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, mstage, mphase);
+                else mma_main<0, 0, true>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, mstage, mphase);
+                if (elect_one()) umma_commit_to<true>(smem_u32(&accum_bar));
             } else if (elect_one()) {
                 // peer CTA: no MMAs of its own; tell the leader when each of this CTA's stages has landed
                 const int PADp = p.KS / 2;
@@ -333,14 +313,14 @@ conv4d_tc_kernel(const TcArgs p) {
             __syncwarp();
         }
 #define NC_TC_CASE(NT_, KS_) \
-        if (!done && p.NT == NT_ && p.KSTEPS == KS_) { mma_main<NT_, KS_>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase); done = true; }
+        if (!done && p.NT == NT_ && p.KSTEPS == KS_) { mma_main<NT_, KS_>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, mstage, mphase); done = true; }
         NC_TC_CASE(3, 5) NC_TC_CASE(6, 5) NC_TC_CASE(2, 5) NC_TC_CASE(4, 5)
         NC_TC_CASE(1, 1) NC_TC_CASE(2, 1) NC_TC_CASE(3, 1) NC_TC_CASE(4, 1) NC_TC_CASE(5, 1) NC_TC_CASE(6, 1) NC_TC_CASE(7, 1) NC_TC_CASE(8, 1)
         NC_TC_CASE(3, 3) NC_TC_CASE(4, 3) NC_TC_CASE(2, 3)
 #undef NC_TC_CASE
         if (!PAIR) {
-        if (!done) mma_main<0, 0>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, t_start, mstage, mphase);
-        if (elect_one()) { TC_STAMP(1); umma_commit(&accum_bar); }
+        if (!done) mma_main<0, 0>(p, i, j, stage0, full_bar, empty_bar, peer_full, tmem_base, mstage, mphase);
+        if (elect_one()) umma_commit(&accum_bar);
         }
         __syncwarp();
     } else {
@@ -348,7 +328,6 @@ conv4d_tc_kernel(const TcArgs p) {
         const int q = warp & 3;
         const int et = threadIdx.x - 64;                 // 0..127
         mbar_wait_sleep(&accum_bar, 0, 400);
-        if (et == 0) TC_STAMP(2);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         // OG > 1 (mode M4 on a shared input): the N columns hold OG branch groups of 16 out-channels side by side;
         // each is drained and stored as its own output group
@@ -430,10 +409,8 @@ conv4d_tc_kernel(const TcArgs p) {
             if (wide) tmem_ld16_issue(lane_base + 16u, rb);
             for (int t = 0; t < p.NT; ++t) {
                 const int row = t * 128 + q * 32 + lane;
-                if (p.dbg && blockIdx.x == 2000 && et == 0) p.dbg[32000 + 3 * t] = clock64() - t_start;
                 tmem_ld16_wait(ra);
                 if (wide) tmem_ld16_wait(rb);
-                if (p.dbg && blockIdx.x == 2000 && et == 0) p.dbg[32001 + 3 * t] = clock64() - t_start;
                 if (t + 1 < p.NT) {
                     tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N), na);
                     if (wide) tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N + 16), nb);
@@ -446,7 +423,6 @@ conv4d_tc_kernel(const TcArgs p) {
                     for (int u = 0; u < 16; ++u)
                         if (16 + u < p.NG) sts_f32(osm + (uint32_t)((16 + u) * out_rows + row) * 4u, __uint_as_float(rb[u]));
                 }
-                if (p.dbg && blockIdx.x == 2000 && et == 0) p.dbg[32002 + 3 * t] = clock64() - t_start;
                 if (t + 1 < p.NT) {
                     tmem_ld16_wait(na);
                     if (wide) tmem_ld16_wait(nb);
@@ -456,7 +432,6 @@ conv4d_tc_kernel(const TcArgs p) {
             }
         }
         asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (et == 0) TC_STAMP(3);
 
         if (p.out_mode == 2) {
             // ---- CB16 store: this chunk's rows of the haloed plane (halo columns/rows written as zeros), 16 B per
@@ -548,7 +523,6 @@ conv4d_tc_kernel(const TcArgs p) {
         }   // og
     }
 
-    if (threadIdx.x == 64) TC_STAMP(4);
     // ---- teardown ------------------------------------------------------------------------------
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
@@ -564,315 +538,12 @@ conv4d_tc_kernel(const TcArgs p) {
 
 
 // ---------------------------------------------------------------------------------------------
-// Persistent, TMEM-double-buffered variant for the many-channel layers (mode M1, CB16 output, CTA pairs).
-//
-// One CTA pair per SM pair walks the plane list.  The 512 TMEM columns hold TWO accumulator sets, so the leader's MMA
-// stream runs on while the epilogue warps drain, shift-sum and store the previous plane: the tensor pipe no longer
-// idles during prologue/epilogue (which was ~25 % of a CTA's life in the one-plane-per-CTA kernel), barriers and TMEM
-// are set up once, and the stage ring (which no longer doubles as the output plane) keeps streaming across planes.
-//   warp 0: producer (both CTAs)        warp 1: MMA issuer (leader) / stage relay (peer)        warps 2-5: epilogue
-//   barriers: full/empty per stage, peer_full per stage (leader), acc_full[2] (multicast commit), acc_empty[2] (leader,
-//   one arrive per CTA after its TMEM reads), mask_full[2] / mask_empty[2] (dgrad ReLU mask staging)
-// ---------------------------------------------------------------------------------------------
-constexpr int kPStages = 8;
-
-__device__ __forceinline__ void tile_coords(const TcArgs &p, int tile, int &b, int &g, int &i, int &j) {
-    j = tile % p.d2; tile /= p.d2;
-    i = tile % p.d1; tile /= p.d1;
-    g = tile % p.G;
-    b = tile / p.G;
-}
-
-__global__ void __launch_bounds__(kTcThreads, 1)
-conv4d_tc_persist_kernel(const TcArgs p) {
-    extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t full_bar[kPStages], empty_bar[kPStages], peer_full[kPStages];
-    __shared__ __align__(8) uint64_t acc_full[2], acc_empty[2], mask_full[2], mask_empty[2];
-    __shared__ uint32_t tmem_base_s;
-    __shared__ int s_gshift[kMaxGroups];
-
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint32_t cta_rank;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(cta_rank));
-    const int chunk = (int)cta_rank;                     // the pair = the two row chunks of a plane
-    const int cluster_id = blockIdx.x >> 1, nclusters = gridDim.x >> 1;
-    const int PAD = p.KS / 2;
-    const int k0 = chunk * p.R;
-    const int rows_out = min(p.R, p.d3 - k0);
-    const int rows_pad = p.d3 + 2 * PAD;
-    const size_t plane_cb = (size_t)rows_pad * p.P;
-    const size_t ij_count = (size_t)p.d1 * p.d2;
-    const bool has_mask = p.mask_mode == 3;
-    const uint32_t mbytes = (uint32_t)rows_out * p.P * 16u;
-
-    if (threadIdx.x < kMaxGroups) s_gshift[threadIdx.x] = p.gshift[threadIdx.x];
-    if (warp == 1 && lane == 0) {
-        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); mbar_init(&peer_full[s], 1); }
-        for (int s = 0; s < 2; ++s) {
-            mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 2);
-            mbar_init(&mask_full[s], 1); mbar_init(&mask_empty[s], 1);
-        }
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    }
-    if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
-        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
-    }
-    {   // zero, once, the tail of each channel-half buffer behind the rows the bulk copies overwrite (read by the last
-        // tiles' discarded rows; must stay finite).  The chunk, hence the tail, is the same for every plane of this CTA.
-        const uint4 z = make_uint4(0, 0, 0, 0);
-        const int copied = min(p.R + p.KS - 1, rows_pad - k0) * p.P;
-        const int tail = p.npos_pad - copied;
-        for (int e = threadIdx.x; e < p.stages * 2 * tail; e += kTcThreads) {
-            const int s = e / (2 * tail), r = e - s * 2 * tail;
-            const int half = r / tail, pos = copied + (r - half * tail);
-            reinterpret_cast<uint4 *>(smem + (size_t)s * p.stage_bytes)[(size_t)half * p.npos_pad + pos] = z;
-        }
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-    }
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = tmem_base_s;
-    const uint32_t sm0 = smem_u32_pinned(smem);
-
-
-    if (warp == 0) {
-        // ===== producer: streams every plane's (d1,d2) stages, then that plane's ReLU-mask chunk =====
-        if (elect_one()) {
-            int stage = 0;
-            uint32_t phase = 0;
-            const int rows_in = min(p.R + p.KS - 1, rows_pad - k0);
-            const uint32_t half_bytes = (uint32_t)rows_in * p.P * 16u;
-            const uint32_t wb = p.w_bytes / 2u;                      // this CTA's half of the weight columns
-            const uint32_t tx_bytes = 2u * half_bytes + wb;
-            const size_t plane_halves = plane_cb * 8;
-            const size_t blk_halves = 2 * ij_count * plane_halves, half_off = ij_count * plane_halves;
-            const uint32_t w_halves = p.w_bytes / 2;
-            const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
-            const uint32_t full0 = smem_u32_pinned(full_bar), empty0 = smem_u32_pinned(empty_bar);
-            const uint32_t mfull0 = smem_u32_pinned(mask_full), mempty0 = smem_u32_pinned(mask_empty);
-            int n = 0;
-            for (int tile = cluster_id; tile < p.ntiles; tile += nclusters, ++n) {
-                int b, g, i, j;
-                tile_coords(p, tile, b, g, i, j);
-                const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
-                const __half *src_base = p.act + bg * blk_halves + (size_t)k0 * p.P * 8;
-                const __half *w_base = p.wp + (size_t)g * p.KS * p.KS * w_halves + (size_t)cta_rank * (wb / 2u);
-                for (int t1 = 0; t1 < p.KS; ++t1) {
-                    const int ii = i + t1 - PAD;
-                    if (ii < 0 || ii >= p.d1) continue;
-                    for (int t2 = 0; t2 < p.KS; ++t2) {
-                        const int jj = j + t2 - PAD;
-                        if (jj < 0 || jj >= p.d2) continue;
-                        mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
-                        const uint32_t sb = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
-                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(tx_bytes) : "memory");
-                        const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves;
-                        bulk_g2s_u32(sb, src0, half_bytes, fb);
-                        bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
-                        bulk_g2s_u32(sb + p.data_bytes, w_base + (size_t)(t1 * p.KS + t2) * w_halves, wb, fb);
-                        if (++stage == p.stages) { stage = 0; phase ^= 1; }
-                    }
-                }
-                if (has_mask) {
-                    // after the plane's stages: waiting for the mask buffer (free once the epilogue of plane n-2 has
-                    // stored) must not hold back the stage stream
-                    const uint32_t mb = (uint32_t)(n & 1);
-                    mbar_wait_u32(mempty0 + mb * 8u, (((uint32_t)n >> 1) & 1u) ^ 1u);
-                    const uint32_t mf = mfull0 + mb * 8u, dst = sm0 + p.mask_off + mb * p.mask_stride;
-                    const __half *msrc = (const __half *)p.mask +
-                        ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8 + (size_t)(k0 + PAD) * p.P * 8;
-                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mf), "r"(2u * mbytes) : "memory");
-                    bulk_g2s_u32(dst, msrc, mbytes, mf);
-                    bulk_g2s_u32(dst + mbytes, msrc + ij_count * plane_cb * 8, mbytes, mf);
-                }
-            }
-        }
-        __syncwarp();
-    } else if (warp == 1) {
-        if (cta_rank == 0) {
-            // ===== MMA issuer (leader): accumulator set n&1; waits until BOTH CTAs' epilogues have drained it =====
-            int stage = 0;
-            uint32_t phase = 0;
-            const uint32_t aempty0 = smem_u32_pinned(acc_empty), afull0 = smem_u32_pinned(acc_full);
-            int n = 0;
-            for (int tile = cluster_id; tile < p.ntiles; tile += nclusters, ++n) {
-                int b, g, i, j;
-                tile_coords(p, tile, b, g, i, j);
-                const uint32_t buf = (uint32_t)(n & 1);
-                mbar_wait_u32(aempty0 + buf * 8u, (((uint32_t)n >> 1) & 1u) ^ 1u);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t tb = tmem_base + buf * 256u;
-                if (p.NT == 3 && p.KSTEPS == 5) mma_main<3, 5, true>(p, i, j, smem, full_bar, empty_bar, peer_full, tb, 0, stage, phase);
-                else mma_main<0, 0, true>(p, i, j, smem, full_bar, empty_bar, peer_full, tb, 0, stage, phase);
-                if (elect_one()) umma_commit_to<true>(afull0 + buf * 8u);
-                __syncwarp();
-            }
-        } else if (elect_one()) {
-            // ===== stage relay (peer): tells the leader when each of this CTA's stages has landed =====
-            const uint32_t full0 = smem_u32_pinned(full_bar);
-            uint32_t remote0;
-            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote0) : "r"(smem_u32(peer_full)), "r"(0));
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int tile = cluster_id; tile < p.ntiles; tile += nclusters) {
-                int b, g, i, j;
-                tile_coords(p, tile, b, g, i, j);
-                const int nplanes = (min(i + PAD, p.d1 - 1) - max(i - PAD, 0) + 1) * (min(j + PAD, p.d2 - 1) - max(j - PAD, 0) + 1);
-                for (int it = 0; it < nplanes; ++it) {
-                    mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
-                    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote0 + (uint32_t)stage * 8u) : "memory");
-                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
-                }
-            }
-        }
-        __syncwarp();
-    } else {
-        // ===== epilogue (warps 2..5 <-> TMEM lane quadrants warp%4): drains set n&1 while the issuer fills the other =====
-        const int q = warp & 3;
-        const int et = threadIdx.x - 64;                 // 0..127
-        const uint32_t osm = sm0 + p.out_off;
-        const uint32_t afull0 = smem_u32_pinned(acc_full), mfull0 = smem_u32_pinned(mask_full);
-        uint32_t aempty_leader;                          // the leader's acc_empty[0] as a cluster address
-        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(aempty_leader) : "r"(smem_u32(acc_empty)), "r"(0));
-        float bv[16];
-#pragma unroll
-        for (int o = 0; o < 16; ++o) bv[o] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;
-        const int ra = chunk == 0 ? 0 : k0 + PAD;
-        const int rb = chunk == p.nchunks - 1 ? rows_pad : k0 + PAD + rows_out;
-        const int npos = (rb - ra) * p.P;
-        int n = 0;
-        for (int tile = cluster_id; tile < p.ntiles; tile += nclusters, ++n) {
-            int b, g, i, j;
-            tile_coords(p, tile, b, g, i, j);
-            const uint32_t buf = (uint32_t)(n & 1), par = ((uint32_t)n >> 1) & 1u;
-            mbar_wait_sleep(&acc_full[buf], par, 200);
-            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            // shifted sums: out[m - shift_gi][o] (+)= D[m][gi*16 + o]; group 0 writes bias + D, the others accumulate
-            const uint32_t lane_base = tmem_base + buf * 256u + ((uint32_t)(q * 32) << 16);
-            const int npair = (p.NT + 1) >> 1, nit = p.NG * npair;
-            uint32_t r0[16], r1[16], n0[16], n1[16];
-            tmem_ld16_issue(lane_base, r0);
-            if (p.NT > 1) tmem_ld16_issue(lane_base + (uint32_t)p.N, r1);
-            int gi = 0, t = 0;
-            for (int it = 0; it < nit; ++it) {
-                const bool two = t + 1 < p.NT;
-                const int sh = s_gshift[gi];
-                tmem_ld16_wait(r0);
-                if (two) tmem_ld16_wait(r1);
-                int gn = gi, tn = t + 2;
-                if (tn >= p.NT) { tn = 0; ++gn; }
-                if (it + 1 < nit) {
-                    tmem_ld16_issue(lane_base + (uint32_t)(tn * p.N + gn * 16), n0);
-                    if (tn + 1 < p.NT) tmem_ld16_issue(lane_base + (uint32_t)((tn + 1) * p.N + gn * 16), n1);
-                }
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    if (h == 1 && !two) break;
-                    const uint32_t(&r)[16] = h ? r1 : r0;
-                    const int dest = (t + h) * 128 + q * 32 + lane - sh;
-                    if (dest >= 0) {
-                        const uint32_t dst = osm + (uint32_t)dest * (kOutStride * 4u);
-                        if (gi == 0) {
-#pragma unroll
-                            for (int w4 = 0; w4 < 4; ++w4)
-                                sts_v4(dst + 16u * w4,
-                                       make_float4(bv[4 * w4 + 0] + __uint_as_float(r[4 * w4 + 0]), bv[4 * w4 + 1] + __uint_as_float(r[4 * w4 + 1]),
-                                                   bv[4 * w4 + 2] + __uint_as_float(r[4 * w4 + 2]), bv[4 * w4 + 3] + __uint_as_float(r[4 * w4 + 3])));
-                        } else {
-                            float4 a[4];
-#pragma unroll
-                            for (int w4 = 0; w4 < 4; ++w4) a[w4] = lds_v4(dst + 16u * w4);
-#pragma unroll
-                            for (int w4 = 0; w4 < 4; ++w4) {
-                                a[w4].x += __uint_as_float(r[4 * w4 + 0]); a[w4].y += __uint_as_float(r[4 * w4 + 1]);
-                                a[w4].z += __uint_as_float(r[4 * w4 + 2]); a[w4].w += __uint_as_float(r[4 * w4 + 3]);
-                                sts_v4(dst + 16u * w4, a[w4]);
-                            }
-                        }
-                    }
-                }
-                if (it + 1 < nit) {
-                    tmem_ld16_wait(n0);
-                    if (tn + 1 < p.NT) tmem_ld16_wait(n1);
-#pragma unroll
-                    for (int u = 0; u < 16; ++u) { r0[u] = n0[u]; r1[u] = n1[u]; }
-                }
-                if (gn != gi) {
-                    if (it + 1 == nit) asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");   // all TMEM reads done
-                    asm volatile("bar.sync 1, 128;" ::: "memory");       // last tile pair of this group
-                }
-                gi = gn; t = tn;
-            }
-            // this CTA's half of accumulator set `buf` is drained: one arrive per CTA on the LEADER's barrier
-            if (et == 0)
-                asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(aempty_leader + buf * 8u) : "memory");
-            // ---- store: CB16 (+ position-major twin), this chunk's rows of the haloed plane, halo written as zeros ----
-            const uint32_t mb = buf;
-            if (has_mask) mbar_wait_u32(mfull0 + mb * 8u, par);
-            const uint32_t msm = sm0 + p.mask_off + mb * p.mask_stride;
-            const size_t base_off = ((((size_t)b * p.G + g) * 2) * ij_count + (size_t)i * p.d2 + j) * plane_cb * 8;
-            __half *ob = (__half *)p.out + base_off;
-            for (int e = et; e < 2 * npos; e += 128) {
-                const int half = e / npos, pp = e - half * npos;
-                const int kk = ra + pp / p.P, ll = pp % p.P;
-                const int kr = kk - PAD - k0, lc = ll - PAD;
-                const size_t goff = ((size_t)half * ij_count * plane_cb + (size_t)kk * p.P + ll) * 8;
-                __align__(16) __half hv[8];
-                if (kr >= 0 && kr < rows_out && lc >= 0 && lc < p.d4) {
-                    const uint32_t src = osm + (uint32_t)((kr * p.P + lc) * kOutStride + half * 8) * 4u;
-                    const float4 a = lds_v4(src), c = lds_v4(src + 16u);
-                    float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
-                    if (has_mask) {
-                        const uint4 mraw = lds_u4(msm + (uint32_t)half * mbytes + (uint32_t)(kr * p.P + ll) * 16u);
-                        const __half *mh = reinterpret_cast<const __half *>(&mraw);
-#pragma unroll
-                        for (int c8 = 0; c8 < 8; ++c8) if (!(__half2float(mh[c8]) > 0.f)) v[c8] = 0.f;
-                    }
-#pragma unroll
-                    for (int c8 = 0; c8 < 8; ++c8) {
-                        float x = v[c8];
-                        if (p.relu) x = fmaxf(x, 0.f);
-                        hv[c8] = __float2half_rn((half * 8 + c8) < p.Cout ? x : 0.f);
-                    }
-                } else {
-#pragma unroll
-                    for (int c8 = 0; c8 < 8; ++c8) hv[c8] = __float2half_rn(0.f);
-                }
-                *reinterpret_cast<uint4 *>(ob + goff) = *reinterpret_cast<const uint4 *>(hv);
-                if (p.out_pm) {
-                    const int pos = kk * p.P + ll;
-                    const size_t pm_off = ((((size_t)b * p.G + g) * ij_count + (size_t)i * p.d2 + j) * plane_cb + pos) * 16 +
-                                          (size_t)((half ^ ((pos >> 2) & 1)) * 8);
-                    *reinterpret_cast<uint4 *>(p.out_pm + pm_off) = *reinterpret_cast<const uint4 *>(hv);
-                }
-            }
-            asm volatile("bar.sync 1, 128;" ::: "memory");       // the output plane and the mask buffer are free again
-            if (has_mask && et == 0) {
-                const uint32_t me = smem_u32(&mask_empty[mb]);
-                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(me) : "memory");
-            }
-        }
-    }
-    // ---- teardown: neither CTA may leave while the other's MMAs / remote arrives can still touch it ----
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-    __syncthreads();
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
-}
-// ---------------------------------------------------------------------------------------------
 // CB16 packing
 // ---------------------------------------------------------------------------------------------
 // planar [nblk, C, vol] (T) -> CB16 [nblk][2][ij][d3+2p][P][8], halo = 0.
 //   tap_mode 0: channels = the tensor's C (<= 16) channels
 //   tap_mode 1: C == 1, channel t = x[.., l + t - p]                 (taps along the last axis)
 //   tap_mode 2: C == 1, channel t = x[.., j - t + p, ..]             (taps along the second axis, mirrored)
-//   tap_mode 3: C == 1, half u, channel t = x[.., k + u, l + t - p] seen from the haloed position: two
-//               consecutive d3 taps x all d4 taps in the 16 channels (forward mode M3)
 template <typename T>
 __global__ void __launch_bounds__(256)
 cb16_pack_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1, int d2, int d3, int d4, int pad,
@@ -888,16 +559,7 @@ cb16_pack_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, int d1
         const size_t ijx = pp / ((size_t)P * rows);
         const int k = kk - pad, l = ll - pad;
         __align__(16) __half v[8];
-        if (tap_mode == 3) {
-            // haloed position (kk,ll), half u: channel t = x[kk - p + u, ll - 2p + t]; evaluated on halo rows too
-            const int ks = k + half;
-#pragma unroll
-            for (int c = 0; c < 8; ++c) {
-                const int lt = l - pad + c;
-                v[c] = __float2half_rn((c < taps && ks >= 0 && ks < d3 && lt >= 0 && lt < d4)
-                                           ? ldf(x + blk * vol + ijx * plane + (size_t)ks * d4 + lt) : 0.f);
-            }
-        } else if (k >= 0 && k < d3 && l >= 0 && l < d4) {
+        if (k >= 0 && k < d3 && l >= 0 && l < d4) {
             const size_t pos = ijx * plane + (size_t)k * d4 + l;
             if (tap_mode == 0) {
 #pragma unroll
@@ -949,16 +611,16 @@ cb16_pack_rows_kernel(const T *__restrict__ x, __half *__restrict__ cb, int C, i
     __align__(16) __half v[8];
 #pragma unroll
     for (int c = 0; c < 8; ++c) v[c] = __float2half_rn(0.f);
-    if (tap_mode == 1 || tap_mode == 3) {
+    if (tap_mode == 1) {
         // lane holds x[row][lane - 2p]; channel c of haloed column ll is the value of lane ll + c
-        const int ks = tap_mode == 3 ? k + half : k;
+        const int ks = k;
         const int col = lane - 2 * pad;
         float e = 0.f;
         if (ks >= 0 && ks < d3 && col >= 0 && col < d4) e = ldf(x + (size_t)blk * vol + (size_t)ijx * plane + (size_t)ks * d4 + col);
 #pragma unroll
         for (int c = 0; c < 8; ++c) {
             const float o = __shfl_down_sync(0xffffffffu, e, c);
-            if (c < taps && lane + c < 32 && (tap_mode == 3 || inside)) v[c] = __float2half_rn(o);
+            if (c < taps && lane + c < 32 && inside) v[c] = __float2half_rn(o);
         }
     } else if (inside) {
         const size_t pos = (size_t)ijx * plane + (size_t)k * d4 + l;
@@ -1008,11 +670,11 @@ cb16_pack_wide_rows_kernel(const T *__restrict__ x, __half *__restrict__ cb, int
         __align__(16) __half v[8];
 #pragma unroll
         for (int c = 0; c < 8; ++c) v[c] = __float2half_rn(0.f);
-        if (tap_mode == 1 || tap_mode == 3) {
-            const int ks = tap_mode == 3 ? k + half : k;
+        if (tap_mode == 1) {
+            const int ks = k;
             const bool row_ok = ks >= 0 && ks < d3;
             const T *xr = x + (size_t)blk * vol + (size_t)ijx * plane + (size_t)(row_ok ? ks : 0) * d4;
-            if (row_ok && (tap_mode == 3 || inside)) {
+            if (row_ok && inside) {
 #pragma unroll
                 for (int c = 0; c < 8; ++c) {
                     const int col = ll - 2 * pad + c;
@@ -1285,12 +947,9 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
             g = g * a.OG + n / 16;
         } else if (a.mode == 1) {          // N = (t4, o), K-step = t3, channel = ci
             t3 = ks; t4 = n / a.CoutPad; oe = n % a.CoutPad; ci = kch;
-        } else if (a.mode == 2) {   // N = (t3, t4), single out channel, channel = ci
+        } else {                    // mode 2: N = (t3, t4), single out channel, channel = ci
             t3 = n / k; t4 = n % k; oe = 0; ci = kch;
             ok = n < k * k;
-        } else {                    // N = (t3 pair, o), channel = (t3 parity, t4 tap), single in channel
-            t3 = 2 * (n / a.CoutPad) + half; oe = n % a.CoutPad; t4 = c8; ci = 0;
-            ok = c8 < k;
         }
         float v = 0.f;
         if (ok && t3 < k && t4 < k && oe < a.d.Cout_e && ci < a.d.Cin_e)
@@ -1302,9 +961,6 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-long long *g_tc_debug_buffer = nullptr;     // set through ncnet_debug_set_tc_timing (development only)
-int g_tc_debug_mode = 0;
-
 struct TcPlan {
     int mode, KSTEPS, N, NG, CoutPad, P, R, nchunks, NT, npos_pad, stages, inner, OG;
     uint32_t tmem_cols;
@@ -1318,9 +974,7 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask
     pl.ok = false;
     if (Cin_e > 16 || Cout_e > 16 || (k != 3 && k != 5)) return pl;
     pl.inner = k;
-    static const bool force_m3 = [] { const char *e = getenv("NCNET_TC_M3"); return e && e[0] == '1'; }();   // development knob
-    if (Cin_e == 1 && Cout_e > 1 && !force_m3) { pl.mode = 4; pl.CoutPad = 16; pl.NG = 1; pl.KSTEPS = k; pl.inner = (k * k + 15) / 16; }
-    else if (Cin_e == 1 && Cout_e > 1) { pl.mode = 3; pl.CoutPad = 16; pl.NG = (k + 1) / 2; pl.KSTEPS = 1; }
+    if (Cin_e == 1 && Cout_e > 1) { pl.mode = 4; pl.CoutPad = 16; pl.NG = 1; pl.KSTEPS = k; pl.inner = (k * k + 15) / 16; }
     else if (Cout_e == 1)          { pl.mode = 2; pl.CoutPad = 1; pl.NG = k * k; pl.KSTEPS = 1; }
     else                           { pl.mode = 1; pl.CoutPad = 16; pl.NG = k; pl.KSTEPS = k; }
     pl.N = pl.mode == 2 ? ((k * k + 15) / 16) * 16 : pl.NG * 16;
@@ -1329,8 +983,8 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask
     pl.P = d4 + k - 1;
     const int pad = k / 2;
     const int max_aoff = (pl.mode == 1 || pl.mode == 4) ? (k - 1) * pl.P : 0;
-    // largest epilogue row shift (mode 3 reads the haloed row at column l + pad, hence the extra pad)
-    const int max_shift = pl.mode == 4 ? 0 : pl.mode == 1 ? (k - 1) : (pl.mode == 2 ? (k - 1) * pl.P + (k - 1) : 2 * (pl.NG - 1) * pl.P + pad);
+    // largest epilogue row shift
+    const int max_shift = pl.mode == 4 ? 0 : pl.mode == 1 ? (k - 1) : (k - 1) * pl.P + (k - 1);
     pl.w_bytes = (uint32_t)pl.KSTEPS * 2u * pl.N * 16u;
     // budget: one CTA per SM may use all 512 TMEM columns and ~220 KB; two co-resident CTAs (whose
     // epilogue/prologue then overlap the other's MMA main loop) get 256 columns and ~108 KB each
@@ -1421,19 +1075,18 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     const int og = (d.G_e == 2 && Gx == 1 && d.Cin_e == 1 && !d.dgrad && !mask) ? 2 : 1;
     const TcPlan pl = tc_plan(d.Cin_e, d.Cout_e, d.k, d3, d4, mask && mask_dtype == NCNET_CB16, og);
     if (!pl.ok) return 2;
-    if (x_dtype == NCNET_CB16 && (pl.mode == 3 || pl.mode == 4)) return 2;   // the tap im2col needs the planar single-channel input
+    if (x_dtype == NCNET_CB16 && pl.mode == 4) return 2;   // the tap im2col needs the planar single-channel input
     if (y_dtype == NCNET_CB16 && pl.CoutPad < 16) return 2;
     if (mask && ((mask_dtype == NCNET_CB16) != (y_dtype == NCNET_CB16))) return 2;
     // CTA pairs for the many-channel layers: the two chunks of a plane run as one cluster, one M256 MMA stream
-    static const bool pair_off = [] { const char *e = getenv("NCNET_TC_PAIR"); return e && e[0] == '0'; }();
-    const int pair = (!pair_off && pl.mode == 1 && pl.nchunks == 2 && pl.tmem_cols <= 256 && (pl.N / 2) % 8 == 0) ? 1 : 0;
+    const int pair = (pl.mode == 1 && pl.nchunks == 2 && pl.tmem_cols <= 256 && (pl.N / 2) % 8 == 0) ? 1 : 0;
     uint8_t *sc = (uint8_t *)scratch;
     const __half *act;
     size_t used = 0;
     if (x_dtype == NCNET_CB16) {
         act = (const __half *)x;
     } else {
-        int rc = cb16_pack(x, x_dtype, sc, B * Gx, d.Cin_e, d1, d2, d3, d4, d.k, pl.mode == 3 ? 3 : (pl.mode == 4 ? 4 : 0), st);
+        int rc = cb16_pack(x, x_dtype, sc, B * Gx, d.Cin_e, d1, d2, d3, d4, d.k, pl.mode == 4 ? 4 : 0, st);
         if (rc) return rc;
         act = (const __half *)sc;
         used = align256(cb16_bytes((size_t)B * Gx * (pl.mode == 4 ? pl.inner : 1), d1, d2, d3, d4, d.k));
@@ -1459,8 +1112,6 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     a.mask_mode = !mask ? 0 : (mask_dtype == NCNET_CB16 ? 3 : (mask_dtype == NCNET_F16 ? 2 : 1));
     a.stage_bytes = pl.stage_bytes; a.data_bytes = pl.data_bytes; a.w_bytes = pl.w_bytes; a.mask_off = pl.mask_off;
     a.out_pm = out_pm;
-    a.dbg = g_tc_debug_buffer;
-    a.dbg_mode = g_tc_debug_mode;
     // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=f16 (0), both K-major, N>>3 at bit 17, M>>4 at bit 24
     a.idesc = (1u << 4) | ((uint32_t)(pl.N >> 3) << 17) | ((uint32_t)((pair ? 256 : 128) >> 4) << 24);
     a.pair = pair;
@@ -1471,8 +1122,7 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
         if (gi < pl.NG) {
             if (pl.mode == 4) s = 0;                                    // one group, taps are in the channels / K-steps
             else if (pl.mode == 1) s = gi;                              // group = d4 tap
-            else if (pl.mode == 2) s = (gi / d.k) * pl.P + (gi % d.k);  // group = (d3, d4)
-            else s = 2 * gi * pl.P + pad;                               // group = d3 tap pair; the d4 taps sit in the channels of column l + pad
+            else s = (gi / d.k) * pl.P + (gi % d.k);                    // mode 2: group = (d3, d4)
         }
         a.gshift[gi] = s;
     }
@@ -1481,40 +1131,6 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
     const long long ctas = (long long)B * (d.G_e / pl.OG) * d1 * d2 * pl.nchunks;
     NC_CHECK(ctas < (1ll << 31), "conv4d(tc): grid too large");
-    // persistent, TMEM-double-buffered pair kernel for CB16 -> CB16 layers
-    // (opt-in: measured 3.95 ms against 3.71 ms for the two-CTAs-per-SM pair kernel on the 16->16 layer at B = 16 -- with
-    // one pair per SM pair the main loop needs 33 B/clk/SM of L2->shared traffic, above the ~26 B/clk the chip delivers)
-    static const bool persist_on = [] { const char *e = getenv("NCNET_TC_PERSIST"); return e && e[0] == '1'; }();
-    if (pair && persist_on && a.out_mode == 2 && (a.mask_mode == 0 || a.mask_mode == 3) && !a.dbg && pl.NT * pl.N <= 256 &&
-        pl.stages <= kPStages) {
-        const uint32_t stage_p = ((pl.data_bytes + pl.w_bytes / 2u + 127u) / 128u) * 128u;
-        const uint32_t outb = (((uint32_t)pl.NT * 128u * kOutStride * 4u) + 127u) / 128u * 128u;
-        const uint32_t maskb = a.mask_mode == 3 ? (((uint32_t)2 * pl.R * pl.P * 16u + 127u) / 128u * 128u) : 0u;
-        const uint32_t budget = 220u * 1024u;
-        int stages_p = (int)((budget - outb - 2u * maskb) / stage_p);
-        if (stages_p > kPStages) stages_p = kPStages;
-        if (stages_p >= 3) {
-            TcArgs q = a;
-            q.stages = stages_p; q.stage_bytes = stage_p;
-            q.out_off = (uint32_t)stages_p * stage_p;
-            q.mask_off = q.out_off + outb; q.mask_stride = maskb;
-            q.ntiles = B * a.G * d1 * d2;
-            const size_t smem_p = (size_t)q.mask_off + 2u * maskb;
-            e = cudaFuncSetAttribute(conv4d_tc_persist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_p);
-            NC_CHECK(e == cudaSuccess, "conv4d(tc): smem attribute: %s", cudaGetErrorString(e));
-            const int nclusters = q.ntiles < kNumSMs / 2 ? q.ntiles : kNumSMs / 2;
-            cudaLaunchConfig_t cfg{};
-            cfg.gridDim = dim3((unsigned)(2 * nclusters)); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = smem_p; cfg.stream = st;
-            cudaLaunchAttribute attr[1];
-            attr[0].id = cudaLaunchAttributeClusterDimension;
-            attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-            cfg.attrs = attr; cfg.numAttrs = 1;
-            e = cudaLaunchKernelEx(&cfg, conv4d_tc_persist_kernel, q);
-            NC_CHECK(e == cudaSuccess, "conv4d(tc): persistent cluster launch: %s", cudaGetErrorString(e));
-            NC_LAUNCH_OK("conv4d_tc_persist_kernel");
-            return 0;
-        }
-    }
     if (pair) {
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3((unsigned)ctas); cfg.blockDim = dim3(kTcThreads); cfg.dynamicSmemBytes = pl.smem_bytes; cfg.stream = st;
@@ -1554,7 +1170,3 @@ int conv4d_tc_dgrad(const void *gy, int gy_dtype, const float *w, const void *ma
 }
 
 }  // namespace ncnet
-
-// development hook (not part of include/ncnet_b200.h): device buffer of 4096*8 int64 phase timestamps
-extern "C" void ncnet_debug_set_tc_timing(void *device_buffer) { ncnet::g_tc_debug_buffer = (long long *)device_buffer; }
-extern "C" void ncnet_debug_set_tc_mode(int mode) { ncnet::g_tc_debug_mode = mode; }

@@ -280,8 +280,7 @@ static WgPmPlan pm_plan(int d3, int d4, int k) {
     // two d2 taps per CTA (one grad plane staged per two X planes: the kernel is close to the L2->shared ceiling) when a
     // 2-deep ring of such stages fits; else one tap and a deeper ring
     w.N = 16 * k;
-    const char *env = getenv("NCNET_WG_NAV");      // development knob
-    for (w.nav = (env && env[0] == '1') ? 1 : 2; w.nav >= 1; --w.nav) {
+    for (w.nav = 2; w.nav >= 1; --w.nav) {
         w.a_bytes = (uint32_t)w.nav * w.a1_bytes;
         w.stage_bytes = ((w.a_bytes + (uint32_t)npos_b * 32u + 1023u) / 1024u) * 1024u;
         int stages = (int)((220u * 1024u) / w.stage_bytes);

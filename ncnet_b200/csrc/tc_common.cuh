@@ -1,7 +1,6 @@
 // sm_100a building blocks shared by the tensor-core kernels: mbarrier, TMA (bulk + tensor tile),
 // UMMA shared-memory descriptors, tcgen05.mma / commit / ld, and the host-side tensor-map encoder.
 #pragma once
-#include <cuda.h>           // CUtensorMap types only; the driver entry point is fetched at run time
 #include "common.cuh"
 
 namespace ncnet {
@@ -99,16 +98,6 @@ __device__ __forceinline__ void bulk_g2s_u32(uint32_t dst, const void *src, uint
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
-// 5-D tensor tile global -> shared (SASS: UTMALDG); out-of-bounds elements arrive as zeros
-__device__ __forceinline__ void tma_tile_5d(void *dst, const CUtensorMap *map, int c0, int c1, int c2, int c3, int c4,
-                                            uint64_t *bar) {
-    asm volatile(
-        "cp.async.bulk.tensor.5d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4, %5, %6}], [%7];"
-        ::"r"(smem_u32(dst)), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(c3), "r"(c4), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void prefetch_tmap(const CUtensorMap *map) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(map) : "memory");
-}
 // UMMA shared-memory descriptor, SWIZZLE_NONE, version 1 (sm_100).
 //   K-major : SBO = stride between 8-row groups, LBO = stride between the 16-byte K chunks
 //   MN-major: SBO = stride between 8-element M/N groups, LBO = stride between groups of 8 K rows
@@ -164,33 +153,6 @@ __device__ __forceinline__ void tmem_ld8(uint32_t taddr, float (&v)[8]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 #pragma unroll
     for (int i = 0; i < 8; ++i) v[i] = __uint_as_float(r[i]);
-}
-
-// Host: tensor map over a channel-blocked fp16 activation tensor [nhalves][d1*d2][d3][d4][8]
-// with a (8, box_l, box_k, 1, 1) box; no swizzle, zero fill outside the tensor.
-inline int make_act_tmap(CUtensorMap *map, const void *base, size_t nhalves, int d1, int d2, int d3, int d4, int box_l,
-                         int box_k) {
-    typedef CUresult (*EncodeFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
-                                 const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
-                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-    static EncodeFn fn = nullptr;
-    if (!fn) {
-        void *p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
-        if (e != cudaSuccess || !p) return fail("tensor map: cuTensorMapEncodeTiled unavailable (%s)", cudaGetErrorString(e));
-        fn = (EncodeFn)p;
-    }
-    if (box_l > 256 || box_k > 256) return fail("tensor map: box %dx%d exceeds the 256-element limit", box_l, box_k);
-    const cuuint64_t dims[5] = {8, (cuuint64_t)d4, (cuuint64_t)d3, (cuuint64_t)d1 * d2, (cuuint64_t)nhalves};
-    const cuuint64_t strides[4] = {16, (cuuint64_t)d4 * 16, (cuuint64_t)d3 * d4 * 16, (cuuint64_t)d1 * d2 * d3 * d4 * 16};
-    const cuuint32_t box[5] = {8, (cuuint32_t)box_l, (cuuint32_t)box_k, 1, 1};
-    const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 5, const_cast<void *>(base), dims, strides, box, estr,
-                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
-                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail("tensor map: cuTensorMapEncodeTiled failed (%d)", (int)r);
-    return 0;
 }
 
 }  // namespace tc
