@@ -11,7 +11,9 @@
  *     dense, row-major, in the reference's own layout;
  *   - the library never allocates or frees device memory and keeps no pointer
  *     after returning; scratch is passed in by the caller (sizes from the
- *     *_scratch_bytes queries);
+ *     *_scratch_bytes queries).  The one exception is
+ *     ncnet_mutual_matching_fwd_noalloc, whose scratch is an array built into
+ *     the library and whose per-device address the library caches;
  *   - `stream` is a cudaStream_t passed as void*; launches are asynchronous,
  *     nothing synchronises the device;
  *   - return 0 on success, non-zero on error; ncnet_last_error() returns the
@@ -111,8 +113,10 @@ int ncnet_mutual_matching_bwd(const void *x, const void *grad_y, const uint64_t 
  * that first call with the device current and before starting any stream capture.  All calls on a
  * device share the one table: it still holds the previous call's maxima on entry (the part a call
  * uses is cleared on its stream first), and two calls whose kernels overlap on the GPU -- different
- * streams without an ordering between them -- race on it.  The arg-max keys are not returned, so
- * this variant serves inference; the backward pass needs ncnet_mutual_matching_fwd. */
+ * streams without an ordering between them -- race on it.  The cached address belongs to the CUDA
+ * context it was looked up in: after cudaDeviceReset (or any teardown of the primary context) it is
+ * stale and this entry point must not be called again in that process.  The arg-max keys are not
+ * returned, so this variant serves inference; the backward pass needs ncnet_mutual_matching_fwd. */
 int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, int nA, int nB, int in_groups,
                                       int dtype, void *stream);
 

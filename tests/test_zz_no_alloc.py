@@ -44,6 +44,17 @@ def test_noalloc_matches_plain_entry_point_twice(cuda):
     x2 = (torch.rand(2, 2, 7, 5, 6, 9, device=cuda) * 0.1).half().contiguous()
     a2, b2 = _both(lib, x2, 2)
     assert torch.isfinite(a2.float()).all() and torch.equal(a2, b2)
+    # the property itself: a warm call takes no device memory (neither from the driver nor from torch's pool)
+    y = torch.empty_like(x2[:, :1])
+    st = torch.cuda.current_stream().cuda_stream
+    torch.cuda.synchronize()
+    free0, _ = torch.cuda.mem_get_info()
+    held0, reserved0 = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    _cabi.check(lib.ncnet_mutual_matching_fwd_noalloc(x2.data_ptr(), y.data_ptr(), 2, 35, 54, 2, _cabi.F16, st), "noalloc")
+    torch.cuda.synchronize()
+    free1, _ = torch.cuda.mem_get_info()
+    assert free1 == free0 and torch.cuda.memory_allocated() == held0 and torch.cuda.memory_reserved() == reserved0
+    assert torch.equal(y, b2)
     # and against the CPU oracle, within the fp32 tolerance of the parity tests
     from oracle import head as O
     ref = O.mutual_matching(x1[:1].cpu())
