@@ -74,6 +74,15 @@ int ncnet_corr4d_fwd(const void *fa, const void *fb, void *out, int B, int C, in
 size_t ncnet_corr4d_tc_scratch_bytes(int B, int C, int nA, int nB);
 int ncnet_corr4d_fwd_tc(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB,
                         int dtype, int relu_l2norm, int l2norm_inputs, void *stream);
+/* Correlation with the relocalisation max-pool fused into its epilogue -- lib/model.py:269-272 (FeatureCorrelation
+ * followed by maxpool4d, lib/model.py:177-191) for one image pair (the reference's maxpool4d is batch-1 only).
+ * fa: [C,hA,wA], fb: [C,hB,wB], sides even, k_size = 2.  value: [hA/2,wA/2,hB/2,wB/2] in `dtype`; max_i..max_l: the
+ * window-relative arg-max offsets of the same shape (idx_bytes 8 = int64 as the reference returns them, 1 = uint8).
+ * Bit-identical to ncnet_corr4d_fwd_tc followed by ncnet_maxpool4d_fwd, but the un-pooled volume (16x the output) is
+ * never written.  scratch: ncnet_corr4d_tc_scratch_bytes(1, C, hA*wA, hB*wB).  relu_l2norm / l2norm_inputs as above. */
+int ncnet_corr4d_pool_fwd_tc(const void *fa, const void *fb, void *value, void *max_i, void *max_j, void *max_k,
+                             void *max_l, void *scratch, int C, int hA, int wA, int hB, int wB, int k_size,
+                             int idx_bytes, int dtype, int relu_l2norm, int l2norm_inputs, void *stream);
 /* gradient of the plain (un-normalised) correlation wrt both feature maps (autograd of lib/model.py:113) */
 int ncnet_corr4d_bwd(const void *grad_out, const void *fa, const void *fb, void *grad_fa, void *grad_fb,
                      int B, int C, int nA, int nB, int dtype, void *stream);

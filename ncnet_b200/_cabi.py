@@ -28,6 +28,7 @@ SIGNATURES = {
     "ncnet_corr4d_fwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "ncnet_corr4d_tc_scratch_bytes": (_sz, [_i] * 4),
     "ncnet_corr4d_fwd_tc": (_i, [_p, _p, _p, _p] + [_i] * 7 + [_p]),
+    "ncnet_corr4d_pool_fwd_tc": (_i, [_p] * 8 + [_i] * 10 + [_p]),
     "ncnet_corr4d_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_keys_bytes": (_sz, [_i, _i, _i]),
     "ncnet_mutual_matching_sums_bytes": (_sz, [_i, _i, _i]),

@@ -147,6 +147,8 @@ namespace ncnet {
 size_t corr4d_tc_scratch_bytes(int B, int C, int nA, int nB);
 int corr4d_tc_fwd(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB, int dtype,
                   int relu_l2norm, int l2norm_inputs, cudaStream_t st);
+int corr4d_pool_tc_fwd(const void *fa, const void *fb, void *value, void *const idx[4], void *scratch, int C, int hA, int wA,
+                       int hB, int wB, int idx_bytes, int dtype, int relu_l2norm, int l2norm_inputs, cudaStream_t st);
 }  // namespace ncnet
 
 using namespace ncnet;
@@ -162,6 +164,21 @@ extern "C" int ncnet_corr4d_fwd_tc(const void *fa, const void *fb, void *out, vo
     NC_CHECK(B > 0 && C > 0 && nA > 0 && nB > 0, "corr4d_fwd_tc: bad shape");
     NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "corr4d_fwd_tc: unsupported dtype %d", dtype);
     return corr4d_tc_fwd(fa, fb, out, scratch, B, C, nA, nB, dtype, relu_l2norm, l2norm_inputs, (cudaStream_t)stream);
+}
+
+extern "C" int ncnet_corr4d_pool_fwd_tc(const void *fa, const void *fb, void *value, void *max_i, void *max_j, void *max_k,
+                                        void *max_l, void *scratch, int C, int hA, int wA, int hB, int wB, int k_size,
+                                        int idx_bytes, int dtype, int relu_l2norm, int l2norm_inputs, void *stream) {
+    NC_CHECK(fa && fb && value && max_i && max_j && max_k && max_l && scratch, "corr4d_pool_fwd_tc: null pointer");
+    NC_CHECK(C > 0 && hA > 0 && wA > 0 && hB > 0 && wB > 0, "corr4d_pool_fwd_tc: bad shape");
+    NC_CHECK(k_size == 2, "corr4d_pool_fwd_tc: k_size %d not supported by the fused kernel (2 only; use ncnet_corr4d_fwd_tc + "
+             "ncnet_maxpool4d_fwd)", k_size);
+    NC_CHECK(hA % 2 == 0 && wA % 2 == 0 && hB % 2 == 0 && wB % 2 == 0, "corr4d_pool_fwd_tc: feature map sides must be even");
+    NC_CHECK(idx_bytes == 1 || idx_bytes == 8, "corr4d_pool_fwd_tc: idx_bytes must be 1 or 8");
+    NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "corr4d_pool_fwd_tc: unsupported dtype %d", dtype);
+    void *const idx[4] = {max_i, max_j, max_k, max_l};
+    return corr4d_pool_tc_fwd(fa, fb, value, idx, scratch, C, hA, wA, hB, wB, idx_bytes, dtype, relu_l2norm, l2norm_inputs,
+                              (cudaStream_t)stream);
 }
 
 extern "C" int ncnet_feature_l2norm(const void *x, void *y, int B, int C, int HW, int dtype, void *stream) {

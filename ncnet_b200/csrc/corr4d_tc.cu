@@ -7,6 +7,15 @@
 // (128|256 positions x 64 channels) operand tile of a pipeline stage is ONE contiguous run -> one cp.async.bulk per
 // operand per stage.  fp32 accumulation in TMEM (128 x 256 tile), epilogue: optional ReLU + singleton-dim L2 norm
 // (normalization=True), rows streamed straight to the [B,nA,nB] volume.
+//
+// Fused relocalisation pooling (lib/model.py:269-272 + 177-191, k_size = 2): the pack kernel orders the positions of
+// both feature maps window-major -- packed index = 4 * (2x2 window, row-major over the pooled grid) + (i%2)*2 + (j%2)
+// -- so the four source cells of a pooling window are four consecutive accumulator rows (= four neighbouring lanes of
+// an epilogue warp) and the four target cells four consecutive accumulator columns.  The epilogue takes the maximum
+// of each 4x4 block (4 columns in registers, then a butterfly over the lane quad; ties -> lowest (i,j,k,l) code, the
+// reference's scan order) and writes the pooled value and the four window offsets; the 16x larger volume never
+// reaches memory.  Values are rounded to the storage type before they are compared, so the result is bit-identical
+// to maxpool4d of the stored un-pooled volume.
 #include "common.cuh"
 #include "tc_common.cuh"
 
@@ -20,13 +29,26 @@ constexpr int kCorrKB = 64;            // channels per stage
 constexpr int kCorrBM = 128, kCorrBN = 256;
 
 // [B, C, n] (T) -> fp16 [B][KB][npad/8][64][8]; positions >= n and channels >= C are zero.
+// pool_w > 0: the map is [n / pool_w, pool_w] and packed position p holds the cell of 2x2 window p/4 (row-major over the
+// pooled grid) at in-window offset ((p%4)/2, (p%4)%2).
 template <typename T>
 __global__ void __launch_bounds__(256)
-corr_pack_kernel(const T *__restrict__ f, __half *__restrict__ out, int C, int n, int npad, int kblocks, int l2norm) {
+corr_pack_kernel(const T *__restrict__ f, __half *__restrict__ out, int C, int n, int npad, int kblocks, int l2norm,
+                 int pool_w) {
     const int b = blockIdx.z;
     const int mg = blockIdx.x * blockDim.x + threadIdx.x;       // group of 8 positions
     if (mg >= npad / 8) return;
     const T *fb = f + (size_t)b * C * n;
+    int src[8];                                                 // source position of each packed position, -1 = padding
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+        const int a = mg * 8 + u;
+        src[u] = a < n ? a : -1;
+        if (pool_w > 0 && a < n) {
+            const int win = a >> 2, q = a & 3, ww = pool_w >> 1;
+            src[u] = ((win / ww) * 2 + (q >> 1)) * pool_w + (win % ww) * 2 + (q & 1);
+        }
+    }
     float inv[8];
 #pragma unroll
     for (int u = 0; u < 8; ++u) inv[u] = 1.f;
@@ -35,8 +57,7 @@ corr_pack_kernel(const T *__restrict__ f, __half *__restrict__ out, int C, int n
         for (int c = 0; c < C; ++c)
 #pragma unroll
             for (int u = 0; u < 8; ++u) {
-                const int a = mg * 8 + u;
-                const float v = a < n ? ldf(fb + (size_t)c * n + a) : 0.f;
+                const float v = src[u] >= 0 ? ldf(fb + (size_t)c * n + src[u]) : 0.f;
                 ss[u] += v * v;
             }
 #pragma unroll
@@ -45,10 +66,8 @@ corr_pack_kernel(const T *__restrict__ f, __half *__restrict__ out, int C, int n
     for (int c = blockIdx.y; c < kblocks * kCorrKB; c += gridDim.y) {
         __align__(16) __half v[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int a = mg * 8 + u;
-            v[u] = __float2half_rn((c < C && a < n) ? ldf(fb + (size_t)c * n + a) * inv[u] : 0.f);
-        }
+        for (int u = 0; u < 8; ++u)
+            v[u] = __float2half_rn((c < C && src[u] >= 0) ? ldf(fb + (size_t)c * n + src[u]) * inv[u] : 0.f);
         const size_t off = ((((size_t)b * kblocks + c / kCorrKB) * (npad / 8) + mg) * kCorrKB + (c % kCorrKB)) * 8;
         *reinterpret_cast<uint4 *>(out + off) = *reinterpret_cast<const uint4 *>(v);
     }
@@ -60,7 +79,69 @@ struct CorrArgs {
     int nA, nB, npadA, npadB, kblocks;
     int relu_l2norm, out_f16;
     uint32_t idesc;
+    // fused 2x2x2x2 max-pool (pool != 0): out = pooled values [nA/4, nB/4]; idx[4] = max_i, max_j, max_k, max_l
+    int pool, idx_bytes;
+    void *idx[4];
 };
+
+template <typename T>
+__device__ __forceinline__ float corr_post(float x, int relu_l2norm);
+template <>
+__device__ __forceinline__ float corr_post<float>(float x, int relu_l2norm) {
+    if (relu_l2norm) {
+        x = fmaxf(x, 0.f);
+        x = x / sqrtf(x * x + 1e-6f);
+    }
+    return x;
+}
+template <>
+__device__ __forceinline__ float corr_post<__half>(float x, int relu_l2norm) {
+    if (relu_l2norm) {
+        x = rnd<__half>(fmaxf(rnd<__half>(x), 0.f));
+        x = x / rnd<__half>(sqrtf(rnd<__half>(rnd<__half>(x * x) + 1e-6f)));
+    }
+    return rnd<__half>(x);
+}
+
+// epilogue of the fused pooling: this thread's accumulator row r (a window-major source position) and 16 columns
+template <typename T>
+__device__ __forceinline__ void corr_pool_chunk(const CorrArgs &p, const float (&v)[16], int r, int t0, int lane) {
+    const int aq = lane & 3;                       // in-window source offset code (i%2)*2 + (j%2)
+    float bv[4];
+    int bc[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        float best = corr_post<T>(v[4 * g], p.relu_l2norm);
+        int code = 0;
+#pragma unroll
+        for (int c = 1; c < 4; ++c) {
+            const float x = corr_post<T>(v[4 * g + c], p.relu_l2norm);
+            if (x > best) { best = x; code = c; }
+        }
+        code += aq * 4;                            // (i,j,k,l) row-major window scan order
+#pragma unroll
+        for (int o = 1; o <= 2; o <<= 1) {
+            const float ov = __shfl_xor_sync(0xffffffffu, best, o);
+            const int oc = __shfl_xor_sync(0xffffffffu, code, o);
+            if (ov > best || (ov == best && oc < code)) { best = ov; code = oc; }
+        }
+        bv[g] = best; bc[g] = code;
+    }
+    // lane aq of the quad writes pooled column aq of this chunk
+    const float mv = aq == 0 ? bv[0] : (aq == 1 ? bv[1] : (aq == 2 ? bv[2] : bv[3]));
+    const int mc = aq == 0 ? bc[0] : (aq == 1 ? bc[1] : (aq == 2 ? bc[2] : bc[3]));
+    const int prow = r >> 2, pcol = (t0 >> 2) + aq;
+    const int pA = p.nA >> 2, pB = p.nB >> 2;
+    if (prow >= pA || pcol >= pB) return;
+    const size_t o = (size_t)prow * pB + pcol;
+    stf((T *)p.out + o, mv);
+    const int off[4] = {mc >> 3, (mc >> 2) & 1, (mc >> 1) & 1, mc & 1};
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        if (p.idx_bytes == 1) ((unsigned char *)p.idx[d])[o] = (unsigned char)off[d];
+        else ((long long *)p.idx[d])[o] = off[d];
+    }
+}
 
 __global__ void __launch_bounds__(kCorrThreads, 1)
 corr4d_tc_kernel(const CorrArgs p) {
@@ -139,6 +220,12 @@ corr4d_tc_kernel(const CorrArgs p) {
         for (int c0 = 0; c0 < n_cols; c0 += 16) {
             float v[16];
             tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+            if (p.pool) {        // whole warp stays converged: the quad butterfly needs all four lanes
+                const int t0p = nt * kCorrBN + c0;
+                if (p.out_f16) corr_pool_chunk<__half>(p, v, a, t0p, lane);
+                else corr_pool_chunk<float>(p, v, a, t0p, lane);
+                continue;
+            }
             if (a >= p.nA) continue;
             const int t0 = nt * kCorrBN + c0;
             if (t0 >= p.nB) continue;
@@ -192,21 +279,28 @@ size_t corr4d_tc_scratch_bytes(int B, int C, int nA, int nB) {
     return corr_align((size_t)B * kblocks * pad128(nA) * kCorrKB * 2) + corr_align((size_t)B * kblocks * pad128(nB) * kCorrKB * 2) + 256;
 }
 
+struct CorrPool {
+    int wA, wB, idx_bytes;       // widths of the two feature maps (0 = no pooling)
+    void *idx[4];
+};
+
 template <typename T>
 static int corr_tc_run(const void *fa, const void *fb, void *out, void *scratch, int B, int C, int nA, int nB, int relu_l2norm,
-                       int l2norm_inputs, cudaStream_t st) {
+                       int l2norm_inputs, cudaStream_t st, CorrPool pool = CorrPool{}) {
     const int kblocks = (C + kCorrKB - 1) / kCorrKB;
     const int npadA = pad128(nA), npadB = pad128(nB);
     NC_CHECK(B <= 65535, "corr4d(tc): batch too large");
     __half *pa = (__half *)scratch;
     __half *pb = (__half *)((uint8_t *)scratch + corr_align((size_t)B * kblocks * npadA * kCorrKB * 2));
-    corr_pack_kernel<T><<<dim3((npadA / 8 + 255) / 256, 64, B), 256, 0, st>>>((const T *)fa, pa, C, nA, npadA, kblocks, l2norm_inputs);
+    corr_pack_kernel<T><<<dim3((npadA / 8 + 255) / 256, 64, B), 256, 0, st>>>((const T *)fa, pa, C, nA, npadA, kblocks, l2norm_inputs, pool.wA);
     NC_LAUNCH_OK("corr_pack_kernel(A)");
-    corr_pack_kernel<T><<<dim3((npadB / 8 + 255) / 256, 64, B), 256, 0, st>>>((const T *)fb, pb, C, nB, npadB, kblocks, l2norm_inputs);
+    corr_pack_kernel<T><<<dim3((npadB / 8 + 255) / 256, 64, B), 256, 0, st>>>((const T *)fb, pb, C, nB, npadB, kblocks, l2norm_inputs, pool.wB);
     NC_LAUNCH_OK("corr_pack_kernel(B)");
     CorrArgs a{};
     a.pa = pa; a.pb = pb; a.out = out; a.nA = nA; a.nB = nB; a.npadA = npadA; a.npadB = npadB; a.kblocks = kblocks;
     a.relu_l2norm = relu_l2norm; a.out_f16 = sizeof(T) == 2;
+    a.pool = pool.wA > 0; a.idx_bytes = pool.idx_bytes;
+    for (int d = 0; d < 4; ++d) a.idx[d] = pool.idx[d];
     // D = f32, A = B = f16, both MN-major, M = 128; N is patched per tile
     a.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(kCorrBN >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
     const size_t smem = (size_t)kCorrStages * (kCorrBM + kCorrBN) / 8 * kCorrKB * 16;
@@ -223,6 +317,16 @@ int corr4d_tc_fwd(const void *fa, const void *fb, void *out, void *scratch, int 
                   int relu_l2norm, int l2norm_inputs, cudaStream_t st) {
     if (dtype == NCNET_F32) return corr_tc_run<float>(fa, fb, out, scratch, B, C, nA, nB, relu_l2norm, l2norm_inputs, st);
     return corr_tc_run<__half>(fa, fb, out, scratch, B, C, nA, nB, relu_l2norm, l2norm_inputs, st);
+}
+
+int corr4d_pool_tc_fwd(const void *fa, const void *fb, void *value, void *const idx[4], void *scratch, int C, int hA, int wA,
+                       int hB, int wB, int idx_bytes, int dtype, int relu_l2norm, int l2norm_inputs, cudaStream_t st) {
+    CorrPool pool{};
+    pool.wA = wA; pool.wB = wB; pool.idx_bytes = idx_bytes;
+    for (int d = 0; d < 4; ++d) pool.idx[d] = idx[d];
+    if (dtype == NCNET_F32)
+        return corr_tc_run<float>(fa, fb, value, scratch, 1, C, hA * wA, hB * wB, relu_l2norm, l2norm_inputs, st, pool);
+    return corr_tc_run<__half>(fa, fb, value, scratch, 1, C, hA * wA, hB * wB, relu_l2norm, l2norm_inputs, st, pool);
 }
 
 }  // namespace ncnet

@@ -140,6 +140,38 @@ def feature_correlation(fa: torch.Tensor, fb: torch.Tensor, shape: str = "4D", n
     return m.reshape(b, ha * wa, hb, wb)
 
 
+def feature_correlation_pooled(fa: torch.Tensor, fb: torch.Tensor, k_size: int = 2, normalization: bool = False,
+                               l2norm_inputs: bool = False, index_dtype: torch.dtype = torch.int64):
+    """``maxpool4d(FeatureCorrelation('4D', normalization)(fa, fb), k_size)`` (reference lib/model.py:269-272) in one
+    tensor-core kernel that never writes the un-pooled volume.  Inference only (no gradient), batch 1, k_size 2, even
+    feature-map sides.  ``l2norm_inputs``: fa / fb are un-normalised trunk outputs and featureL2Norm
+    (lib/model.py:85-86) is applied while the operands are packed.  Returns (value, max_i, max_j, max_k, max_l)."""
+    _need_cuda(fa, fb)
+    if fa.dtype != fb.dtype:
+        raise TypeError("feature_correlation_pooled: dtype mismatch")
+    b, c, ha, wa = fa.shape
+    _, _, hb, wb = fb.shape
+    if b != 1:
+        raise RuntimeError("feature_correlation_pooled: batch size must be 1 (maxpool4d is batch-1 in the reference)")
+    fa, fb = fa.detach().contiguous(), fb.detach().contiguous()
+    shp = (1, 1, ha // 2, wa // 2, hb // 2, wb // 2)
+    val = torch.empty(shp, device=fa.device, dtype=fa.dtype)
+    idx = [torch.empty(shp, device=fa.device, dtype=index_dtype) for _ in range(4)]
+    L = _cabi.lib()
+    scratch = torch.empty(L.ncnet_corr4d_tc_scratch_bytes(1, c, ha * wa, hb * wb), device=fa.device, dtype=torch.uint8)
+    with torch.cuda.device(fa.device):
+        _cabi.check(L.ncnet_corr4d_pool_fwd_tc(_ptr(fa), _ptr(fb), _ptr(val), *[_ptr(t) for t in idx], _ptr(scratch), c, ha, wa,
+                                               hb, wb, int(k_size), {torch.int64: 8, torch.uint8: 1}[index_dtype], _dt(fa),
+                                               int(normalization), int(l2norm_inputs), _stream()), "corr4d_pool_fwd_tc")
+    _count(3)
+    return (val, idx[0], idx[1], idx[2], idx[3])
+
+
+def can_fuse_correlation_pool(fa: torch.Tensor, fb: torch.Tensor, k_size: int) -> bool:
+    return (k_size == 2 and fa.shape[0] == 1 and default_conv_mode() == CONV_TC16 and all(s % 2 == 0 for s in (*fa.shape[2:], *fb.shape[2:]))
+            and not (torch.is_grad_enabled() and (fa.requires_grad or fb.requires_grad)))
+
+
 # ------------------------------------------------------------------------------------------- #
 # MutualMatching
 # ------------------------------------------------------------------------------------------- #

@@ -199,11 +199,19 @@ class ImMatchNet(nn.Module):
     def match_features(self, feature_A, feature_B):
         """The hot path: correlation -> [maxpool4d] -> MutualMatching -> NeighConsensus ->
         MutualMatching (reference lib/model.py:269-282)."""
-        corr4d = self.FeatureCorrelation(feature_A, feature_B)
         delta4d = None
-        if self.relocalization_k_size > 1:
-            corr4d, max_i, max_j, max_k, max_l = maxpool4d(corr4d, k_size=self.relocalization_k_size)
+        fc = self.FeatureCorrelation
+        if (self.relocalization_k_size > 1 and fc.shape == '4D'
+                and F_.can_fuse_correlation_pool(feature_A, feature_B, self.relocalization_k_size)):
+            # correlation and relocalisation pooling in one kernel: the un-pooled volume is never written
+            corr4d, max_i, max_j, max_k, max_l = F_.feature_correlation_pooled(
+                feature_A, feature_B, self.relocalization_k_size, normalization=fc.normalization)
             delta4d = (max_i, max_j, max_k, max_l)
+        else:
+            corr4d = fc(feature_A, feature_B)
+            if self.relocalization_k_size > 1:
+                corr4d, max_i, max_j, max_k, max_l = maxpool4d(corr4d, k_size=self.relocalization_k_size)
+                delta4d = (max_i, max_j, max_k, max_l)
         corr4d = MutualMatching(corr4d)
         nc = self.NeighConsensus
         if nc.symmetric_mode and nc.channels[-1] == 1:
