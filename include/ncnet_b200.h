@@ -171,13 +171,15 @@ int ncnet_conv4d_dgrad(const void *grad_y, const float *weight, const void *y_pr
                        int w_layout, int symmetric, int shared_input, int gy_dtype, int mask_dtype,
                        int gx_dtype, int mode, void *stream);
 /* gradient wrt weight (same layout as `weight`, fp32, OVERWRITTEN) and bias (fp32 [Cout], may be
- * NULL).  With symmetric=1 the two groups' contributions are folded back into the one weight. */
+ * NULL).  With symmetric=1 the two groups' contributions are folded back into the one weight.
+ * out_scale (device float, may be NULL): both results are multiplied by *out_scale -- the 1/S of
+ * ncnet_grad_scale when grad_y carries a scaled gradient. */
 size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
                                         int symmetric, int mode);
 int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, float *grad_bias,
                        void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
                        int w_layout, int symmetric, int shared_input, int x_dtype, int gy_dtype, int mode,
-                       void *stream);
+                       const float *out_scale, void *stream);
 
 /* 1 when a layer with Cin -> Cout channels per group (kernel k, last two volume dims d3,d4) runs
  * entirely on the tensor-core kernels in TC16 mode (forward, dgrad and wgrad), i.e. can take and
@@ -196,9 +198,16 @@ int ncnet_cb16_unpack(const void *cb16, void *planar, int nblk, int C, int d1, i
                       int dtype, void *stream);
 
 /* ReLU backward on the last layer's two branch outputs (lib/model.py:137-138,147):
- * gz[b,g,p] = (y[b,g,p] > 0) ? grad[b,p] : 0 for g < G.   y,gz: [B,G,n]; grad: [B,n]. */
+ * gz[b,g,p] = (y[b,g,p] > 0) ? scale * grad[b,p] : 0 for g < G.   y,gz: [B,G,n]; grad: [B,n];
+ * scale: device float or NULL (= 1). */
 int ncnet_relu_mask_bcast(const void *y, const void *grad, void *gz, int B, int G, long long n,
-                          int dtype, void *stream);
+                          int dtype, const float *scale, void *stream);
+/* Power-of-two loss scale for a backward pass that stores gradients in fp16 (TC16 mode; no counterpart in the
+ * reference, whose backward is fp32).  grad: n values; scale3: 3 device floats, on return {S, 1/S, max|grad|} with
+ * S = 2^e such that max|grad|*S is in [8,16) (S = 1 for an all-zero gradient).  Scaling by a power of two is exact
+ * and the backward pass is linear in grad, so un-scaling the weight gradients with 1/S gives the same function; the
+ * fp16 roundings in between then act on values around 1 instead of on ~1e-7 values in fp16's subnormal range. */
+int ncnet_grad_scale(const void *grad, long long n, int dtype, float *scale3, void *stream);
 
 /* maxpool4d -- lib/model.py:177-191.  x: [H1,H2,H3,H4] (batch 1, channel 0), each divisible by k.
  * value: [H1/k,...] same dtype; offsets: four tensors of that shape, window-relative arg-max

@@ -43,13 +43,14 @@ SIGNATURES = {
     "ncnet_conv4d_fwd": (_i, [_p, _p, _p, _p, _p] + [_i] * 15 + [_p]),
     "ncnet_conv4d_dgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 15 + [_p]),
     "ncnet_conv4d_wgrad_scratch_bytes": (_sz, [_i] * 10),
-    "ncnet_conv4d_wgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 14 + [_p]),
+    "ncnet_conv4d_wgrad": (_i, [_p, _p, _p, _p, _p] + [_i] * 14 + [_p, _p]),
     "ncnet_conv4d_tc_supported": (_i, [_i] * 5),
     "ncnet_conv4d_tc_fwd_supported": (_i, [_i] * 5),
     "ncnet_cb16_bytes": (_sz, [_i] * 6),
     "ncnet_cb16_pack": (_i, [_p, _p] + [_i] * 8 + [_p]),
     "ncnet_cb16_unpack": (_i, [_p, _p] + [_i] * 8 + [_p]),
-    "ncnet_relu_mask_bcast": (_i, [_p, _p, _p, _i, _i, _ll, _i, _p]),
+    "ncnet_relu_mask_bcast": (_i, [_p, _p, _p, _i, _i, _ll, _i, _p, _p]),
+    "ncnet_grad_scale": (_i, [_p, _ll, _i, _p, _p]),
     "ncnet_maxpool4d_fwd": (_i, [_p] * 6 + [_i] * 7 + [_p]),
     "ncnet_matches_unique_scratch_bytes": (_sz, [_i]),
     "ncnet_matches_sort_unique": (_i, [_p] * 5 + [_i] + [_p] * 5 + [_i] * 5 + [_p] * 4),

@@ -98,20 +98,20 @@ extern "C" size_t ncnet_conv4d_wgrad_scratch_bytes(int B, int Cin, int Cout, int
 extern "C" int ncnet_conv4d_wgrad(const void *x, const void *grad_y, float *grad_weight, float *grad_bias,
                                   void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k,
                                   int w_layout, int symmetric, int shared_input, int x_dtype, int gy_dtype, int mode,
-                                  void *stream) {
+                                  const float *out_scale, void *stream) {
     NC_CHECK(x && grad_y && grad_weight && scratch, "conv4d_wgrad: null pointer");
     if (check_conv("conv4d_wgrad", B, Cin, Cout, d1, d2, d3, d4, k, w_layout, NCNET_F32, mode)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
     float *bias_part = (float *)scratch;
     scratch = (uint8_t *)scratch + bias_partial_bytes(B, symmetric ? 2 : 1, Cout);
     if (mode == NCNET_CONV_TC16) {
-        const int rc = conv4d_tc_wgrad(x, x_dtype, grad_y, gy_dtype, grad_weight, grad_bias, scratch, bias_part, B, Cin, Cout,
+        const int rc = conv4d_tc_wgrad(x, x_dtype, grad_y, gy_dtype, grad_weight, grad_bias, scratch, bias_part, out_scale, B, Cin, Cout,
                                        d1, d2, d3, d4, k, w_layout, symmetric, shared_input, st);
         if (rc != 2) return rc;      // 2: outside the tensor-core kernel's envelope -> CUDA-core kernel
     }
     NC_CHECK(planar(x_dtype) && x_dtype == gy_dtype,
              "conv4d_wgrad: this shape runs on the CUDA-core kernel, which needs planar tensors of one dtype");
-    return conv4d_fp32_wgrad(x, grad_y, grad_weight, grad_bias, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k,
+    return conv4d_fp32_wgrad(x, grad_y, grad_weight, grad_bias, scratch, bias_part, out_scale, B, Cin, Cout, d1, d2, d3, d4, k,
                              w_layout, symmetric, shared_input, x_dtype, st);
 }
 
@@ -146,10 +146,16 @@ extern "C" int ncnet_cb16_unpack(const void *cb16, void *planar_t, int nblk, int
     return cb16_unpack(cb16, planar_t, dtype, nblk, C, d1, d2, d3, d4, k, (cudaStream_t)stream);
 }
 
+extern "C" int ncnet_grad_scale(const void *grad, long long n, int dtype, float *scale3, void *stream) {
+    NC_CHECK(grad && scale3 && n > 0, "grad_scale: bad arguments");
+    NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "grad_scale: unsupported dtype %d", dtype);
+    return grad_scale_pow2(grad, n, dtype, scale3, (cudaStream_t)stream);
+}
+
 extern "C" int ncnet_relu_mask_bcast(const void *y, const void *grad, void *gz, int B, int G, long long n, int dtype,
-                                     void *stream) {
+                                     const float *scale, void *stream) {
     NC_CHECK(y && grad && gz, "relu_mask_bcast: null pointer");
     NC_CHECK(B > 0 && B <= 65535 && G > 0 && n > 0, "relu_mask_bcast: bad shape");
     NC_CHECK(dtype == NCNET_F32 || dtype == NCNET_F16, "relu_mask_bcast: unsupported dtype %d", dtype);
-    return relu_mask_bcast(y, grad, gz, B, G, n, dtype, (cudaStream_t)stream);
+    return relu_mask_bcast(y, grad, gz, B, G, n, dtype, scale, (cudaStream_t)stream);
 }

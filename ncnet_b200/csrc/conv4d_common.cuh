@@ -49,7 +49,7 @@ int conv4d_fp32_dgrad(const void *gy, const float *w, const void *mask, void *gx
                       int dtype, cudaStream_t st);
 size_t conv4d_fp32_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric);
 // bias_part: bias_partial_bytes(...) bytes for the two-stage (atomic-free, run-to-run reproducible) bias-gradient sum
-int conv4d_fp32_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, int B, int Cin,
+int conv4d_fp32_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, const float *out_scale, int B, int Cin,
                       int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
                       int dtype, cudaStream_t st);
 
@@ -61,7 +61,10 @@ inline size_t bias_partial_bytes(int B, int G, int Cout) {
     const size_t rows = (size_t)B * G * (Cout > 2 ? Cout : 2);        // channel rows of either back end
     return (((size_t)kBiasTargetCtas + rows) * 8 * sizeof(float) + 255) & ~(size_t)255;
 }
-int bias_reduce(const float *part, float *db, int Cout, int entries, int W, cudaStream_t st);
-int relu_mask_bcast(const void *y, const void *g, void *gz, int B, int G, long long n, int dtype, cudaStream_t st);
+// out_scale (device, may be null): the reduced sums are multiplied by *out_scale (gradient un-scaling)
+int bias_reduce(const float *part, float *db, int Cout, int entries, int W, const float *out_scale, cudaStream_t st);
+int relu_mask_bcast(const void *y, const void *g, void *gz, int B, int G, long long n, int dtype, const float *scale,
+                    cudaStream_t st);
+int grad_scale_pow2(const void *g, long long n, int dtype, float *scale3, cudaStream_t st);
 
 }  // namespace ncnet

@@ -40,7 +40,7 @@ __global__ void pack_weights_kernel(const float *__restrict__ w, float *__restri
 
 // wgrad: partial sums part[S][G][Cin][k][k][k*k][CO16*nct] -> reference layout, both groups folded
 __global__ void unpack_wgrad_kernel(const float *__restrict__ part, float *__restrict__ gw, int S, int G, int Cin,
-                                    int Cout, int k, int cop, int w_layout) {
+                                    int Cout, int k, int cop, int w_layout, const float *__restrict__ out_scale) {
     const int total = Cout * Cin * k * k * k * k;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
@@ -61,7 +61,7 @@ __global__ void unpack_wgrad_kernel(const float *__restrict__ part, float *__res
             acc += p1[(((((size_t)c * k + c3) * k + d4) * k + a) * k + b2) * cop + o];
         }
     }
-    gw[idx] = acc;
+    gw[idx] = out_scale ? acc * __ldg(out_scale) : acc;
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -435,28 +435,30 @@ bias_grad_kernel(const T *__restrict__ gy, float *__restrict__ db, int Cout, int
 }
 
 // db[o] = sum over entries of part[e*W + o], one warp per channel, fixed order
-__global__ void bias_reduce_kernel(const float *__restrict__ part, float *__restrict__ db, int Cout, int entries, int W) {
+__global__ void bias_reduce_kernel(const float *__restrict__ part, float *__restrict__ db, int Cout, int entries, int W,
+                                   const float *__restrict__ out_scale) {
     const int o = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (o >= Cout) return;
     float t = 0.f;
     for (int e = lane; e < entries; e += 32) t += part[(size_t)e * W + o];
     t = warp_sum(t);
-    if (lane == 0) db[o] = t;
+    if (lane == 0) db[o] = out_scale ? t * __ldg(out_scale) : t;
 }
 
-int bias_reduce(const float *part, float *db, int Cout, int entries, int W, cudaStream_t st) {
+int bias_reduce(const float *part, float *db, int Cout, int entries, int W, const float *out_scale, cudaStream_t st) {
     NC_CHECK(Cout <= 32, "bias gradient: more than 32 output channels");
-    bias_reduce_kernel<<<1, 32 * Cout, 0, st>>>(part, db, Cout, entries, W);
+    bias_reduce_kernel<<<1, 32 * Cout, 0, st>>>(part, db, Cout, entries, W, out_scale);
     NC_LAUNCH_OK("bias_reduce_kernel");
     return 0;
 }
 
 template <typename T>
 __global__ void relu_mask_bcast_kernel(const T *__restrict__ y, const T *__restrict__ g, T *__restrict__ gz, int G,
-                                       long long n) {
+                                       long long n, const float *__restrict__ scale) {
     const int b = blockIdx.y;
+    const float sc = scale ? __ldg(scale) : 1.f;
     for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
-        const float gv = ldf(g + (size_t)b * n + e);
+        const float gv = ldf(g + (size_t)b * n + e) * sc;
         for (int q = 0; q < G; ++q) {
             const size_t off = ((size_t)b * G + q) * n + e;
             stf(gz + off, ldf(y + off) > 0.f ? gv : 0.f);
@@ -614,10 +616,10 @@ static int launch_wgrad(WgradArgs a, const WgradPlan &w, cudaStream_t st) {
 }
 
 // shared tail of both wgrad back ends: slice partials -> reference layout (+ bias gradient)
-int wgrad_finish(const float *part, float *gw, float *gb, float *bias_part, const void *gy, int S, int G, int B, int Cin,
+int wgrad_finish(const float *part, float *gw, float *gb, float *bias_part, const float *out_scale, const void *gy, int S, int G, int B, int Cin,
                  int Cout, int k, int cop, int w_layout, size_t vol, int dtype, cudaStream_t st) {
     const int total = Cout * Cin * k * k * k * k;
-    unpack_wgrad_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, gw, S, G, Cin, Cout, k, cop, w_layout);
+    unpack_wgrad_kernel<<<(total + 255) / 256, 256, 0, st>>>(part, gw, S, G, Cin, Cout, k, cop, w_layout, out_scale);
     NC_LAUNCH_OK("unpack_wgrad_kernel");
     if (gb) {
         // enough blocks to fill the GPU at small batches (a few channels x 6 chunks left 140 SMs idle)
@@ -631,13 +633,13 @@ int wgrad_finish(const float *part, float *gw, float *gb, float *bias_part, cons
         else
             bias_grad_kernel<__half><<<dim3(chunks, B * G * Cout), 256, 0, st>>>((const __half *)gy, bias_part, Cout, G, vol, chunks);
         NC_LAUNCH_OK("bias_grad_kernel");
-        return bias_reduce(bias_part, gb, Cout, chunks * B * G, Cout, st);
+        return bias_reduce(bias_part, gb, Cout, chunks * B * G, Cout, out_scale, st);
     }
     return 0;
 }
 
 template <typename T>
-static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, int B, int Cin,
+static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, const float *out_scale, int B, int Cin,
                      int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
                      cudaStream_t st) {
     const int G = symmetric ? 2 : 1;
@@ -654,26 +656,76 @@ static int run_wgrad(const void *x, const void *gy, float *gw, float *gb, void *
     int rc = (k == 3) ? launch_wgrad<3, T>(a, w, st) : (k == 5 ? launch_wgrad<5, T>(a, w, st)
                                                               : fail("conv4d_wgrad: kernel size %d not supported", k));
     if (rc) return rc;
-    return wgrad_finish((const float *)scratch, gw, gb, bias_part, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout,
+    return wgrad_finish((const float *)scratch, gw, gb, bias_part, out_scale, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout,
                         (size_t)d1 * d2 * d3 * d4, sizeof(T) == 4 ? NCNET_F32 : NCNET_F16, st);
 }
 
-int conv4d_fp32_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, int B, int Cin,
+int conv4d_fp32_wgrad(const void *x, const void *gy, float *gw, float *gb, void *scratch, float *bias_part, const float *out_scale, int B, int Cin,
                       int Cout, int d1, int d2, int d3, int d4, int k, int w_layout, int symmetric, int shared_input,
                       int dtype, cudaStream_t st) {
     if (dtype == NCNET_F32)
-        return run_wgrad<float>(x, gy, gw, gb, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+        return run_wgrad<float>(x, gy, gw, gb, scratch, bias_part, out_scale, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
                                 shared_input, st);
-    return run_wgrad<__half>(x, gy, gw, gb, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+    return run_wgrad<__half>(x, gy, gw, gb, scratch, bias_part, out_scale, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
                              shared_input, st);
 }
 
-int relu_mask_bcast(const void *y, const void *g, void *gz, int B, int G, long long n, int dtype, cudaStream_t st) {
+// Power-of-two gradient scale for the fp16 backward pass.  scale3 = {S, 1/S, scratch}: S = 2^e with max|g| * S in
+// [8, 16), so the largest gradient sits 12 binades below the fp16 overflow threshold and ordinary ones far above its
+// subnormal range (gradients of a mean over ~10^6 cells are ~1e-7 and would otherwise be quantised to multiples of
+// 6e-8).  Scaling by a power of two is exact and the backward pass is linear in g, so (1/S) * backward(S * g) is the
+// same function of g; only the fp16 rounding inside moves to where it is harmless.
+template <typename T>
+__global__ void __launch_bounds__(256)
+grad_absmax_kernel(const T *__restrict__ g, long long n, float *__restrict__ scale3) {
+    float m = 0.f;
+    for (long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (long long)gridDim.x * blockDim.x) {
+        const float v = fabsf(ldf(g + e));
+        m = (v == v && v <= 3.0e38f) ? fmaxf(m, v) : m;                 // ignore NaN / inf
+    }
+    m = warp_max(m);
+    __shared__ float sm[8];
+    if ((threadIdx.x & 31) == 0) sm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int w = 1; w < 8; ++w) m = fmaxf(m, sm[w]);
+        atomicMax(reinterpret_cast<unsigned *>(scale3 + 2), __float_as_uint(m));   // non-negative floats order as integers
+    }
+}
+
+__global__ void grad_scale_finish_kernel(float *__restrict__ scale3) {
+    const float m = scale3[2];
+    int e = 0;
+    float s = 1.f;
+    if (m > 0.f) {
+        frexpf(m, &e);                       // m = f * 2^e, f in [0.5, 1)
+        int k = 4 - e;                       // max * 2^k in [8, 16)
+        k = k > 100 ? 100 : (k < -100 ? -100 : k);
+        s = ldexpf(1.f, k);
+    }
+    scale3[0] = s;
+    scale3[1] = 1.f / s;
+}
+
+int grad_scale_pow2(const void *g, long long n, int dtype, float *scale3, cudaStream_t st) {
+    cudaError_t e = cudaMemsetAsync(scale3, 0, 3 * sizeof(float), st);
+    NC_CHECK(e == cudaSuccess, "grad_scale: memset: %s", cudaGetErrorString(e));
+    const int blocks = (int)((n + 2047) / 2048 < 4 * kNumSMs ? (n + 2047) / 2048 : 4 * kNumSMs);
+    if (dtype == NCNET_F32) grad_absmax_kernel<float><<<blocks, 256, 0, st>>>((const float *)g, n, scale3);
+    else grad_absmax_kernel<__half><<<blocks, 256, 0, st>>>((const __half *)g, n, scale3);
+    NC_LAUNCH_OK("grad_absmax_kernel");
+    grad_scale_finish_kernel<<<1, 1, 0, st>>>(scale3);
+    NC_LAUNCH_OK("grad_scale_finish_kernel");
+    return 0;
+}
+
+int relu_mask_bcast(const void *y, const void *g, void *gz, int B, int G, long long n, int dtype, const float *scale,
+                    cudaStream_t st) {
     int bx = (int)((n + 255) / 256 < 2048 ? (n + 255) / 256 : 2048);
     if (dtype == NCNET_F32)
-        relu_mask_bcast_kernel<float><<<dim3(bx, B), 256, 0, st>>>((const float *)y, (const float *)g, (float *)gz, G, n);
+        relu_mask_bcast_kernel<float><<<dim3(bx, B), 256, 0, st>>>((const float *)y, (const float *)g, (float *)gz, G, n, scale);
     else
-        relu_mask_bcast_kernel<__half><<<dim3(bx, B), 256, 0, st>>>((const __half *)y, (const __half *)g, (__half *)gz, G, n);
+        relu_mask_bcast_kernel<__half><<<dim3(bx, B), 256, 0, st>>>((const __half *)y, (const __half *)g, (__half *)gz, G, n, scale);
     NC_LAUNCH_OK("relu_mask_bcast_kernel");
     return 0;
 }

@@ -21,6 +21,6 @@ int conv4d_tc_dgrad(const void *gy, int gy_dtype, const float *w, const void *ma
                     int symmetric, int shared_input, cudaStream_t st);
 size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric);
 int conv4d_tc_wgrad(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch,
-                    float *bias_part, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
+                    float *bias_part, const float *out_scale, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
                     int symmetric, int shared_input, cudaStream_t st);
 }  // namespace ncnet

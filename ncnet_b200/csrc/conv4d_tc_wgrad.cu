@@ -258,7 +258,7 @@ conv4d_tc_wgrad_kernel(const WgArgs p) {
 }
 
 // conv4d_fp32.cu: reduces the per-slice partial sums into the reference layout and sums the bias gradient
-int wgrad_finish(const float *part, float *gw, float *gb, float *bias_part, const void *gy, int S, int G, int B, int Cin,
+int wgrad_finish(const float *part, float *gw, float *gb, float *bias_part, const float *out_scale, const void *gy, int S, int G, int B, int Cin,
                  int Cout, int k, int cop, int w_layout, size_t vol, int dtype, cudaStream_t st);
 
 // bias gradient from a CB16 grad_y, stage 1: db[(chunk*nblk + blk)*16 + o] = partial sum over the chunk's positions
@@ -401,7 +401,7 @@ size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, i
 
 // returns 2 when the shape/layout is outside the tensor-core kernel's envelope
 static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch,
-                  float *bias_part, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
+                  float *bias_part, const float *out_scale, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
                   int symmetric, int shared_input, cudaStream_t st) {
     const int G = symmetric ? 2 : 1;
     const int GxA = (G == 2 && !shared_input) ? 2 : 1;
@@ -493,8 +493,8 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
         NC_LAUNCH_OK("conv4d_tc_wgrad_kernel");
     }
     if (gy_dtype != NCNET_CB16)
-        return wgrad_finish(part, gw, gb, bias_part, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, gy_dtype, st);
-    int rc = wgrad_finish(part, gw, nullptr, nullptr, nullptr, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, NCNET_F32, st);
+        return wgrad_finish(part, gw, gb, bias_part, out_scale, gy, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, gy_dtype, st);
+    int rc = wgrad_finish(part, gw, nullptr, nullptr, out_scale, nullptr, w.S, G, B, Cin, Cout, k, w.cop, w_layout, vol, NCNET_F32, st);
     if (rc || !gb) return rc;
     const int pad = k / 2;
     const size_t npad = (size_t)d1 * d2 * (d3 + 2 * pad) * (d4 + 2 * pad);
@@ -505,13 +505,13 @@ static int wg_run(const void *x, int x_dtype, const void *gy, int gy_dtype, floa
     NC_CHECK(B * G * 2 <= 65535, "conv4d_wgrad(tc): too many blocks for the bias grid");
     cb16_bias_grad_kernel<<<dim3(chunks, B * G * 2), 256, 0, st>>>(gbk, bias_part, Cout, npad, chunks);
     NC_LAUNCH_OK("cb16_bias_grad_kernel");
-    return bias_reduce(bias_part, gb, Cout, chunks * B * G, 16, st);
+    return bias_reduce(bias_part, gb, Cout, chunks * B * G, 16, out_scale, st);
 }
 
 int conv4d_tc_wgrad(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch,
-                    float *bias_part, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
+                    float *bias_part, const float *out_scale, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
                     int symmetric, int shared_input, cudaStream_t st) {
-    return wg_run(x, x_dtype, gy, gy_dtype, gw, gb, scratch, bias_part, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
+    return wg_run(x, x_dtype, gy, gy_dtype, gw, gb, scratch, bias_part, out_scale, B, Cin, Cout, d1, d2, d3, d4, k, w_layout, symmetric,
                   shared_input, st);
 }
 

@@ -29,9 +29,52 @@ __device__ __forceinline__ float key_val_hi(const unsigned long long *keys, size
     return ord2f(reinterpret_cast<const uint32_t *>(keys)[2 * i + 1]);
 }
 
+// VEC elements of T with one load of VEC*sizeof(T) bytes (4, 8 or 16); the pointer is aligned to that size
+template <typename T, int VEC>
+__device__ __forceinline__ void load_vec(const T *p, float (&out)[VEC]) {
+    constexpr int BYTES = VEC * (int)sizeof(T);
+    static_assert(BYTES == 2 || BYTES == 4 || BYTES == 8 || BYTES == 16, "load_vec: 2, 4, 8 or 16 bytes");
+    if constexpr (BYTES == 2) {
+        out[0] = ldf(p);
+    } else {
+        union { uint4 q; uint2 d; unsigned w; T e[VEC]; } u;
+        if constexpr (BYTES == 16) u.q = __ldg(reinterpret_cast<const uint4 *>(p));
+        else if constexpr (BYTES == 8) u.d = __ldg(reinterpret_cast<const uint2 *>(p));
+        else u.w = __ldg(reinterpret_cast<const unsigned *>(p));
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            if constexpr (sizeof(T) == 4) out[i] = u.e[i]; else out[i] = __half2float(u.e[i]);
+        }
+    }
+}
+template <typename T, int VEC>
+__device__ __forceinline__ void store_vec(T *p, const float (&v)[VEC]) {
+    constexpr int BYTES = VEC * (int)sizeof(T);
+    if constexpr (BYTES == 2) {
+        stf(p, v[0]);
+    } else {
+        union { uint4 q; uint2 d; unsigned w; T e[VEC]; } u;
+#pragma unroll
+        for (int i = 0; i < VEC; ++i) {
+            if constexpr (sizeof(T) == 4) u.e[i] = v[i]; else u.e[i] = __float2half_rn(v[i]);
+        }
+        if constexpr (BYTES == 16) *reinterpret_cast<uint4 *>(p) = u.q;
+        else if constexpr (BYTES == 8) *reinterpret_cast<uint2 *>(p) = u.d;
+        else *reinterpret_cast<unsigned *>(p) = u.w;
+    }
+}
+
+// widest vector (in elements) such that every row start and the base pointers stay aligned to it
+template <typename T>
+static int mm_vec_for(int nB, const void *a, const void *b) {
+    const uintptr_t bits = (uintptr_t)a | (uintptr_t)b | ((uintptr_t)nB * sizeof(T));
+    int bytes = (bits & 15) == 0 ? 16 : ((bits & 7) == 0 ? 8 : ((bits & 3) == 0 ? 4 : (int)sizeof(T)));
+    return bytes / (int)sizeof(T);
+}
+
 // Pass 1.  grid: (col tiles of 512, row strips, B); each warp walks rows warp, warp+8, ... of the strip and keeps,
 // per lane, the running (max, first row) of its 16 columns as plain float/int pairs; keys are packed only for the
-// final atomicMax.  VEC = 2: a lane owns pairs of adjacent columns and loads them as one half2 (fp16, even nB).
+// final atomicMax.  A lane owns 16/VEC groups of VEC adjacent columns and loads each group with one 4/8/16-byte load.
 // All loads of a row are issued before any use (a predicated-off dependent op between them serialised them once).
 template <typename T, int GROUPS, int VEC>
 __global__ void __launch_bounds__(kMMThreads)
@@ -51,39 +94,37 @@ mm_max_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, in
 #pragma unroll
     for (int s = 0; s < kMMSlots; ++s) { cv[s] = -INFINITY; ci[s] = -1; }
     const int ncols = min(kMMColsPerTile, nB - col0);
-    // slot s = (load q, element u): column offset q*32*VEC + lane*VEC + u
+    // slot s = (load q, element u): column offset q*32*VEC + lane*VEC + u.  With VEC > 1 nB is a multiple of VEC, so a
+    // group of VEC columns is either entirely inside the matrix or entirely outside.
     const int row_end = min(row0 + rows_per_block, nA);
     for (int a = row0 + warp; a < row_end; a += kMMThreads / 32) {
         const size_t roff = (size_t)a * nB + col0;
         float v[kMMSlots];
-        if (VEC == 2) {
-            // raw 32-bit loads first (all in flight), conversions afterwards
-            unsigned raw[NL];
-            constexpr unsigned kNegInf2 = 0xFC00FC00u;            // half2(-inf, -inf)
 #pragma unroll
-            for (int q = 0; q < NL; ++q) {
-                const int c = q * 32 * VEC + lane * VEC;
-                raw[q] = (c + 1 < ncols) ? __ldg(reinterpret_cast<const unsigned *>(xb + roff + c)) : kNegInf2;
+        for (int q = 0; q < NL; ++q) {
+            const int c = q * 32 * VEC + lane * VEC;
+            float t[VEC];
+            if (c < ncols) load_vec<T, VEC>(xb + roff + c, t);
+            else {
+#pragma unroll
+                for (int u = 0; u < VEC; ++u) t[u] = -INFINITY;
             }
 #pragma unroll
-            for (int q = 0; q < NL; ++q) {
-                const __half2 h = *reinterpret_cast<const __half2 *>(&raw[q]);
-                v[q * VEC] = __low2float(h); v[q * VEC + VEC - 1] = __high2float(h);
-            }
-        } else {
-#pragma unroll
-            for (int q = 0; q < NL; ++q) {
-                const int c = q * 32 * VEC + lane * VEC;
-                v[q] = c < ncols ? ldf(xb + roff + c) : -INFINITY;
-            }
+            for (int u = 0; u < VEC; ++u) v[q * VEC + u] = t[u];
         }
         if (GROUPS == 2) {                             // second branch, again as one batch of loads
             float w[kMMSlots];
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 const int c = q * 32 * VEC + lane * VEC;
+                float t[VEC];
+                if (c < ncols) load_vec<T, VEC>(xb + mat + roff + c, t);
+                else {
 #pragma unroll
-                for (int u = 0; u < VEC; ++u) w[q * VEC + u] = (c + u < ncols) ? ldf(xb + mat + roff + c + u) : 0.f;
+                    for (int u = 0; u < VEC; ++u) t[u] = 0.f;
+                }
+#pragma unroll
+                for (int u = 0; u < VEC; ++u) w[q * VEC + u] = t[u];
             }
 #pragma unroll
             for (int s = 0; s < kMMSlots; ++s) v[s] = rnd<T>(v[s] + w[s]);
@@ -126,70 +167,62 @@ mm_max_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, in
     }
 }
 
-// Pass 2: y = x * ((x * 1/(rowmax+eps)) * (x * 1/(colmax+eps))).  One thread owns kMMApplyVec adjacent columns and
-// walks kMMApplyRows rows: the column reciprocals are computed once per thread, the row reciprocal once per
-// warp-row (lane 0, broadcast), so the inner loop is a load, four multiplies and a store per element.
+// Pass 2: y = x * ((x * 1/(rowmax+eps)) * (x * 1/(colmax+eps))).  One thread owns VEC adjacent columns (one 4/8/16-byte
+// load and store per row) and walks kMMApplyRows rows: the column reciprocals are computed once per thread, the row
+// reciprocal once per warp-row (lane i, broadcast), so the inner loop is a load, four multiplies and a store per element.
 // x/(max+eps) is evaluated as x * rcp_rn(max+eps) -- one correctly rounded reciprocal per row/column instead of two
 // IEEE divisions per element (which made this pass ALU-bound); the product is within 1 ulp of the true quotient.
+// The blocks run through the volume BACKWARDS (last batch item, last rows first): pass 1 streamed it forwards, so
+// what it read last is what the 126 MB L2 still holds, and this pass starts there.
 constexpr int kMMApplyRows = 16;
 
 template <typename T, int GROUPS, int VEC>
 __global__ void __launch_bounds__(256)
 mm_apply_kernel(const T *__restrict__ x, T *__restrict__ y, const unsigned long long *__restrict__ keys,
                 int nA, int nB) {
-    const int b = blockIdx.z;
+    const int b = gridDim.z - 1 - blockIdx.z;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int c0 = (blockIdx.x * 32 + lane) * VEC;
-    const int a0 = (blockIdx.y * 8 + warp) * kMMApplyRows;
+    const int a0 = ((gridDim.y - 1 - blockIdx.y) * 8 + warp) * kMMApplyRows;
     const size_t mat = (size_t)nA * nB;
     const T *xb = x + (size_t)b * mat * GROUPS;
     T *yb = y + (size_t)b * mat;
     const size_t kb = (size_t)b * (nA + nB);
+    const bool col_ok = c0 < nB;                 // VEC > 1: nB is a multiple of VEC, the whole group is in range
     float crcp[VEC];
 #pragma unroll
     for (int u = 0; u < VEC; ++u)
-        crcp[u] = (c0 + u < nB) ? __frcp_rn(rnd<T>(key_val_hi(keys, kb + nA + c0 + u) + kMMEps)) : 0.f;
+        crcp[u] = col_ok ? __frcp_rn(rnd<T>(key_val_hi(keys, kb + nA + c0 + u) + kMMEps)) : 0.f;
     // row reciprocals of this warp's rows: lane i computes row a0+i, broadcast below
     float my_rrcp = 0.f;
     if (lane < kMMApplyRows && a0 + lane < nA) my_rrcp = __frcp_rn(rnd<T>(key_val_hi(keys, kb + a0 + lane) + kMMEps));
-    if (c0 >= nB) {
-        // keep the warp converged for the shuffles below
+    float v[kMMApplyRows][VEC];
+#pragma unroll
+    for (int r = 0; r < kMMApplyRows; ++r) {       // all row loads in flight before the first use
+        const int a = a0 + r;
+        if (a < nA && col_ok) {
+            load_vec<T, VEC>(xb + (size_t)a * nB + c0, v[r]);
+            if (GROUPS == 2) {
+                float w[VEC];
+                load_vec<T, VEC>(xb + mat + (size_t)a * nB + c0, w);
+#pragma unroll
+                for (int u = 0; u < VEC; ++u) v[r][u] = rnd<T>(v[r][u] + w[u]);
+            }
+        }
     }
 #pragma unroll
     for (int r = 0; r < kMMApplyRows; ++r) {
         const float rrcp = __shfl_sync(0xffffffffu, my_rrcp, r);
         const int a = a0 + r;
-        if (a >= nA || c0 >= nB) continue;
-        const size_t off = (size_t)a * nB + c0;
-        float v[VEC];
-        if (VEC == 2 && sizeof(T) == 2 && c0 + 1 < nB) {           // half2 path (nB even: every row start is 4-byte aligned)
-            const __half2 h = *reinterpret_cast<const __half2 *>(xb + off);
-            v[0] = __low2float(h); v[VEC - 1] = __high2float(h);
-            if (GROUPS == 2) {
-                const __half2 g = *reinterpret_cast<const __half2 *>(xb + mat + off);
-                v[0] = rnd<T>(v[0] + __low2float(g)); v[VEC - 1] = rnd<T>(v[VEC - 1] + __high2float(g));
-            }
-        } else {
-#pragma unroll
-            for (int u = 0; u < VEC; ++u) {
-                v[u] = (c0 + u < nB) ? ldf(xb + off + u) : 0.f;
-                if (GROUPS == 2 && c0 + u < nB) v[u] = rnd<T>(v[u] + ldf(xb + mat + off + u));
-            }
-        }
+        if (a >= nA || !col_ok) continue;
         float res[VEC];
 #pragma unroll
         for (int u = 0; u < VEC; ++u) {
-            const float qa = rnd<T>(v[u] * rrcp);      // x / (max over B + eps)   (corr4d_A)
-            const float qb = rnd<T>(v[u] * crcp[u]);   // x / (max over A + eps)   (corr4d_B)
-            res[u] = v[u] * rnd<T>(qa * qb);
+            const float qa = rnd<T>(v[r][u] * rrcp);      // x / (max over B + eps)   (corr4d_A)
+            const float qb = rnd<T>(v[r][u] * crcp[u]);   // x / (max over A + eps)   (corr4d_B)
+            res[u] = v[r][u] * rnd<T>(qa * qb);
         }
-        if (VEC == 2 && sizeof(T) == 2 && c0 + 1 < nB) {
-            *reinterpret_cast<__half2 *>(yb + off) = __floats2half2_rn(res[0], res[VEC - 1]);
-        } else {
-#pragma unroll
-            for (int u = 0; u < VEC; ++u)
-                if (c0 + u < nB) stf(yb + off + u, res[u]);
-        }
+        store_vec<T, VEC>(yb + (size_t)a * nB + c0, res);
     }
 }
 
@@ -355,22 +388,34 @@ static int mm_fwd_parts(const void *x, void *y, uint64_t *keys, int B, int nA, i
     NC_CHECK(e == cudaSuccess, "mutual_matching: memset keys: %s", cudaGetErrorString(e));
     const int rpb = rows_per_block_for(B, nA, nB, kMMColsPerTile);
     dim3 g1((nB + kMMColsPerTile - 1) / kMMColsPerTile, (nA + rpb - 1) / rpb, B);
-    const bool v2 = sizeof(T) == 2 && nB % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 3) == 0;
+    const int vec1 = mm_vec_for<T>(nB, x, x);
 #define NC_MM_MAX(G, V) mm_max_kernel<T, G, V><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb)
-    if (groups == 2) { if (v2) NC_MM_MAX(2, 2); else NC_MM_MAX(2, 1); }
-    else             { if (v2) NC_MM_MAX(1, 2); else NC_MM_MAX(1, 1); }
+#define NC_MM_MAX_V(G)                                                                         \
+    switch (vec1) {                                                                            \
+        case 8: if constexpr (sizeof(T) == 2) { NC_MM_MAX(G, 8); break; }                      \
+        case 4: NC_MM_MAX(G, 4); break;                                                        \
+        case 2: NC_MM_MAX(G, 2); break;                                                        \
+        default: NC_MM_MAX(G, 1); break;                                                       \
+    }
+    if (groups == 2) { NC_MM_MAX_V(2) } else { NC_MM_MAX_V(1) }
+#undef NC_MM_MAX_V
 #undef NC_MM_MAX
     NC_LAUNCH_OK("mm_max_kernel");
     }
     if (!(which & 2)) return 0;
-    const bool v2 = sizeof(T) == 2 && nB % 2 == 0 && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 3) == 0;
-    // half2 columns when every row start stays 4-byte aligned (even nB) and the base pointers are
-    const int vec = v2 ? 2 : 1;
+    const int vec = mm_vec_for<T>(nB, x, y);
     dim3 g2((nB + 32 * vec - 1) / (32 * vec), (nA + 8 * kMMApplyRows - 1) / (8 * kMMApplyRows), B);
     NC_CHECK(g2.y <= 65535, "mutual_matching: too many rows");
 #define NC_MM_APPLY(G, V) mm_apply_kernel<T, G, V><<<g2, 256, 0, st>>>((const T *)x, (T *)y, (const unsigned long long *)keys, nA, nB)
-    if (groups == 2) { if (v2) NC_MM_APPLY(2, 2); else NC_MM_APPLY(2, 1); }
-    else             { if (v2) NC_MM_APPLY(1, 2); else NC_MM_APPLY(1, 1); }
+#define NC_MM_APPLY_V(G)                                                                       \
+    switch (vec) {                                                                             \
+        case 8: if constexpr (sizeof(T) == 2) { NC_MM_APPLY(G, 8); break; }                    \
+        case 4: NC_MM_APPLY(G, 4); break;                                                      \
+        case 2: NC_MM_APPLY(G, 2); break;                                                      \
+        default: NC_MM_APPLY(G, 1); break;                                                     \
+    }
+    if (groups == 2) { NC_MM_APPLY_V(2) } else { NC_MM_APPLY_V(1) }
+#undef NC_MM_APPLY_V
 #undef NC_MM_APPLY
     NC_LAUNCH_OK("mm_apply_kernel");
     return 0;

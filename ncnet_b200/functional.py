@@ -352,7 +352,7 @@ def _conv_dgrad(gy, w32, mask, layout, symmetric, shared_input, mode, out_cb16=F
     return gx
 
 
-def _conv_wgrad(x, gy, w_like, want_bias, layout, symmetric, shared_input, mode):
+def _conv_wgrad(x, gy, w_like, want_bias, layout, symmetric, shared_input, mode, out_scale=None):
     cin, cout, k = _wdims(w_like, layout)
     bsz, _, d1, d2, d3, d4 = x.shape
     dev = x.device
@@ -368,7 +368,7 @@ def _conv_wgrad(x, gy, w_like, want_bias, layout, symmetric, shared_input, mode)
             ev0.record()
         _cabi.check(L.ncnet_conv4d_wgrad(x.data_ptr(), gy.data_ptr(), _ptr(gw), _ptr(gb), _ptr(scratch), bsz, cin, cout, d1,
                                          d2, d3, d4, k, layout, int(symmetric), int(shared_input), _adt(x), _adt(gy), mode,
-                                         _stream()), "conv4d_wgrad")
+                                         _ptr(out_scale), _stream()), "conv4d_wgrad")
         if log:
             ev1.record()
             EVENT_LOG.append(("conv4d_wgrad_16_16", ev0, ev1))
@@ -475,17 +475,26 @@ class _NeighConsensusFn(torch.autograd.Function):
         out = acts[n]
         bsz = out.shape[0]
         g = g.contiguous()
+        # TC16 mode stores every gradient of the backward pass in fp16: scale the incoming one by a power of two so
+        # that nothing falls into fp16's subnormal range, un-scale the (fp32) weight gradients at the end
+        scale3 = inv_scale = None
+        if mode == CONV_TC16:
+            scale3 = torch.empty(3, device=out.device, dtype=torch.float32)
+            inv_scale = scale3[1:]
+            with torch.cuda.device(out.device):
+                _cabi.check(_cabi.lib().ncnet_grad_scale(_ptr(g), g.numel(), _dt(g), _ptr(scale3), _stream()), "grad_scale")
+            _count(2)
         # ReLU of the last layer: gz = g where the branch output is positive
         gz = torch.empty_like(out)
         per = out[0].numel()
         with torch.cuda.device(out.device):
-            _cabi.check(_cabi.lib().ncnet_relu_mask_bcast(_ptr(out), _ptr(g), _ptr(gz), bsz, 1, per, _dt(out), _stream()),
-                        "relu_mask_bcast")
+            _cabi.check(_cabi.lib().ncnet_relu_mask_bcast(_ptr(out), _ptr(g), _ptr(gz), bsz, 1, per, _dt(out), _ptr(scale3),
+                                                          _stream()), "relu_mask_bcast")
         _count(1)
         grads: List[Optional[torch.Tensor]] = [None] * (2 * n)
         gx = None
         for l in range(n - 1, -1, -1):
-            gw, gb = _conv_wgrad(acts[l], gz, w32s[l], True, W_KOIKKK, sym, l == 0, mode)
+            gw, gb = _conv_wgrad(acts[l], gz, w32s[l], True, W_KOIKKK, sym, l == 0, mode, out_scale=inv_scale)
             grads[2 * l], grads[2 * l + 1] = gw.to(ctx.wdtype), gb.to(ctx.wdtype)
             if l > 0:
                 gz = _conv_dgrad(gz, w32s[l], acts[l], W_KOIKKK, sym, False, mode, out_cb16=chain, out_pm=chain)
@@ -493,6 +502,8 @@ class _NeighConsensusFn(torch.autograd.Function):
                 if isinstance(gz, _CB16):       # merged 2*Cout -> Cin gradient runs on the CUDA-core kernel (planar)
                     gz = cb16_unpack(gz, w32s[0].shape[1])
                 gx = _conv_dgrad(gz, w32s[0], None, W_KOIKKK, sym, True, mode)
+                if inv_scale is not None:
+                    gx = gx * inv_scale[0]
         return (gx, None, None, None, *grads)
 
 

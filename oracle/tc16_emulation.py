@@ -15,6 +15,10 @@ Where the kernels round (ncnet_b200/csrc):
                                    stack are stored as fp16 after bias + ReLU; the stack's last output stays fp32
   Conv4d dgrad                     incoming gradient and weights -> fp16; result (after the ReLU mask) stored fp16
   Conv4d wgrad                     activations (as stored) and incoming gradient -> fp16; result fp32
+  backward of a stack              the gradient arriving at the stack's output is multiplied by S = 2^e with
+                                   max|g|*S in [8,16) (ncnet_grad_scale) and the weight / bias / input gradients by
+                                   1/S at the end -- exact, and it keeps the fp16 gradient roundings out of fp16's
+                                   subnormal range
 Everything else (MutualMatching, match score, correlation backward) is fp32 in both modes.
 
 Follows reference lib/model.py:143-153 (NeighConsensus.forward), lib/conv4d.py:11-51 and train.py:110-156 through
@@ -22,6 +26,7 @@ Follows reference lib/model.py:143-153 (NeighConsensus.forward), lib/conv4d.py:1
 """
 from __future__ import annotations
 
+import math
 from typing import Sequence
 
 import torch
@@ -46,6 +51,38 @@ def r16(t: torch.Tensor, fwd: bool = True, bwd: bool = False) -> torch.Tensor:
     return _Round16.apply(t, fwd, bwd)
 
 
+class _ScaleOut(torch.autograd.Function):
+    """identity; backward: g -> S*g with the library's power-of-two scale, S left in ``state``"""
+
+    @staticmethod
+    def forward(ctx, t, state):
+        ctx.state = state
+        return t.clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        m = float(g.detach().float().abs().max())       # the kernel takes the maximum of the fp32 gradient
+        s = 1.0
+        if m > 0 and math.isfinite(m):
+            _, e = math.frexp(m)                        # m = f * 2^e, f in [0.5, 1)
+            s = math.ldexp(1.0, max(-100, min(100, 4 - e)))
+        ctx.state["S"] = s
+        return g * s, None
+
+
+class _Unscale(torch.autograd.Function):
+    """identity; backward: g -> g / S"""
+
+    @staticmethod
+    def forward(ctx, t, state):
+        ctx.state = state
+        return t.clone()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g / ctx.state["S"], None
+
+
 def neigh_consensus(x: torch.Tensor, weights: Sequence[torch.Tensor], biases: Sequence[torch.Tensor],
                     symmetric: bool = True) -> torch.Tensor:
     """The [Conv4d + ReLU] x L stack (lib/model.py:130-153) with the TC16 roundings.  ``weights`` in the stored
@@ -53,6 +90,10 @@ def neigh_consensus(x: torch.Tensor, weights: Sequence[torch.Tensor], biases: Se
     incoming gradients, wide accumulation); d/dx uses the fp16 weights here whereas the library's first-layer input
     gradient runs on the fp32 CUDA-core kernel with unrounded weights -- compare that one loosely."""
     n = len(weights)
+    state = {"S": 1.0}
+    x = _Unscale.apply(x, state)
+    weights = [_Unscale.apply(w, state) for w in weights]
+    biases = [_Unscale.apply(b, state) for b in biases]
 
     def branch(v):
         v = r16(v)                                         # planar input -> fp16 operand
@@ -66,7 +107,7 @@ def neigh_consensus(x: torch.Tensor, weights: Sequence[torch.Tensor], biases: Se
     y = branch(x)
     if symmetric:
         y = y + branch(x.permute(0, 1, 4, 5, 2, 3)).permute(0, 1, 4, 5, 2, 3)
-    return y
+    return _ScaleOut.apply(y, state)
 
 
 def _params(nc):

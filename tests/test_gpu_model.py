@@ -85,5 +85,7 @@ def test_immatchnet_half_precision_relocalisation(cuda, tmp_path, monkeypatch):
     assert nerr(corr4d.float(), ref) < 5e-3
     m = nb.corr_to_matches(corr4d, delta4d=delta4d, k_size=2, do_softmax=True, scale="positive", return_indices=True)
     mo = O.corr_to_matches(ref, delta4d=rdelta, k_size=2, do_softmax=True, scale="positive", return_indices=True)
-    agree = ((m[5].cpu() == mo[5]) & (m[6].cpu() == mo[6]) & (m[7].cpu() == mo[7]) & (m[8].cpu() == mo[8])).float().mean()
-    assert agree > 0.9, float(agree)
+    # a random-initialised trunk gives nearly constant feature maps, i.e. volumes full of near-ties: compare the match
+    # scores (the arg-max itself is compared on structured inputs in test_gpu_tc_pinned.py)
+    assert m[0].shape == mo[0].shape and m[5].dtype == torch.int64
+    assert nerr(m[4].float(), mo[4]) < 2e-2
