@@ -223,14 +223,17 @@ int ncnet_maxpool4d_fwd(const void *x, void *value, void *max_i, void *max_j, vo
  * offset tensors [fs1,fs2,fs3,fs4] (batch 1 only, may be NULL), idx_bytes as above, k_size the
  * pooling factor.  lut_*: fp32 coordinate tables of lengths fs2*k, fs1*k, fs4*k, fs3*k built
  * by the caller exactly like lib/point_tnf.py:16-27.  Outputs [B,N]: xA,yA,xB,yB,score fp32;
- * iA,jA,iB,jB int64. */
+ * iA,jA,iB,jB int64.  scratch: ncnet_corr_to_matches_scratch_bytes(...) bytes (0 for most shapes: only the
+ * invert=0 reduction over a volume with few batch items and many source cells splits its rows over CTAs and
+ * combines them through scratch; NULL is accepted when the query returns 0). */
+size_t ncnet_corr_to_matches_scratch_bytes(int B, int fs1, int fs2, int fs3, int fs4, int invert, int dtype);
 int ncnet_corr_to_matches(const void *corr, int B, int fs1, int fs2, int fs3, int fs4,
                           int do_softmax, int invert, int k_size,
                           const void *delta_iA, const void *delta_jA, const void *delta_iB,
                           const void *delta_jB, int idx_bytes,
                           const float *lut_xA, const float *lut_yA, const float *lut_xB, const float *lut_yB,
                           float *xA, float *yA, float *xB, float *yB, float *score,
-                          int64_t *iA, int64_t *jA, int64_t *iB, int64_t *jB, int dtype, void *stream);
+                          int64_t *iA, int64_t *jA, int64_t *iB, int64_t *jB, void *scratch, int dtype, void *stream);
 
 /* InLoc match post-processing -- eval_inloc.py:151-203, on the device instead of numpy on the host.
  * Input: the (xA,yA,xB,yB,score) columns of corr_to_matches for one direction (n1 matches) and optionally the

@@ -57,7 +57,8 @@ SIGNATURES = {
     "ncnet_points_axis_transform": (_i, [_p, _p, _i, _p, _i, _i, _i, _p]),
     "ncnet_bilinear_point_tnf": (_i, [_p] * 5 + [_i, _p, _p, _i, _i, _p]),
     "ncnet_pck": (_i, [_p, _p, _p, C.c_float, _p, _i, _i, _p]),
-    "ncnet_corr_to_matches": (_i, [_p] + [_i] * 8 + [_p] * 4 + [_i] + [_p] * 4 + [_p] * 9 + [_i, _p]),
+    "ncnet_corr_to_matches_scratch_bytes": (_sz, [_i] * 7),
+    "ncnet_corr_to_matches": (_i, [_p] + [_i] * 8 + [_p] * 4 + [_i] + [_p] * 4 + [_p] * 9 + [_p, _i, _p]),
 }
 
 

@@ -29,41 +29,6 @@ __device__ __forceinline__ float key_val_hi(const unsigned long long *keys, size
     return ord2f(reinterpret_cast<const uint32_t *>(keys)[2 * i + 1]);
 }
 
-// VEC elements of T with one load of VEC*sizeof(T) bytes (4, 8 or 16); the pointer is aligned to that size
-template <typename T, int VEC>
-__device__ __forceinline__ void load_vec(const T *p, float (&out)[VEC]) {
-    constexpr int BYTES = VEC * (int)sizeof(T);
-    static_assert(BYTES == 2 || BYTES == 4 || BYTES == 8 || BYTES == 16, "load_vec: 2, 4, 8 or 16 bytes");
-    if constexpr (BYTES == 2) {
-        out[0] = ldf(p);
-    } else {
-        union { uint4 q; uint2 d; unsigned w; T e[VEC]; } u;
-        if constexpr (BYTES == 16) u.q = __ldg(reinterpret_cast<const uint4 *>(p));
-        else if constexpr (BYTES == 8) u.d = __ldg(reinterpret_cast<const uint2 *>(p));
-        else u.w = __ldg(reinterpret_cast<const unsigned *>(p));
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-            if constexpr (sizeof(T) == 4) out[i] = u.e[i]; else out[i] = __half2float(u.e[i]);
-        }
-    }
-}
-template <typename T, int VEC>
-__device__ __forceinline__ void store_vec(T *p, const float (&v)[VEC]) {
-    constexpr int BYTES = VEC * (int)sizeof(T);
-    if constexpr (BYTES == 2) {
-        stf(p, v[0]);
-    } else {
-        union { uint4 q; uint2 d; unsigned w; T e[VEC]; } u;
-#pragma unroll
-        for (int i = 0; i < VEC; ++i) {
-            if constexpr (sizeof(T) == 4) u.e[i] = v[i]; else u.e[i] = __float2half_rn(v[i]);
-        }
-        if constexpr (BYTES == 16) *reinterpret_cast<uint4 *>(p) = u.q;
-        else if constexpr (BYTES == 8) *reinterpret_cast<uint2 *>(p) = u.d;
-        else *reinterpret_cast<unsigned *>(p) = u.w;
-    }
-}
-
 // widest vector (in elements) such that every row start and the base pointers stay aligned to it
 template <typename T>
 static int mm_vec_for(int nB, const void *a, const void *b) {

@@ -173,8 +173,167 @@ matches_over_rows_kernel(MatchArgs p) {
     }
 }
 
-// arg-max over the contiguous (target) axis: one warp per row
+// ---------------------------------------------------------------------------------------------
+// The same reduction for volumes with few batch items and many rows (InLoc): one CTA per (32*VEC-column tile, row
+// chunk), VEC adjacent columns per lane with one 4/8/16-byte load, per-column results combined across the row chunks
+// through scratch memory.  soft-max: kernel 1 leaves (max, sum of exp) per (chunk, column), kernel 2 merges them (in
+// chunk order) and takes the arg-max of the rounded soft-max values with a 64-bit atomicMax of (value, first index);
+// without soft-max kernel 1 does the atomicMax directly.  A last kernel turns the keys into matches.
+// ---------------------------------------------------------------------------------------------
+constexpr int kSplitU = 4;          // rows in flight per warp iteration
+
+template <typename T, int VEC, int PHASE>        // PHASE 0: raw arg-max; 1: soft-max statistics; 2: soft-max arg-max
+__global__ void __launch_bounds__(256)
+matches_rows_split_kernel(MatchArgs p, unsigned long long *__restrict__ keys, float2 *__restrict__ part, int rows_per_chunk) {
+    const int nA = p.fs1 * p.fs2, nB = p.fs3 * p.fs4;
+    const int b = blockIdx.z, chunk = blockIdx.y, R = gridDim.y;
+    const int lane = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const int c0 = (blockIdx.x * 32 + lane) * VEC;
+    const bool ok = c0 < nB;                                    // nB is a multiple of VEC
+    const T *x = (const T *)p.corr + (size_t)b * nA * nB;
+    const int r0 = chunk * rows_per_chunk, r1 = min(nA, r0 + rows_per_chunk);
+    float M[VEC], S[VEC];
+    unsigned long long best[VEC];
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) { M[u] = -INFINITY; S[u] = 0.f; best[u] = 0ull; }
+    if (PHASE == 2 && ok) {                                     // merge the chunks' statistics, in chunk order
+#pragma unroll
+        for (int u = 0; u < VEC; ++u) {
+            float mm = -INFINITY;
+            for (int q = 0; q < R; ++q) mm = fmaxf(mm, part[((size_t)b * R + q) * nB + c0 + u].x);
+            float ss = 0.f;
+            for (int q = 0; q < R; ++q) {
+                const float2 t = part[((size_t)b * R + q) * nB + c0 + u];
+                ss += (t.x == -INFINITY) ? 0.f : t.y * expf(t.x - mm);
+            }
+            M[u] = mm; S[u] = ss;
+        }
+    }
+    float m[VEC], sacc[VEC];
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) { m[u] = -INFINITY; sacc[u] = 0.f; }
+    if (ok)
+        for (int a0 = r0 + ty; a0 < r1; a0 += 8 * kSplitU) {
+            float v[kSplitU][VEC];
+#pragma unroll
+            for (int k = 0; k < kSplitU; ++k) {
+                const int a = a0 + 8 * k;
+                if (a < r1) load_vec<T, VEC>(x + (size_t)a * nB + c0, v[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < kSplitU; ++k) {
+                const int a = a0 + 8 * k;
+                if (a >= r1) break;
+#pragma unroll
+                for (int u = 0; u < VEC; ++u) {
+                    if (PHASE == 1) {
+                        if (v[k][u] > m[u]) { sacc[u] = sacc[u] * expf(m[u] - v[k][u]); m[u] = v[k][u]; }
+                        sacc[u] += expf(v[k][u] - m[u]);
+                    } else {
+                        const float q = PHASE == 2 ? rnd<T>(expf(v[k][u] - M[u]) / S[u]) : v[k][u];
+                        const unsigned long long key = pack_key(q, (uint32_t)a);
+                        best[u] = key > best[u] ? key : best[u];
+                    }
+                }
+            }
+        }
+    // combine the 8 warps of the CTA
+    __shared__ float s_m[8][32 * VEC + 1], s_s[8][32 * VEC + 1];
+    __shared__ unsigned long long s_k[8][32 * VEC + 1];
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) {
+        if (PHASE == 1) { s_m[ty][lane * VEC + u] = m[u]; s_s[ty][lane * VEC + u] = sacc[u]; }
+        else s_k[ty][lane * VEC + u] = best[u];
+    }
+    __syncthreads();
+    for (int cc = threadIdx.x; cc < 32 * VEC; cc += 256) {
+        const int col = blockIdx.x * 32 * VEC + cc;
+        if (col >= nB) continue;
+        if (PHASE == 1) {
+            float mm = -INFINITY;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) mm = fmaxf(mm, s_m[w][cc]);
+            float ss = 0.f;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) ss += (s_m[w][cc] == -INFINITY) ? 0.f : s_s[w][cc] * expf(s_m[w][cc] - mm);
+            part[((size_t)b * R + chunk) * nB + col] = make_float2(mm, ss);
+        } else {
+            unsigned long long k = 0ull;
+#pragma unroll
+            for (int w = 0; w < 8; ++w) k = s_k[w][cc] > k ? s_k[w][cc] : k;
+            if (k) atomicMax(keys + (size_t)b * nB + col, k);
+        }
+    }
+}
+
+__global__ void matches_emit_kernel(MatchArgs p, const unsigned long long *__restrict__ keys) {
+    const int nB = p.fs3 * p.fs4;
+    const int col = blockIdx.x * blockDim.x + threadIdx.x, b = blockIdx.y;
+    if (col >= nB) return;
+    const unsigned long long k = keys[(size_t)b * nB + col];
+    emit_match(p, b, col, (int)key_idx(k), key_val(k));
+}
+
+struct SplitPlan { int vec, col_tiles, R, rows_per_chunk; size_t keys_bytes, total; };
+
+static int vec_elems(uintptr_t bits, int elem, int cap) {
+    const int bytes = (bits & 15) == 0 ? 16 : ((bits & 7) == 0 ? 8 : ((bits & 3) == 0 ? 4 : elem));
+    const int v = bytes / elem;
+    return v > cap ? cap : (v < 1 ? 1 : v);
+}
+
+// R > 1 only when the one-CTA-per-column-tile kernel would leave most SMs idle
+static SplitPlan split_plan(int B, int nA, int nB, int elem) {
+    SplitPlan s{};
+    s.vec = vec_elems((uintptr_t)nB * elem, elem, 4);            // the base pointer is checked at launch
+    s.col_tiles = (nB + 32 * s.vec - 1) / (32 * s.vec);
+    int R = (2 * kNumSMs + s.col_tiles * B - 1) / (s.col_tiles * B);
+    if (R > 32) R = 32;
+    if (R < 1 || nA < 1024) R = 1;          // short reductions: one launch of the one-CTA-per-tile kernel is quicker
+    s.rows_per_chunk = ((nA + R - 1) / R + 7) / 8 * 8;
+    s.R = (nA + s.rows_per_chunk - 1) / s.rows_per_chunk;
+    s.keys_bytes = ((size_t)B * nB * 8 + 255) & ~(size_t)255;
+    s.total = s.keys_bytes + (size_t)B * s.R * nB * sizeof(float2);
+    return s;
+}
+
+template <typename T, int VEC>
+static int launch_split(const MatchArgs &p, const SplitPlan &sp, void *scratch, cudaStream_t st) {
+    const int nB = p.fs3 * p.fs4;
+    unsigned long long *keys = (unsigned long long *)scratch;
+    float2 *part = (float2 *)((uint8_t *)scratch + sp.keys_bytes);
+    cudaError_t e = cudaMemsetAsync(keys, 0, (size_t)p.B * nB * 8, st);
+    NC_CHECK(e == cudaSuccess, "corr_to_matches: memset: %s", cudaGetErrorString(e));
+    dim3 grid(sp.col_tiles, sp.R, p.B);
+    if (p.do_softmax) {
+        matches_rows_split_kernel<T, VEC, 1><<<grid, 256, 0, st>>>(p, keys, part, sp.rows_per_chunk);
+        NC_LAUNCH_OK("matches_rows_split_kernel(stats)");
+        matches_rows_split_kernel<T, VEC, 2><<<grid, 256, 0, st>>>(p, keys, part, sp.rows_per_chunk);
+    } else {
+        matches_rows_split_kernel<T, VEC, 0><<<grid, 256, 0, st>>>(p, keys, part, sp.rows_per_chunk);
+    }
+    NC_LAUNCH_OK("matches_rows_split_kernel");
+    matches_emit_kernel<<<dim3((nB + 255) / 256, p.B), 256, 0, st>>>(p, keys);
+    NC_LAUNCH_OK("matches_emit_kernel");
+    return 0;
+}
+
 template <typename T>
+static int launch_split_t(const MatchArgs &p, const SplitPlan &sp, void *scratch, cudaStream_t st) {
+    int vec = sp.vec;
+    while (vec > 1 && ((uintptr_t)p.corr % (vec * sizeof(T))) != 0) vec >>= 1;      // misaligned base pointer
+    SplitPlan q = sp;
+    q.vec = vec;
+    q.col_tiles = (p.fs3 * p.fs4 + 32 * vec - 1) / (32 * vec);
+    switch (vec) {
+        case 4: return launch_split<T, 4>(p, q, scratch, st);
+        case 2: return launch_split<T, 2>(p, q, scratch, st);
+        default: return launch_split<T, 1>(p, q, scratch, st);
+    }
+}
+
+// arg-max over the contiguous (target) axis: one warp per row
+template <typename T, int VEC>
 __global__ void __launch_bounds__(256)
 matches_over_cols_kernel(MatchArgs p) {
     const int nA = p.fs1 * p.fs2, nB = p.fs3 * p.fs4;
@@ -184,22 +343,42 @@ matches_over_cols_kernel(MatchArgs p) {
     if (row >= nA) return;
     const T *x = (const T *)p.corr + ((size_t)b * nA + row) * nB;
     unsigned long long best = 0ull;
+    // the row is walked in groups of VEC adjacent columns per lane (one 4/8/16-byte load; nB is a multiple of VEC)
     if (p.do_softmax) {
         float m = -INFINITY;
-        for (int c = lane; c < nB; c += 32) m = fmaxf(m, ldf(x + c));
+        for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+            float v[VEC];
+            load_vec<T, VEC>(x + c, v);
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) m = fmaxf(m, v[u]);
+        }
         m = warp_max(m);
         float s = 0.f;
-        for (int c = lane; c < nB; c += 32) s += expf(ldf(x + c) - m);
+        for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+            float v[VEC];
+            load_vec<T, VEC>(x + c, v);
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) s += expf(v[u] - m);
+        }
         s = warp_sum(s);
-        for (int c = lane; c < nB; c += 32) {
-            const float v = rnd<T>(expf(ldf(x + c) - m) / s);
-            const unsigned long long k = pack_key(v, (uint32_t)c);
-            best = k > best ? k : best;
+        for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+            float v[VEC];
+            load_vec<T, VEC>(x + c, v);
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) {
+                const unsigned long long k = pack_key(rnd<T>(expf(v[u] - m) / s), (uint32_t)(c + u));
+                best = k > best ? k : best;
+            }
         }
     } else {
-        for (int c = lane; c < nB; c += 32) {
-            const unsigned long long k = pack_key(ldf(x + c), (uint32_t)c);
-            best = k > best ? k : best;
+        for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+            float v[VEC];
+            load_vec<T, VEC>(x + c, v);
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) {
+                const unsigned long long k = pack_key(v[u], (uint32_t)(c + u));
+                best = k > best ? k : best;
+            }
         }
     }
     best = warp_max_u64(best);
@@ -231,12 +410,18 @@ extern "C" int ncnet_maxpool4d_fwd(const void *x, void *value, void *max_i, void
     return fail("maxpool4d: unsupported dtype %d", dtype);
 }
 
+extern "C" size_t ncnet_corr_to_matches_scratch_bytes(int B, int fs1, int fs2, int fs3, int fs4, int invert, int dtype) {
+    if (B < 1 || fs1 < 1 || fs2 < 1 || fs3 < 1 || fs4 < 1 || invert) return 0;
+    const SplitPlan sp = split_plan(B, fs1 * fs2, fs3 * fs4, dtype == NCNET_F16 ? 2 : 4);
+    return sp.R > 1 ? sp.total : 0;
+}
+
 extern "C" int ncnet_corr_to_matches(const void *corr, int B, int fs1, int fs2, int fs3, int fs4, int do_softmax,
                                      int invert, int k_size, const void *delta_iA, const void *delta_jA,
                                      const void *delta_iB, const void *delta_jB, int idx_bytes, const float *lut_xA,
                                      const float *lut_yA, const float *lut_xB, const float *lut_yB, float *xA,
                                      float *yA, float *xB, float *yB, float *score, int64_t *iA, int64_t *jA,
-                                     int64_t *iB, int64_t *jB, int dtype, void *stream) {
+                                     int64_t *iB, int64_t *jB, void *scratch, int dtype, void *stream) {
     NC_CHECK(corr && lut_xA && lut_yA && lut_xB && lut_yB && xA && yA && xB && yB && score && iA && jA && iB && jB,
              "corr_to_matches: null pointer");
     NC_CHECK(B > 0 && B <= 65535 && fs1 > 0 && fs2 > 0 && fs3 > 0 && fs4 > 0 && k_size >= 1, "corr_to_matches: bad shape");
@@ -256,14 +441,27 @@ extern "C" int ncnet_corr_to_matches(const void *corr, int B, int fs1, int fs2, 
     cudaStream_t st = (cudaStream_t)stream;
     const int nA = fs1 * fs2, nB = fs3 * fs4;
     if (dtype != NCNET_F32 && dtype != NCNET_F16) return fail("corr_to_matches: unsupported dtype %d", dtype);
+    const int elem = dtype == NCNET_F16 ? 2 : 4;
     if (!invert) {
+        const SplitPlan sp = split_plan(B, nA, nB, elem);
+        if (sp.R > 1) {          // few batch items, many rows: split the rows over CTAs (scratch from the query above)
+            NC_CHECK(scratch, "corr_to_matches: this shape needs ncnet_corr_to_matches_scratch_bytes() bytes of scratch");
+            return dtype == NCNET_F32 ? launch_split_t<float>(p, sp, scratch, st) : launch_split_t<__half>(p, sp, scratch, st);
+        }
         dim3 grid((nB + 31) / 32, B);
         if (dtype == NCNET_F32) matches_over_rows_kernel<float><<<grid, 256, 0, st>>>(p);
         else matches_over_rows_kernel<__half><<<grid, 256, 0, st>>>(p);
     } else {
         dim3 grid((nA + 7) / 8, B);
-        if (dtype == NCNET_F32) matches_over_cols_kernel<float><<<grid, 256, 0, st>>>(p);
-        else matches_over_cols_kernel<__half><<<grid, 256, 0, st>>>(p);
+        const int vec = vec_elems((uintptr_t)corr | ((uintptr_t)nB * elem), elem, 8);
+#define NC_COLS(T, V) matches_over_cols_kernel<T, V><<<grid, 256, 0, st>>>(p)
+        if (dtype == NCNET_F32) {
+            switch (vec) { case 4: NC_COLS(float, 4); break; case 2: NC_COLS(float, 2); break; default: NC_COLS(float, 1); }
+        } else {
+            switch (vec) { case 8: NC_COLS(__half, 8); break; case 4: NC_COLS(__half, 4); break; case 2: NC_COLS(__half, 2); break;
+                           default: NC_COLS(__half, 1); }
+        }
+#undef NC_COLS
     }
     NC_LAUNCH_OK("corr_to_matches kernel");
     return 0;

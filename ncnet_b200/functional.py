@@ -585,12 +585,14 @@ def corr_to_matches(corr4d, delta4d=None, k_size=1, do_softmax=False, scale="cen
         idx_bytes = 8 if deltas[0].dtype == torch.int64 else 1
         if any(d.dtype != deltas[0].dtype for d in deltas):
             raise TypeError("corr_to_matches: delta4d tensors must share one integer dtype")
+    nscratch = _cabi.lib().ncnet_corr_to_matches_scratch_bytes(b, f1, f2, f3, f4, int(bool(invert_matching_direction)), _dt(x))
+    scratch = torch.empty(nscratch, device=dev, dtype=torch.uint8) if nscratch else None
     with torch.cuda.device(dev):
         _cabi.check(_cabi.lib().ncnet_corr_to_matches(
             _ptr(x), b, f1, f2, f3, f4, int(bool(do_softmax)), int(bool(invert_matching_direction)), int(k_size),
             *[_ptr(d) for d in deltas], idx_bytes, *[_ptr(t) for t in luts], *[_ptr(t) for t in fo],
-            *[_ptr(t) for t in io], _dt(x), _stream()), "corr_to_matches")
-    _count(1)
+            *[_ptr(t) for t in io], _ptr(scratch), _dt(x), _stream()), "corr_to_matches")
+    _count(4 if nscratch else 1)
     xa, ya, xb, yb, score = fo
     if x.dtype != torch.float32:
         score = score.to(x.dtype)

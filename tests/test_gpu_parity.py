@@ -364,3 +364,25 @@ def test_stacked_weak_loss_equals_two_pass_loss(nb, cuda):
     assert abs(float(l1) - float(l2)) < 1e-7 + 1e-5 * abs(float(l2))
     for a, b in zip(g1, g2):
         assert nerr(a, b) < 1e-4
+
+
+@pytest.mark.parametrize("dt,softmax", [(torch.float32, True), (torch.float32, False), (torch.float16, True)])
+def test_corr_to_matches_long_reduction_split_rows(nb, cuda, dt, softmax):
+    """nA >= 1024 source cells with a single batch item: the B->A reduction splits its rows over CTAs and merges them
+    through scratch (csrc/pool_matches.cu); indices and coordinates still equal the oracle's, both directions."""
+    torch.manual_seed(62)
+    shape = (1, 1, 40, 30, 33, 28)
+    x = torch.rand(shape).to(dt)
+    for t in range(33 * 28):                          # a clear winner per target cell, plus exact ties below it
+        x[0, 0, (7 * t) % 40, (11 * t) % 30, t // 28, t % 28] = 2.0 + (t % 5)
+    x[0, 0, 3, 4, :, :] = x[0, 0, 5, 6, :, :]
+    from ncnet_b200 import _cabi
+    assert _cabi.lib().ncnet_corr_to_matches_scratch_bytes(1, 40, 30, 33, 28, 0, _cabi.F16 if dt == torch.float16 else _cabi.F32) > 0
+    for inv in (False, True):
+        m = nb.corr_to_matches(x.to(cuda), do_softmax=softmax, return_indices=True, invert_matching_direction=inv)
+        mo = O.corr_to_matches(x.float(), do_softmax=softmax, return_indices=True, invert_matching_direction=inv)
+        for k in (5, 6, 7, 8):
+            assert torch.equal(m[k].cpu(), mo[k]), (inv, k)
+        for k in range(4):
+            assert torch.equal(m[k].cpu(), mo[k])
+        assert nerr(m[4].float(), mo[4]) < (2e-3 if dt == torch.float16 else 1e-5)
