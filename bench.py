@@ -285,12 +285,18 @@ def run_ours(args):
         return loss
 
     # ---- warm-up (eager): also measures the launches per step ------------------------------------------------
+    # (on a side stream, and leaving no autograd graph alive: both are preconditions of the capture below)
     l0 = F_.LAUNCHES["n"]
     first_loss = None
-    for w in range(args.warmup):
-        loss = step_body()
-        if w == 0:
-            first_loss = loss.detach().clone()
+    side = torch.cuda.Stream(device=dev)
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        for w in range(args.warmup):
+            loss = step_body()
+            if w == 0:
+                first_loss = loss.detach().clone()
+            del loss
+    torch.cuda.current_stream().wait_stream(side)
     launches_per_step = (F_.LAUNCHES["n"] - l0) // max(args.warmup, 1)
     barrier()
 
