@@ -5,8 +5,11 @@
          NC 3-3 / 16-1, corr_to_matches in both directions with the relocalisation offsets (lib/point_tnf.py:12-80)
          at the 1600-px (100x75 features) and 3200-px (200x150 features) image sizes of the reference's InLoc runs.
 
+  full : BASELINE.json configs[0] -- ImMatchNet.forward on a 400x400 image pair through the real constructor
+         (ResNet-101 trunk on stock torchvision/cuDNN, random init: NCNET_TRUNK_WEIGHTS=random), batch 1.
+
 Prints one JSON line per case: ms per pair (CUDA events, median of 5 after 2 warm-ups) and the split by stage.
-Synthetic features, random-init weights.  usage: python scripts/inloc_bench.py [pf] [il16] [il32]"""
+Synthetic features, random-init weights.  usage: python scripts/inloc_bench.py [pf] [il16] [il32] [full]"""
 import json, sys
 import torch
 sys.path.insert(0, ".")
@@ -47,11 +50,18 @@ def timed(fn, iters=5, warm=2):
 def run(name, net, fa, fb, k_size):
     state = {}
 
+    fused = k_size > 1 and F_.can_fuse_correlation_pool(fa, fb, k_size)
+
     def corr():
-        state["c"] = net.FeatureCorrelation(fa, fb)
+        if fused:        # correlation + relocalisation pooling in one kernel (what ImMatchNet.match_features runs)
+            state["p"] = F_.feature_correlation_pooled(fa, fb, k_size)
+            state["c"] = state["p"][0]
+        else:
+            state["c"] = net.FeatureCorrelation(fa, fb)
 
     def pool():
-        state["p"] = nb.maxpool4d(state["c"], k_size=k_size) if k_size > 1 else (state["c"],)
+        if not fused:
+            state["p"] = nb.maxpool4d(state["c"], k_size=k_size) if k_size > 1 else (state["c"],)
 
     def mm1():
         state["m"] = nb.MutualMatching(state["p"][0])
@@ -62,6 +72,10 @@ def run(name, net, fa, fb, k_size):
 
     def matches():
         d = tuple(state["p"][1:]) if k_size > 1 else None
+        if fa.shape[0] == 1:     # eval_inloc.py:151-203: both directions, duplicates removed, recentred rows [N,5]
+            from ncnet_b200.eval_util import inloc_matches
+            state["rows"] = inloc_matches(state["o"], delta4d=d, k_size=max(1, k_size), do_softmax=True)
+            return
         for inv in (False, True):
             nb.corr_to_matches(state["o"], delta4d=d, k_size=max(1, k_size), do_softmax=True, invert_matching_direction=inv)
 
@@ -71,8 +85,8 @@ def run(name, net, fa, fb, k_size):
     with torch.no_grad():
         total = timed(whole)
         split = {}
-        for lab, fn in (("correlation", corr), ("maxpool4d", pool), ("mutual_matching", mm1),
-                        ("neigh_consensus+mutual_matching", nc), ("corr_to_matches x2", matches)):
+        for lab, fn in (("correlation+maxpool4d (fused)" if fused else "correlation", corr), ("maxpool4d", pool), ("mutual_matching", mm1),
+                        ("neigh_consensus+mutual_matching", nc), ("matches both directions + dedup", matches)):
             split[lab] = round(timed(fn), 4)
     b = fa.shape[0]
     print(json.dumps({"case": name, "batch": b, "ms_per_call": round(total, 4), "pairs_per_s": round(b / total * 1e3, 2),
@@ -87,6 +101,19 @@ if __name__ == "__main__":
         for b in (1, 16):
             fa = torch.rand(b, 1024, 25, 25, device=dev); fb = torch.rand(b, 1024, 25, 25, device=dev)
             run(f"PF-Pascal head forward + matches, batch {b}", net, fa, fb, 0)
+    if "full" in want:
+        import os
+        os.environ["NCNET_TRUNK_WEIGHTS"] = "random"
+        model = nb.ImMatchNet(ncons_kernel_sizes=[5, 5, 5], ncons_channels=[16, 16, 1], use_cuda=True)
+        batch = {"source_image": torch.randn(1, 3, 400, 400, device=dev), "target_image": torch.randn(1, 3, 400, 400, device=dev)}
+        with torch.no_grad():
+            t_full = timed(lambda: model(batch))
+            fa = model.FeatureExtraction(batch["source_image"]); fb = model.FeatureExtraction(batch["target_image"])
+            t_head = timed(lambda: model.match_features(fa, fb))
+            t_trunk = timed(lambda: (model.FeatureExtraction(batch["source_image"]), model.FeatureExtraction(batch["target_image"])))
+        print(json.dumps({"case": "config 1: ImMatchNet.forward, 400x400 pair, batch 1 (ResNet-101[:layer3] trunk on torchvision/cuDNN + head)",
+                          "ms_full_forward": round(t_full, 4), "ms_head_only": round(t_head, 4), "ms_trunk_x2": round(t_trunk, 4),
+                          "pairs_per_s_full": round(1e3 / t_full, 2), "pairs_per_s_head": round(1e3 / t_head, 2)}), flush=True)
     for tag, (h, w) in (("il16", (100, 74)), ("il32", (200, 150))):
         if tag not in want:
             continue
