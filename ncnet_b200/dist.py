@@ -152,33 +152,179 @@ def slab_mutual_matching(x_slab: torch.Tensor, group=None, sum_branches: bool = 
     return y
 
 
-def slab_neigh_consensus(x_slab: torch.Tensor, nc, rank: int, world: int, group=None) -> torch.Tensor:
-    """NeighConsensus (lib/model.py:143-153) on a slab: before every Conv4d layer the k//2 boundary rows are
-    exchanged with the neighbouring ranks (point-to-point), the layer runs on the extended slab and the borrowed
-    rows are cropped.  Both symmetric branches stay slab-local (transposed-filter identity).
-    Returns the un-summed branch outputs [B, G*C_last, rows, ...] like ``forward_branches``."""
-    from .functional import _conv_fwd, default_conv_mode, W_KOIKKK
+def _p2p(sends, recvs, group=None):
+    """One batch of point-to-point transfers: sends / recvs are lists of (tensor, peer).  NCCL moves device memory
+    directly (NVLink); under gloo (the CPU-side tests, or several ranks sharing one GPU) CUDA tensors are staged through
+    host memory because gloo has no device-to-device send."""
+    if not sends and not recvs:
+        return
+    staged = dist.get_backend(group) == "gloo"
+    ops, landing = [], []
+    for t, peer in sends:
+        ops.append(dist.P2POp(dist.isend, t.cpu() if (staged and t.is_cuda) else t, peer, group))
+    for t, peer in recvs:
+        if staged and t.is_cuda:
+            h = torch.empty(t.shape, dtype=t.dtype)
+            landing.append((t, h))
+            ops.append(dist.P2POp(dist.irecv, h, peer, group))
+        else:
+            ops.append(dist.P2POp(dist.irecv, t, peer, group))
+    for req in dist.batch_isend_irecv(ops):
+        req.wait()
+    for t, h in landing:
+        t.copy_(h)
+
+
+def exchange_halo_cb16_(act, halo: int, rank: int, world: int, group=None) -> int:
+    """In-place halo exchange on a CB16 activation tensor (include/ncnet_b200.h: NCNET_CB16) that already has room for
+    the neighbours' rows: its first-axis extent is halo_lo + rows + halo_hi.  A (block, channel-half) of CB16 is
+    [d1][d2][haloed plane][8], so ``halo`` rows are ONE contiguous run per (block, half): the boundary rows go out of
+    the tensor and the neighbours' rows land in it without any staging copy, concatenation or crop.
+    Returns the bytes this rank received."""
+    if world == 1 or halo == 0:
+        return 0
+    bsz, ch, d1e, d2, d3, d4 = act.shape
+    pad = act.k // 2
+    row_bytes = d2 * (d3 + 2 * pad) * (d4 + 2 * pad) * 16
+    nrun = act.buf.numel() // (d1e * row_bytes) if not act.pm else None
+    if act.pm:
+        raise RuntimeError("exchange_halo_cb16_: CB16 tensors with a position-major twin are not exchanged")
+    view = act.buf[: nrun * d1e * row_bytes].view(nrun, d1e, row_bytes)
+    h_lo = halo if rank > 0 else 0
+    h_hi = halo if rank < world - 1 else 0
+    sends, recvs = [], []
+    for i in range(nrun):
+        if rank > 0:
+            sends.append((view[i, h_lo:h_lo + halo], rank - 1))
+            recvs.append((view[i, 0:h_lo], rank - 1))
+        if rank < world - 1:
+            sends.append((view[i, d1e - h_hi - halo:d1e - h_hi], rank + 1))
+            recvs.append((view[i, d1e - h_hi:d1e], rank + 1))
+    _p2p(sends, recvs, group)
+    return sum(t.numel() for t, _ in recvs)
+
+
+def slab_neigh_consensus(x_slab: torch.Tensor, nc, rank: int, world: int, group=None, stats=None) -> torch.Tensor:
+    """NeighConsensus (lib/model.py:143-153) on a slab of rows.  The slab is extended ONCE by the halo of the whole
+    stack's first layer (k//2 rows per existing neighbour; the 1-channel input rows are cheap to fetch); every layer
+    then runs on that fixed extent.  A layer's output on the borrowed rows is computed from incomplete input and is
+    wrong there -- before the next layer reads it, those rows are overwritten in place with the neighbour's (correct)
+    rows (``exchange_halo_cb16_``).  In tensor-core mode the hidden activations stay in CB16 from launch to launch.
+    Both symmetric branches stay slab-local (transposed-filter identity).
+    Returns the un-summed branch outputs [B, G*C_last, rows, ...] like ``forward_branches``.
+    ``stats`` (dict, optional) receives the halo bytes received per layer."""
+    from .functional import _CB16, _conv_fwd, _stack_can_chain, default_conv_mode, W_KOIKKK
     ws, bs = nc._params()
     mode = default_conv_mode()
-    cur = x_slab.contiguous()
+    ks = [w.shape[0] for w in ws]
+    if len(set(ks)) != 1:
+        raise RuntimeError("slab_neigh_consensus: one kernel size per stack")
+    halo = ks[0] // 2
+    rows = x_slab.shape[2]
+    if world > 1 and rows < halo:
+        raise RuntimeError(f"slab of {rows} rows is thinner than the halo {halo}")
+    chain = _stack_can_chain(ks, [w.shape[1] for w in ws], x_slab.shape[4], x_slab.shape[5], mode, need_backward=False)
+    cur = exchange_halo(x_slab.contiguous(), halo, rank, world, group)       # 1-channel input: rows fetched once
+    received = [cur.numel() * cur.element_size() - x_slab.numel() * x_slab.element_size()]
     for l, (w, bvec) in enumerate(zip(ws, bs)):
-        halo = w.shape[0] // 2
-        ext = exchange_halo(cur, halo, rank, world, group)
-        y = _conv_fwd(ext, w.detach().float().contiguous(), bvec.detach().float().contiguous(), W_KOIKKK,
-                      nc.symmetric_mode, l == 0, True, mode)
-        cur = crop_halo(y, halo, rank, world)
-    return cur
+        last = l == len(ws) - 1
+        if l > 0:
+            if isinstance(cur, _CB16):
+                received.append(exchange_halo_cb16_(cur, halo, rank, world, group))
+            else:                       # planar hidden activations (fp32 mode): crop + re-fetch
+                own = crop_halo(cur, halo, rank, world)
+                cur = exchange_halo(own, halo, rank, world, group)
+                received.append((cur.numel() - own.numel()) * cur.element_size())
+        cur = _conv_fwd(cur, w.detach().float().contiguous(), bvec.detach().float().contiguous(), W_KOIKKK,
+                        nc.symmetric_mode, l == 0, True, mode, out_cb16=chain and not last)
+    if stats is not None:
+        stats["halo_bytes_received_per_layer"] = received
+    return crop_halo(cur, halo, rank, world)
 
 
-def slab_match_features(model, feature_A: torch.Tensor, feature_B: torch.Tensor, rank: int, world: int, group=None):
+def slab_match_features(model, feature_A: torch.Tensor, feature_B: torch.Tensor, rank: int, world: int, group=None,
+                        stats=None):
     """The head of ``ImMatchNet.match_features`` for this rank's rows of the volume: the correlation rows are
     computed locally from the (replicated) features, so only the halo rows and the target maxima cross NVLink."""
     lo, hi = slab_bounds(feature_A.shape[2], rank, world)
     corr = model.FeatureCorrelation(feature_A[:, :, lo:hi].contiguous(), feature_B)
     corr = slab_mutual_matching(corr, group)
-    br = slab_neigh_consensus(corr, model.NeighConsensus, rank, world, group)
+    br = slab_neigh_consensus(corr, model.NeighConsensus, rank, world, group, stats)
     if model.NeighConsensus.symmetric_mode and br.shape[1] == 2:
         return slab_mutual_matching(br, group, sum_branches=True)
     c = br.shape[1] // 2 if model.NeighConsensus.symmetric_mode else br.shape[1]
     summed = br[:, :c] + br[:, c:] if model.NeighConsensus.symmetric_mode else br
     return slab_mutual_matching(summed, group)
+
+
+def slab_corr_to_matches(corr_slab: torch.Tensor, fs1: int, rank: int, world: int, group=None, do_softmax: bool = False,
+                         scale: str = "centered", invert_matching_direction: bool = False):
+    """``corr_to_matches(..., return_indices=True)`` (lib/point_tnf.py:12-80, no relocalisation) for a volume sharded into
+    slabs of source rows; every rank returns the matches of the WHOLE volume.
+      * A->B (``invert_matching_direction``): each source cell's best target is local to its slab -- the per-rank
+        results are gathered in rank order.
+      * B->A: per target cell each rank contributes its local (max, first arg-max, sum of exp(x - max)) -- the column
+        halves of ``ncnet_match_score_fwd``'s keys / sums -- and the ranks' candidates are merged: the winner is the
+        largest maximum (lowest rank, i.e. lowest source row, on ties), the soft-max score is 1 / sum_r s_r exp(m_r - M).
+    Equal to the single-GPU result except where two source cells of different slabs tie after the soft-max's rounding."""
+    from . import _cabi
+    from .functional import _dt, _ptr, _stream, _count, corr_to_matches, _axis_lut
+    x = corr_slab.detach().contiguous()
+    b, _, rows, f2, f3, f4 = x.shape
+    lo, _hi = slab_bounds(fs1, rank, world)
+    dev = x.device
+    lo_v = -1.0 if scale == "centered" else 0.0
+    multi = dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1
+
+    def gather(t):
+        if not multi:
+            return [t]
+        counts = [(h - l) * f2 for l, h in (slab_bounds(fs1, r, world) for r in range(world))]
+        padded = torch.zeros((b, max(counts)), device=dev, dtype=t.dtype)      # equal sizes for the collective
+        padded[:, : t.shape[1]] = t
+        outs = [torch.empty_like(padded) for _ in range(world)]
+        dist.all_gather(outs, padded, group=group)
+        return [o[:, :c] for o, c in zip(outs, counts)]
+
+    if invert_matching_direction:
+        m = corr_to_matches(x, do_softmax=do_softmax, scale=scale, return_indices=True, invert_matching_direction=True)
+        ia = m[5] + lo                                        # local source row -> global
+        ya = _axis_lut(lo_v, fs1, dev)[ia]
+        parts = [gather(t) for t in (m[0], ya, m[2], m[3], m[4], ia, m[6], m[7], m[8])]
+        return tuple(torch.cat(p, 1) for p in parts)
+    na, nb = rows * f2, f3 * f4
+    lib = _cabi.lib()
+    keys = torch.empty(b * (na + nb), device=dev, dtype=torch.int64)
+    sums = torch.empty(lib.ncnet_mutual_matching_sums_bytes(b, na, nb) // 4, device=dev, dtype=torch.float32)
+    score = torch.empty((), device=dev, dtype=torch.float32)
+    with torch.cuda.device(dev):
+        _cabi.check(lib.ncnet_match_score_fwd(_ptr(x), _ptr(keys), _ptr(sums), None, _ptr(score), b, na, nb, _dt(x), _stream()),
+                    "match_score_fwd")
+    _count(4)
+    ck = keys.view(b, na + nb)[:, na:]                        # per target cell: (ordered max bits << 32) | ~first row
+    hi32 = (ck >> 32) & 0xFFFFFFFF
+    bits = torch.where(hi32 >= 0x80000000, hi32 - 0x80000000, 0xFFFFFFFF - hi32)       # inverse of common.cuh f2ord
+    m_loc = (bits & 0xFFFFFFFF).to(torch.int32).view(torch.float32)
+    a_loc = 0xFFFFFFFF - (ck & 0xFFFFFFFF)                    # local flat source index
+    s_loc = sums.view(-1)[: b * (na + nb)].view(b, na + nb)[:, na:]
+    ia_g = a_loc // f2 + lo
+    ja_g = a_loc % f2
+    cand = torch.stack([m_loc.double(), s_loc.double(), ia_g.double(), ja_g.double()], 0).contiguous()   # [4,b,nb]
+    if multi:
+        allc = [torch.empty_like(cand) for _ in range(world)]
+        dist.all_gather(allc, cand, group=group)
+        allc = torch.stack(allc, 0)                           # [world,4,b,nb]
+    else:
+        allc = cand[None]
+    mr, sr = allc[:, 0], allc[:, 1]
+    M, win = mr.max(0)                                        # first (lowest-rank) maximum wins
+    S = (sr * torch.exp((mr - M[None]).float()).double()).float().sum(0) if do_softmax else None
+    pick = lambda q: torch.gather(allc[:, q], 0, win[None])[0]
+    ia, ja = pick(2).long(), pick(3).long()
+    own = torch.arange(nb, device=dev)[None].expand(b, -1)
+    ib, jb = own // f4, own % f4
+    sc = (1.0 / S) if do_softmax else M.float()
+    if x.dtype != torch.float32:
+        sc = sc.to(x.dtype)
+    luts = [_axis_lut(lo_v, n, dev) for n in (f2, fs1, f4, f3)]
+    return (luts[0][ja], luts[1][ia], luts[2][jb], luts[3][ib], sc, ia, ja, ib, jb)
