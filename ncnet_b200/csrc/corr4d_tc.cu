@@ -23,7 +23,7 @@ namespace ncnet {
 
 using namespace tc;
 
-constexpr int kCorrThreads = 192;
+constexpr int kCorrThreads = 320;      // warp 0: producer, warp 1: MMA issuer, warps 2-9: epilogue (two per TMEM lane quadrant)
 constexpr int kCorrStages = 4;
 constexpr int kCorrKB = 64;            // channels per stage
 constexpr int kCorrBM = 128, kCorrBN = 256;
@@ -143,6 +143,44 @@ __device__ __forceinline__ void corr_pool_chunk(const CorrArgs &p, const float (
     }
 }
 
+// fp16 outputs: the same 4x4 reduction on packed integer keys -- (order-preserving 16 bits of the rounded value) << 4 |
+// (15 - window code) -- so one integer max per comparison returns the larger value and, on ties, the lower code.
+__device__ __forceinline__ void corr_pool_chunk_half(const CorrArgs &p, const float (&v)[16], int r, int t0, int lane) {
+    const int aq = lane & 3;
+    uint32_t bk[4];
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+        uint32_t best = 0u;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const float x = p.relu_l2norm ? corr_post<__half>(v[4 * g + c], 1) : v[4 * g + c];
+            uint32_t h = __half_as_ushort(__float2half_rn(x));
+            h = h == 0x8000u ? 0u : h;                                   // -0 compares equal to +0
+            const uint32_t o = (h & 0x8000u) ? (~h & 0xffffu) : (h | 0x8000u);
+            const uint32_t key = (o << 4) | (uint32_t)(15 - (aq * 4 + c));
+            best = max(best, key);
+        }
+        best = max(best, __shfl_xor_sync(0xffffffffu, best, 1));
+        best = max(best, __shfl_xor_sync(0xffffffffu, best, 2));
+        bk[g] = best;
+    }
+    const uint32_t mk = aq == 0 ? bk[0] : (aq == 1 ? bk[1] : (aq == 2 ? bk[2] : bk[3]));
+    const int prow = r >> 2, pcol = (t0 >> 2) + aq;
+    const int pA = p.nA >> 2, pB = p.nB >> 2;
+    if (prow >= pA || pcol >= pB) return;
+    const size_t o = (size_t)prow * pB + pcol;
+    const uint32_t ob = mk >> 4;
+    const unsigned short hb = (unsigned short)((ob & 0x8000u) ? (ob & 0x7fffu) : (~ob & 0xffffu));
+    ((__half *)p.out)[o] = __ushort_as_half(hb);
+    const int mc = 15 - (int)(mk & 15u);
+    const int off[4] = {mc >> 3, (mc >> 2) & 1, (mc >> 1) & 1, mc & 1};
+#pragma unroll
+    for (int d = 0; d < 4; ++d) {
+        if (p.idx_bytes == 1) ((unsigned char *)p.idx[d])[o] = (unsigned char)off[d];
+        else ((long long *)p.idx[d])[o] = off[d];
+    }
+}
+
 __global__ void __launch_bounds__(kCorrThreads, 1)
 corr4d_tc_kernel(const CorrArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -210,19 +248,21 @@ corr4d_tc_kernel(const CorrArgs p) {
         if (elect_one()) umma_commit(&accum_bar);
         __syncwarp();
     } else {
-        const int q = warp & 3;
+        const int q = warp & 3;                              // TMEM lane quadrant this warp may read
+        const int chalf = (warp - 2) >> 2;                   // which half of the tile's columns it takes
         mbar_wait(&accum_bar, 0);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int a = mt * kCorrBM + q * 32 + lane;
         const size_t row = ((size_t)b * p.nA + a) * p.nB;
         // rows start 16-byte aligned when nB is a multiple of 8 (fp16) / 4 (fp32) and the base pointer is aligned
         const bool vec_ok = (p.nB % (p.out_f16 ? 8 : 4)) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0;
-        for (int c0 = 0; c0 < n_cols; c0 += 16) {
+        const int c_end = min(n_cols, (chalf + 1) * (kCorrBN / 2));
+        for (int c0 = chalf * (kCorrBN / 2); c0 < c_end; c0 += 16) {
             float v[16];
             tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
             if (p.pool) {        // whole warp stays converged: the quad butterfly needs all four lanes
                 const int t0p = nt * kCorrBN + c0;
-                if (p.out_f16) corr_pool_chunk<__half>(p, v, a, t0p, lane);
+                if (p.out_f16) corr_pool_chunk_half(p, v, a, t0p, lane);
                 else corr_pool_chunk<float>(p, v, a, t0p, lane);
                 continue;
             }

@@ -62,54 +62,75 @@ mm_max_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, in
     // slot s = (load q, element u): column offset q*32*VEC + lane*VEC + u.  With VEC > 1 nB is a multiple of VEC, so a
     // group of VEC columns is either entirely inside the matrix or entirely outside.
     const int row_end = min(row0 + rows_per_block, nA);
-    for (int a = row0 + warp; a < row_end; a += kMMThreads / 32) {
-        const size_t roff = (size_t)a * nB + col0;
-        float v[kMMSlots];
+    constexpr int RU = 2;                              // rows in flight per warp iteration
+    for (int a0 = row0 + warp; a0 < row_end; a0 += RU * (kMMThreads / 32)) {
+        float v[RU][kMMSlots];
 #pragma unroll
-        for (int q = 0; q < NL; ++q) {
-            const int c = q * 32 * VEC + lane * VEC;
-            float t[VEC];
-            if (c < ncols) load_vec<T, VEC>(xb + roff + c, t);
-            else {
-#pragma unroll
-                for (int u = 0; u < VEC; ++u) t[u] = -INFINITY;
-            }
-#pragma unroll
-            for (int u = 0; u < VEC; ++u) v[q * VEC + u] = t[u];
-        }
-        if (GROUPS == 2) {                             // second branch, again as one batch of loads
-            float w[kMMSlots];
+        for (int r = 0; r < RU; ++r) {                 // every load of both rows is issued before any use
+            const int a = a0 + r * (kMMThreads / 32);
+            const size_t roff = (size_t)a * nB + col0;
 #pragma unroll
             for (int q = 0; q < NL; ++q) {
                 const int c = q * 32 * VEC + lane * VEC;
                 float t[VEC];
-                if (c < ncols) load_vec<T, VEC>(xb + mat + roff + c, t);
+                if (a < row_end && c < ncols) load_vec<T, VEC>(xb + roff + c, t);
                 else {
 #pragma unroll
-                    for (int u = 0; u < VEC; ++u) t[u] = 0.f;
+                    for (int u = 0; u < VEC; ++u) t[u] = -INFINITY;
                 }
 #pragma unroll
-                for (int u = 0; u < VEC; ++u) w[q * VEC + u] = t[u];
+                for (int u = 0; u < VEC; ++u) v[r][q * VEC + u] = t[u];
             }
+            if (GROUPS == 2) {                         // second branch, again as one batch of loads
 #pragma unroll
-            for (int s = 0; s < kMMSlots; ++s) v[s] = rnd<T>(v[s] + w[s]);
+                for (int q = 0; q < NL; ++q) {
+                    const int c = q * 32 * VEC + lane * VEC;
+                    float t[VEC];
+                    if (a < row_end && c < ncols) load_vec<T, VEC>(xb + mat + roff + c, t);
+                    else {
+#pragma unroll
+                        for (int u = 0; u < VEC; ++u) t[u] = 0.f;
+                    }
+#pragma unroll
+                    for (int u = 0; u < VEC; ++u) v[r][q * VEC + u] = rnd<T>(v[r][q * VEC + u] + t[u]);
+                }
+            }
         }
-        float rv = -INFINITY;
-        int rc = 0x7fffffff;
+        float rv[RU];
+        int rc[RU];
 #pragma unroll
-        for (int q = 0; q < NL; ++q)
+        for (int r = 0; r < RU; ++r) {
+            const int a = a0 + r * (kMMThreads / 32);
+            rv[r] = -INFINITY; rc[r] = 0x7fffffff;
 #pragma unroll
-            for (int u = 0; u < VEC; ++u) {
-                const int s = q * VEC + u;
-                if (v[s] > cv[s]) { cv[s] = v[s]; ci[s] = a; }
-                if (v[s] > rv) { rv = v[s]; rc = col0 + q * 32 * VEC + lane * VEC + u; }
-            }
-        // warp arg-max with first-index tie-break
-        const float m = warp_max(rv);
-        int cand = rv == m ? rc : 0x7fffffff;
+            for (int q = 0; q < NL; ++q)
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) cand = min(cand, __shfl_xor_sync(0xffffffffu, cand, o));
-        if (lane == 0 && cand != 0x7fffffff) atomicMax(rowkeys + a, pack_key(m, (uint32_t)cand));
+                for (int u = 0; u < VEC; ++u) {
+                    const int s = q * VEC + u;
+                    if (v[r][s] > cv[s]) { cv[s] = v[r][s]; ci[s] = a; }
+                    if (v[r][s] > rv[r]) { rv[r] = v[r][s]; rc[r] = col0 + q * 32 * VEC + lane * VEC + u; }
+                }
+        }
+        // warp arg-max with first-index tie-break, the RU rows' shuffle chains interleaved
+        float m[RU];
+        int cand[RU];
+#pragma unroll
+        for (int r = 0; r < RU; ++r) m[r] = rv[r];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int r = 0; r < RU; ++r) m[r] = fmaxf(m[r], __shfl_xor_sync(0xffffffffu, m[r], o));
+#pragma unroll
+        for (int r = 0; r < RU; ++r) cand[r] = rv[r] == m[r] ? rc[r] : 0x7fffffff;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int r = 0; r < RU; ++r) cand[r] = min(cand[r], __shfl_xor_sync(0xffffffffu, cand[r], o));
+#pragma unroll
+        for (int r = 0; r < RU; ++r) {
+            const int a = a0 + r * (kMMThreads / 32);
+            if (lane == 0 && a < row_end && cand[r] != 0x7fffffff) atomicMax(rowkeys + a, pack_key(m[r], (uint32_t)cand[r]));
+        }
     }
 
     __shared__ unsigned long long sm[kMMThreads / 32][kMMColsPerTile];
