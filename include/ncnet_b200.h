@@ -95,6 +95,10 @@ int ncnet_corr4d_bwd(const void *grad_out, const void *fa, const void *fb, void 
 size_t ncnet_mutual_matching_keys_bytes(int B, int nA, int nB);
 int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys, int B, int nA, int nB,
                               int in_groups, int dtype, void *stream);
+/* The same forward pass for callers that will not run the backward pass (inference): pass 1 tracks the maxima only,
+ * which halves its instruction count; `keys` then holds (max value, index 0) and must not be given to _bwd. */
+int ncnet_mutual_matching_fwd_infer(const void *x, void *y, uint64_t *keys, int B, int nA, int nB,
+                                    int in_groups, int dtype, void *stream);
 /* The two passes of ncnet_mutual_matching_fwd on their own, for volumes sharded into slabs along the first
  * source axis (BASELINE.json config 4): every rank runs _max on its rows, the per-target halves of `keys`
  * (entries [nA, nA+nB) of each batch item) are max-reduced across ranks by the caller, then every rank runs

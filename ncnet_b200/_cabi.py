@@ -33,6 +33,7 @@ SIGNATURES = {
     "ncnet_mutual_matching_keys_bytes": (_sz, [_i, _i, _i]),
     "ncnet_mutual_matching_sums_bytes": (_sz, [_i, _i, _i]),
     "ncnet_mutual_matching_fwd": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "ncnet_mutual_matching_fwd_infer": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_max": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_apply": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "ncnet_mutual_matching_bwd": (_i, [_p, _p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),

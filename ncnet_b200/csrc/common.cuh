@@ -73,6 +73,20 @@ __device__ __forceinline__ void load_vec(const T *p, float (&out)[VEC]) {
         }
     }
 }
+// the same for a pointer into shared memory (ordinary loads: the read-only data path is for global memory)
+template <typename T, int VEC>
+__device__ __forceinline__ void load_vec_smem(const T *p, float (&out)[VEC]) {
+    constexpr int BYTES = VEC * (int)sizeof(T);
+    union { uint4 q; uint2 d; unsigned w; unsigned short h; T e[VEC]; } u;
+    if constexpr (BYTES == 16) u.q = *reinterpret_cast<const uint4 *>(p);
+    else if constexpr (BYTES == 8) u.d = *reinterpret_cast<const uint2 *>(p);
+    else if constexpr (BYTES == 4) u.w = *reinterpret_cast<const unsigned *>(p);
+    else u.h = *reinterpret_cast<const unsigned short *>(p);
+#pragma unroll
+    for (int i = 0; i < VEC; ++i) {
+        if constexpr (sizeof(T) == 4) out[i] = u.e[i]; else out[i] = __half2float(u.e[i]);
+    }
+}
 template <typename T, int VEC>
 __device__ __forceinline__ void store_vec(T *p, const float (&v)[VEC]) {
     constexpr int BYTES = VEC * (int)sizeof(T);

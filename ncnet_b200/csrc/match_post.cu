@@ -25,49 +25,48 @@ __device__ __forceinline__ void load_match(const MatchCols &a, const MatchCols &
 
 constexpr int kPostTile = 256;
 
-// Pass 1: keep[i] = 1 unless another match has the same four coordinates and wins the reference's tie-break
-// (the copy that comes first after sorting by descending score; equal scores: the lower concatenated index).
-// Also clears the output rows and the counter.
+// The duplicate search and the ranking compare all pairs (i, j).  Both run on a 2-D grid of (i tile, j tile) CTAs so
+// that even a few thousand matches fill the GPU; a CTA stages its j tile in shared memory, every thread owns one i.
+// Pass 1: dup[i] = 1 when another match has the same four coordinates and wins the reference's tie-break (the copy
+// that comes first after sorting by descending score; equal scores: the lower concatenated index).
 __global__ void __launch_bounds__(kPostTile)
-match_keep_kernel(MatchCols a, MatchCols b, unsigned char *__restrict__ keep, float *__restrict__ out, int *__restrict__ count) {
+match_dup_kernel(MatchCols a, MatchCols b, int *__restrict__ dup, float *__restrict__ out, int *__restrict__ count) {
     __shared__ float t[5][kPostTile];
     const int n = a.n + b.n;
     const int i = blockIdx.x * kPostTile + threadIdx.x;
+    const int j0 = blockIdx.y * kPostTile, j = j0 + threadIdx.x;
     float me[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
     if (i < n) load_match(a, b, i, me);
-    bool dup = false;
-    for (int j0 = 0; j0 < n; j0 += kPostTile) {
-        const int j = j0 + threadIdx.x;
-        if (j < n) {
-            float v[5];
-            load_match(a, b, j, v);
+    if (j < n) {
+        float v[5];
+        load_match(a, b, j, v);
 #pragma unroll
-            for (int q = 0; q < 5; ++q) t[q][threadIdx.x] = v[q];
-        }
-        __syncthreads();
-        const int lim = min(kPostTile, n - j0);
-        if (i < n)
-            for (int u = 0; u < lim; ++u) {
-                const bool same = t[0][u] == me[0] && t[1][u] == me[1] && t[2][u] == me[2] && t[3][u] == me[3];
-                const float s = t[4][u];
-                dup |= same && (s > me[4] || (s == me[4] && j0 + u < i));
-            }
-        __syncthreads();
+        for (int q = 0; q < 5; ++q) t[q][threadIdx.x] = v[q];
     }
-    if (i < n) {
-        keep[i] = dup ? 0 : 1;
+    __syncthreads();
+    const int lim = min(kPostTile, n - j0);
+    bool hit = false;
+    if (i < n)
+        for (int u = 0; u < lim; ++u) {
+            if (t[0][u] != me[0]) continue;                       // most pairs differ in the first coordinate
+            const bool same = t[1][u] == me[1] && t[2][u] == me[2] && t[3][u] == me[3];
+            const float s = t[4][u];
+            hit |= same && (s > me[4] || (s == me[4] && j0 + u < i));
+        }
+    if (hit) dup[i] = 1;                                          // every writer stores the same value
+    if (blockIdx.y == 0 && i < n) {
 #pragma unroll
         for (int q = 0; q < 5; ++q) out[(size_t)i * 5 + q] = 0.f;
     }
-    if (i == 0) *count = 0;
+    if (blockIdx.y == 0 && i == 0) *count = 0;
 }
 
-__device__ __forceinline__ bool coords_less(const float *p, float x0, float x1, float x2, float x3) {
+__device__ __forceinline__ bool coords_less(float p0, float p1, float p2, float p3, float x0, float x1, float x2, float x3) {
     // lexicographic order of the columns of [xA; yA; xB; yB], the order np.unique(axis=1) returns
-    if (p[0] != x0) return p[0] < x0;
-    if (p[1] != x1) return p[1] < x1;
-    if (p[2] != x2) return p[2] < x2;
-    return p[3] < x3;
+    if (p0 != x0) return p0 < x0;
+    if (p1 != x1) return p1 < x1;
+    if (p2 != x2) return p2 < x2;
+    return p3 < x3;
 }
 
 // v * (n-1) / n + 0.5/n, the three fp32 roundings of  y*(fs*k-1)/(fs*k)+0.5/(fs*k)  (eval_inloc.py:185-194)
@@ -76,51 +75,48 @@ __device__ __forceinline__ float recentre(float v, int n) {
     return __fadd_rn(__fdiv_rn(__fmul_rn(v, (float)(n - 1)), (float)n), (float)(0.5 / (double)n));
 }
 
-// Pass 2: a kept match goes to row (number of kept matches with smaller coordinates).
+// Pass 2: pos[i] += number of kept matches of this j tile with smaller coordinates (integer atomics: order-independent).
 __global__ void __launch_bounds__(kPostTile)
-match_emit_kernel(MatchCols a, MatchCols b, const unsigned char *__restrict__ keep, float *__restrict__ out,
-                  int *__restrict__ count, int nyA, int nxA, int nyB, int nxB) {
+match_rank_kernel(MatchCols a, MatchCols b, const int *__restrict__ dup, int *__restrict__ pos) {
     __shared__ float t[4][kPostTile];
-    __shared__ unsigned char tk[kPostTile];
+    __shared__ int tk[kPostTile];
     const int n = a.n + b.n;
     const int i = blockIdx.x * kPostTile + threadIdx.x;
+    const int j0 = blockIdx.y * kPostTile, j = j0 + threadIdx.x;
     float me[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
     bool mine = false;
-    if (i < n) { load_match(a, b, i, me); mine = !keep || keep[i] != 0; }
-    int pos = 0;
-    if (!keep) {                      // single direction: the reference removes nothing and keeps the order
-        if (i < n) {
-            float *o = out + (size_t)i * 5;
-            o[0] = recentre(me[0], nxA); o[1] = recentre(me[1], nyA); o[2] = recentre(me[2], nxB); o[3] = recentre(me[3], nyB);
-            o[4] = me[4];
-        }
-        if (i == 0) *count = n;
-        return;
-    }
-    for (int j0 = 0; j0 < n; j0 += kPostTile) {
-        const int j = j0 + threadIdx.x;
-        if (j < n) {
-            float v[5];
-            load_match(a, b, j, v);
+    if (i < n) { load_match(a, b, i, me); mine = dup[i] == 0; }
+    if (j < n) {
+        float v[5];
+        load_match(a, b, j, v);
 #pragma unroll
-            for (int q = 0; q < 4; ++q) t[q][threadIdx.x] = v[q];
-            tk[threadIdx.x] = keep[j];
-        }
-        __syncthreads();
-        const int lim = min(kPostTile, n - j0);
-        if (mine)
-            for (int u = 0; u < lim; ++u) {
-                const float p[4] = {t[0][u], t[1][u], t[2][u], t[3][u]};
-                pos += (tk[u] && coords_less(p, me[0], me[1], me[2], me[3])) ? 1 : 0;
-            }
-        __syncthreads();
+        for (int q = 0; q < 4; ++q) t[q][threadIdx.x] = v[q];
+        tk[threadIdx.x] = dup[j] == 0;
     }
-    if (mine) {
-        float *o = out + (size_t)pos * 5;
-        o[0] = recentre(me[0], nxA); o[1] = recentre(me[1], nyA); o[2] = recentre(me[2], nxB); o[3] = recentre(me[3], nyB);
-        o[4] = me[4];
-        atomicAdd(count, 1);          // integer: order-independent
-    }
+    __syncthreads();
+    const int lim = min(kPostTile, n - j0);
+    int cnt = 0;
+    if (mine)
+        for (int u = 0; u < lim; ++u)
+            cnt += (tk[u] && coords_less(t[0][u], t[1][u], t[2][u], t[3][u], me[0], me[1], me[2], me[3])) ? 1 : 0;
+    if (mine && cnt) atomicAdd(pos + i, cnt);
+}
+
+// Pass 3: a kept match goes to row pos[i].  dup == nullptr: single direction, nothing removed, order kept.
+__global__ void __launch_bounds__(kPostTile)
+match_emit_kernel(MatchCols a, MatchCols b, const int *__restrict__ dup, const int *__restrict__ pos, float *__restrict__ out,
+                  int *__restrict__ count, int nyA, int nxA, int nyB, int nxB) {
+    const int n = a.n + b.n;
+    const int i = blockIdx.x * kPostTile + threadIdx.x;
+    if (i >= n) return;
+    if (!dup && i == 0) *count = n;
+    if (dup && dup[i]) return;
+    float me[5];
+    load_match(a, b, i, me);
+    float *o = out + (size_t)(dup ? pos[i] : i) * 5;
+    o[0] = recentre(me[0], nxA); o[1] = recentre(me[1], nyA); o[2] = recentre(me[2], nxB); o[3] = recentre(me[3], nyB);
+    o[4] = me[4];
+    if (dup) atomicAdd(count, 1);          // integer: order-independent
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -202,7 +198,7 @@ __global__ void pck_kernel(const float *__restrict__ src, const float *__restric
 
 using namespace ncnet;
 
-extern "C" size_t ncnet_matches_unique_scratch_bytes(int n) { return n > 0 ? (((size_t)n + 255) & ~(size_t)255) : 0; }
+extern "C" size_t ncnet_matches_unique_scratch_bytes(int n) { return n > 0 ? (((size_t)n * 8 + 255) & ~(size_t)255) : 0; }
 
 extern "C" int ncnet_matches_sort_unique(const float *xA, const float *yA, const float *xB, const float *yB,
                                          const float *score, int n1, const float *xA2, const float *yA2,
@@ -216,12 +212,18 @@ extern "C" int ncnet_matches_sort_unique(const float *xA, const float *yA, const
     cudaStream_t st = (cudaStream_t)stream;
     MatchCols a{xA, yA, xB, yB, score, n1}, b{xA2, yA2, xB2, yB2, score2, n2};
     const int n = n1 + n2, blocks = (n + kPostTile - 1) / kPostTile;
+    int *dup = nullptr, *pos = nullptr;
     if (n2 > 0) {
-        match_keep_kernel<<<blocks, kPostTile, 0, st>>>(a, b, (unsigned char *)scratch, out, count);
-        NC_LAUNCH_OK("match_keep_kernel");
+        dup = (int *)scratch; pos = dup + n;
+        cudaError_t e = cudaMemsetAsync(scratch, 0, (size_t)n * 8, st);
+        NC_CHECK(e == cudaSuccess, "matches_sort_unique: memset: %s", cudaGetErrorString(e));
+        NC_CHECK(blocks <= 65535, "matches_sort_unique: too many matches for the grid");
+        match_dup_kernel<<<dim3(blocks, blocks), kPostTile, 0, st>>>(a, b, dup, out, count);
+        NC_LAUNCH_OK("match_dup_kernel");
+        match_rank_kernel<<<dim3(blocks, blocks), kPostTile, 0, st>>>(a, b, dup, pos);
+        NC_LAUNCH_OK("match_rank_kernel");
     }
-    match_emit_kernel<<<blocks, kPostTile, 0, st>>>(a, b, n2 > 0 ? (const unsigned char *)scratch : nullptr, out, count,
-                                                    recentre_yA, recentre_xA, recentre_yB, recentre_xB);
+    match_emit_kernel<<<blocks, kPostTile, 0, st>>>(a, b, dup, pos, out, count, recentre_yA, recentre_xA, recentre_yB, recentre_xB);
     NC_LAUNCH_OK("match_emit_kernel");
     return 0;
 }

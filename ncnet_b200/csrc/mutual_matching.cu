@@ -153,6 +153,83 @@ mm_max_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, in
     }
 }
 
+// Pass 1 without the arg-max (inference: nothing will ask for the backward pass).  Same tiling; the inner loop is one
+// max per element for the column and one for the row, four rows in flight per warp, keys carry index 0.
+template <typename T, int GROUPS, int VEC>
+__global__ void __launch_bounds__(kMMThreads)
+mm_max_vals_kernel(const T *__restrict__ x, unsigned long long *__restrict__ keys, int nA, int nB, int rows_per_block) {
+    constexpr int NL = kMMSlots / VEC;
+    constexpr int RU = 4;
+    const int b = blockIdx.z;
+    const int row0 = blockIdx.y * rows_per_block;
+    const int col0 = blockIdx.x * kMMColsPerTile;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const size_t mat = (size_t)nA * nB;
+    const T *xb = x + (size_t)b * mat * GROUPS;
+    unsigned long long *rowkeys = keys + (size_t)b * (nA + nB);
+    unsigned long long *colkeys = rowkeys + nA;
+    float cv[kMMSlots];
+#pragma unroll
+    for (int s = 0; s < kMMSlots; ++s) cv[s] = -INFINITY;
+    const int ncols = min(kMMColsPerTile, nB - col0);
+    const int row_end = min(row0 + rows_per_block, nA);
+    for (int a0 = row0 + warp; a0 < row_end; a0 += RU * (kMMThreads / 32)) {
+        float v[RU][kMMSlots];
+#pragma unroll
+        for (int r = 0; r < RU; ++r) {
+            const int a = a0 + r * (kMMThreads / 32);
+            const size_t roff = (size_t)a * nB + col0;
+#pragma unroll
+            for (int q = 0; q < NL; ++q) {
+                const int c = q * 32 * VEC + lane * VEC;
+                float t[VEC];
+                if (a < row_end && c < ncols) {
+                    load_vec<T, VEC>(xb + roff + c, t);
+                    if (GROUPS == 2) {
+                        float w[VEC];
+                        load_vec<T, VEC>(xb + mat + roff + c, w);
+#pragma unroll
+                        for (int u = 0; u < VEC; ++u) t[u] = rnd<T>(t[u] + w[u]);
+                    }
+                } else {
+#pragma unroll
+                    for (int u = 0; u < VEC; ++u) t[u] = -INFINITY;
+                }
+#pragma unroll
+                for (int u = 0; u < VEC; ++u) v[r][q * VEC + u] = t[u];
+            }
+        }
+        float m[RU];
+#pragma unroll
+        for (int r = 0; r < RU; ++r) {
+            m[r] = -INFINITY;
+#pragma unroll
+            for (int s = 0; s < kMMSlots; ++s) { cv[s] = fmaxf(cv[s], v[r][s]); m[r] = fmaxf(m[r], v[r][s]); }
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1)
+#pragma unroll
+            for (int r = 0; r < RU; ++r) m[r] = fmaxf(m[r], __shfl_xor_sync(0xffffffffu, m[r], o));
+#pragma unroll
+        for (int r = 0; r < RU; ++r) {
+            const int a = a0 + r * (kMMThreads / 32);
+            if (lane == r && a < row_end && m[r] > -INFINITY) atomicMax(rowkeys + a, pack_key(m[r], 0u));
+        }
+    }
+    __shared__ float sm[kMMThreads / 32][kMMColsPerTile];
+#pragma unroll
+    for (int q = 0; q < NL; ++q)
+#pragma unroll
+        for (int u = 0; u < VEC; ++u) sm[warp][q * 32 * VEC + lane * VEC + u] = cv[q * VEC + u];
+    __syncthreads();
+    for (int cc = threadIdx.x; cc < ncols; cc += kMMThreads) {
+        float best = -INFINITY;
+#pragma unroll
+        for (int w = 0; w < kMMThreads / 32; ++w) best = fmaxf(best, sm[w][cc]);
+        if (best > -INFINITY) atomicMax(colkeys + col0 + cc, pack_key(best, 0u));
+    }
+}
+
 // Pass 2: y = x * ((x * 1/(rowmax+eps)) * (x * 1/(colmax+eps))).  One thread owns VEC adjacent columns (one 4/8/16-byte
 // load and store per row) and walks kMMApplyRows rows: the column reciprocals are computed once per thread, the row
 // reciprocal once per warp-row (lane i, broadcast), so the inner loop is a load, four multiplies and a store per element.
@@ -356,7 +433,7 @@ static int rows_per_block_for(int B, int nA, int nB, int tile_cols) {
     return rpb;
 }
 
-// which: bit 0 = pass 1 (maxima -> keys), bit 1 = pass 2 (keys -> y)
+// which: bit 0 = pass 1 (maxima -> keys), bit 1 = pass 2 (keys -> y), bit 2 = pass 1 without the arg-max indices
 template <typename T>
 static int mm_fwd_parts(const void *x, void *y, uint64_t *keys, int B, int nA, int nB, int groups, int which,
                         cudaStream_t st);
@@ -375,7 +452,11 @@ static int mm_fwd_parts(const void *x, void *y, uint64_t *keys, int B, int nA, i
     const int rpb = rows_per_block_for(B, nA, nB, kMMColsPerTile);
     dim3 g1((nB + kMMColsPerTile - 1) / kMMColsPerTile, (nA + rpb - 1) / rpb, B);
     const int vec1 = mm_vec_for<T>(nB, x, x);
-#define NC_MM_MAX(G, V) mm_max_kernel<T, G, V><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb)
+#define NC_MM_MAX(G, V)                                                                                                    \
+    do {                                                                                                                   \
+        if (which & 4) mm_max_vals_kernel<T, G, V><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb); \
+        else mm_max_kernel<T, G, V><<<g1, kMMThreads, 0, st>>>((const T *)x, (unsigned long long *)keys, nA, nB, rpb);      \
+    } while (0)
 #define NC_MM_MAX_V(G)                                                                         \
     switch (vec1) {                                                                            \
         case 8: if constexpr (sizeof(T) == 2) { NC_MM_MAX(G, 8); break; }                      \
@@ -447,6 +528,17 @@ extern "C" int ncnet_mutual_matching_fwd(const void *x, void *y, uint64_t *keys,
     if (dtype == NCNET_F32) return mm_fwd<float>(x, y, keys, B, nA, nB, in_groups, st);
     if (dtype == NCNET_F16) return mm_fwd<__half>(x, y, keys, B, nA, nB, in_groups, st);
     return fail("mutual_matching_fwd: unsupported dtype %d", dtype);
+}
+
+extern "C" int ncnet_mutual_matching_fwd_infer(const void *x, void *y, uint64_t *keys, int B, int nA, int nB,
+                                               int in_groups, int dtype, void *stream) {
+    NC_CHECK(x && y && keys, "mutual_matching_fwd_infer: null pointer");
+    NC_CHECK(B > 0 && nA > 0 && nB > 0 && B <= 65535, "mutual_matching_fwd_infer: bad shape B=%d nA=%d nB=%d", B, nA, nB);
+    NC_CHECK(in_groups == 1 || in_groups == 2, "mutual_matching_fwd_infer: in_groups must be 1 or 2");
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == NCNET_F32) return mm_fwd_parts<float>(x, y, keys, B, nA, nB, in_groups, 3 | 4, st);
+    if (dtype == NCNET_F16) return mm_fwd_parts<__half>(x, y, keys, B, nA, nB, in_groups, 3 | 4, st);
+    return fail("mutual_matching_fwd_infer: unsupported dtype %d", dtype);
 }
 
 extern "C" int ncnet_mutual_matching_max(const void *x, uint64_t *keys, int B, int nA, int nB, int in_groups, int dtype,
@@ -538,9 +630,10 @@ extern "C" int ncnet_mutual_matching_fwd_noalloc(const void *x, void *y, int B, 
     unsigned long long *keys = nullptr;
     if (static_keys_for_current_device(&keys)) return 1;
     cudaStream_t st = (cudaStream_t)stream;
-    // mm_fwd clears the `need` keys it is about to use (they still hold the previous call's maxima)
-    if (dtype == NCNET_F32) return mm_fwd<float>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, st);
-    if (dtype == NCNET_F16) return mm_fwd<__half>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, st);
+    // pass 1 clears the `need` keys it is about to use (they still hold the previous call's maxima); the arg-max
+    // indices are not returned by this entry point, so the values-only pass 1 serves it
+    if (dtype == NCNET_F32) return mm_fwd_parts<float>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, 3 | 4, st);
+    if (dtype == NCNET_F16) return mm_fwd_parts<__half>(x, y, (uint64_t *)keys, B, nA, nB, in_groups, 3 | 4, st);
     return fail("mutual_matching_fwd_noalloc: unsupported dtype %d", dtype);
 }
 

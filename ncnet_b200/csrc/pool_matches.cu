@@ -157,6 +157,7 @@ matches_over_rows_kernel(MatchArgs p) {
                 for (int u = 0; u < U; ++u) {
                     const int a = a0 + 8 * u;
                     if (a >= nA) break;
+                    if (v[u] < M - (sizeof(T) == 2 ? 1e-2f : 1e-4f)) continue;      // cannot reach the maximal rounded soft-max
                     const float q = rnd<T>(expf(v[u] - M) / S);
                     const unsigned long long k = pack_key(q, (uint32_t)a);
                     best = k > best ? k : best;
@@ -209,9 +210,17 @@ matches_rows_split_kernel(MatchArgs p, unsigned long long *__restrict__ keys, fl
             M[u] = mm; S[u] = ss;
         }
     }
-    float m[VEC], sacc[VEC];
+    float m[VEC], sacc[VEC], thr[VEC];
+    // PHASE 2: only values within `tau` of the column maximum can reach the maximal ROUNDED soft-max value (their
+    // soft-max is within e^-tau of the largest: 1e-4 is ~1700 fp32 ulps, 1e-2 is ~10 fp16 ulps), so the exp / divide /
+    // round / 64-bit key work is done for those few; everything else costs one compare
+    const float tau = sizeof(T) == 2 ? 1e-2f : 1e-4f;
 #pragma unroll
-    for (int u = 0; u < VEC; ++u) { m[u] = -INFINITY; sacc[u] = 0.f; }
+    for (int u = 0; u < VEC; ++u) { m[u] = -INFINITY; sacc[u] = 0.f; thr[u] = M[u] - tau; }
+    float bv[VEC];
+    int bi[VEC];
+#pragma unroll
+    for (int u = 0; u < VEC; ++u) { bv[u] = -INFINITY; bi[u] = 0; }
     if (ok)
         for (int a0 = r0 + ty; a0 < r1; a0 += 8 * kSplitU) {
             float v[kSplitU][VEC];
@@ -219,24 +228,42 @@ matches_rows_split_kernel(MatchArgs p, unsigned long long *__restrict__ keys, fl
             for (int k = 0; k < kSplitU; ++k) {
                 const int a = a0 + 8 * k;
                 if (a < r1) load_vec<T, VEC>(x + (size_t)a * nB + c0, v[k]);
-            }
+                else {
 #pragma unroll
-            for (int k = 0; k < kSplitU; ++k) {
-                const int a = a0 + 8 * k;
-                if (a >= r1) break;
+                    for (int u = 0; u < VEC; ++u) v[k][u] = -INFINITY;
+                }
+            }
+            if (PHASE == 1) {                     // one rescale of the running sum per kSplitU rows
 #pragma unroll
                 for (int u = 0; u < VEC; ++u) {
-                    if (PHASE == 1) {
-                        if (v[k][u] > m[u]) { sacc[u] = sacc[u] * expf(m[u] - v[k][u]); m[u] = v[k][u]; }
-                        sacc[u] += expf(v[k][u] - m[u]);
-                    } else {
-                        const float q = PHASE == 2 ? rnd<T>(expf(v[k][u] - M[u]) / S[u]) : v[k][u];
-                        const unsigned long long key = pack_key(q, (uint32_t)a);
-                        best[u] = key > best[u] ? key : best[u];
+                    float mn = m[u];
+#pragma unroll
+                    for (int k = 0; k < kSplitU; ++k) mn = fmaxf(mn, v[k][u]);
+                    float acc = sacc[u] * expf(m[u] - mn);        // first iteration: 0 * exp(-inf) = 0
+#pragma unroll
+                    for (int k = 0; k < kSplitU; ++k) acc += expf(v[k][u] - mn);      // rows past the end: exp(-inf) = 0
+                    sacc[u] = acc; m[u] = mn;
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < kSplitU; ++k) {
+                    const int a = a0 + 8 * k;
+#pragma unroll
+                    for (int u = 0; u < VEC; ++u) {
+                        if (PHASE == 0) {         // raw values: (value, first row) as a float / int pair
+                            if (v[k][u] > bv[u]) { bv[u] = v[k][u]; bi[u] = a; }
+                        } else if (v[k][u] >= thr[u]) {
+                            const unsigned long long key = pack_key(rnd<T>(expf(v[k][u] - M[u]) / S[u]), (uint32_t)a);
+                            best[u] = key > best[u] ? key : best[u];
+                        }
                     }
                 }
             }
         }
+    if (PHASE == 0) {
+#pragma unroll
+        for (int u = 0; u < VEC; ++u) best[u] = bv[u] > -INFINITY ? pack_key(bv[u], (uint32_t)bi[u]) : 0ull;
+    }
     // combine the 8 warps of the CTA
     __shared__ float s_m[8][32 * VEC + 1], s_s[8][32 * VEC + 1];
     __shared__ unsigned long long s_k[8][32 * VEC + 1];
@@ -333,15 +360,68 @@ static int launch_split_t(const MatchArgs &p, const SplitPlan &sp, void *scratch
 }
 
 // arg-max over the contiguous (target) axis: one warp per row
-template <typename T, int VEC>
+// STAGE: the warp copies its row into shared memory while it takes the maximum, the later passes read it from there
+// (one DRAM read of the volume; without it the rows of all resident warps exceed L2 at InLoc sizes and are re-read).
+template <typename T, int VEC, bool STAGE>
 __global__ void __launch_bounds__(256)
 matches_over_cols_kernel(MatchArgs p) {
+    extern __shared__ __align__(16) unsigned char cols_smem[];
     const int nA = p.fs1 * p.fs2, nB = p.fs3 * p.fs4;
     const int b = blockIdx.y;
     const int lane = threadIdx.x & 31;
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
     if (row >= nA) return;
     const T *x = (const T *)p.corr + ((size_t)b * nA + row) * nB;
+    if (STAGE) {
+        T *mine = reinterpret_cast<T *>(cols_smem) + (size_t)(threadIdx.x >> 5) * (((size_t)nB + 7) & ~(size_t)7);
+        float m = -INFINITY;
+        for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+            float v[VEC];
+            load_vec<T, VEC>(x + c, v);
+            store_vec<T, VEC>(mine + c, v);
+#pragma unroll
+            for (int u = 0; u < VEC; ++u) m = fmaxf(m, v[u]);
+        }
+        __syncwarp();
+        x = mine;                                  // generic pointer into shared memory from here on
+        unsigned long long best = 0ull;
+        if (p.do_softmax) {
+            m = warp_max(m);
+            float s = 0.f;
+            for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+                float v[VEC];
+                load_vec_smem<T, VEC>(x + c, v);
+#pragma unroll
+                for (int u = 0; u < VEC; ++u) s += expf(v[u] - m);
+            }
+            s = warp_sum(s);
+            const float thr = m - (sizeof(T) == 2 ? 1e-2f : 1e-4f);      // see matches_rows_split_kernel
+            for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+                float v[VEC];
+                load_vec_smem<T, VEC>(x + c, v);
+#pragma unroll
+                for (int u = 0; u < VEC; ++u)
+                    if (v[u] >= thr) {
+                        const unsigned long long k = pack_key(rnd<T>(expf(v[u] - m) / s), (uint32_t)(c + u));
+                        best = k > best ? k : best;
+                    }
+            }
+        } else {
+            float bv = -INFINITY;
+            int bi = 0;
+            for (int c = lane * VEC; c < nB; c += 32 * VEC) {
+                float v[VEC];
+                load_vec_smem<T, VEC>(x + c, v);
+#pragma unroll
+                for (int u = 0; u < VEC; ++u)
+                    if (v[u] > bv) { bv = v[u]; bi = c + u; }
+            }
+            best = bv > -INFINITY ? pack_key(bv, (uint32_t)bi) : 0ull;
+        }
+        best = warp_max_u64(best);
+        if (lane == 0) emit_match(p, b, row, (int)key_idx(best), key_val(best));
+        return;
+    }
     unsigned long long best = 0ull;
     // the row is walked in groups of VEC adjacent columns per lane (one 4/8/16-byte load; nB is a multiple of VEC)
     if (p.do_softmax) {
@@ -454,7 +534,21 @@ extern "C" int ncnet_corr_to_matches(const void *corr, int B, int fs1, int fs2, 
     } else {
         dim3 grid((nA + 7) / 8, B);
         const int vec = vec_elems((uintptr_t)corr | ((uintptr_t)nB * elem), elem, 8);
-#define NC_COLS(T, V) matches_over_cols_kernel<T, V><<<grid, 256, 0, st>>>(p)
+        // stage the rows in shared memory when 8 of them fit (rows padded to 16 bytes)
+        const size_t row_b = (((size_t)nB + 7) & ~(size_t)7) * elem;
+        const bool stage = 8 * row_b <= 200 * 1024;
+        const size_t smem = stage ? 8 * row_b : 0;
+#define NC_COLS(T, V)                                                                                                   \
+    do {                                                                                                                \
+        if (stage) {                                                                                                    \
+            cudaError_t e__ = cudaFuncSetAttribute(matches_over_cols_kernel<T, V, true>,                                \
+                                                   cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);             \
+            NC_CHECK(e__ == cudaSuccess, "corr_to_matches: smem attribute: %s", cudaGetErrorString(e__));                \
+            matches_over_cols_kernel<T, V, true><<<grid, 256, smem, st>>>(p);                                           \
+        } else {                                                                                                        \
+            matches_over_cols_kernel<T, V, false><<<grid, 256, 0, st>>>(p);                                             \
+        }                                                                                                               \
+    } while (0)
         if (dtype == NCNET_F32) {
             switch (vec) { case 4: NC_COLS(float, 4); break; case 2: NC_COLS(float, 2); break; default: NC_COLS(float, 1); }
         } else {

@@ -92,17 +92,16 @@ def exchange_halo(slab: torch.Tensor, halo: int, rank: int, world: int, group=No
     rows = slab.shape[2]
     if rows < halo:
         raise RuntimeError(f"exchange_halo: slab of {rows} rows is thinner than the halo {halo}")
-    ops, recv_lo, recv_hi = [], None, None
+    sends, recvs, recv_lo, recv_hi = [], [], None, None
     send_lo = slab[:, :, :halo].contiguous()
     send_hi = slab[:, :, rows - halo:].contiguous()
     if rank > 0:
         recv_lo = torch.empty_like(send_lo)
-        ops += [dist.P2POp(dist.isend, send_lo, rank - 1, group), dist.P2POp(dist.irecv, recv_lo, rank - 1, group)]
+        sends.append((send_lo, rank - 1)), recvs.append((recv_lo, rank - 1))
     if rank < world - 1:
         recv_hi = torch.empty_like(send_hi)
-        ops += [dist.P2POp(dist.isend, send_hi, rank + 1, group), dist.P2POp(dist.irecv, recv_hi, rank + 1, group)]
-    for req in dist.batch_isend_irecv(ops):
-        req.wait()
+        sends.append((send_hi, rank + 1)), recvs.append((recv_hi, rank + 1))
+    _p2p(sends, recvs, group)
     parts = [t for t in (recv_lo, slab, recv_hi) if t is not None]
     return torch.cat(parts, dim=2)
 
@@ -173,6 +172,17 @@ def _p2p(sends, recvs, group=None):
         req.wait()
     for t, h in landing:
         t.copy_(h)
+
+
+def _all_gather(outs, t, group=None):
+    """dist.all_gather; under gloo CUDA tensors go through the host (gloo gathers CPU tensors only)."""
+    if dist.get_backend(group) == "gloo" and t.is_cuda:
+        houts = [torch.empty(o.shape, dtype=o.dtype) for o in outs]
+        dist.all_gather(houts, t.cpu(), group=group)
+        for o, h in zip(outs, houts):
+            o.copy_(h)
+    else:
+        dist.all_gather(outs, t, group=group)
 
 
 def exchange_halo_cb16_(act, halo: int, rank: int, world: int, group=None) -> int:
@@ -283,7 +293,7 @@ def slab_corr_to_matches(corr_slab: torch.Tensor, fs1: int, rank: int, world: in
         padded = torch.zeros((b, max(counts)), device=dev, dtype=t.dtype)      # equal sizes for the collective
         padded[:, : t.shape[1]] = t
         outs = [torch.empty_like(padded) for _ in range(world)]
-        dist.all_gather(outs, padded, group=group)
+        _all_gather(outs, padded, group)
         return [o[:, :c] for o, c in zip(outs, counts)]
 
     if invert_matching_direction:
@@ -312,7 +322,7 @@ def slab_corr_to_matches(corr_slab: torch.Tensor, fs1: int, rank: int, world: in
     cand = torch.stack([m_loc.double(), s_loc.double(), ia_g.double(), ja_g.double()], 0).contiguous()   # [4,b,nb]
     if multi:
         allc = [torch.empty_like(cand) for _ in range(world)]
-        dist.all_gather(allc, cand, group=group)
+        _all_gather(allc, cand, group)
         allc = torch.stack(allc, 0)                           # [world,4,b,nb]
     else:
         allc = cand[None]

@@ -69,5 +69,5 @@ def inloc_matches(corr4d, delta4d=None, k_size=1, do_softmax=True, matching_both
     with torch.cuda.device(dev):
         _cabi.check(lib.ncnet_matches_sort_unique(*[_ptr(t) for t in a], n1, *[_ptr(t) for t in b], n2, n[0], n[1], n[2], n[3],
                                                   _ptr(rows), _ptr(count), _ptr(scratch), _stream()), "matches_sort_unique")
-    _count(2 if n2 else 1)
+    _count(4 if n2 else 1)
     return rows, count

@@ -185,11 +185,14 @@ class _MutualMatchingFn(torch.autograd.Function):
         na, nb = f1 * f2, f3 * f4
         y = torch.empty(b, 1, f1, f2, f3, f4, device=x.device, dtype=x.dtype)
         keys = torch.empty(b * (na + nb), device=x.device, dtype=torch.int64)
+        # no gradient will be asked for: pass 1 need not track the arg-max indices the backward pass consumes
+        infer = not ctx.needs_input_grad[0]
+        fn = _cabi.lib().ncnet_mutual_matching_fwd_infer if infer else _cabi.lib().ncnet_mutual_matching_fwd
         with torch.cuda.device(x.device):
-            _cabi.check(_cabi.lib().ncnet_mutual_matching_fwd(_ptr(xc), _ptr(y), _ptr(keys), b, na, nb, g, _dt(xc),
-                                                              _stream()), "mutual_matching_fwd")
+            _cabi.check(fn(_ptr(xc), _ptr(y), _ptr(keys), b, na, nb, g, _dt(xc), _stream()), "mutual_matching_fwd")
         _count(2)
-        ctx.save_for_backward(xc, keys)
+        if not infer:
+            ctx.save_for_backward(xc, keys)
         return y
 
     @staticmethod
