@@ -289,6 +289,72 @@ mm_apply_kernel(const T *__restrict__ x, T *__restrict__ y, const unsigned long 
     }
 }
 
+// Pass 2 for fp16 volumes on packed half2 arithmetic.  The reference's half path rounds after every operation; a
+// native half multiply rounds the exact product once, which is the same value as the fp32 product of two halves
+// (exact: 22 significant bits) rounded to half -- so  qa*qb  and  x*(qa*qb)  are single HMUL2s, and the two quotients
+// are fp32 multiplies by the row / column reciprocal packed to half2 by one conversion: ~5 instructions per element
+// instead of ~23 (this pass was issue-bound on fp16 volumes).
+template <int GROUPS, int VEC>
+__global__ void __launch_bounds__(256)
+mm_apply_half_kernel(const __half *__restrict__ x, __half *__restrict__ y, const unsigned long long *__restrict__ keys,
+                     int nA, int nB) {
+    static_assert(VEC % 2 == 0, "half2 lanes");
+    constexpr int NP = VEC / 2;
+    const int b = gridDim.z - 1 - blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int c0 = (blockIdx.x * 32 + lane) * VEC;
+    const int a0 = ((gridDim.y - 1 - blockIdx.y) * 8 + warp) * kMMApplyRows;
+    const size_t mat = (size_t)nA * nB;
+    const __half *xb = x + (size_t)b * mat * GROUPS;
+    __half *yb = y + (size_t)b * mat;
+    const size_t kb = (size_t)b * (nA + nB);
+    const bool col_ok = c0 < nB;
+    float crcp[VEC];
+#pragma unroll
+    for (int u = 0; u < VEC; ++u)
+        crcp[u] = col_ok ? __frcp_rn(rnd<__half>(key_val_hi(keys, kb + nA + c0 + u) + kMMEps)) : 0.f;
+    float my_rrcp = 0.f;
+    if (lane < kMMApplyRows && a0 + lane < nA) my_rrcp = __frcp_rn(rnd<__half>(key_val_hi(keys, kb + a0 + lane) + kMMEps));
+    union Vec { uint4 q; uint2 d; unsigned w; __half2 h[NP]; };
+    Vec v[kMMApplyRows];
+    auto ld = [&](const __half *p, Vec &o) {
+        if constexpr (VEC == 8) o.q = __ldg(reinterpret_cast<const uint4 *>(p));
+        else if constexpr (VEC == 4) o.d = __ldg(reinterpret_cast<const uint2 *>(p));
+        else o.w = __ldg(reinterpret_cast<const unsigned *>(p));
+    };
+#pragma unroll
+    for (int r = 0; r < kMMApplyRows; ++r) {       // all row loads in flight before the first use
+        const int a = a0 + r;
+        if (a < nA && col_ok) {
+            ld(xb + (size_t)a * nB + c0, v[r]);
+            if (GROUPS == 2) {
+                Vec w;
+                ld(xb + mat + (size_t)a * nB + c0, w);
+#pragma unroll
+                for (int q = 0; q < NP; ++q) v[r].h[q] = __hadd2(v[r].h[q], w.h[q]);
+            }
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < kMMApplyRows; ++r) {
+        const float rrcp = __shfl_sync(0xffffffffu, my_rrcp, r);
+        const int a = a0 + r;
+        if (a >= nA || !col_ok) continue;
+        Vec o;
+#pragma unroll
+        for (int q = 0; q < NP; ++q) {
+            const float2 xf = __half22float2(v[r].h[q]);
+            const __half2 qa = __floats2half2_rn(xf.x * rrcp, xf.y * rrcp);                       // x / (max over B + eps)
+            const __half2 qb = __floats2half2_rn(xf.x * crcp[2 * q], xf.y * crcp[2 * q + 1]);     // x / (max over A + eps)
+            o.h[q] = __hmul2(v[r].h[q], __hmul2(qa, qb));
+        }
+        __half *dst = yb + (size_t)a * nB + c0;
+        if constexpr (VEC == 8) *reinterpret_cast<uint4 *>(dst) = o.q;
+        else if constexpr (VEC == 4) *reinterpret_cast<uint2 *>(dst) = o.d;
+        else *reinterpret_cast<unsigned *>(dst) = o.w;
+    }
+}
+
 // Row / column sums without floating-point atomics (their arrival order would make the result differ from run to
 // run).  The sum kernels run on a (column tile, row strip, batch) grid; every CTA owns one (tile, strip) cell and
 // writes its partial row sums to rpart[b][tile][a] and its partial column sums to cpart[b][strip][c].  Every entry
@@ -473,7 +539,13 @@ static int mm_fwd_parts(const void *x, void *y, uint64_t *keys, int B, int nA, i
     const int vec = mm_vec_for<T>(nB, x, y);
     dim3 g2((nB + 32 * vec - 1) / (32 * vec), (nA + 8 * kMMApplyRows - 1) / (8 * kMMApplyRows), B);
     NC_CHECK(g2.y <= 65535, "mutual_matching: too many rows");
-#define NC_MM_APPLY(G, V) mm_apply_kernel<T, G, V><<<g2, 256, 0, st>>>((const T *)x, (T *)y, (const unsigned long long *)keys, nA, nB)
+#define NC_MM_APPLY(G, V)                                                                                                     \
+    do {                                                                                                                      \
+        if constexpr (sizeof(T) == 2 && (V) % 2 == 0)                                                                         \
+            mm_apply_half_kernel<G, ((V) % 2 == 0 ? (V) : 2)><<<g2, 256, 0, st>>>((const __half *)x, (__half *)y, (const unsigned long long *)keys, nA, nB); \
+        else                                                                                                                  \
+            mm_apply_kernel<T, G, V><<<g2, 256, 0, st>>>((const T *)x, (T *)y, (const unsigned long long *)keys, nA, nB);      \
+    } while (0)
 #define NC_MM_APPLY_V(G)                                                                       \
     switch (vec) {                                                                             \
         case 8: if constexpr (sizeof(T) == 2) { NC_MM_APPLY(G, 8); break; }                    \

@@ -181,7 +181,7 @@ matches_over_rows_kernel(MatchArgs p) {
 // chunk order) and takes the arg-max of the rounded soft-max values with a 64-bit atomicMax of (value, first index);
 // without soft-max kernel 1 does the atomicMax directly.  A last kernel turns the keys into matches.
 // ---------------------------------------------------------------------------------------------
-constexpr int kSplitU = 4;          // rows in flight per warp iteration
+constexpr int kSplitU = 8;          // rows in flight per warp iteration
 
 template <typename T, int VEC, int PHASE>        // PHASE 0: raw arg-max; 1: soft-max statistics; 2: soft-max arg-max
 __global__ void __launch_bounds__(256)
@@ -375,12 +375,22 @@ matches_over_cols_kernel(MatchArgs p) {
     if (STAGE) {
         T *mine = reinterpret_cast<T *>(cols_smem) + (size_t)(threadIdx.x >> 5) * (((size_t)nB + 7) & ~(size_t)7);
         float m = -INFINITY;
-        for (int c = lane * VEC; c < nB; c += 32 * VEC) {
-            float v[VEC];
-            load_vec<T, VEC>(x + c, v);
-            store_vec<T, VEC>(mine + c, v);
+        for (int c4 = lane * VEC; c4 < nB; c4 += 4 * 32 * VEC) {      // four loads in flight per lane
+            float v[4][VEC];
 #pragma unroll
-            for (int u = 0; u < VEC; ++u) m = fmaxf(m, v[u]);
+            for (int k = 0; k < 4; ++k) {
+                const int c = c4 + k * 32 * VEC;
+                if (c < nB) load_vec<T, VEC>(x + c, v[k]);
+            }
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int c = c4 + k * 32 * VEC;
+                if (c < nB) {
+                    store_vec<T, VEC>(mine + c, v[k]);
+#pragma unroll
+                    for (int u = 0; u < VEC; ++u) m = fmaxf(m, v[k][u]);
+                }
+            }
         }
         __syncwarp();
         x = mine;                                  // generic pointer into shared memory from here on
