@@ -538,6 +538,228 @@ conv4d_tc_kernel(const TcArgs p) {
 
 
 // ---------------------------------------------------------------------------------------------
+// Single-output-channel layers (mode M2) as a WALK along jA.
+//
+// In the kernel above a CTA owns one output plane (i, j) and stages its k*k input planes (i+t1-p, j+t2-p): every
+// input plane travels from L2 to shared memory k*k times, and at Cout = 1 (N = 16 or 32 columns per MMA) that traffic,
+// not the tensor pipe, bounds the layer (measured: 12.7 GB through the L2->SM crossbar for a 0.54 GB input at the
+// PF-Pascal shape; the InLoc 16->1 layer moves 9x its 3.8 GB input).  Here a CTA owns (b, group, i, row chunk) and
+// walks the input columns jj = 0 .. d2-1.  A staged plane (i+t1-p, jj) is used at once for the k outputs
+// j = jj-p .. jj+p it contributes to (weights of tap t2 = jj-j+p), whose accumulators are k live slots of TMEM
+// (slot = j mod k); each input plane is staged k times instead of k*k.  Output j is complete when column j+p is done:
+// the issuer commits to the slot's "full" barrier and goes on with column j+p+1, whose MMAs touch the other k-1 live
+// outputs first and the new output j+p+1+... (which reuses the freed slot) last, so the epilogue warps' drain of the
+// slot overlaps the tensor pipe's work.  The epilogue is the M2 one: the k*k tap columns are parked in shared memory
+// and each output position sums its k*k shifted reads, plus bias and ReLU, and stores planar.
+// ---------------------------------------------------------------------------------------------
+constexpr int kWalkStagesMax = 8;
+constexpr int kWalkSlotsMax = 5;
+
+struct WalkArgs {
+    const __half *act;      // CB16 input
+    const __half *wp;       // [G][k*k][2][N][8] fp16 (mode M2 packing)
+    const float *bias;
+    void *out;              // planar [B, G, vol]
+    int B, G, Gx;
+    int d1, d2, d3, d4, KS, P;
+    int R, nchunks, NT, N, NG;
+    int npos_pad, stages;
+    int relu, out_f16;
+    uint32_t idesc, stage_bytes, w_bytes, out_off, w_off;
+};
+
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv4d_tc_walk_kernel(const WalkArgs p) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full_bar[kWalkStagesMax], empty_bar[kWalkStagesMax], w_bar;
+    __shared__ __align__(8) uint64_t acc_full[kWalkSlotsMax], acc_empty[kWalkSlotsMax];
+    __shared__ uint32_t tmem_base_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int bx = blockIdx.x;
+    const int chunk = bx % p.nchunks; bx /= p.nchunks;
+    const int i = bx % p.d1; bx /= p.d1;
+    const int g = bx % p.G;
+    const int b = bx / p.G;
+    const int K = p.KS, PAD = K / 2;
+    const int k0 = chunk * p.R;
+    const int rows_out = min(p.R, p.d3 - k0);
+    const int rows_pad = p.d3 + 2 * PAD;
+    const size_t plane_cb = (size_t)rows_pad * p.P;
+    const size_t ij_count = (size_t)p.d1 * p.d2;
+    const int out_rows = p.NT * 128;
+
+    if (warp == 1 && lane == 0) {
+        for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+        for (int s = 0; s < K; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 1); }
+        mbar_init(&w_bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    {   // the tail of each channel-half buffer behind the copied rows is read by the last tiles' (discarded) rows
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        const int copied = min(p.R + K - 1, rows_pad - k0) * p.P;
+        const int tail = p.npos_pad - copied;
+        for (int e = threadIdx.x; e < p.stages * 2 * tail; e += kTcThreads) {
+            const int s = e / (2 * tail), r = e - s * 2 * tail;
+            const int half = r / tail, pos = copied + (r - half * tail);
+            reinterpret_cast<uint4 *>(smem + (size_t)s * p.stage_bytes)[(size_t)half * p.npos_pad + pos] = z;
+        }
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t sm0 = smem_u32_pinned(smem);
+    const uint32_t full0 = smem_u32_pinned(full_bar), empty0 = smem_u32_pinned(empty_bar);
+    const uint32_t accf0 = smem_u32_pinned(acc_full), acce0 = smem_u32_pinned(acc_empty);
+    const int t1_lo = max(0, PAD - i), t1_hi = min(K - 1, p.d1 - 1 - i + PAD);      // valid d1 taps of this output row
+
+    if (warp == 0) {
+        // ===== producer: the weights once, then the planes (i+t1-p, jj) column by column =====
+        if (elect_one()) {
+            const uint32_t wb = smem_u32(&w_bar);
+            asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(wb), "r"(p.w_bytes) : "memory");
+            bulk_g2s_u32(sm0 + p.w_off, p.wp + (size_t)g * (p.w_bytes / 2), p.w_bytes, wb);
+            const int rows_in = min(p.R + K - 1, rows_pad - k0);
+            const uint32_t half_bytes = (uint32_t)rows_in * p.P * 16u;
+            const size_t bg = (size_t)b * p.Gx + (p.Gx == 1 ? 0 : g);
+            const size_t plane_halves = plane_cb * 8;
+            const __half *src_base = p.act + bg * 2 * ij_count * plane_halves + (size_t)k0 * p.P * 8;
+            const size_t half_off = ij_count * plane_halves;
+            const uint32_t half1_off = (uint32_t)p.npos_pad * 16u;
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int jj = 0; jj < p.d2; ++jj)
+                for (int t1 = t1_lo; t1 <= t1_hi; ++t1) {
+                    const int ii = i + t1 - PAD;
+                    mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
+                    const uint32_t sb = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(2u * half_bytes) : "memory");
+                    const __half *src0 = src_base + (size_t)(ii * p.d2 + jj) * plane_halves;
+                    bulk_g2s_u32(sb, src0, half_bytes, fb);
+                    bulk_g2s_u32(sb + half1_off, src0 + half_off, half_bytes, fb);
+                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (elect_one()) {
+            mbar_wait(&w_bar, 0);
+            const uint32_t lbo_a = (uint32_t)p.npos_pad << 16, lbo_b = (uint32_t)p.N << 16;
+            const uint64_t hi = (uint64_t)((128u >> 4) | (1u << 14)) << 32;                 // SBO = 128 B, descriptor version 1
+            const uint32_t sm4 = sm0 >> 4, stage4 = p.stage_bytes >> 4, w4 = (sm0 + p.w_off) >> 4;
+            const uint32_t slab4 = (uint32_t)p.N * 2u;                                      // 16-byte units per (t1,t2) weight slab
+            int stage = 0;
+            uint32_t phase = 0;
+            for (int jj = 0; jj < p.d2; ++jj) {
+                const int jl = max(0, jj - PAD), jh = min(p.d2 - 1, jj + PAD);
+                // the output that starts at this column (its first contribution): j = jj + PAD, or every touched output at jj = 0
+                for (int t1 = t1_lo; t1 <= t1_hi; ++t1) {
+                    mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const uint32_t s4 = sm4 + (uint32_t)stage * stage4;
+                    for (int j = jl; j <= jh; ++j) {                 // ascending: the newest output (largest j) comes last
+                        const int slot = j % K;
+                        const bool is_new = (jj == 0 || j == jj + PAD) && t1 == t1_lo;
+                        if (is_new && j >= K) {                      // the slot's previous output (j - K) must have been drained
+                            mbar_wait_u32(acce0 + (uint32_t)slot * 8u, (uint32_t)((j / K) - 1) & 1u);
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        }
+                        const int t2 = jj - j + PAD;
+                        const uint64_t bdesc = hi | (uint64_t)(lbo_b | (w4 + (uint32_t)(t1 * K + t2) * slab4));
+                        const uint32_t dcol = tmem_base + (uint32_t)(slot * p.NT * p.N);
+                        for (int t = 0; t < p.NT; ++t)
+                            umma_f16(dcol + (uint32_t)(t * p.N), hi | (uint64_t)(lbo_a | (s4 + (uint32_t)t * 128u)), bdesc, p.idesc,
+                                     is_new ? 0u : 1u);
+                    }
+                    umma_commit_to<false>(empty0 + (uint32_t)stage * 8u);
+                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
+                }
+                // outputs whose last contributing column this was
+                for (int j = jl; j <= jh; ++j)
+                    if (min(p.d2 - 1, j + PAD) == jj) umma_commit_to<false>(accf0 + (uint32_t)(j % K) * 8u);
+            }
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: one output plane (chunk) per step of the walk =====
+        const int q = warp & 3;
+        const int et = threadIdx.x - 64;
+        const uint32_t osm = sm0 + p.out_off;
+        const bool wide = p.NG > 16;
+        const float bias0 = p.bias ? __ldg(p.bias) : 0.f;
+        const size_t plane_pos = (size_t)p.d3 * p.d4;
+        const size_t vol = ij_count * plane_pos;
+        for (int j = 0; j < p.d2; ++j) {
+            const int slot = j % K;
+            mbar_wait_sleep(&acc_full[slot], (uint32_t)(j / K) & 1u, 200);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * p.NT * p.N);
+            for (int t = 0; t < p.NT; ++t) {
+                const int row = t * 128 + q * 32 + lane;
+                uint32_t ra[16], rb[16];
+                tmem_ld16_issue(lane_base + (uint32_t)(t * p.N), ra);
+                if (wide) tmem_ld16_issue(lane_base + (uint32_t)(t * p.N + 16), rb);
+                tmem_ld16_wait(ra);
+                if (wide) tmem_ld16_wait(rb);
+#pragma unroll
+                for (int u = 0; u < 16; ++u)
+                    if (u < p.NG) sts_f32(osm + (uint32_t)(u * out_rows + row) * 4u, __uint_as_float(ra[u]));
+                if (wide) {
+#pragma unroll
+                    for (int u = 0; u < 16; ++u)
+                        if (16 + u < p.NG) sts_f32(osm + (uint32_t)((16 + u) * out_rows + row) * 4u, __uint_as_float(rb[u]));
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            asm volatile("bar.sync 1, 128;" ::: "memory");
+            if (et == 0) {       // the slot may be overwritten: every warp's TMEM reads have completed
+                asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acce0 + (uint32_t)slot * 8u) : "memory");
+            }
+            // planar store: one warp per output row, lanes along l; the k*k tap columns summed at their shifts
+            const int ew = et >> 5;
+            for (int rr = ew; rr < rows_out; rr += 4) {
+                const size_t off0 = ((size_t)b * p.G + g) * vol + ((size_t)i * p.d2 + j) * plane_pos + (size_t)(k0 + rr) * p.d4;
+                for (int l = lane; l < p.d4; l += 32) {
+                    const uint32_t src = osm + (uint32_t)(rr * p.P + l) * 4u, col = (uint32_t)out_rows * 4u;
+                    float a0 = bias0, a1 = 0.f, a2 = 0.f;
+                    if (K == 5) {
+                        float a3 = 0.f, a4 = 0.f;
+#pragma unroll
+                        for (int t3 = 0; t3 < 5; ++t3) {
+                            const uint32_t s3 = src + (uint32_t)(t3 * 5) * col + (uint32_t)(t3 * p.P) * 4u;
+                            a0 += lds_f32(s3); a1 += lds_f32(s3 + col + 4u); a2 += lds_f32(s3 + 2u * col + 8u);
+                            a3 += lds_f32(s3 + 3u * col + 12u); a4 += lds_f32(s3 + 4u * col + 16u);
+                        }
+                        a0 = (a0 + a1) + (a2 + a3) + a4;
+                    } else {
+#pragma unroll
+                        for (int t3 = 0; t3 < 3; ++t3) {
+                            const uint32_t s3 = src + (uint32_t)(t3 * 3) * col + (uint32_t)(t3 * p.P) * 4u;
+                            a0 += lds_f32(s3); a1 += lds_f32(s3 + col + 4u); a2 += lds_f32(s3 + 2u * col + 8u);
+                        }
+                        a0 = (a0 + a1) + a2;
+                    }
+                    if (p.relu) a0 = fmaxf(a0, 0.f);
+                    if (p.out_f16) ((__half *)p.out)[off0 + l] = __float2half_rn(a0);
+                    else ((float *)p.out)[off0 + l] = a0;
+                }
+            }
+            asm volatile("bar.sync 1, 128;" ::: "memory");        // the column planes are free for the next output
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
 // CB16 packing
 // ---------------------------------------------------------------------------------------------
 // planar [nblk, C, vol] (T) -> CB16 [nblk][2][ij][d3+2p][P][8], halo = 0.
@@ -1048,6 +1270,49 @@ static TcPlan tc_plan(int Cin_e, int Cout_e, int k, int d3, int d4, bool cb_mask
 
 static size_t align256(size_t v) { return (v + 255) & ~(size_t)255; }
 
+struct WalkPlan {
+    bool ok;
+    int N, NT, R, nchunks, npos_pad, stages;
+    uint32_t stage_bytes, w_bytes, w_off, out_off;
+    size_t smem;
+};
+
+// plan of conv4d_tc_walk_kernel: k live accumulator slots of NT tiles x N columns in the 512 TMEM columns
+static WalkPlan walk_plan(int k, int d3, int d4) {
+    WalkPlan w{};
+    w.ok = false;
+    if (k != 3 && k != 5) return w;
+    w.N = (k * k + 15) / 16 * 16;
+    const int nt_max = 512 / (k * w.N);
+    const int P = d4 + k - 1, max_shift = (k - 1) * P + (k - 1);
+    auto tiles = [&](int R) { return ((R - 1) * P + d4 + max_shift + 127) / 128; };
+    int R = d3;
+    while (R >= 1 && tiles(R) > nt_max) --R;
+    if (R < 1) return w;
+    w.nchunks = (d3 + R - 1) / R;
+    w.R = (d3 + w.nchunks - 1) / w.nchunks;
+    w.NT = tiles(w.R);
+    int npos = w.NT * 128;
+    if ((w.R + k - 1) * P > npos) npos = (w.R + k - 1) * P;
+    npos = (npos + 7) / 8 * 8;
+    if (npos > 16383) return w;
+    w.npos_pad = npos;
+    w.stage_bytes = ((uint32_t)(2 * npos * 16) + 127u) / 128u * 128u;
+    w.w_bytes = (uint32_t)(k * k * w.N * 32);
+    const uint32_t out_bytes = ((uint32_t)(w.NT * 128 * k * k * 4) + 127u) / 128u * 128u;
+    const uint32_t fixed = ((w.w_bytes + 127u) / 128u * 128u) + out_bytes;
+    const uint32_t budget = 220u * 1024u;
+    if (fixed + 2u * w.stage_bytes > budget) return w;
+    int stages = (int)((budget - fixed) / w.stage_bytes);
+    w.stages = stages > kWalkStagesMax ? kWalkStagesMax : stages;
+    w.w_off = (uint32_t)w.stages * w.stage_bytes;
+    w.out_off = w.w_off + ((w.w_bytes + 127u) / 128u * 128u);
+    w.smem = (size_t)w.out_off + out_bytes;
+    if (w.smem < 120u * 1024u) w.smem = 120u * 1024u;      // one CTA per SM: each takes all 512 TMEM columns
+    w.ok = true;
+    return w;
+}
+
 size_t conv4d_tc_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric) {
     const int G = symmetric ? 2 : 1;
     (void)Cin; (void)Cout;
@@ -1100,6 +1365,27 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
         const int blocks = (int)((total + 255) / 256 < 1184 ? (total + 255) / 256 : 1184);
         pack_w_tc_kernel<<<blocks, 256, 0, st>>>(w, wp, a);
         NC_LAUNCH_OK("pack_w_tc_kernel");
+    }
+    if (pl.mode == 2 && !mask && (y_dtype == NCNET_F32 || y_dtype == NCNET_F16)) {
+        // single output channel: walk along jA with k live output planes in TMEM (each input plane staged k times, not k*k)
+        const WalkPlan wk = walk_plan(d.k, d3, d4);
+        if (wk.ok) {
+            WalkArgs q{};
+            q.act = act; q.wp = wp; q.bias = bias; q.out = y;
+            q.B = B; q.G = d.G_e; q.Gx = Gx;
+            q.d1 = d1; q.d2 = d2; q.d3 = d3; q.d4 = d4; q.KS = d.k; q.P = pl.P;
+            q.R = wk.R; q.nchunks = wk.nchunks; q.NT = wk.NT; q.N = wk.N; q.NG = d.k * d.k;
+            q.npos_pad = wk.npos_pad; q.stages = wk.stages; q.relu = relu; q.out_f16 = y_dtype == NCNET_F16;
+            q.idesc = (1u << 4) | ((uint32_t)(wk.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            q.stage_bytes = wk.stage_bytes; q.w_bytes = wk.w_bytes; q.out_off = wk.out_off; q.w_off = wk.w_off;
+            cudaError_t e = cudaFuncSetAttribute(conv4d_tc_walk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)wk.smem);
+            NC_CHECK(e == cudaSuccess, "conv4d(tc,walk): smem attribute: %s", cudaGetErrorString(e));
+            const long long ctas = (long long)B * d.G_e * d1 * wk.nchunks;
+            NC_CHECK(ctas < (1ll << 31), "conv4d(tc,walk): grid too large");
+            conv4d_tc_walk_kernel<<<(unsigned)ctas, kTcThreads, wk.smem, st>>>(q);
+            NC_LAUNCH_OK("conv4d_tc_walk_kernel");
+            return 0;
+        }
     }
     TcArgs a{};
     a.act = act; a.wp = wp; a.bias = bias; a.mask = mask; a.out = y;
