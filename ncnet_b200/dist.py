@@ -44,35 +44,44 @@ class GradBucket:
         p0 = self.params[0]
         self.flat = torch.zeros(self.numel, device=p0.device, dtype=torch.float32)
 
-    def pack(self) -> torch.Tensor:
-        off = 0
+    def _views(self):
+        off, out = 0, []
         for p in self.params:
             n = p.numel()
-            if p.grad is None:
-                self.flat[off:off + n].zero_()
-            else:
-                self.flat[off:off + n].copy_(p.grad.reshape(-1))
+            out.append(self.flat[off:off + n].view_as(p))
             off += n
+        return out
+
+    def pack(self) -> torch.Tensor:
+        """One multi-tensor copy of all gradients into the flat buffer (a missing gradient counts as zero)."""
+        views = self._views()
+        have = [(v, p.grad) for v, p in zip(views, self.params) if p.grad is not None]
+        for v, p in zip(views, self.params):
+            if p.grad is None:
+                v.zero_()
+        if have:
+            torch._foreach_copy_([v for v, _ in have], [g for _, g in have])
         return self.flat
 
     def unpack(self) -> None:
-        off = 0
-        for p in self.params:
-            n = p.numel()
-            g = self.flat[off:off + n].view_as(p).to(p.dtype)
+        views = self._views()
+        for v, p in zip(views, self.params):
             if p.grad is None:
-                p.grad = g.clone()
-            else:
-                p.grad.copy_(g)
-            off += n
+                p.grad = torch.empty_like(p)
+        torch._foreach_copy_([p.grad for p in self.params], views)
 
-    def all_reduce_mean(self, group=None) -> None:
-        """grad <- mean over ranks (each rank's loss is the mean over its equal-sized shard)."""
+    def all_reduce_mean(self, group=None, local_batch=None, global_batch=None) -> None:
+        """grad <- gradient of the mean loss over the GLOBAL batch.  Each rank's loss is the mean over its own shard,
+        so with equal shards this is the plain mean over ranks (the default); with unequal shards (batch not divisible
+        by the world size) pass ``local_batch`` and ``global_batch``: the rank's gradient is weighted by its share."""
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
             return
+        if (local_batch is None) != (global_batch is None):
+            raise ValueError("all_reduce_mean: give both local_batch and global_batch, or neither")
+        weight = 1.0 / dist.get_world_size(group) if local_batch is None else float(local_batch) / float(global_batch)
         self.pack()
+        self.flat.mul_(weight)
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
-        self.flat.div_(dist.get_world_size(group))
         self.unpack()
 
 
