@@ -568,6 +568,75 @@ struct WalkArgs {
     uint32_t idesc, stage_bytes, w_bytes, out_off, w_off;
 };
 
+// MMA issue loop of the walk (one lane).  K_C / NT_C > 0: compile-time kernel size and tile count -- the per-MMA work
+// of the issuing lane is then two adds (it runs ~10 cycles per instruction, an M128xN32xK16 MMA retires in 40).
+template <int K_C, int NT_C>
+__device__ __forceinline__ void walk_issue(const WalkArgs &p, int t1_lo, int t1_hi, uint32_t sm0, uint32_t tmem_base,
+                                           uint32_t full0, uint32_t empty0, uint32_t accf0, uint32_t acce0) {
+    constexpr int KM = K_C > 0 ? K_C : 5, NTM = NT_C > 0 ? NT_C : 1;
+    const int K = K_C > 0 ? K_C : p.KS, NT = NT_C > 0 ? NT_C : p.NT, PAD = K / 2;
+    const uint32_t lbo_a = (uint32_t)p.npos_pad << 16, lbo_b = (uint32_t)p.N << 16;
+    const uint64_t hi = (uint64_t)((128u >> 4) | (1u << 14)) << 32;                 // SBO = 128 B, descriptor version 1
+    const uint32_t sm4 = sm0 >> 4, stage4 = p.stage_bytes >> 4, w4 = (sm0 + p.w_off) >> 4;
+    const uint32_t slab4 = (uint32_t)p.N * 2u;                                      // 16-byte units per (t1,t2) weight slab
+    const uint32_t slot_cols = (uint32_t)(NT * p.N);
+    uint32_t a_rel[NTM];
+#pragma unroll
+    for (int t = 0; t < NTM; ++t) a_rel[t] = lbo_a | ((uint32_t)t * 128u);
+    int stage = 0;
+    uint32_t phase = 0;
+    int slot_lo = (K - PAD) % K;                     // slot of output j = jj - PAD, kept incrementally (j mod K)
+    for (int jj = 0; jj < p.d2; ++jj) {
+        for (int t1 = t1_lo; t1 <= t1_hi; ++t1) {
+            mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint32_t s4 = sm4 + (uint32_t)stage * stage4;
+            const uint32_t wrow = lbo_b | (w4 + (uint32_t)(t1 * K + (K - 1)) * slab4);     // tap t2 = K-1-dd for output dd
+            int slot = slot_lo;
+#pragma unroll
+            for (int dd = 0; dd < KM; ++dd) {        // outputs j = jj - PAD + dd, ascending: the newest comes last
+                if (dd < K) {
+                    const int j = jj - PAD + dd;
+                    if (j >= 0 && j < p.d2) {
+                        const bool is_new = (jj == 0 || dd == K - 1) && t1 == t1_lo;
+                        if (is_new && j >= K) {      // the slot's previous output (j - K) must have been drained
+                            mbar_wait_u32(acce0 + (uint32_t)slot * 8u, (uint32_t)((j / K) - 1) & 1u);
+                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        }
+                        const uint64_t bdesc = hi | (uint64_t)(wrow - (uint32_t)dd * slab4);
+                        const uint32_t dcol = tmem_base + (uint32_t)slot * slot_cols;
+                        const uint32_t acc = is_new ? 0u : 1u;
+                        if (NT_C > 0) {
+#pragma unroll
+                            for (int t = 0; t < NTM; ++t)
+                                umma_f16(dcol + (uint32_t)(t * p.N), hi | (uint64_t)(a_rel[t] + s4), bdesc, p.idesc, acc);
+                        } else {
+                            for (int t = 0; t < NT; ++t)
+                                umma_f16(dcol + (uint32_t)(t * p.N), hi | (uint64_t)((lbo_a | ((uint32_t)t * 128u)) + s4), bdesc, p.idesc, acc);
+                        }
+                    }
+                    if (++slot == K) slot = 0;
+                }
+            }
+            umma_commit_to<false>(empty0 + (uint32_t)stage * 8u);
+            if (++stage == p.stages) { stage = 0; phase ^= 1; }
+        }
+        // outputs whose last contributing column this was: j = jj - PAD, and at the last column every later one
+        {
+            int slot = slot_lo;
+#pragma unroll
+            for (int dd = 0; dd < KM; ++dd) {
+                if (dd < K) {
+                    const int j = jj - PAD + dd;
+                    if (j >= 0 && j < p.d2 && min(p.d2 - 1, j + PAD) == jj) umma_commit_to<false>(accf0 + (uint32_t)slot * 8u);
+                    if (++slot == K) slot = 0;
+                }
+            }
+        }
+        if (++slot_lo == K) slot_lo = 0;
+    }
+}
+
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv4d_tc_walk_kernel(const WalkArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -651,40 +720,11 @@ conv4d_tc_walk_kernel(const WalkArgs p) {
         // ===== MMA issuer =====
         if (elect_one()) {
             mbar_wait(&w_bar, 0);
-            const uint32_t lbo_a = (uint32_t)p.npos_pad << 16, lbo_b = (uint32_t)p.N << 16;
-            const uint64_t hi = (uint64_t)((128u >> 4) | (1u << 14)) << 32;                 // SBO = 128 B, descriptor version 1
-            const uint32_t sm4 = sm0 >> 4, stage4 = p.stage_bytes >> 4, w4 = (sm0 + p.w_off) >> 4;
-            const uint32_t slab4 = (uint32_t)p.N * 2u;                                      // 16-byte units per (t1,t2) weight slab
-            int stage = 0;
-            uint32_t phase = 0;
-            for (int jj = 0; jj < p.d2; ++jj) {
-                const int jl = max(0, jj - PAD), jh = min(p.d2 - 1, jj + PAD);
-                // the output that starts at this column (its first contribution): j = jj + PAD, or every touched output at jj = 0
-                for (int t1 = t1_lo; t1 <= t1_hi; ++t1) {
-                    mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
-                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                    const uint32_t s4 = sm4 + (uint32_t)stage * stage4;
-                    for (int j = jl; j <= jh; ++j) {                 // ascending: the newest output (largest j) comes last
-                        const int slot = j % K;
-                        const bool is_new = (jj == 0 || j == jj + PAD) && t1 == t1_lo;
-                        if (is_new && j >= K) {                      // the slot's previous output (j - K) must have been drained
-                            mbar_wait_u32(acce0 + (uint32_t)slot * 8u, (uint32_t)((j / K) - 1) & 1u);
-                            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                        }
-                        const int t2 = jj - j + PAD;
-                        const uint64_t bdesc = hi | (uint64_t)(lbo_b | (w4 + (uint32_t)(t1 * K + t2) * slab4));
-                        const uint32_t dcol = tmem_base + (uint32_t)(slot * p.NT * p.N);
-                        for (int t = 0; t < p.NT; ++t)
-                            umma_f16(dcol + (uint32_t)(t * p.N), hi | (uint64_t)(lbo_a | (s4 + (uint32_t)t * 128u)), bdesc, p.idesc,
-                                     is_new ? 0u : 1u);
-                    }
-                    umma_commit_to<false>(empty0 + (uint32_t)stage * 8u);
-                    if (++stage == p.stages) { stage = 0; phase ^= 1; }
-                }
-                // outputs whose last contributing column this was
-                for (int j = jl; j <= jh; ++j)
-                    if (min(p.d2 - 1, j + PAD) == jj) umma_commit_to<false>(accf0 + (uint32_t)(j % K) * 8u);
-            }
+            if (K == 5 && p.NT == 3) walk_issue<5, 3>(p, t1_lo, t1_hi, sm0, tmem_base, full0, empty0, accf0, acce0);
+            else if (K == 5 && p.NT == 2) walk_issue<5, 2>(p, t1_lo, t1_hi, sm0, tmem_base, full0, empty0, accf0, acce0);
+            else if (K == 3 && p.NT == 10) walk_issue<3, 10>(p, t1_lo, t1_hi, sm0, tmem_base, full0, empty0, accf0, acce0);
+            else if (K == 3 && p.NT == 9) walk_issue<3, 9>(p, t1_lo, t1_hi, sm0, tmem_base, full0, empty0, accf0, acce0);
+            else walk_issue<0, 0>(p, t1_lo, t1_hi, sm0, tmem_base, full0, empty0, accf0, acce0);
         }
         __syncwarp();
     } else {
@@ -701,13 +741,18 @@ conv4d_tc_walk_kernel(const WalkArgs p) {
             mbar_wait_sleep(&acc_full[slot], (uint32_t)(j / K) & 1u, 200);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * p.NT * p.N);
+            // the next tile's TMEM loads are in flight while this tile's columns are parked
+            uint32_t ra[16], rb[16], na[16], nb[16];
+            tmem_ld16_issue(lane_base, ra);
+            if (wide) tmem_ld16_issue(lane_base + 16u, rb);
             for (int t = 0; t < p.NT; ++t) {
                 const int row = t * 128 + q * 32 + lane;
-                uint32_t ra[16], rb[16];
-                tmem_ld16_issue(lane_base + (uint32_t)(t * p.N), ra);
-                if (wide) tmem_ld16_issue(lane_base + (uint32_t)(t * p.N + 16), rb);
                 tmem_ld16_wait(ra);
                 if (wide) tmem_ld16_wait(rb);
+                if (t + 1 < p.NT) {
+                    tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N), na);
+                    if (wide) tmem_ld16_issue(lane_base + (uint32_t)((t + 1) * p.N + 16), nb);
+                }
 #pragma unroll
                 for (int u = 0; u < 16; ++u)
                     if (u < p.NG) sts_f32(osm + (uint32_t)(u * out_rows + row) * 4u, __uint_as_float(ra[u]));
@@ -715,6 +760,12 @@ conv4d_tc_walk_kernel(const WalkArgs p) {
 #pragma unroll
                     for (int u = 0; u < 16; ++u)
                         if (16 + u < p.NG) sts_f32(osm + (uint32_t)((16 + u) * out_rows + row) * 4u, __uint_as_float(rb[u]));
+                }
+                if (t + 1 < p.NT) {
+                    tmem_ld16_wait(na);
+                    if (wide) tmem_ld16_wait(nb);
+#pragma unroll
+                    for (int u = 0; u < 16; ++u) { ra[u] = na[u]; rb[u] = nb[u]; }
                 }
             }
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");

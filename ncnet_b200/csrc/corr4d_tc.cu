@@ -257,9 +257,28 @@ corr4d_tc_kernel(const CorrArgs p) {
         // rows start 16-byte aligned when nB is a multiple of 8 (fp16) / 4 (fp32) and the base pointer is aligned
         const bool vec_ok = (p.nB % (p.out_f16 ? 8 : 4)) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0;
         const int c_end = min(n_cols, (chalf + 1) * (kCorrBN / 2));
-        for (int c0 = chalf * (kCorrBN / 2); c0 < c_end; c0 += 16) {
+        // tcgen05.ld has a few hundred cycles of latency: the next chunk's load is in flight while this one is processed
+        const uint32_t lane_base = tmem_base + ((uint32_t)(q * 32) << 16);
+        const int c_begin = chalf * (kCorrBN / 2);
+        uint32_t cur[16], nxt[16];
+        if (c_begin < c_end) tmem_ld16_issue(lane_base + (uint32_t)c_begin, cur);
+        for (int c0 = c_begin; c0 < c_end; c0 += 16) {
             float v[16];
-            tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+            tmem_ld16_wait(cur);
+#pragma unroll
+            for (int u = 0; u < 16; ++u) v[u] = __uint_as_float(cur[u]);
+            if (c0 + 16 < c_end) tmem_ld16_issue(lane_base + (uint32_t)(c0 + 16), nxt);
+            struct Rotate {          // at the end of the iteration (every exit path): the next chunk becomes the current one
+                uint32_t (&c)[16], (&n)[16];
+                bool on;
+                __device__ ~Rotate() {
+                    if (on) {
+                        tmem_ld16_wait(n);
+#pragma unroll
+                        for (int u = 0; u < 16; ++u) c[u] = n[u];
+                    }
+                }
+            } rotate{cur, nxt, c0 + 16 < c_end};
             if (p.pool) {        // whole warp stays converged: the quad butterfly needs all four lanes
                 const int t0p = nt * kCorrBN + c0;
                 if (p.out_f16) corr_pool_chunk_half(p, v, a, t0p, lane);

@@ -66,13 +66,13 @@ for half, ks, chs, shape in ((False, [3, 3], [16, 1], (16, 10, 14, 12)), (True, 
             for sm in (False, True):
                 ref = nb.corr_to_matches(full, do_softmax=sm, return_indices=True, invert_matching_direction=inv)
                 got = D.slab_corr_to_matches(slab, shape[0], rank, world, do_softmax=sm, invert_matching_direction=inv)
-                same = torch.stack([a == b for a, b in zip(got[5:], ref[5:])]).all(0)
+                idx_same = torch.stack([a == b for a, b in zip(got[5:], ref[5:])]).all(0)
                 xy_same = torch.stack([a == b for a, b in zip(got[:4], ref[:4])]).all(0)
                 sc_err = ((got[4].float() - ref[4].float()).abs().max() / ref[4].float().abs().max()).item()
                 # fp32: exact.  fp16 with soft-max: the one-GPU kernel takes the first source cell whose ROUNDED half
                 # soft-max equals the maximum, the merge takes the first raw maximum -- they differ on rounding ties
                 need = 0.97 if (half and sm) else 1.0
-                match_ok &= same.float().mean().item() >= need and xy_same.float().mean().item() >= need
+                match_ok &= idx_same.float().mean().item() >= need and xy_same.float().mean().item() >= need
                 match_ok &= sc_err < (2e-3 if half else 1e-5)
     t = torch.tensor([err, 0.0 if same else 1.0, 0.0 if match_ok else 1.0], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MAX)
