@@ -268,26 +268,19 @@ corr4d_tc_kernel(const CorrArgs p) {
 #pragma unroll
             for (int u = 0; u < 16; ++u) v[u] = __uint_as_float(cur[u]);
             if (c0 + 16 < c_end) tmem_ld16_issue(lane_base + (uint32_t)(c0 + 16), nxt);
-            struct Rotate {          // at the end of the iteration (every exit path): the next chunk becomes the current one
-                uint32_t (&c)[16], (&n)[16];
-                bool on;
-                __device__ ~Rotate() {
-                    if (on) {
-                        tmem_ld16_wait(n);
-#pragma unroll
-                        for (int u = 0; u < 16; ++u) c[u] = n[u];
-                    }
-                }
-            } rotate{cur, nxt, c0 + 16 < c_end};
+            // The per-lane work below diverges (rows / columns outside the matrix skip it); tcgen05.ld / wait::ld are
+            // .sync.aligned, so the hand-over to the next chunk happens after the lanes have reconverged (end of the body).
+            const bool has_next = c0 + 16 < c_end;
+            [&] {
             if (p.pool) {        // whole warp stays converged: the quad butterfly needs all four lanes
                 const int t0p = nt * kCorrBN + c0;
                 if (p.out_f16) corr_pool_chunk_half(p, v, a, t0p, lane);
                 else corr_pool_chunk<float>(p, v, a, t0p, lane);
-                continue;
+                return;
             }
-            if (a >= p.nA) continue;
+            if (a >= p.nA) return;
             const int t0 = nt * kCorrBN + c0;
-            if (t0 >= p.nB) continue;
+            if (t0 >= p.nB) return;
 #pragma unroll
             for (int u = 0; u < 16; ++u) {
                 float x = v[u];
@@ -322,6 +315,13 @@ corr4d_tc_kernel(const CorrArgs p) {
                     if (p.out_f16) ((__half *)p.out)[row + t0 + u] = __float2half_rn(v[u]);
                     else ((float *)p.out)[row + t0 + u] = v[u];
                 }
+            }
+            }();
+            __syncwarp();
+            if (has_next) {
+                tmem_ld16_wait(nxt);
+#pragma unroll
+                for (int u = 0; u < 16; ++u) cur[u] = nxt[u];
             }
         }
     }
