@@ -276,12 +276,28 @@ def run_ours(args):
             assert shard_check < 1e-3, f"sharded gradient differs from the unsharded one: nerr {shard_check:.3e}"
         barrier()
 
-    def step_body():
+    # One step = compute phase A (forward, backward, gradients packed into the flat bucket), the gradient all-reduce,
+    # compute phase B (gradients unpacked, Adam).  At N = 1 there is no collective and A+B are one CUDA graph; at N > 1
+    # A and B are two graphs and the NCCL all-reduce is issued between their replays (capturing NCCL inside the graph
+    # invalidated the capture on this stack).
+    def phase_a():
         opt.zero_grad(set_to_none=True)
         loss = weak_loss_of_stacked(net, src2, tgt2)
         loss.backward()
-        bucket.all_reduce_mean()
+        if world > 1:
+            bucket.pack_weighted()
+        return loss
+
+    def phase_b():
+        if world > 1:
+            bucket.unpack()
         opt.step()
+
+    def step_body():
+        loss = phase_a()
+        if world > 1:
+            bucket.all_reduce_flat()
+        phase_b()
         return loss
 
     # ---- warm-up (eager): also measures the launches per step ------------------------------------------------
@@ -300,24 +316,37 @@ def run_ours(args):
     launches_per_step = (F_.LAUNCHES["n"] - l0) // max(args.warmup, 1)
     barrier()
 
-    graph, static_loss, graph_note = None, None, "off (NCNET_BENCH_GRAPH=0)"
+    graph, graph_b, static_loss, graph_note = None, None, None, "off (NCNET_BENCH_GRAPH=0)"
     if use_graph:
         try:
             graph = torch.cuda.CUDAGraph()
             opt.zero_grad(set_to_none=True)
-            with torch.cuda.graph(graph):
-                static_loss = step_body()
-            graph_note = "whole step (forward, backward, gradient all-reduce, Adam) replayed as one CUDA graph"
+            if world == 1:
+                with torch.cuda.graph(graph):
+                    static_loss = phase_a()
+                    phase_b()
+                graph_note = "whole step (forward, backward, Adam) replayed as one CUDA graph"
+            else:
+                with torch.cuda.graph(graph):
+                    static_loss = phase_a()
+                graph_b = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(graph_b, pool=graph.pool()):
+                    phase_b()
+                graph_note = ("two CUDA graphs per step (forward + backward + gradient packing; gradient unpacking + Adam) "
+                              "with the NCCL all-reduce of the flat gradient bucket issued between their replays")
         except Exception as exc:                     # capture unsupported on this stack: time the eager step instead
-            graph, graph_note = None, f"capture failed ({type(exc).__name__}: {exc}); eager"
+            graph, graph_b, graph_note = None, None, f"capture failed ({type(exc).__name__}: {str(exc)[:120]}); eager"
             torch.cuda.synchronize()
     barrier()
 
     def step():
-        if graph is not None:
-            graph.replay()
-            return static_loss
-        return step_body()
+        if graph is None:
+            return step_body()
+        graph.replay()
+        if graph_b is not None:
+            bucket.all_reduce_flat()
+            graph_b.replay()
+        return static_loss
 
     step()                                           # first replay outside the timed region
     barrier()
@@ -447,7 +476,11 @@ def run_ours(args):
             line["cpu_baseline"] = {k: base[k] for k in ("value", "unit", "cores", "kind", "sample")}
         _emit(line)
     if world > 1:
-        dist.destroy_process_group()
+        # every rank is past its last collective; leave without tearing the communicator down collectively
+        dist.barrier()
+        torch.cuda.synchronize()
+        sys.stdout.flush(), sys.stderr.flush()
+        os._exit(0)
 
 
 def _emit(line: dict) -> None:

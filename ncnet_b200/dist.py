@@ -78,11 +78,19 @@ class GradBucket:
             return
         if (local_batch is None) != (global_batch is None):
             raise ValueError("all_reduce_mean: give both local_batch and global_batch, or neither")
+        self.pack_weighted(group, local_batch, global_batch)
+        self.all_reduce_flat(group)
+        self.unpack()
+
+    # the three phases on their own, for callers that replay the compute phases as CUDA graphs and keep the
+    # collective outside the captures (bench.py)
+    def pack_weighted(self, group=None, local_batch=None, global_batch=None) -> None:
         weight = 1.0 / dist.get_world_size(group) if local_batch is None else float(local_batch) / float(global_batch)
         self.pack()
         self.flat.mul_(weight)
+
+    def all_reduce_flat(self, group=None) -> None:
         dist.all_reduce(self.flat, op=dist.ReduceOp.SUM, group=group)
-        self.unpack()
 
 
 # ------------------------------------------------------------------------------------------- #
