@@ -258,22 +258,31 @@ def run_ours(args):
         torch.cuda.synchronize()
 
     # ---- before anything is timed: the sharded gradient must equal the single-GPU gradient ------------------
+    # (everything before the capture runs on a side stream and leaves no autograd graph alive: an AccumulateGrad node
+    # that outlives its iteration on the default stream invalidates the capture)
+    side = torch.cuda.Stream(device=dev)
     shard_check = None
     if world > 1:
-        loss = weak_loss_of_stacked(net, src2, tgt2)
-        loss.backward()
-        bucket.all_reduce_mean()
-        g_sharded = torch.cat([p.grad.reshape(-1) for p in params]).clone()
-        net.zero_grad(set_to_none=True)
-        if rank == 0:
-            fa_d, fb_d = fa_h.to(dev), fb_h.to(dev)
-            full_loss = weak_loss_of_stacked(net, torch.cat([fa_d, torch.roll(fa_d, -1, 0)]), torch.cat([fb_d, fb_d]))
-            full_loss.backward()
-            g_full = torch.cat([p.grad.reshape(-1) for p in params])
-            shard_check = ((g_sharded - g_full).abs().max() / g_full.abs().max()).item()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            loss = weak_loss_of_stacked(net, src2, tgt2)
+            loss.backward()
+            del loss
+            bucket.all_reduce_mean()
+            g_sharded = torch.cat([p.grad.reshape(-1) for p in params]).clone()
             net.zero_grad(set_to_none=True)
-            del fa_d, fb_d, g_full
-            assert shard_check < 1e-3, f"sharded gradient differs from the unsharded one: nerr {shard_check:.3e}"
+            if rank == 0:
+                fa_d, fb_d = fa_h.to(dev), fb_h.to(dev)
+                full_loss = weak_loss_of_stacked(net, torch.cat([fa_d, torch.roll(fa_d, -1, 0)]), torch.cat([fb_d, fb_d]))
+                full_loss.backward()
+                del full_loss
+                g_full = torch.cat([p.grad.reshape(-1) for p in params])
+                shard_check = ((g_sharded - g_full).abs().max() / g_full.abs().max()).item()
+                net.zero_grad(set_to_none=True)
+                del fa_d, fb_d, g_full
+                assert shard_check < 1e-3, f"sharded gradient differs from the unsharded one: nerr {shard_check:.3e}"
+            del g_sharded
+        torch.cuda.current_stream().wait_stream(side)
         barrier()
 
     # One step = compute phase A (forward, backward, gradients packed into the flat bucket), the gradient all-reduce,
@@ -304,7 +313,6 @@ def run_ours(args):
     # (on a side stream, and leaving no autograd graph alive: both are preconditions of the capture below)
     l0 = F_.LAUNCHES["n"]
     first_loss = None
-    side = torch.cuda.Stream(device=dev)
     side.wait_stream(torch.cuda.current_stream())
     with torch.cuda.stream(side):
         for w in range(args.warmup):
