@@ -76,7 +76,7 @@ corr_pack_kernel(const T *__restrict__ f, __half *__restrict__ out, int C, int n
 struct CorrArgs {
     const __half *pa, *pb;
     void *out;
-    int nA, nB, npadA, npadB, kblocks;
+    int B, nA, nB, npadA, npadB, kblocks;
     int relu_l2norm, out_f16;
     uint32_t idesc;
     // fused 2x2x2x2 max-pool (pool != 0): out = pooled values [nA/4, nB/4]; idx[4] = max_i, max_j, max_k, max_l
@@ -184,32 +184,38 @@ __device__ __forceinline__ void corr_pool_chunk_half(const CorrArgs &p, const fl
 __global__ void __launch_bounds__(kCorrThreads, 1)
 corr4d_tc_kernel(const CorrArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t full_bar[kCorrStages], empty_bar[kCorrStages], accum_bar;
+    // Persistent: CTA c works on tiles c, c + gridDim.x, ... (N tile fastest, then M tile, then batch).  The 512 TMEM
+    // columns hold TWO 128 x 256 accumulators: the MMA warp fills one while the eight epilogue warps drain the other,
+    // and the operand ring keeps streaming across tile boundaries.
+    __shared__ __align__(8) uint64_t full_bar[kCorrStages], empty_bar[kCorrStages], acc_full[2], acc_empty[2];
     __shared__ uint32_t tmem_base_s;
     constexpr uint32_t kABytes = kCorrBM / 8 * kCorrKB * 16, kBBytes = kCorrBN / 8 * kCorrKB * 16;   // 16 KB, 32 KB
     constexpr uint32_t kStage = kABytes + kBBytes;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int nt = blockIdx.x, mt = blockIdx.y, b = blockIdx.z;
+    const int n_tiles_n = (p.npadB + kCorrBN - 1) / kCorrBN, n_tiles_m = p.npadA / kCorrBM;
+    const int total_tiles = p.B * n_tiles_m * n_tiles_n;
 
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < kCorrStages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        mbar_init(&accum_bar, 1);
+        for (int s = 0; s < 2; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 8); }      // 8 epilogue warps
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(256) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-    const uint32_t tmem_base = tmem_base_s;
-    // the last N tile may be narrower than 256 positions (npadB is a multiple of 128)
-    const int n_cols = min(kCorrBN, p.npadB - nt * kCorrBN);
-    const uint32_t b_bytes = (uint32_t)(n_cols / 8) * kCorrKB * 16;
+    const uint32_t tmem_base0 = tmem_base_s;
 
     if (warp == 0) {
         int stage = 0; uint32_t phase = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const int nt = tile % n_tiles_n, mt = (tile / n_tiles_n) % n_tiles_m, b = tile / (n_tiles_n * n_tiles_m);
+        // the last N tile may be narrower than 256 positions (npadB is a multiple of 128)
+        const int n_cols = min(kCorrBN, p.npadB - nt * kCorrBN);
+        const uint32_t b_bytes = (uint32_t)(n_cols / 8) * kCorrKB * 16;
         for (int kb = 0; kb < p.kblocks; ++kb) {
             mbar_wait(&empty_bar[stage], phase ^ 1);
             if (elect_one()) {
@@ -223,13 +229,24 @@ corr4d_tc_kernel(const CorrArgs p) {
             __syncwarp();
             if (++stage == kCorrStages) { stage = 0; phase ^= 1; }
         }
+        }
     } else if (warp == 1) {
         int stage = 0; uint32_t phase = 0;
         // MN-major, no swizzle: LBO = 128 B between groups of 8 channels, SBO = 1 KB between groups of 8 positions
         const uint64_t hi = ((uint64_t)(((uint32_t)(kCorrKB * 16) >> 4) | (1u << 14))) << 32;
         const uint32_t lbo_field = (128u >> 4) << 16;
         const uint32_t smem0 = smem_u32_pinned(smem);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int nt = tile % n_tiles_n;
+        const int n_cols = min(kCorrBN, p.npadB - nt * kCorrBN);
         const uint32_t idesc = (p.idesc & ~(0x3fu << 17)) | ((uint32_t)(n_cols >> 3) << 17);
+        const int as = it & 1;                               // accumulator stage of this tile
+        const uint32_t tmem_base = tmem_base0 + (uint32_t)(as * kCorrBN);
+        if (it >= 2) {                                       // the epilogue must have drained this stage's previous tile
+            mbar_wait(&acc_empty[as], (uint32_t)((it >> 1) - 1) & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        }
         for (int kb = 0; kb < p.kblocks; ++kb) {
             mbar_wait(&full_bar[stage], phase);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -245,12 +262,19 @@ corr4d_tc_kernel(const CorrArgs p) {
             __syncwarp();
             if (++stage == kCorrStages) { stage = 0; phase ^= 1; }
         }
-        if (elect_one()) umma_commit(&accum_bar);
+        if (elect_one()) umma_commit(&acc_full[as]);
         __syncwarp();
+        }
     } else {
         const int q = warp & 3;                              // TMEM lane quadrant this warp may read
         const int chalf = (warp - 2) >> 2;                   // which half of the tile's columns it takes
-        mbar_wait(&accum_bar, 0);
+        int it = 0;
+        for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int nt = tile % n_tiles_n, mt = (tile / n_tiles_n) % n_tiles_m, b = tile / (n_tiles_n * n_tiles_m);
+        const int n_cols = min(kCorrBN, p.npadB - nt * kCorrBN);
+        const int as = it & 1;
+        const uint32_t tmem_base = tmem_base0 + (uint32_t)(as * kCorrBN);
+        mbar_wait(&acc_full[as], (uint32_t)(it >> 1) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const int a = mt * kCorrBM + q * 32 + lane;
         const size_t row = ((size_t)b * p.nA + a) * p.nB;
@@ -324,10 +348,15 @@ corr4d_tc_kernel(const CorrArgs p) {
                 for (int u = 0; u < 16; ++u) cur[u] = nxt[u];
             }
         }
+        // this warp has read its share of the accumulator: hand the stage back to the MMA warp
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&acc_empty[as])) : "memory");
+        }
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(256) : "memory");
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base0), "r"(512) : "memory");
 }
 
 static size_t corr_align(size_t v) { return (v + 255) & ~(size_t)255; }
@@ -356,7 +385,7 @@ static int corr_tc_run(const void *fa, const void *fb, void *out, void *scratch,
     corr_pack_kernel<T><<<dim3((npadB / 8 + 255) / 256, 64, B), 256, 0, st>>>((const T *)fb, pb, C, nB, npadB, kblocks, l2norm_inputs, pool.wB);
     NC_LAUNCH_OK("corr_pack_kernel(B)");
     CorrArgs a{};
-    a.pa = pa; a.pb = pb; a.out = out; a.nA = nA; a.nB = nB; a.npadA = npadA; a.npadB = npadB; a.kblocks = kblocks;
+    a.pa = pa; a.pb = pb; a.out = out; a.B = B; a.nA = nA; a.nB = nB; a.npadA = npadA; a.npadB = npadB; a.kblocks = kblocks;
     a.relu_l2norm = relu_l2norm; a.out_f16 = sizeof(T) == 2;
     a.pool = pool.wA > 0; a.idx_bytes = pool.idx_bytes;
     for (int d = 0; d < 4; ++d) a.idx[d] = pool.idx[d];
@@ -365,8 +394,9 @@ static int corr_tc_run(const void *fa, const void *fb, void *out, void *scratch,
     const size_t smem = (size_t)kCorrStages * (kCorrBM + kCorrBN) / 8 * kCorrKB * 16;
     cudaError_t e = cudaFuncSetAttribute(corr4d_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     NC_CHECK(e == cudaSuccess, "corr4d(tc): smem attribute: %s", cudaGetErrorString(e));
-    dim3 grid((npadB + kCorrBN - 1) / kCorrBN, npadA / kCorrBM, B);
-    NC_CHECK(grid.y <= 65535, "corr4d(tc): too many row tiles");
+    const long long tiles = (long long)((npadB + kCorrBN - 1) / kCorrBN) * (npadA / kCorrBM) * B;
+    NC_CHECK(tiles < (1ll << 31), "corr4d(tc): too many tiles");
+    const unsigned grid = (unsigned)(tiles < kNumSMs ? tiles : kNumSMs);      // one persistent CTA per SM
     corr4d_tc_kernel<<<grid, kCorrThreads, smem, st>>>(a);
     NC_LAUNCH_OK("corr4d_tc_kernel");
     return 0;
