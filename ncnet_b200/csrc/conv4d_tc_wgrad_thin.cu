@@ -111,9 +111,13 @@ struct ThinWalk {
     __device__ __forceinline__ void next(const WgThinArgs &p) {
         if (++j == p.d2) { j = 0; if (++i == p.d1) { i = 0; ++b; } }
     }
-    // row index of the T2 plane, or -1 when it falls outside the volume
-    __device__ __forceinline__ int t2_row(const WgThinArgs &p, int t1) const {
-        const int ii = i + p.sgn * (t1 - p.KS / 2);
+    // The walk runs over the T2 planes (the tap-packed single-channel tensor: the larger stream, ngrp planes per
+    // step), so the k tap classes that run together read the SAME T2 plane and L2 serves k-1 of them; the 16-channel
+    // plane each class pairs it with is row  i - sgn*(t1 - p)  (returned here, -1 when it falls outside the volume)
+    // and is the one re-read from DRAM a few rows later.  (Anchoring the walk on the 16-channel planes re-read the
+    // T2 planes instead: 5.5 GB of DRAM reads per launch for 0.43 GB of input at the PF-Pascal shape.)
+    __device__ __forceinline__ int w16_row(const WgThinArgs &p, int t1) const {
+        const int ii = i - p.sgn * (t1 - p.KS / 2);
         return (ii < 0 || ii >= p.d1) ? -1 : ii;
     }
 };
@@ -163,16 +167,16 @@ conv4d_tc_wgrad_thin_kernel(const WgThinArgs p) {
             ThinWalk w;
             w.start(p, pbeg);
             for (int pl = pbeg; pl < pend; ++pl, w.next(p)) {
-                const int ii = w.t2_row(p, t1);
+                const int ii = w.w16_row(p, t1);
                 if (ii < 0) continue;
                 mbar_wait_u32(empty0 + (uint32_t)stage * 8u, phase ^ 1);
                 const uint32_t sa = sm0 + (uint32_t)stage * p.stage_bytes, fb = full0 + (uint32_t)stage * 8u;
                 asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"((uint32_t)(1 + p.ngrp) * p.plane_bytes) : "memory");
                 const size_t bga = (size_t)w.b * p.G + g, bgt = (size_t)w.b * p.Gt + (p.Gt == 1 ? 0 : g);
-                bulk_g2s_u32(sa + p.a_off, p.w16 + (bga * ijn + (size_t)w.i * p.d2 + w.j) * plane_h, p.plane_bytes, fb);
+                bulk_g2s_u32(sa + p.a_off, p.w16 + (bga * ijn + (size_t)ii * p.d2 + w.j) * plane_h, p.plane_bytes, fb);
                 for (int gr = 0; gr < p.ngrp; ++gr)
                     bulk_g2s_u32(sa + p.a_bytes + (uint32_t)gr * p.b1_bytes,
-                                 p.t2 + ((bgt * p.ngrp + gr) * ijn + (size_t)ii * p.d2 + w.j) * plane_h, p.plane_bytes, fb);
+                                 p.t2 + ((bgt * p.ngrp + gr) * ijn + (size_t)w.i * p.d2 + w.j) * plane_h, p.plane_bytes, fb);
                 if (++stage == p.stages) { stage = 0; phase ^= 1; }
             }
         }
@@ -189,7 +193,7 @@ conv4d_tc_wgrad_thin_kernel(const WgThinArgs p) {
             ThinWalk w;
             w.start(p, pbeg);
             for (int pl = pbeg; pl < pend; ++pl, w.next(p)) {
-                if (w.t2_row(p, t1) < 0) continue;
+                if (w.w16_row(p, t1) < 0) continue;
                 mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint32_t sa4 = (sm0 + (uint32_t)stage * p.stage_bytes) >> 4;
@@ -218,7 +222,7 @@ conv4d_tc_wgrad_thin_kernel(const WgThinArgs p) {
         {
             ThinWalk w;
             w.start(p, pbeg);
-            for (int pl = pbeg; pl < pend && !any; ++pl, w.next(p)) any = w.t2_row(p, t1) >= 0;
+            for (int pl = pbeg; pl < pend && !any; ++pl, w.next(p)) any = w.w16_row(p, t1) >= 0;
         }
         const int KS = p.KS;
         const int m = q * 32 + lane, r = m >> 4, ch = m & 15;
