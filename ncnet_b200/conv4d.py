@@ -28,6 +28,9 @@ class Conv4d(Module):
                 raise ValueError("Conv4d: only cubic kernels are supported")
             kernel_size = kernel_size[0]
         k = int(kernel_size)
+        if k not in (3, 5):
+            # the reference accepts any odd size; this library's kernels cover the sizes its configurations use
+            raise ValueError(f"Conv4d: kernel_size {k} is outside this library's envelope (3 or 5)")
         self.in_channels, self.out_channels = in_channels, out_channels
         self.kernel_size = (k, k, k, k)
         self.stride, self.padding, self.dilation, self.groups = (1,) * 4, (0,) * 4, (1,) * 4, 1
@@ -45,6 +48,9 @@ class Conv4d(Module):
         self.use_half = False
 
     def forward(self, input):
+        if self.out_channels > 16 and torch.is_grad_enabled() and self.weight.requires_grad:
+            raise RuntimeError(f"Conv4d: the weight gradient covers at most 16 output channels (this layer has "
+                               f"{self.out_channels}); run it under torch.no_grad() or freeze its weight")
         return conv4d(input, self.weight, bias=self.bias, permute_filters=not self.pre_permuted_filters,
                       use_half=self.use_half)
 
