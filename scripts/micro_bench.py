@@ -69,19 +69,17 @@ with torch.no_grad():
                 row["cpu_oracle_ms_per_item"] = cpu_ms(lambda: O.mutual_matching(xc)); row["gpu_ms_per_item"] = ms / b
             emit(**row)
             del x, y, keys
-        for n in (16, 32, 40, 50):            # maxpool4d k=2 needs even sides
+        # maxpool4d k=2 (batch 1 like the reference): the InLoc pre-pooling volumes, and 50^4
+        for name, shape in (("N=50 fp16", (1, 1, 50, 50, 50, 50)), ("IL16 fp16 (100x74x100x74)", (1, 1, 100, 74, 100, 74)),
+                            ("IL32 fp16 (200x150x200x150)", (1, 1, 200, 150, 200, 150))):
+            x = torch.rand(*shape, device=dev).half()
+            nout = x.numel() // 16
             for idt, ib in ((torch.int64, 8), (torch.uint8, 1)):
-                reps = max(1, (300 << 20) // (n ** 4 * 2))
-                xs = [torch.rand(1, 1, n, n, n, n, device=dev).half() for _ in range(min(reps, 8))]
-                it = {"i": 0}
-                def fn():
-                    it["i"] = (it["i"] + 1) % len(xs)
-                    F_.maxpool4d(xs[it["i"]], 2, index_dtype=idt)
-                ms = timeit(fn, reps=len(xs))
-                byts = n ** 4 * 2 + (n ** 4 // 16) * (2 + 4 * ib)
-                emit(kernel=f"maxpool4d k=2 ({'int64' if ib == 8 else 'uint8'} offsets)", case=f"N={n} fp16 ({len(xs)} volumes in rotation)", ms=ms,
+                ms = timeit(lambda: F_.maxpool4d(x, 2, index_dtype=idt), iters=5, reps=4 if x.numel() < (1 << 27) else 1)
+                byts = x.numel() * 2 + nout * (2 + 4 * ib)
+                emit(kernel=f"maxpool4d k=2 ({'int64' if ib == 8 else 'uint8'} offsets)", case=name, ms=ms,
                      achieved_GBs=byts / ms / 1e6, frac_of_hbm=byts / ms / 1e6 / PEAKS["hbm_gbs"])
-                del xs
+            del x
         for name, shape, dt in (("PF B=16 fp32", (16, 1, 25, 25, 25, 25), torch.float32), ("N=50 B=8 fp32", (8, 1, 50, 50, 50, 50), torch.float32),
                                 ("IL32 pooled fp16", (1, 1, 100, 75, 100, 75), torch.float16)):
             x = torch.rand(*shape, device=dev).to(dt)

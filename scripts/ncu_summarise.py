@@ -26,7 +26,7 @@ def to_bytes(v, unit):
 
 for r in rows[2:]:
     name = r[idx["Kernel Name"]]
-    if "ncnet" not in name:
+    if "conv4d" not in name and "ncnet" not in name:
         continue
     out.append(",".join('"%s"' % r[idx[c]] for c in cols))
     grid = int(float(r[idx["launch__grid_size"]].replace(",", ""))) if "launch__grid_size" in idx else 0
