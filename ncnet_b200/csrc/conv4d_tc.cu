@@ -1185,6 +1185,7 @@ struct TcPackW {
     int mode;       // 1,2,3,4
     int KSTEPS, N, CoutPad, inner, OG;
     int pairsplit;  // 1: per (d1,d2) slab the N columns are split in two contiguous halves [rank][K-step][2][N/2][8] (CTA pairs)
+                    // 2: the split is outermost within a group: [G][rank][k*k slabs][K-step][2][N/2][8] (resident weights, walk16)
 };
 
 // -> [G][k*inner][KSTEPS][2][N][8] fp16   (inner = k d2 taps; mode 4: channel blocks of the (d2,d4) taps)
@@ -1195,13 +1196,14 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
          idx += (long long)gridDim.x * blockDim.x) {
         long long r = idx;
         const int c8 = (int)(r % 8); r /= 8;
-        int n, half, ks;
+        int n, half, ks, rank_hi = -1;
         if (a.pairsplit) {
             const int nh = a.N / 2;
             n = (int)(r % nh); r /= nh;
             half = (int)(r % 2); r /= 2;
             ks = (int)(r % a.KSTEPS); r /= a.KSTEPS;
-            n += (int)(r % 2) * nh; r /= 2;
+            if (a.pairsplit == 1) { n += (int)(r % 2) * nh; r /= 2; }
+            else rank_hi = nh;
         } else {
             n = (int)(r % a.N); r /= a.N;
             half = (int)(r % 2); r /= 2;
@@ -1209,6 +1211,7 @@ __global__ void pack_w_tc_kernel(const float *__restrict__ w, __half *__restrict
         }
         int t2 = (int)(r % a.inner); r /= a.inner;
         const int t1 = (int)(r % k); r /= k;
+        if (rank_hi > 0) { n += (int)(r % 2) * rank_hi; r /= 2; }
         int g = (int)r;
         const int kch = half * 8 + c8;
         int oe, ci, t3, t4;
@@ -1394,8 +1397,13 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
     if (x_dtype == NCNET_CB16 && pl.mode == 4) return 2;   // the tap im2col needs the planar single-channel input
     if (y_dtype == NCNET_CB16 && pl.CoutPad < 16) return 2;
     if (mask && ((mask_dtype == NCNET_CB16) != (y_dtype == NCNET_CB16))) return 2;
-    // CTA pairs for the many-channel layers: the two chunks of a plane run as one cluster, one M256 MMA stream
-    const int pair = (pl.mode == 1 && pl.nchunks == 2 && pl.tmem_cols <= 256 && (pl.N / 2) % 8 == 0) ? 1 : 0;
+    // many-channel layers: persistent CTA pairs walking along jA with the weights resident (conv4d_tc_walk16.cu) ...
+    // (k = 5, CB16 output: a column step of k*k*k MMAs leaves the four epilogue warps time to drain a chunk; at k = 3 and
+    // for planar outputs the per-plane kernel below is the faster one)
+    const bool w16 = pl.mode == 1 && d.k == 5 && y_dtype == NCNET_CB16 && (!mask || mask_dtype == NCNET_CB16) &&
+                     conv4d_tc_walk16_ok(d.k, d3, d4) && !getenv("NCNET_NO_W16");
+    // ... else CTA pairs per output plane: the two chunks of a plane run as one cluster, one M256 MMA stream
+    const int pair = w16 ? 2 : (pl.mode == 1 && pl.nchunks == 2 && pl.tmem_cols <= 256 && (pl.N / 2) % 8 == 0) ? 1 : 0;
     uint8_t *sc = (uint8_t *)scratch;
     const __half *act;
     size_t used = 0;
@@ -1417,6 +1425,9 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
         pack_w_tc_kernel<<<blocks, 256, 0, st>>>(w, wp, a);
         NC_LAUNCH_OK("pack_w_tc_kernel");
     }
+    if (w16)
+        return conv4d_tc_walk16_run(act, wp, bias, (const __half *)mask, (__half *)y, out_pm, B, d.G_e, Gx, d.Cout_e, d1, d2, d3, d4, d.k,
+                                    relu, st);
     if (pl.mode == 2 && !mask && (y_dtype == NCNET_F32 || y_dtype == NCNET_F16)) {
         // single output channel: walk along jA with k live output planes in TMEM (each input plane staged k times, not k*k)
         const WalkPlan wk = walk_plan(d.k, d3, d4);

@@ -19,6 +19,10 @@ int conv4d_tc_fwd(const void *x, int x_dtype, const float *w, const float *bias,
 int conv4d_tc_dgrad(const void *gy, int gy_dtype, const float *w, const void *mask, int mask_dtype, void *gx, int gx_dtype,
                     void *scratch, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
                     int symmetric, int shared_input, cudaStream_t st);
+// conv4d_tc_walk16.cu: mode M1 layers with CB16 output on persistent CTA pairs with resident weights; returns 2 outside its envelope
+bool conv4d_tc_walk16_ok(int k, int d3, int d4);
+int conv4d_tc_walk16_run(const __half *act, const __half *wp, const float *bias, const __half *mask, __half *out, __half *out_pm,
+                         int B, int G, int Gx, int Cout, int d1, int d2, int d3, int d4, int k, int relu, cudaStream_t st);
 size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric);
 int conv4d_tc_wgrad(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch,
                     float *bias_part, const float *out_scale, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,

@@ -35,7 +35,7 @@ for r in rows[2:]:
     # the 16->16 launches are the largest grids of their kernels
     if "conv4d_tc_wgrad_pm_kernel" in name:
         key = "conv4d_wgrad"
-    elif "conv4d_tc_kernel<1>" in name or "conv4d_tc_kernel<true>" in name:
+    elif "conv4d_tc_walk16_kernel" in name or "conv4d_tc_kernel<1>" in name or "conv4d_tc_kernel<true>" in name:
         key = "conv4d_fwd"
     else:
         continue
