@@ -55,11 +55,14 @@ for bsz, ks, chans, dims in ((2, [5, 5, 5], [16, 16, 1], (25, 25, 25, 25)), (2, 
         y.backward(gout)
         return torch.cat([y.detach().flatten()] + [p_.grad.flatten() / p_.grad.abs().max().clamp_min(1e-30) for p_ in nc.parameters()])
     new, old, tn, to = both(run)
-    e = rel(new, old)
-    good = e < 1e-4
+    ny = x.numel()
+    e, eg = rel(new[:ny], old[:ny]), rel(new[ny:], old[ny:])
+    # forward: only the summation order differs (a hidden fp16 activation may round the other way: ~1e-5); gradients: a
+    # pre-activation within rounding of zero may switch its ReLU mask, one term of a sum over the volume (<~ 1/cells)
+    good = e < 1e-4 and eg < 5e-3
     ok &= good
-    print(json.dumps({"case": f"stack B={bsz} k={ks} ch={chans} {dims} fwd+bwd", "rel_diff": e, "ms_walk16": round(tn, 4), "ms_per_plane": round(to, 4),
-                      "ok": good}), flush=True)
+    print(json.dumps({"case": f"stack B={bsz} k={ks} ch={chans} {dims} fwd+bwd", "rel_diff_fwd": e, "rel_diff_grads": eg, "ms_walk16": round(tn, 4),
+                      "ms_per_plane": round(to, 4), "ok": good}), flush=True)
 # inference (no gradients): the PF-Pascal stack at batch 1 and 16
 for bsz in (1, 16):
     nc = nb.NeighConsensus(True, [5, 5, 5], [16, 16, 1]).to(dev)
