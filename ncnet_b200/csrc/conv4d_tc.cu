@@ -1416,6 +1416,10 @@ static int run_tc(const void *x, int x_dtype, const float *w, const float *bias,
         used = align256(cb16_bytes((size_t)B * Gx * (pl.mode == 4 ? pl.inner : 1), d1, d2, d3, d4, d.k));
     }
     __half *wp = (__half *)(sc + used);
+    // single-input-channel layers writing CB16: persistent walk along iA with the d1 taps folded into N (conv4d_tc_walk1.cu)
+    if (pl.mode == 4 && y_dtype == NCNET_CB16 && (!mask || mask_dtype == NCNET_CB16) && conv4d_tc_walk1_ok(d.k, og, d3, d4) &&
+        !getenv("NCNET_NO_W1"))
+        return conv4d_tc_walk1_run(act, w, wp, d, bias, (const __half *)mask, (__half *)y, out_pm, B, og, Gx, d1, d2, d3, d4, relu, st);
     {
         TcPackW a{};
         a.d = d; a.mode = pl.mode; a.KSTEPS = pl.KSTEPS; a.N = pl.N; a.CoutPad = pl.CoutPad; a.inner = pl.inner; a.OG = pl.OG;

@@ -23,6 +23,13 @@ int conv4d_tc_dgrad(const void *gy, int gy_dtype, const float *w, const void *ma
 bool conv4d_tc_walk16_ok(int k, int d3, int d4);
 int conv4d_tc_walk16_run(const __half *act, const __half *wp, const float *bias, const __half *mask, __half *out, __half *out_pm,
                          int B, int G, int Gx, int Cout, int d1, int d2, int d3, int d4, int k, int relu, cudaStream_t st);
+// conv4d_tc_walk1.cu: mode M4 layers (Cin == 1) with CB16 output as a persistent walk along iA; og = 2: both branches of a
+// shared input side by side in N
+struct PackDesc;
+bool conv4d_tc_walk1_ok(int k, int og, int d3, int d4);
+int conv4d_tc_walk1_run(const __half *act, const float *w, __half *wp, const PackDesc &d, const float *bias, const __half *mask,
+                        __half *out, __half *out_pm, int B, int og, int Gx, int d1, int d2, int d3, int d4, int relu,
+                        cudaStream_t st);
 size_t conv4d_tc_wgrad_scratch_bytes(int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int symmetric);
 int conv4d_tc_wgrad(const void *x, int x_dtype, const void *gy, int gy_dtype, float *gw, float *gb, void *scratch,
                     float *bias_part, const float *out_scale, int B, int Cin, int Cout, int d1, int d2, int d3, int d4, int k, int w_layout,
