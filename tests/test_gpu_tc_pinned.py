@@ -50,7 +50,6 @@ def _double(onc, ks, chs):
 @pytest.mark.parametrize("ks,chs,dims,bsz", [
     ([5, 5, 5], [16, 16, 1], (3, 4, 25, 25), 2),     # PF plane: six position chunks -> three CTA pairs per plane (walk16), walk along iA (walk1)
     ([5, 5, 5], [16, 16, 1], (6, 5, 9, 10), 2),      # one chunk per plane: the pair's second CTA has nothing to load
-    ([5, 5, 5, 5], [16, 16, 16, 1], (7, 6, 8, 9), 1),   # two 16->16 layers chained
     ([5, 5, 5], [16, 16, 1], (2, 80, 9, 10), 2),     # long jA axis: several work items per persistent CTA (the TMEM ring carries over)
     ([5, 5, 5], [16, 16, 1], (27, 3, 11, 12), 1),    # long iA axis: jA segments in walk16, more outputs than TMEM ring slots in walk1
     ([3, 3], [16, 1], (5, 6, 20, 13), 2),            # InLoc stack
