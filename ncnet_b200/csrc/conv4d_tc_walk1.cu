@@ -24,7 +24,7 @@
 namespace ncnet {
 using namespace tc;
 
-constexpr int kW1Threads = 192;
+constexpr int kW1Threads = 320;      // TMA producer, MMA issuer, 8 epilogue warps
 constexpr int kW1StagesMax = 8;
 constexpr int kW1SlotsMax = 32;
 
@@ -79,7 +79,7 @@ conv4d_tc_walk1_kernel(const Walk1Args p) {
 
     if (warp == 1 && lane == 0) {
         for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-        for (int s = 0; s < R; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], 1); }
+        for (int s = 0; s < R; ++s) { mbar_init(&acc_full[s], 1); mbar_init(&acc_empty[s], OG); }      // OG == 2: both warp sets read the slot
         mbar_init(&w_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -97,7 +97,7 @@ conv4d_tc_walk1_kernel(const Walk1Args p) {
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = tmem_base_s;
-    if (warp >= 2) {        // every accumulator column starts at zero: all MMAs accumulate
+    if (warp >= 2 && warp < 6) {        // every accumulator column starts at zero: all MMAs accumulate
         const uint32_t lane_base = tmem_base + ((uint32_t)((warp & 3) * 32) << 16);
         for (int c = 0; c < 512; c += 16) tmem_st16_zero(lane_base + (uint32_t)c);
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -193,16 +193,21 @@ conv4d_tc_walk1_kernel(const Walk1Args p) {
         }
         __syncwarp();
     } else {
-        // ===== epilogue (warps 2..5 <-> TMEM lane quadrants warp%4): one output chunk per completed plane =====
-        const int q = warp & 3;
-        const int et = threadIdx.x - 64;
+        // ===== epilogue: 8 warps (two per TMEM lane quadrant warp%4), one output chunk per completed plane =====
+        // OG == 2: warp set s (warps 2..5 / 6..9) owns branch s of every output; OG == 1: set s owns the outputs with n % 2 == s.
+        // Every address is a per-item base plus a constant stride per output plane: the loop body is TMEM load, 16 x
+        // (bias, ReLU / mask, fp16), two to four 16-byte stores.
+        const int ew = warp - 2, set = ew >> 2, q = warp & 3;
+        const int et = (ew & 3) * 32 + lane;             // 0..127 within the set
+        const int og = OG == 2 ? set : 0;
         const int off_h = PAD * p.P + PAD;               // haloed position of flattened output m: m + off_h
-        float bv[OG][16];
+        float bv[16];
 #pragma unroll
-        for (int og = 0; og < OG; ++og)
-#pragma unroll
-            for (int o = 0; o < 16; ++o) bv[og][o] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;      // the branches share the layer's bias
+        for (int o = 0; o < 16; ++o) bv[o] = (p.bias && o < p.Cout) ? __ldg(p.bias + o) : 0.f;     // the branches share the layer's bias
         const uint4 z4 = make_uint4(0, 0, 0, 0);
+        const size_t half_halves = ij_count * (size_t)plane_cb * 8;          // between the channel halves of a CB16 block
+        const size_t step_cb = (size_t)p.d2 * plane_cb * 8, step_pm = (size_t)p.d2 * plane_cb * 16;     // per output plane i
+        const bool full_ch = p.Cout == 16;
         int n = 0;
         for (int t = cl; t < p.items; t += p.cpg) {
             const W1Item it = w1_item(p, t);
@@ -210,71 +215,79 @@ conv4d_tc_walk1_kernel(const Walk1Args p) {
             const int hp = m + off_h;
             const bool in_plane = m < p.M_out;
             const bool valid = in_plane && (m % p.P) < p.d4;
-            const int pm_half_swap = (hp >> 2) & 1;
+            const size_t blk_idx = (size_t)it.b * p.G + gp * OG + og;
+            const size_t cb0 = ((blk_idx * 2) * ij_count + (size_t)it.j) * (size_t)plane_cb * 8;       // plane (i = 0, j), half 0
+            const size_t pm0 = (blk_idx * ij_count + (size_t)it.j) * (size_t)plane_cb * 16;
+            const int swap8 = ((hp >> 2) & 1) * 8;
             for (int i = 0; i < p.d1; ++i, ++n) {
+                if (OG == 1 && (n & 1) != set) continue;             // warp-uniform
                 const int slot = n % R;
-                const size_t plane_idx = (size_t)i * p.d2 + it.j;
+                __half *ob = p.out + cb0 + (size_t)i * step_cb;
+                __half *opm = p.out_pm ? p.out_pm + pm0 + (size_t)i * step_pm : nullptr;
                 // the ReLU mask of this position (dgrad) is fetched while the plane's last MMAs are still running
-                uint4 mk[OG][2];
+                uint4 mk0 = z4, mk1 = z4;
                 if (p.mask && valid) {
-#pragma unroll
-                    for (int og = 0; og < OG; ++og) {
-                        const size_t base_off = ((((size_t)it.b * p.G + gp * OG + og) * 2) * ij_count + plane_idx) * (size_t)plane_cb * 8;
-                        mk[og][0] = *reinterpret_cast<const uint4 *>(p.mask + base_off + (size_t)hp * 8);
-                        mk[og][1] = *reinterpret_cast<const uint4 *>(p.mask + base_off + (ij_count * plane_cb + (size_t)hp) * 8);
-                    }
+                    const __half *mp = p.mask + cb0 + (size_t)i * step_cb + (size_t)hp * 8;
+                    mk0 = *reinterpret_cast<const uint4 *>(mp);
+                    mk1 = *reinterpret_cast<const uint4 *>(mp + half_halves);
                 }
                 mbar_wait_sleep(&acc_full[slot], (uint32_t)(n / R) & 1u, 50);
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * NCOL);
-                uint32_t r[OG][16];
-#pragma unroll
-                for (int og = 0; og < OG; ++og) tmem_ld16_issue(taddr + (uint32_t)(og * 16), r[og]);
-#pragma unroll
-                for (int og = 0; og < OG; ++og) tmem_ld16_wait(r[og]);
-#pragma unroll
-                for (int og = 0; og < OG; ++og) tmem_st16_zero(taddr + (uint32_t)(og * 16));      // ready for its next output
+                const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(slot * NCOL + og * 16);
+                uint32_t r[16];
+                tmem_ld16_issue(taddr, r);
+                tmem_ld16_wait(r);
+                tmem_st16_zero(taddr);                               // ready for the slot's next output
                 asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                 asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                asm volatile("bar.sync %0, 128;" ::"r"(1 + set) : "memory");
                 if (et == 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(acce0 + (uint32_t)slot * 8u) : "memory");
+                if (in_plane) {
+                    uint4 h0 = z4, h1 = z4;
+                    if (valid) {
+                        float x[16];
 #pragma unroll
-                for (int og = 0; og < OG; ++og) {
-                    const size_t blk_idx = (size_t)it.b * p.G + gp * OG + og;
-                    __half *ob = p.out + ((blk_idx * 2) * ij_count + plane_idx) * (size_t)plane_cb * 8;
-                    __half *opm = p.out_pm ? p.out_pm + (blk_idx * ij_count + plane_idx) * (size_t)plane_cb * 16 : nullptr;
-                    if (in_plane) {
-#pragma unroll
-                        for (int half = 0; half < 2; ++half) {
-                            __align__(16) __half hv[8];
-                            const __half *mh = reinterpret_cast<const __half *>(&mk[og][half]);
+                        for (int o = 0; o < 16; ++o) {
+                            x[o] = __uint_as_float(r[o]) + bv[o];
+                            if (p.relu) x[o] = fmaxf(x[o], 0.f);
+                            if (!full_ch && o >= p.Cout) x[o] = 0.f;
+                        }
+                        if (p.mask) {
+                            const __half *mh0 = reinterpret_cast<const __half *>(&mk0), *mh1 = reinterpret_cast<const __half *>(&mk1);
 #pragma unroll
                             for (int c8 = 0; c8 < 8; ++c8) {
-                                const int o = half * 8 + c8;
-                                float x = __uint_as_float(r[og][o]) + bv[og][o];
-                                if (p.relu) x = fmaxf(x, 0.f);
-                                if (p.mask && valid && !(__half2float(mh[c8]) > 0.f)) x = 0.f;
-                                hv[c8] = __float2half_rn((valid && o < p.Cout) ? x : 0.f);
+                                if (!(__half2float(mh0[c8]) > 0.f)) x[c8] = 0.f;
+                                if (!(__half2float(mh1[c8]) > 0.f)) x[8 + c8] = 0.f;
                             }
-                            *reinterpret_cast<uint4 *>(ob + ((size_t)half * ij_count * plane_cb + (size_t)hp) * 8) = *reinterpret_cast<const uint4 *>(hv);
-                            if (opm) *reinterpret_cast<uint4 *>(opm + (size_t)hp * 16 + (size_t)((half ^ pm_half_swap) * 8)) = *reinterpret_cast<const uint4 *>(hv);
+                        }
+                        __half2 *p0 = reinterpret_cast<__half2 *>(&h0), *p1 = reinterpret_cast<__half2 *>(&h1);
+#pragma unroll
+                        for (int c2 = 0; c2 < 4; ++c2) {
+                            p0[c2] = __floats2half2_rn(x[2 * c2], x[2 * c2 + 1]);
+                            p1[c2] = __floats2half2_rn(x[8 + 2 * c2], x[8 + 2 * c2 + 1]);
                         }
                     }
-                    // the halo rows above the first / below the last output position
-                    if (it.chunk == 0) {
-                        for (int e = et; e < 2 * off_h; e += 128) {
-                            const int half = e >= off_h ? 1 : 0, pos = e - half * off_h;
-                            *reinterpret_cast<uint4 *>(ob + ((size_t)half * ij_count * plane_cb + (size_t)pos) * 8) = z4;
-                            if (opm) *reinterpret_cast<uint4 *>(opm + (size_t)pos * 16 + (size_t)half * 8) = z4;
-                        }
+                    *reinterpret_cast<uint4 *>(ob + (size_t)hp * 8) = h0;
+                    *reinterpret_cast<uint4 *>(ob + half_halves + (size_t)hp * 8) = h1;
+                    if (opm) {       // position-major twin: 32 B per position, halves swapped by bit 7 of the in-plane byte offset
+                        *reinterpret_cast<uint4 *>(opm + (size_t)hp * 16 + swap8) = h0;
+                        *reinterpret_cast<uint4 *>(opm + (size_t)hp * 16 + (8 - swap8)) = h1;
                     }
-                    if (it.chunk == p.nchunks - 1) {
-                        const int lo = p.M_out + off_h, cnt = plane_cb - lo;
-                        for (int e = et; e < 2 * cnt; e += 128) {
-                            const int half = e >= cnt ? 1 : 0, pos = lo + (e - half * cnt);
-                            *reinterpret_cast<uint4 *>(ob + ((size_t)half * ij_count * plane_cb + (size_t)pos) * 8) = z4;
-                            if (opm) *reinterpret_cast<uint4 *>(opm + (size_t)pos * 16 + (size_t)half * 8) = z4;
-                        }
+                }
+                // the halo rows above the first / below the last output position
+                if (it.chunk == 0) {
+                    for (int e = et; e < 2 * off_h; e += 128) {
+                        const int half = e >= off_h ? 1 : 0, pos = e - half * off_h;
+                        *reinterpret_cast<uint4 *>(ob + (size_t)half * half_halves + (size_t)pos * 8) = z4;
+                        if (opm) *reinterpret_cast<uint4 *>(opm + (size_t)pos * 16 + (size_t)half * 8) = z4;
+                    }
+                }
+                if (it.chunk == p.nchunks - 1) {
+                    const int lo = p.M_out + off_h, cnt = plane_cb - lo;
+                    for (int e = et; e < 2 * cnt; e += 128) {
+                        const int half = e >= cnt ? 1 : 0, pos = lo + (e - half * cnt);
+                        *reinterpret_cast<uint4 *>(ob + (size_t)half * half_halves + (size_t)pos * 8) = z4;
+                        if (opm) *reinterpret_cast<uint4 *>(opm + (size_t)pos * 16 + (size_t)half * 8) = z4;
                     }
                 }
             }
