@@ -35,6 +35,26 @@ __device__ __forceinline__ void mma_ts(uint32_t d, uint32_t a_tmem, uint64_t b, 
                  ::"r"(d), "r"(a_tmem), "l"(b), "r"(idesc) : "memory");
 }
 
+// A fetched by the first MMA of each group of GRP (collector::a::fill) and reused by the others (collector::a::use)
+template <int GRP>
+__device__ __forceinline__ void run_coll(const RateArgs &p, uint32_t sa4, uint32_t sb4, uint32_t tb) {
+    uint64_t bv[2 * GRP];
+    uint32_t dv[2 * GRP];
+    const uint64_t a = p.adesc | (uint64_t)sa4;
+#pragma unroll
+    for (int u = 0; u < 2 * GRP; ++u) {
+        bv[u] = p.bdesc | (uint64_t)(sb4 + (uint32_t)(u % p.cyc) * p.b_step);
+        dv[u] = tb + (uint32_t)((u % p.nacc) * p.N);
+    }
+    for (int it = 0; it < p.iters; it += 2 * GRP) {
+#pragma unroll
+        for (int u = 0; u < 2 * GRP; ++u) {
+            if (u % GRP == 0) mma_desc<1>(dv[u], a, bv[u], p.idesc);
+            else mma_desc<2>(dv[u], a, bv[u], p.idesc);
+        }
+    }
+}
+
 __global__ void __launch_bounds__(128) rate_kernel(const RateArgs p) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ __align__(8) uint64_t bar;
@@ -78,7 +98,7 @@ __global__ void __launch_bounds__(128) rate_kernel(const RateArgs p) {
 #pragma unroll
                         for (int u = 0; u < 8; ++u) mma_desc<0>(dv[u], av[u], bv[u], p.idesc);
                     }
-                } else {
+                } else if (p.coll == 1) {
                     for (int it = 0; it < p.iters; it += 8) {       // A refilled every 4th MMA, reused by the next three
 #pragma unroll
                         for (int u = 0; u < 8; ++u) {
@@ -86,7 +106,9 @@ __global__ void __launch_bounds__(128) rate_kernel(const RateArgs p) {
                             else mma_desc<2>(dv[u], av[u], bv[u], p.idesc);
                         }
                     }
-                }
+                } else if (p.coll == 3) run_coll<3>(p, sa4, sb4, tb);
+                else if (p.coll == 5) run_coll<5>(p, sa4, sb4, tb);
+                else run_coll<2>(p, sa4, sb4, tb);
                 umma_commit(&bar);
             }
             __syncwarp();
@@ -138,6 +160,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(128) rate2_kernel(co
                     bv[u] = p.bdesc | (uint64_t)(sb4 + c * p.b_step);
                     dv[u] = tb + (uint32_t)((u % p.nacc) * p.N);
                 }
+                if (p.coll == 5) {      // groups of 5 MMAs sharing A: fill, then four uses
+                    for (int it = 0; it < p.iters; it += 10) {
+#pragma unroll
+                        for (int u = 0; u < 10; ++u) {
+                            const uint32_t dcol = tb + (uint32_t)((u % p.nacc) * p.N);
+                            if (u % 5 == 0)
+                                asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, 1, 0;\n\ttcgen05.mma.cta_group::2.kind::f16.collector::a::fill [%0], %1, %2, %3, q;\n\t}"
+                                             ::"r"(dcol), "l"(av[0]), "l"(bv[u % 8]), "r"(p.idesc) : "memory");
+                            else
+                                asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.b32 q, 1, 0;\n\ttcgen05.mma.cta_group::2.kind::f16.collector::a::use [%0], %1, %2, %3, q;\n\t}"
+                                             ::"r"(dcol), "l"(av[0]), "l"(bv[u % 8]), "r"(p.idesc) : "memory");
+                        }
+                    }
+                } else
                 for (int it = 0; it < p.iters; it += 8) {
 #pragma unroll
                     for (int u = 0; u < 8; ++u)
@@ -186,6 +222,11 @@ int main() {
     for (int N : {80, 256}) cfgs.push_back({"Kmaj sw64  M128", 128, N, 4, 0, 0, 16, 512, 16, 512, 32, 0, 4, 0, 0, 1});
     for (int N : {80, 160, 240}) cfgs.push_back({"Kmaj none  M128 sameA", 128, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 0, 160, 5, 0, 0, 1});
     for (int N : {80, 160, 240}) cfgs.push_back({"Kmaj none  M128 collector", 128, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 0, 160, 5, 1, 0, 1});
+    for (int N : {16, 32, 48, 80}) cfgs.push_back({"Kmaj none  M128 coll x5", 128, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 0, 160, 5, 5, 0, 1});
+    for (int N : {16, 48, 96}) cfgs.push_back({"Kmaj none  M128 coll x3", 128, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 0, 160, 3, 3, 0, 1});
+    for (int N : {80}) cfgs.push_back({"Kmaj none  M128 coll x2", 128, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 0, 160, 2, 2, 0, 1});
+    for (int N : {80}) cfgs.push_back({"MNmaj sw32 M128 coll x5", 128, N, 6, 1, 1, 32, 256, 29 * 32, 256, 0, 32, 5, 5, 0, 1});
+    for (int N : {80}) cfgs.push_back({"MNmaj sw32 M128", 128, N, 6, 1, 1, 32, 256, 29 * 32, 256, 32, 32, 5, 0, 0, 1});
     for (int N : {80, 160, 240, 256}) cfgs.push_back({"A in TMEM  M128", 128, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 0, 0, 1, 0, 1, 1});
     for (int N : {80, 240}) cfgs.push_back({"Kmaj none  M128 2cta/sm", 128, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 29, 0, 5, 0, 0, 2});
     for (int N : {40, 80, 128, 256}) cfgs.push_back({"Kmaj none  M64", 64, N, 0, 0, 0, 8192, 128, (uint32_t)N * 16, 128, 29, 0, 5, 0, 0, 1});
@@ -198,7 +239,7 @@ int main() {
         a.idesc = (1u << 4) | ((uint32_t)c.a_mn << 15) | ((uint32_t)c.b_mn << 16) | ((uint32_t)(c.N >> 3) << 17) | ((uint32_t)(c.M >> 4) << 24);
         a.adesc = desc_hi(c.lbo_a, c.sbo_a, c.layout);
         a.bdesc = desc_hi(c.lbo_b, c.sbo_b, c.layout);
-        a.a_step = c.a_step; a.b_step = c.b_step; a.cyc = c.cyc; a.iters = 2048; a.N = c.N;
+        a.a_step = c.a_step; a.b_step = c.b_step; a.cyc = c.cyc; a.iters = c.coll > 1 ? 2040 : 2048; a.N = c.N;
         a.tmem_cols = c.ctas_per_sm == 2 ? 256 : 512;
         a.nacc = (a.tmem_cols - 16) / c.N; if (a.nacc > 3) a.nacc = 3; if (a.nacc < 1) a.nacc = 1;
         a.coll = c.coll; a.a_tmem = c.a_tmem; a.out = out;
@@ -215,17 +256,18 @@ int main() {
 
     // CTA pairs: N is the TOTAL N of the M256 MMA, each CTA's B descriptor addresses its own N/2 columns
     cudaFuncSetAttribute(rate2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024);
-    for (int per_sm = 1; per_sm <= 2; ++per_sm)
+    for (int per_sm = 1; per_sm <= 3; ++per_sm)
         for (int N : {80, 160, 256}) {
             RateArgs a{};
+            if (per_sm == 3) { if (N != 80) continue; a.coll = 5; }
             a.idesc = (1u << 4) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(256 >> 4) << 24);
             a.adesc = desc_hi(8192, 128, 0);
             a.bdesc = desc_hi((uint32_t)(N / 2) * 16, 128, 0);
-            a.a_step = 29; a.b_step = 0; a.cyc = 5; a.iters = 2048; a.N = N;
+            a.a_step = 29; a.b_step = 0; a.cyc = 5; a.iters = 2040; a.N = N;
             a.tmem_cols = per_sm == 2 ? 256 : 512;
             a.nacc = (a.tmem_cols - 16) / N; if (a.nacc > 3) a.nacc = 3; if (a.nacc < 1) a.nacc = 1;
             a.out = out;
-            const int grid = 148 * per_sm;
+            const int grid = 148 * (per_sm == 2 ? 2 : 1);
             rate2_kernel<<<grid, 128, 96 * 1024>>>(a);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("pair N=%d: ERROR %s\n", N, cudaGetErrorString(e)); return 1; }
@@ -233,7 +275,7 @@ int main() {
             cudaMemcpy(h.data(), out, grid * sizeof(long long), cudaMemcpyDeviceToHost);
             double sum = 0; int cnt = 0;
             for (int i = 0; i < grid; i += 2) { sum += (double)h[i]; ++cnt; }       // leaders
-            printf("%-28s %4d %4d %10.1f %8.1f\n", per_sm == 2 ? "cta_group::2 Kmaj 2pair/2sm" : "cta_group::2 Kmaj none", 256, N,
+            printf("%-28s %4d %4d %10.1f %8.1f\n", per_sm == 3 ? "cta_group::2 Kmaj coll x5" : per_sm == 2 ? "cta_group::2 Kmaj 2pair/2sm" : "cta_group::2 Kmaj none", 256, N,
                    sum / cnt / a.iters, 128 * N / 256.0);
             fflush(stdout);
         }
