@@ -592,58 +592,75 @@ __device__ __forceinline__ void walk_issue(const WalkArgs &p, int t1_lo, int t1_
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint32_t s4 = sm4 + (uint32_t)stage * stage4;
             const uint32_t wrow = lbo_b | (w4 + (uint32_t)(t1 * K + (K - 1)) * slab4);     // tap t2 = K-1-dd for output dd
-            // a tile's A is shared by the (up to k) live outputs j = jj-PAD+dd: tiles outer, outputs inner, A kept in the
-            // tensor core's collector across the group (N = 16 / 32: 16 / 22 cycles per MMA instead of 40)
-            const int dd_lo = max(0, PAD - jj), dd_hi = min(K - 1, p.d2 - 1 - jj + PAD);
-            uint32_t dcol[KM], newmask = 0, defer_bar = 0, defer_par = 0;
-            int defer = -1;       // an output whose slot is still being drained (its previous owner completed one column ago)
-            {
-                int slot = slot_lo;
+            if (NT_C > 0 && jj >= PAD && jj + PAD < p.d2) {
+                // interior column: all k outputs j = jj-PAD+dd are live and only the last (j = jj+PAD) can be new.  A tile's A
+                // is shared by the k outputs: tiles outer, outputs inner, A held in the tensor core's collector (fill, use ...,
+                // lastuse: 16 / 22 cycles per N = 16 / 32 MMA instead of 40); straight-line issue.  A new output whose slot
+                // is still being drained (its previous owner completed one column ago) goes last, without the hint.
+                uint32_t dcol[KM];
+                {
+                    int slot = slot_lo;
 #pragma unroll
-                for (int dd = 0; dd < KM; ++dd) {
-                    dcol[dd] = tmem_base;
+                    for (int dd = 0; dd < KM; ++dd) { dcol[dd] = tmem_base + (uint32_t)slot * slot_cols; if (++slot == K) slot = 0; }
+                }
+                const bool nw = t1 == t1_lo;
+                if (nw) {
+#pragma unroll
+                    for (int t = 0; t < NTM; ++t) {
+                        const uint64_t adesc = hi | (uint64_t)(a_rel[t] + s4);
+                        umma_f16_coll<1, true>(dcol[0] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)wrow, p.idesc, 1u);
+#pragma unroll
+                        for (int dd = 1; dd < KM - 2; ++dd)
+                            umma_f16_coll<2, true>(dcol[dd] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)(wrow - (uint32_t)dd * slab4), p.idesc, 1u);
+                        umma_f16_coll<3, true>(dcol[KM - 2] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)(wrow - (uint32_t)(KM - 2) * slab4), p.idesc, 1u);
+                    }
+                    const int j = jj + PAD;
+                    if (j >= K) {
+                        mbar_wait_u32(acce0 + (uint32_t)((dcol[KM - 1] - tmem_base) / slot_cols) * 8u, (uint32_t)((j / K) - 1) & 1u);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    }
+                    const uint64_t bdesc = hi | (uint64_t)(wrow - (uint32_t)(KM - 1) * slab4);
+#pragma unroll
+                    for (int t = 0; t < NTM; ++t)
+                        umma_f16_coll<0, false>(dcol[KM - 1] + (uint32_t)(t * p.N), hi | (uint64_t)(a_rel[t] + s4), bdesc, p.idesc, 0u);
+                } else {
+#pragma unroll
+                    for (int t = 0; t < NTM; ++t) {
+                        const uint64_t adesc = hi | (uint64_t)(a_rel[t] + s4);
+                        umma_f16_coll<1, true>(dcol[0] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)wrow, p.idesc, 1u);
+#pragma unroll
+                        for (int dd = 1; dd < KM - 1; ++dd)
+                            umma_f16_coll<2, true>(dcol[dd] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)(wrow - (uint32_t)dd * slab4), p.idesc, 1u);
+                        umma_f16_coll<3, true>(dcol[KM - 1] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)(wrow - (uint32_t)(KM - 1) * slab4), p.idesc, 1u);
+                    }
+                }
+            } else {
+                int slot = slot_lo;
+    #pragma unroll
+                for (int dd = 0; dd < KM; ++dd) {        // outputs j = jj - PAD + dd, ascending: the newest comes last
                     if (dd < K) {
-                        if (dd >= dd_lo && dd <= dd_hi) {
-                            const int j = jj - PAD + dd;
-                            dcol[dd] = tmem_base + (uint32_t)slot * slot_cols;
-                            if ((jj == 0 || dd == K - 1) && t1 == t1_lo) {      // first touch of output j
-                                newmask |= 1u << dd;
-                                if (j >= K) { defer = dd; defer_bar = acce0 + (uint32_t)slot * 8u; defer_par = (uint32_t)((j / K) - 1) & 1u; }
+                        const int j = jj - PAD + dd;
+                        if (j >= 0 && j < p.d2) {
+                            const bool is_new = (jj == 0 || dd == K - 1) && t1 == t1_lo;
+                            if (is_new && j >= K) {      // the slot's previous output (j - K) must have been drained
+                                mbar_wait_u32(acce0 + (uint32_t)slot * 8u, (uint32_t)((j / K) - 1) & 1u);
+                                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                            }
+                            const uint64_t bdesc = hi | (uint64_t)(wrow - (uint32_t)dd * slab4);
+                            const uint32_t dcol = tmem_base + (uint32_t)slot * slot_cols;
+                            const uint32_t acc = is_new ? 0u : 1u;
+                            if (NT_C > 0) {
+    #pragma unroll
+                                for (int t = 0; t < NTM; ++t)
+                                    umma_f16(dcol + (uint32_t)(t * p.N), hi | (uint64_t)(a_rel[t] + s4), bdesc, p.idesc, acc);
+                            } else {
+                                for (int t = 0; t < NT; ++t)
+                                    umma_f16(dcol + (uint32_t)(t * p.N), hi | (uint64_t)((lbo_a | ((uint32_t)t * 128u)) + s4), bdesc, p.idesc, acc);
                             }
                         }
                         if (++slot == K) slot = 0;
                     }
                 }
-            }
-            // the deferred output (always the last one) is issued after the others, so the epilogue's drain of its slot
-            // overlaps their MMAs
-            const int dd_main = defer >= 0 ? dd_hi - 1 : dd_hi;
-            if (NT_C > 0) {
-#pragma unroll
-                for (int t = 0; t < NTM; ++t) {
-                    const uint64_t adesc = hi | (uint64_t)(a_rel[t] + s4);
-#pragma unroll
-                    for (int dd = 0; dd < KM; ++dd)
-                        if (dd < K && dd >= dd_lo && dd <= dd_main)
-                            umma_f16_group(dcol[dd] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)(wrow - (uint32_t)dd * slab4), p.idesc,
-                                           (newmask >> dd) & 1u ? 0u : 1u, dd == dd_lo, dd == dd_main);
-                }
-            } else {
-                for (int t = 0; t < NT; ++t) {
-                    const uint64_t adesc = hi | (uint64_t)((lbo_a | ((uint32_t)t * 128u)) + s4);
-#pragma unroll
-                    for (int dd = 0; dd < KM; ++dd)
-                        if (dd < K && dd >= dd_lo && dd <= dd_main)
-                            umma_f16_group(dcol[dd] + (uint32_t)(t * p.N), adesc, hi | (uint64_t)(wrow - (uint32_t)dd * slab4), p.idesc,
-                                           (newmask >> dd) & 1u ? 0u : 1u, dd == dd_lo, dd == dd_main);
-                }
-            }
-            if (defer >= 0) {
-                mbar_wait_u32(defer_bar, defer_par);
-                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-                const uint64_t bdesc = hi | (uint64_t)(wrow - (uint32_t)defer * slab4);
-                for (int t = 0; t < NT; ++t)
-                    umma_f16(dcol[K - 1] + (uint32_t)(t * p.N), hi | (uint64_t)((lbo_a | ((uint32_t)t * 128u)) + s4), bdesc, p.idesc, 0u);
             }
             umma_commit_to<false>(empty0 + (uint32_t)stage * 8u);
             if (++stage == p.stages) { stage = 0; phase ^= 1; }

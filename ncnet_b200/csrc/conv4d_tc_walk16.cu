@@ -61,15 +61,23 @@ __device__ __forceinline__ void umma_f16_pair(uint32_t d, uint64_t a, uint64_t b
     asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                  ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");
 }
-// position in a group of MMAs that share the A tile: the first fetches it into the collector, the last releases it
-__device__ __forceinline__ void umma_f16_pair_group(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc, bool first, bool last) {
-#define NC_PAIR_MMA(Q)                                                                                                                  \
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16" Q " [%0], %1, %2, %3, p;\n\t}" \
-                 ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory")
-    if (first && last) NC_PAIR_MMA("");
-    else if (first) NC_PAIR_MMA(".collector::a::fill");
-    else if (last) NC_PAIR_MMA(".collector::a::lastuse");
-    else NC_PAIR_MMA(".collector::a::use");
+// MODE: A-collector hint (0 none, 1 fill, 2 use, 3 lastuse) for MMAs issued back to back on the same A tile; ACC1: the
+// accumulate flag is the constant 1 (no predicate set-up in the single issuing lane)
+template <int MODE, bool ACC1>
+__device__ __forceinline__ void pair_mma(uint32_t d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t acc) {
+#define NC_PAIR_MMA(Q)                                                                                                                      \
+    do {                                                                                                                                    \
+        if (ACC1)                                                                                                                           \
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, 1, 0;\n\ttcgen05.mma.cta_group::2.kind::f16" Q " [%0], %1, %2, %3, p;\n\t}"  \
+                         ::"r"(d), "l"(a), "l"(b), "r"(idesc) : "memory");                                                                  \
+        else                                                                                                                                \
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::2.kind::f16" Q " [%0], %1, %2, %3, p;\n\t}" \
+                         ::"r"(d), "l"(a), "l"(b), "r"(idesc), "r"(acc) : "memory");                                                        \
+    } while (0)
+    if (MODE == 1) NC_PAIR_MMA(".collector::a::fill");
+    else if (MODE == 2) NC_PAIR_MMA(".collector::a::use");
+    else if (MODE == 3) NC_PAIR_MMA(".collector::a::lastuse");
+    else NC_PAIR_MMA("");
 #undef NC_PAIR_MMA
 }
 // arrives on the barrier at this shared-memory offset in BOTH CTAs of the pair once the MMAs issued so far have completed
@@ -199,35 +207,54 @@ conv4d_tc_walk16_kernel(const Walk16Args p) {
                             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                             const uint32_t s4 = sm4 + (uint32_t)stage * stage4;
                             const uint32_t wrow = lbo_b | (w4 + (uint32_t)(t1 * K + (K - 1)) * SLAB4);   // tap t2 = K-1-dd
-                            // the stage's K-step tile A is shared by the (up to k) live outputs j = jj-PAD+dd: K-step outer,
-                            // outputs inner, A kept in the collector across the group (a new output comes last)
-                            const int dd_lo = max(0, it.j0 - jj + PAD), dd_hi = min(K - 1, it.j1 - 1 - jj + PAD);
-                            uint32_t dcol[K], newmask = 0;
+                            if (jj - PAD >= it.j0 && jj + PAD < it.j1) {
+                                // interior column: all k outputs j = jj-PAD+dd are live and only the last can be new.  The stage's
+                                // K-step tile A is shared by the k outputs: K-step outer, outputs inner, A held in the collector
+                                // (fill, use ..., lastuse: 41 instead of 46 cycles per M256 x N80 MMA); straight-line issue.
+                                const int n0 = n_base + (jj - PAD - it.j0);
+                                uint32_t dcol[K];
+                                {
+                                    int slot = n0 % SL;
 #pragma unroll
-                            for (int dd = 0; dd < K; ++dd) {
-                                dcol[dd] = tmem_base;
-                                if (dd >= dd_lo && dd <= dd_hi) {
+                                    for (int dd = 0; dd < K; ++dd) { dcol[dd] = tmem_base + (uint32_t)(slot * N); if (++slot == SL) slot = 0; }
+                                }
+                                const bool nw = t1 == t1_lo;
+                                if (nw && n0 + K - 1 >= SL) {      // the new output's slot: its previous owner has been drained by both CTAs
+                                    const int n = n0 + K - 1;
+                                    mbar_wait_u32(acce0 + (uint32_t)(n % SL) * 8u, (uint32_t)((n / SL) - 1) & 1u);
+                                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                                }
+#pragma unroll
+                                for (int ks = 0; ks < K; ++ks) {
+                                    const uint64_t adesc = hi | (uint64_t)(a_rel[ks] + s4);
+                                    const uint32_t b0 = wrow + (uint32_t)ks * BSTEP;
+                                    pair_mma<1, true>(dcol[0], adesc, hi | (uint64_t)b0, p.idesc, 1u);
+#pragma unroll
+                                    for (int dd = 1; dd < K - 1; ++dd)
+                                        pair_mma<2, true>(dcol[dd], adesc, hi | (uint64_t)(b0 - (uint32_t)dd * SLAB4), p.idesc, 1u);
+                                    if (ks == 0) pair_mma<3, false>(dcol[K - 1], adesc, hi | (uint64_t)(b0 - (uint32_t)(K - 1) * SLAB4), p.idesc, nw ? 0u : 1u);
+                                    else pair_mma<3, true>(dcol[K - 1], adesc, hi | (uint64_t)(b0 - (uint32_t)(K - 1) * SLAB4), p.idesc, 1u);
+                                }
+                            } else {
+    #pragma unroll
+                                for (int dd = 0; dd < K; ++dd) {        // outputs j = jj - PAD + dd, ascending: a new one comes last
                                     const int j = jj - PAD + dd;
-                                    const int n = n_base + (j - it.j0);
-                                    const int slot = n % SL;
-                                    dcol[dd] = tmem_base + (uint32_t)(slot * N);
-                                    if (t1 == t1_lo && jj == max(j - PAD, 0)) {       // first touch of output j
-                                        newmask |= 1u << dd;
-                                        if (n >= SL) {      // the slot's previous output (n - SL) has been drained by both CTAs
+                                    if (j >= it.j0 && j < it.j1) {
+                                        const int n = n_base + (j - it.j0);
+                                        const int slot = n % SL;
+                                        const bool is_new = t1 == t1_lo && jj == max(j - PAD, 0);
+                                        if (is_new && n >= SL) {        // the slot's previous output (n - SL) has been drained by both CTAs
                                             mbar_wait_u32(acce0 + (uint32_t)slot * 8u, (uint32_t)((n / SL) - 1) & 1u);
                                             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                                         }
+                                        const uint32_t b0 = wrow - (uint32_t)dd * SLAB4;
+                                        const uint32_t dcol = tmem_base + (uint32_t)(slot * N);
+    #pragma unroll
+                                        for (int ks = 0; ks < K; ++ks)
+                                            umma_f16_pair(dcol, hi | (uint64_t)(a_rel[ks] + s4), hi | (uint64_t)(b0 + (uint32_t)ks * BSTEP), p.idesc,
+                                                          (is_new && ks == 0) ? 0u : 1u);
                                     }
                                 }
-                            }
-#pragma unroll
-                            for (int ks = 0; ks < K; ++ks) {
-                                const uint64_t adesc = hi | (uint64_t)(a_rel[ks] + s4);
-#pragma unroll
-                                for (int dd = 0; dd < K; ++dd)
-                                    if (dd >= dd_lo && dd <= dd_hi)
-                                        umma_f16_pair_group(dcol[dd], adesc, hi | (uint64_t)(wrow - (uint32_t)dd * SLAB4 + (uint32_t)ks * BSTEP), p.idesc,
-                                                            (ks == 0 && ((newmask >> dd) & 1u)) ? 0u : 1u, dd == dd_lo, dd == dd_hi);
                             }
                             umma_commit_pair(empty0 + (uint32_t)stage * 8u);       // frees the stage in both CTAs
                             if (++stage == p.stages) { stage = 0; phase ^= 1; }

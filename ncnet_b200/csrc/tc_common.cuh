@@ -120,24 +120,22 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64
 // collector buffer -- the first one fetches it (fill), the others reuse it (use ... lastuse).  Measured on B200
 // (scripts/umma_rate.cu, groups of 5): M128 x N x K16 drops from 39/40/44/52 cycles to 16/22/28/41 at N = 16/32/48/80,
 // the CTA-pair M256 x N80 from 46 to 41.  MODE: 0 = no hint, 1 = fill, 2 = use, 3 = lastuse.
-template <int MODE>
+template <int MODE, bool ACC1>      // ACC1: the accumulate flag is the constant 1 (no predicate set-up in the single issuing lane)
 __device__ __forceinline__ void umma_f16_coll(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
-#define NC_UMMA_COLL(Q)                                                                                          \
-    asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16" Q " [%0], %1, %2, %3, p;\n\t}" \
-                 ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory")
+#define NC_UMMA_COLL(Q)                                                                                                                     \
+    do {                                                                                                                                    \
+        if (ACC1)                                                                                                                           \
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, 1, 0;\n\ttcgen05.mma.cta_group::1.kind::f16" Q " [%0], %1, %2, %3, p;\n\t}"  \
+                         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc) : "memory");                                                     \
+        else                                                                                                                                \
+            asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\ttcgen05.mma.cta_group::1.kind::f16" Q " [%0], %1, %2, %3, p;\n\t}" \
+                         ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");                                           \
+    } while (0)
     if (MODE == 1) NC_UMMA_COLL(".collector::a::fill");
     else if (MODE == 2) NC_UMMA_COLL(".collector::a::use");
     else if (MODE == 3) NC_UMMA_COLL(".collector::a::lastuse");
     else NC_UMMA_COLL("");
 #undef NC_UMMA_COLL
-}
-// run-time position in a group of `cnt` MMAs sharing A: first fills, last releases
-__device__ __forceinline__ void umma_f16_group(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc, bool first,
-                                               bool last) {
-    if (first && last) umma_f16_coll<0>(d_tmem, adesc, bdesc, idesc, acc);
-    else if (first) umma_f16_coll<1>(d_tmem, adesc, bdesc, idesc, acc);
-    else if (last) umma_f16_coll<3>(d_tmem, adesc, bdesc, idesc, acc);
-    else umma_f16_coll<2>(d_tmem, adesc, bdesc, idesc, acc);
 }
 __device__ __forceinline__ void umma_commit(uint64_t *bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
