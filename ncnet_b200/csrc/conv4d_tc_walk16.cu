@@ -196,28 +196,34 @@ conv4d_tc_walk16_kernel(const Walk16Args p) {
                 int stage = 0;
                 uint32_t phase = 0;
                 int n_base = 0;                     // outputs of earlier items (slot = n mod SL)
+                bool prewaited = false;             // the current stage's barriers were already waited for during the previous stage
                 for (int t = cl; t < p.items; t += p.cpg) {
                     const W16Item it = w16_item(p, t);
                     const int t1_lo = max(0, PAD - it.i), t1_hi = min(K - 1, p.d1 - 1 - it.i + PAD);
                     const int jj_lo = max(0, it.j0 - PAD), jj_hi = min(p.d2 - 1, it.j1 - 1 + PAD);
+                    const bool last_item = t + p.cpg >= p.items;
                     for (int jj = jj_lo; jj <= jj_hi; ++jj) {
+                        // interior column: all k outputs j = jj-PAD+dd are live and only the last can be new
+                        const bool interior = jj - PAD >= it.j0 && jj + PAD < it.j1;
+                        const int n0 = n_base + (jj - PAD - it.j0);
+                        uint32_t dcol[K];
+                        {
+                            int slot = interior ? n0 % SL : 0;
+#pragma unroll
+                            for (int dd = 0; dd < K; ++dd) { dcol[dd] = tmem_base + (uint32_t)(slot * N); if (++slot == SL) slot = 0; }
+                        }
                         for (int t1 = t1_lo; t1 <= t1_hi; ++t1) {
-                            mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
-                            mbar_wait_u32(peer0 + (uint32_t)stage * 8u, phase);
+                            if (!prewaited) {
+                                mbar_wait_u32(full0 + (uint32_t)stage * 8u, phase);
+                                mbar_wait_u32(peer0 + (uint32_t)stage * 8u, phase);
+                            }
+                            prewaited = false;
                             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                             const uint32_t s4 = sm4 + (uint32_t)stage * stage4;
                             const uint32_t wrow = lbo_b | (w4 + (uint32_t)(t1 * K + (K - 1)) * SLAB4);   // tap t2 = K-1-dd
-                            if (jj - PAD >= it.j0 && jj + PAD < it.j1) {
-                                // interior column: all k outputs j = jj-PAD+dd are live and only the last can be new.  The stage's
-                                // K-step tile A is shared by the k outputs: K-step outer, outputs inner, A held in the collector
-                                // (fill, use ..., lastuse: 41 instead of 46 cycles per M256 x N80 MMA); straight-line issue.
-                                const int n0 = n_base + (jj - PAD - it.j0);
-                                uint32_t dcol[K];
-                                {
-                                    int slot = n0 % SL;
-#pragma unroll
-                                    for (int dd = 0; dd < K; ++dd) { dcol[dd] = tmem_base + (uint32_t)(slot * N); if (++slot == SL) slot = 0; }
-                                }
+                            if (interior) {
+                                // The stage's K-step tile A is shared by the k outputs: K-step outer, outputs inner, A held in the
+                                // collector (fill, use ..., lastuse: 41 instead of 46 cycles per M256 x N80 MMA); straight-line issue.
                                 const bool nw = t1 == t1_lo;
                                 if (nw && n0 + K - 1 >= SL) {      // the new output's slot: its previous owner has been drained by both CTAs
                                     const int n = n0 + K - 1;
@@ -226,6 +232,14 @@ conv4d_tc_walk16_kernel(const Walk16Args p) {
                                 }
 #pragma unroll
                                 for (int ks = 0; ks < K; ++ks) {
+                                    if (ks == K - 1 && !(last_item && jj == jj_hi && t1 == t1_hi)) {
+                                        // the next stage's barriers are polled while the MMAs issued so far keep the tensor pipe busy
+                                        const int ns = stage + 1 == p.stages ? 0 : stage + 1;
+                                        const uint32_t np = stage + 1 == p.stages ? phase ^ 1u : phase;
+                                        mbar_wait_u32(full0 + (uint32_t)ns * 8u, np);
+                                        mbar_wait_u32(peer0 + (uint32_t)ns * 8u, np);
+                                        prewaited = true;
+                                    }
                                     const uint64_t adesc = hi | (uint64_t)(a_rel[ks] + s4);
                                     const uint32_t b0 = wrow + (uint32_t)ks * BSTEP;
                                     pair_mma<1, true>(dcol[0], adesc, hi | (uint64_t)b0, p.idesc, 1u);

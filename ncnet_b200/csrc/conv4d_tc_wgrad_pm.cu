@@ -246,10 +246,234 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
     }
 }
 
+// ---------------------------------------------------------------------------------------------
+// The same MMA as a WALK along jA (used when the planes are small enough for k + 2 of them to sit in shared memory).
+//
+// In the kernel above a CTA owns two d2 taps and streams (X, X, G) plane triples: 1.6 planes from L2 per tap-plane of
+// 47 MMAs, which holds it to the L2 -> shared-memory rate (39 GB per launch of 32 PF-Pascal volumes, tensor pipe 69 %
+// busy), and consecutive MMAs never share an operand.  Here a CTA owns (group, t1, slice of the (b, iA) rows) and walks
+// jj along the row: the X plane (iA+t1-p, jj) meets the k grad planes (iA, jj+p-t2), t2 = 0..k-1, which live in a ring
+// of k shared-memory buffers -- every step loads ONE X plane and ONE grad plane for k tap-planes of MMAs (0.4 planes
+// per tap-plane), and the k MMAs of a 16-position K block share their A tile (X), which the tensor core keeps in its
+// collector: 41 instead of 52 cycles per M128 x N80 x K16 MMA (scripts/umma_rate.cu).  The oldest grad plane's tap is
+// issued first, alone, so that its buffer is free for the producer while the other k-1 taps run.
+// Accumulators: tap t2 -> TMEM columns [t2*N, (t2+1)*N), live for the CTA's whole life, flushed as per-slice partials.
+// ---------------------------------------------------------------------------------------------
+constexpr int kPwMaxClasses = 10;
+
+struct WgPwArgs {
+    const __half *x;    // PM16 [B*GxA][d1*d2][npos][16]
+    const __half *g;    // PM16 [B*G][d1*d2][npos][16]
+    float *part;        // [S][G][Cin][k][k][k][k][cop]
+    int B, G, GxA, d1, d2, N;
+    int nkb, kb0;
+    int Cin, Cout, cop;
+    uint32_t plane_bytes, a1_bytes, gbuf_bytes, g_off, b_rel, lbo_b, idesc;
+    int cls_start[kPwMaxClasses + 1];       // CTAs of class c = group * k + t1: [cls_start[c], cls_start[c+1])
+};
+
+template <int K>
+__global__ void __launch_bounds__(kPmThreads, 1)
+conv4d_tc_wgrad_pmw_kernel(const WgPwArgs p) {
+    constexpr int PAD = K / 2;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t xfull[2], xempty[2], gfull[K], gempty[K], accum_bar;
+    __shared__ uint32_t tmem_base_s, live_s;
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int c = 0;
+    while ((int)blockIdx.x >= p.cls_start[c + 1]) ++c;
+    const int s = (int)blockIdx.x - p.cls_start[c], ncta = p.cls_start[c + 1] - p.cls_start[c];
+    const int g = c / K, t1 = c % K;
+    const int i_lo = max(0, PAD - t1), i_hi = min(p.d1 - 1, p.d1 - 1 + PAD - t1), nvi = i_hi - i_lo + 1;
+    const int rows = p.B * nvi, per = (rows + ncta - 1) / ncta;
+    const int rbeg = s * per, rend = min(rows, rbeg + per);
+
+    if (warp == 1 && lane == 0) {
+        for (int b = 0; b < 2; ++b) { mbar_init(&xfull[b], 1); mbar_init(&xempty[b], 1); }
+        for (int b = 0; b < K; ++b) { mbar_init(&gfull[b], 1); mbar_init(&gempty[b], 1); }
+        mbar_init(&accum_bar, 1);
+        live_s = 0;
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_s)), "r"(512) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    const uint32_t smem_total = 2u * p.a1_bytes + (uint32_t)K * p.gbuf_bytes;
+    {   // zero everything once: the margins around the planes are read by the shifted views and must stay zero
+        const uint4 z = make_uint4(0, 0, 0, 0);
+        uint4 *d = reinterpret_cast<uint4 *>(smem);
+        for (uint32_t e = threadIdx.x; e < smem_total / 16; e += kPmThreads) d[e] = z;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = tmem_base_s;
+    const uint32_t sm0 = smem_u32_pinned(smem), smg = sm0 + 2u * p.a1_bytes;
+    const uint32_t xf0 = smem_u32_pinned(xfull), xe0 = smem_u32_pinned(xempty), gf0 = smem_u32_pinned(gfull), ge0 = smem_u32_pinned(gempty);
+    const size_t ijn = (size_t)p.d1 * p.d2, plane_h = p.plane_bytes / 2;
+
+    if (warp == 0) {
+        // ===== producer: per step of the walk one grad plane (the one that becomes live) and one X plane =====
+        if (elect_one()) {
+            int xl = 0, gl = 0;                     // X / grad planes loaded so far (buffer = count mod ring size)
+            for (int r = rbeg; r < rend; ++r) {
+                const int b = r / nvi, i = i_lo + (r - b * nvi);
+                const __half *xrow = p.x + (((size_t)b * p.GxA + (p.GxA == 1 ? 0 : g)) * ijn + (size_t)(i + t1 - PAD) * p.d2) * plane_h;
+                const __half *grow = p.g + (((size_t)b * p.G + g) * ijn + (size_t)i * p.d2) * plane_h;
+                for (int jj = 0; jj < p.d2; ++jj) {
+                    const int j_first = jj == 0 ? 0 : jj + PAD, j_last = min(p.d2 - 1, jj + PAD);
+                    for (int j = j_first; j <= j_last; ++j, ++gl) {
+                        const int buf = gl % K;
+                        if (gl >= K) mbar_wait_u32(ge0 + (uint32_t)buf * 8u, (uint32_t)((gl / K) - 1) & 1u);
+                        const uint32_t fb = gf0 + (uint32_t)buf * 8u;
+                        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(p.plane_bytes) : "memory");
+                        bulk_g2s_u32(smg + (uint32_t)buf * p.gbuf_bytes + p.g_off, grow + (size_t)j * plane_h, p.plane_bytes, fb);
+                    }
+                    const int xb = xl & 1;
+                    if (xl >= 2) mbar_wait_u32(xe0 + (uint32_t)xb * 8u, (uint32_t)((xl >> 1) - 1) & 1u);
+                    const uint32_t fb = xf0 + (uint32_t)xb * 8u;
+                    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(fb), "r"(p.plane_bytes) : "memory");
+                    bulk_g2s_u32(sm0 + (uint32_t)xb * p.a1_bytes, xrow + (size_t)jj * plane_h, p.plane_bytes, fb);
+                    ++xl;
+                }
+            }
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (elect_one()) {
+            // descriptor high word: SBO = 256 B (K atoms), version 1, SWIZZLE_32B (layout type 6 at bits 61-63)
+            const uint64_t hi = (uint64_t)((256u >> 4) | (1u << 14) | (6u << 29)) << 32;
+            const uint32_t lbo_a = (32u >> 4) << 16, lbo_b = (p.lbo_b >> 4) << 16;
+            const int nk = p.nkb - p.kb0;
+            const uint32_t n = (uint32_t)p.N;
+            uint32_t inited = 0;
+            int xl = 0, gbase = 0;
+            for (int r = rbeg; r < rend; ++r) {
+                for (int jj = 0; jj < p.d2; ++jj, ++xl) {
+                    const int xb = xl & 1;
+                    mbar_wait_u32(xf0 + (uint32_t)xb * 8u, (uint32_t)(xl >> 1) & 1u);
+                    const int j_first = jj == 0 ? 0 : jj + PAD, j_last = min(p.d2 - 1, jj + PAD);
+                    for (int j = j_first; j <= j_last; ++j) {
+                        const int gi = gbase + j;
+                        mbar_wait_u32(gf0 + (uint32_t)(gi % K) * 8u, (uint32_t)(gi / K) & 1u);
+                    }
+                    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                    const int t2_lo = max(0, jj + PAD - (p.d2 - 1)), t2_hi = min(K - 1, jj + PAD);       // taps whose grad plane j = jj+PAD-t2 exists
+                    const uint32_t a0 = lbo_a | (((sm0 + (uint32_t)xb * p.a1_bytes) >> 4) + (uint32_t)p.kb0 * 32u);
+                    uint32_t b0[K];
+#pragma unroll
+                    for (int t2 = 0; t2 < K; ++t2) {
+                        const int gi = gbase + jj + PAD - t2;
+                        b0[t2] = lbo_b | (((smg + (uint32_t)((gi + K) % K) * p.gbuf_bytes + p.b_rel) >> 4) + (uint32_t)p.kb0 * 32u);
+                    }
+                    if (t2_lo == 0 && t2_hi == K - 1) {
+                        // interior step.  Oldest grad plane first (tap k-1, its last use): its buffer goes back to the producer.
+                        {
+                            uint32_t a = a0, b = b0[K - 1];
+                            const uint32_t d = tmem_base + (uint32_t)(K - 1) * n;
+                            umma_f16(d, hi | (uint64_t)a, hi | (uint64_t)b, p.idesc, (inited >> (K - 1)) & 1u);
+#pragma unroll 4
+                            for (int kb = 1; kb < nk; ++kb) {
+                                a += 32u; b += 32u;
+                                umma_f16_coll<0, true>(d, hi | (uint64_t)a, hi | (uint64_t)b, p.idesc, 1u);
+                            }
+                            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                                         ::"r"(ge0 + (uint32_t)((gbase + jj - PAD) % K) * 8u) : "memory");
+                        }
+                        // the other k-1 taps: K block outer, taps inner, the X tile held in the collector
+                        uint32_t a = a0;
+                        uint32_t b[K - 1];
+#pragma unroll
+                        for (int t2 = 0; t2 < K - 1; ++t2) b[t2] = b0[t2];
+#pragma unroll
+                        for (int t2 = 0; t2 < K - 1; ++t2) {
+                            const uint32_t acc = (inited >> t2) & 1u, d = tmem_base + (uint32_t)t2 * n;
+                            if (t2 == 0) umma_f16_coll<1, false>(d, hi | (uint64_t)a, hi | (uint64_t)b[t2], p.idesc, acc);
+                            else if (t2 == K - 2) umma_f16_coll<3, false>(d, hi | (uint64_t)a, hi | (uint64_t)b[t2], p.idesc, acc);
+                            else umma_f16_coll<2, false>(d, hi | (uint64_t)a, hi | (uint64_t)b[t2], p.idesc, acc);
+                        }
+#pragma unroll 2
+                        for (int kb = 1; kb < nk; ++kb) {
+                            a += 32u;
+#pragma unroll
+                            for (int t2 = 0; t2 < K - 1; ++t2) {
+                                b[t2] += 32u;
+                                const uint32_t d = tmem_base + (uint32_t)t2 * n;
+                                if (t2 == 0) umma_f16_coll<1, true>(d, hi | (uint64_t)a, hi | (uint64_t)b[t2], p.idesc, 1u);
+                                else if (t2 == K - 2) umma_f16_coll<3, true>(d, hi | (uint64_t)a, hi | (uint64_t)b[t2], p.idesc, 1u);
+                                else umma_f16_coll<2, true>(d, hi | (uint64_t)a, hi | (uint64_t)b[t2], p.idesc, 1u);
+                            }
+                        }
+                        inited |= (1u << K) - 1u;
+                    } else {
+                        // first / last columns of the row: the live taps one after the other, oldest grad plane first
+                        for (int t2 = t2_hi; t2 >= t2_lo; --t2) {
+                            uint32_t a = a0, b = b0[0];
+#pragma unroll
+                            for (int u = 1; u < K; ++u) if (u == t2) b = b0[u];
+                            const uint32_t d = tmem_base + (uint32_t)t2 * n;
+                            umma_f16(d, hi | (uint64_t)a, hi | (uint64_t)b, p.idesc, (inited >> t2) & 1u);
+#pragma unroll 4
+                            for (int kb = 1; kb < nk; ++kb) {
+                                a += 32u; b += 32u;
+                                umma_f16_coll<0, true>(d, hi | (uint64_t)a, hi | (uint64_t)b, p.idesc, 1u);
+                            }
+                            inited |= 1u << t2;
+                            const int j = jj + PAD - t2;
+                            if (jj == min(j + PAD, p.d2 - 1))         // this grad plane's last use
+                                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                                             ::"r"(ge0 + (uint32_t)((gbase + j) % K) * 8u) : "memory");
+                        }
+                    }
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                                 ::"r"(xe0 + (uint32_t)xb * 8u) : "memory");
+                }
+                gbase += p.d2;
+            }
+            live_s = inited;
+            __threadfence_block();
+            umma_commit(&accum_bar);
+        }
+        __syncwarp();
+    } else {
+        // ===== epilogue: flush D[t2][(t4,c)][(r,o)] as this slice's partial sums =====
+        const int q = warp & 3;
+        mbar_wait_sleep(&accum_bar, 0, 1000);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t live = *(volatile uint32_t *)&live_s;
+        const int m = q * 32 + lane, t4 = m >> 4, ch = m & 15;
+        if (q * 2 < K) {          // warp q holds the d4 taps 2q and 2q+1
+            const size_t per_group = (size_t)p.Cin * K * K * K * K * p.cop;
+            float *dst = p.part + ((size_t)s * p.G + g) * per_group;
+            for (int t2 = 0; t2 < K; ++t2) {
+                if (!((live >> t2) & 1u)) continue;
+                for (int n0 = 0; n0 < p.N; n0 += 16) {
+                    float val[16];
+                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t2 * p.N + n0), val);
+                    const int t3 = K - 1 - (n0 >> 4);
+                    if (t4 < K && ch < p.Cin) {
+                        float *row = dst + (((((size_t)ch * K + t1) * K + t2) * K + t3) * K + t4) * p.cop;
+#pragma unroll
+                        for (int o = 0; o < 16; ++o) if (o < p.Cout) row[o] = val[o];
+                    }
+                }
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 0) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(512) : "memory");
+}
+
 struct WgPmPlan {
     bool ok;
     int N, nkb, kb0, stages, nav, ncls;
     uint32_t plane_bytes, a1_bytes, a_bytes, stage_bytes, g_off, b_rel, lbo_b, tmem_cols;
+    uint32_t stage_bytes_b;         // one grad buffer with its margins (a multiple of 256 B)
     size_t smem;
 };
 
@@ -276,6 +500,7 @@ static WgPmPlan pm_plan(int d3, int d4, int k) {
     w.g_off = (uint32_t)g_off_pos * 32u;
     w.b_rel = (uint32_t)(g_off_pos - pad * P + pad) * 32u;
     w.lbo_b = (uint32_t)P * 32u;
+    w.stage_bytes_b = (uint32_t)npos_b * 32u;
     if ((w.lbo_b >> 4) > 16383u) return w;
     // two d2 taps per CTA (one grad plane staged per two X planes: the kernel is close to the L2->shared ceiling) when a
     // 2-deep ring of such stages fits; else one tap and a deeper ring
@@ -325,6 +550,54 @@ int conv4d_tc_wgrad_pm_run(const __half *x_cb, const __half *g_cb, const __half 
         g_pm = dst;
     }
     (void)gb_bytes;
+    // planes small enough for k + 2 of them in shared memory: the walk along jA (one X + one grad plane per k tap-planes)
+    {
+        const uint32_t gbuf_bytes = w.stage_bytes_b;
+        const size_t smem_w = 2 * (size_t)w.a1_bytes + (size_t)k * gbuf_bytes;
+        const int ncls = G * k;
+        if (smem_w <= 225u * 1024u && k * w.N <= 512 && ncls <= kPwMaxClasses && d1 >= k && d2 > k && !getenv("NCNET_NO_PMW")) {
+            WgPwArgs q{};
+            q.x = x_pm; q.g = g_pm; q.part = part;
+            q.B = B; q.G = G; q.GxA = GxA; q.d1 = d1; q.d2 = d2; q.N = w.N;
+            q.nkb = w.nkb; q.kb0 = w.kb0; q.Cin = Cin; q.Cout = Cout; q.cop = cop;
+            q.plane_bytes = w.plane_bytes; q.a1_bytes = w.a1_bytes; q.gbuf_bytes = gbuf_bytes;
+            q.g_off = w.g_off; q.b_rel = w.b_rel; q.lbo_b = w.lbo_b;
+            q.idesc = (1u << 4) | (1u << 15) | (1u << 16) | ((uint32_t)(w.N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+            // CTAs per class (group, t1) in proportion to its valid output rows; at most S slices of partial sums each
+            const int pad_ = k / 2;
+            int wsum = 0, wc[kPwMaxClasses], nc[kPwMaxClasses];
+            for (int c = 0; c < ncls; ++c) { const int t1 = c % k; wc[c] = d1 - (t1 > pad_ ? t1 - pad_ : pad_ - t1); wsum += wc[c]; }
+            int used_ctas = 0;
+            for (int c = 0; c < ncls; ++c) {
+                int v = (int)((long long)kNumSMs * wc[c] / wsum);
+                const long long rows = (long long)B * wc[c];
+                if (v > S) v = S;
+                if (v > rows) v = (int)rows;
+                if (v < 1) v = 1;
+                nc[c] = v; used_ctas += v;
+            }
+            for (bool more = true; more && used_ctas < kNumSMs;) {      // hand out the remainder to the most loaded classes
+                more = false;
+                int best = -1;
+                double load = 0.0;
+                for (int c = 0; c < ncls; ++c) {
+                    const double l = (double)wc[c] / nc[c];
+                    if (nc[c] < S && nc[c] < (long long)B * wc[c] && l > load) { load = l; best = c; }
+                }
+                if (best >= 0) { ++nc[best]; ++used_ctas; more = true; }
+            }
+            q.cls_start[0] = 0;
+            for (int c = 0; c < ncls; ++c) q.cls_start[c + 1] = q.cls_start[c] + nc[c];
+            for (int c = ncls + 1; c <= kPwMaxClasses; ++c) q.cls_start[c] = q.cls_start[ncls];
+            cudaError_t e = k == 5 ? cudaFuncSetAttribute(conv4d_tc_wgrad_pmw_kernel<5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w)
+                                   : cudaFuncSetAttribute(conv4d_tc_wgrad_pmw_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_w);
+            NC_CHECK(e == cudaSuccess, "conv4d_wgrad(tc,pm walk): smem attribute: %s", cudaGetErrorString(e));
+            if (k == 5) conv4d_tc_wgrad_pmw_kernel<5><<<q.cls_start[ncls], kPmThreads, smem_w, st>>>(q);
+            else conv4d_tc_wgrad_pmw_kernel<3><<<q.cls_start[ncls], kPmThreads, smem_w, st>>>(q);
+            NC_LAUNCH_OK("conv4d_tc_wgrad_pmw_kernel");
+            return 0;
+        }
+    }
     WgPmArgs a{};
     a.x = x_pm; a.g = g_pm; a.part = part;
     a.B = B; a.G = G; a.GxA = GxA; a.d1 = d1; a.d2 = d2; a.KS = k; a.N = w.N;
