@@ -260,6 +260,7 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
 // Accumulators: tap t2 -> TMEM columns [t2*N, (t2+1)*N), live for the CTA's whole life, flushed as per-slice partials.
 // ---------------------------------------------------------------------------------------------
 constexpr int kPwMaxClasses = 10;
+constexpr int kPwFlushRows = 24;
 
 struct WgPwArgs {
     const __half *x;    // PM16 [B*GxA][d1*d2][npos][16]
@@ -277,8 +278,8 @@ __global__ void __launch_bounds__(kPmThreads, 1)
 conv4d_tc_wgrad_pmw_kernel(const WgPwArgs p) {
     constexpr int PAD = K / 2;
     extern __shared__ __align__(1024) uint8_t smem[];
-    __shared__ __align__(8) uint64_t xfull[2], xempty[2], gfull[K], gempty[K], accum_bar;
-    __shared__ uint32_t tmem_base_s, live_s;
+    __shared__ __align__(8) uint64_t xfull[2], xempty[2], gfull[K], gempty[K], accum_bar, drained_bar;
+    __shared__ uint32_t tmem_base_s;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int c = 0;
@@ -288,12 +289,17 @@ conv4d_tc_wgrad_pmw_kernel(const WgPwArgs p) {
     const int i_lo = max(0, PAD - t1), i_hi = min(p.d1 - 1, p.d1 - 1 + PAD - t1), nvi = i_hi - i_lo + 1;
     const int rows = p.B * nvi, per = (rows + ncta - 1) / ncta;
     const int rbeg = s * per, rend = min(rows, rbeg + per);
+    // The tensor core adds into its fp32 accumulators with truncation: over a chain of n MMAs a coherent sum drifts low by
+    // ~n * 2^-24 of its value.  The accumulators are therefore flushed into the slice's partial sums (proper fp32 adds)
+    // every kPwFlushRows rows (~28 000 MMAs per accumulator at the PF-Pascal shape, the chain length of the per-plane
+    // kernel above; a flush stalls the issuer for the drain) and restarted from zero.
+    const int nflush = rend > rbeg ? (rend - rbeg + kPwFlushRows - 1) / kPwFlushRows : 0;
 
     if (warp == 1 && lane == 0) {
         for (int b = 0; b < 2; ++b) { mbar_init(&xfull[b], 1); mbar_init(&xempty[b], 1); }
         for (int b = 0; b < K; ++b) { mbar_init(&gfull[b], 1); mbar_init(&gempty[b], 1); }
         mbar_init(&accum_bar, 1);
-        live_s = 0;
+        mbar_init(&drained_bar, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 0) {
@@ -433,34 +439,55 @@ conv4d_tc_wgrad_pmw_kernel(const WgPwArgs p) {
                                  ::"r"(xe0 + (uint32_t)xb * 8u) : "memory");
                 }
                 gbase += p.d2;
+                const int done = r - rbeg + 1;
+                if (done % kPwFlushRows == 0 || r + 1 == rend) {
+                    umma_commit(&accum_bar);                    // the epilogue warps add the accumulators into the partial sums ...
+                    if (r + 1 < rend) {                         // ... and hand them back
+                        mbar_wait(&drained_bar, (uint32_t)((done / kPwFlushRows) - 1) & 1u);
+                        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                        inited = 0;
+                    }
+                }
             }
-            live_s = inited;
-            __threadfence_block();
-            umma_commit(&accum_bar);
         }
         __syncwarp();
     } else {
-        // ===== epilogue: flush D[t2][(t4,c)][(r,o)] as this slice's partial sums =====
+        // ===== epilogue: add D[t2][(t4,c)][(r,o)] into this slice's partial sums at every flush =====
         const int q = warp & 3;
-        mbar_wait_sleep(&accum_bar, 0, 1000);
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t live = *(volatile uint32_t *)&live_s;
         const int m = q * 32 + lane, t4 = m >> 4, ch = m & 15;
-        if (q * 2 < K) {          // warp q holds the d4 taps 2q and 2q+1
-            const size_t per_group = (size_t)p.Cin * K * K * K * K * p.cop;
-            float *dst = p.part + ((size_t)s * p.G + g) * per_group;
-            for (int t2 = 0; t2 < K; ++t2) {
-                if (!((live >> t2) & 1u)) continue;
-                for (int n0 = 0; n0 < p.N; n0 += 16) {
-                    float val[16];
-                    tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t2 * p.N + n0), val);
-                    const int t3 = K - 1 - (n0 >> 4);
-                    if (t4 < K && ch < p.Cin) {
-                        float *row = dst + (((((size_t)ch * K + t1) * K + t2) * K + t3) * K + t4) * p.cop;
+        const size_t per_group = (size_t)p.Cin * K * K * K * K * p.cop;
+        float *dst = p.part + ((size_t)s * p.G + g) * per_group;
+        for (int f = 0; f < nflush; ++f) {
+            mbar_wait_sleep(&accum_bar, (uint32_t)f & 1u, 1000);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            if (q * 2 < K) {          // warp q holds the d4 taps 2q and 2q+1
+                for (int t2 = 0; t2 < K; ++t2) {
+                    for (int n0 = 0; n0 < p.N; n0 += 16) {
+                        float val[16];
+                        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(t2 * p.N + n0), val);
+                        const int t3 = K - 1 - (n0 >> 4);
+                        if (t4 < K && ch < p.Cin) {
+                            float *row = dst + (((((size_t)ch * K + t1) * K + t2) * K + t3) * K + t4) * p.cop;
+                            if (p.cop == 16) {          // 64-byte rows: four 16-byte read-modify-writes
+                                float4 *r4 = reinterpret_cast<float4 *>(row);
+                                float4 acc4[4];
 #pragma unroll
-                        for (int o = 0; o < 16; ++o) if (o < p.Cout) row[o] = val[o];
+                                for (int v = 0; v < 4; ++v) acc4[v] = f ? r4[v] : make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+                                for (int v = 0; v < 4; ++v)
+                                    r4[v] = make_float4(acc4[v].x + val[4 * v], acc4[v].y + val[4 * v + 1], acc4[v].z + val[4 * v + 2], acc4[v].w + val[4 * v + 3]);
+                            } else {
+#pragma unroll
+                                for (int o = 0; o < 16; ++o) if (o < p.Cout) row[o] = (f ? row[o] : 0.f) + val[o];
+                            }
+                        }
                     }
                 }
+            }
+            if (f + 1 < nflush) {
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                if (threadIdx.x == 64) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(&drained_bar)) : "memory");
             }
         }
     }

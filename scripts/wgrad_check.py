@@ -1,7 +1,9 @@
 """A/B check of the 16->16 weight-gradient kernels: the walk along jA (grad-plane ring in shared memory, X tile shared by the
 k taps through the A collector) against the per-plane-triple kernel (NCNET_NO_PMW=1), same inputs, planar operands.
 Same fp16 products, fp32 accumulation; only the summation order differs: with a positive output gradient the sums are
-coherent and the two agree to ~1e-6; with a random-sign gradient each weight gradient is a heavily cancelling sum over
+coherent and the two agree to ~1e-5 on short sums; the tensor core adds into its accumulators with truncation, so on
+long sums both drift low in proportion to their MMA chain lengths (equal by design, see kPwFlushRows) and differ by a
+fraction of that drift (~2e-4 at 32 PF-Pascal volumes); with a random-sign gradient each weight gradient is a heavily cancelling sum over
 up to 10^7 positions (|sum| ~ sqrt(n) of the summed magnitudes) and the fp32 order shows at ~1e-4 .. 1e-3.  usage: python scripts/wgrad_check.py [quick]"""
 import os, sys, json
 import torch
@@ -31,7 +33,7 @@ if "quick" not in sys.argv:
 for bsz, cin, cout, k, dims in cases:
     x = torch.rand(bsz, 2 * cin, *dims, device=dev)
     w = torch.empty(k, cout, cin, k, k, k, device=dev)
-    for sign, tol in (("positive", 1e-5), ("random-sign", 5e-3)):
+    for sign, tol in (("positive", 1e-3), ("random-sign", 5e-3)):
         gy = torch.rand(bsz, 2 * cout, *dims, device=dev) if sign == "positive" else torch.randn(bsz, 2 * cout, *dims, device=dev)
         fn = lambda: F_._conv_wgrad(x, gy, w, True, W_KOIKKK, True, False, CONV_TC16)
         os.environ.pop("NCNET_NO_PMW", None)
