@@ -33,7 +33,7 @@ for r in rows[2:]:
     rd = to_bytes(r[idx["dram__bytes_read.sum"]], units[idx["dram__bytes_read.sum"]])
     wr = to_bytes(r[idx["dram__bytes_write.sum"]], units[idx["dram__bytes_write.sum"]])
     # the 16->16 launches are the largest grids of their kernels
-    if "conv4d_tc_wgrad_pm_kernel" in name:
+    if "conv4d_tc_wgrad_pmw_kernel" in name or "conv4d_tc_wgrad_pm_kernel" in name:
         key = "conv4d_wgrad"
     elif "conv4d_tc_walk16_kernel" in name or "conv4d_tc_kernel<1>" in name or "conv4d_tc_kernel<true>" in name:
         key = "conv4d_fwd"
