@@ -260,7 +260,7 @@ conv4d_tc_wgrad_pm_kernel(const WgPmArgs p) {
 // Accumulators: tap t2 -> TMEM columns [t2*N, (t2+1)*N), live for the CTA's whole life, flushed as per-slice partials.
 // ---------------------------------------------------------------------------------------------
 constexpr int kPwMaxClasses = 10;
-constexpr int kPwFlushRows = 24;
+constexpr int kPwFlushRows = 27;
 
 struct WgPwArgs {
     const __half *x;    // PM16 [B*GxA][d1*d2][npos][16]
@@ -291,7 +291,7 @@ conv4d_tc_wgrad_pmw_kernel(const WgPwArgs p) {
     const int rbeg = s * per, rend = min(rows, rbeg + per);
     // The tensor core adds into its fp32 accumulators with truncation: over a chain of n MMAs a coherent sum drifts low by
     // ~n * 2^-24 of its value.  The accumulators are therefore flushed into the slice's partial sums (proper fp32 adds)
-    // every kPwFlushRows rows (~28 000 MMAs per accumulator at the PF-Pascal shape, the chain length of the per-plane
+    // every kPwFlushRows rows (~32 000 MMAs per accumulator at the PF-Pascal shape, about the chain length of the per-plane
     // kernel above; a flush stalls the issuer for the drain) and restarted from zero.
     const int nflush = rend > rbeg ? (rend - rbeg + kPwFlushRows - 1) / kPwFlushRows : 0;
 
