@@ -250,7 +250,7 @@ conv4d_tc_walk16_kernel(const Walk16Args p) {
                                     else pair_mma<3, true>(dcol[K - 1], adesc, hi | (uint64_t)(b0 - (uint32_t)(K - 1) * SLAB4), p.idesc, 1u);
                                 }
                             } else {
-    #pragma unroll
+#pragma unroll
                                 for (int dd = 0; dd < K; ++dd) {        // outputs j = jj - PAD + dd, ascending: a new one comes last
                                     const int j = jj - PAD + dd;
                                     if (j >= it.j0 && j < it.j1) {
@@ -263,7 +263,7 @@ conv4d_tc_walk16_kernel(const Walk16Args p) {
                                         }
                                         const uint32_t b0 = wrow - (uint32_t)dd * SLAB4;
                                         const uint32_t dcol = tmem_base + (uint32_t)(slot * N);
-    #pragma unroll
+#pragma unroll
                                         for (int ks = 0; ks < K; ++ks)
                                             umma_f16_pair(dcol, hi | (uint64_t)(a_rel[ks] + s4), hi | (uint64_t)(b0 + (uint32_t)ks * BSTEP), p.idesc,
                                                           (is_new && ks == 0) ? 0u : 1u);
@@ -361,47 +361,45 @@ conv4d_tc_walk16_kernel(const Walk16Args p) {
                     asm volatile("bar.sync 1, 128;" ::: "memory");
                 }
                 if (m0 < p.M_out) {
-                    {
-                        // CB16 store: the haloed positions this chunk owns (halo rows / columns written as zeros), 16 B per
-                        // (position, channel half), lanes along the contiguous position axis
-                        const int lo = chunk == 0 ? 0 : m0 + off_h;
-                        const int hi_pos = end_m == p.M_out ? plane_cb : end_m + off_h;
-                        const int npos = hi_pos - lo;
-                        const size_t base_off = ((((size_t)it.b * p.G + g) * 2) * ij_count + (size_t)it.i * p.d2 + j) * (size_t)plane_cb * 8;
-                        __half *ob = p.out + base_off;
-                        const __half *mb = p.mask + base_off;
-                        for (int e = et; e < 2 * npos; e += 128) {
-                            const int half = e >= npos ? 1 : 0;
-                            const int hp = lo + (e - half * npos);
-                            const int m = hp - off_h;
-                            const size_t goff = ((size_t)half * ij_count * plane_cb + (size_t)hp) * 8;
-                            __align__(16) __half hv[8];
-                            if (m >= m0 && m < end_m && (m % p.P) < p.d4) {
-                                const uint32_t src = osm + (uint32_t)((m - m0) * kW16OutStride + half * 8) * 4u;
-                                const float4 a = lds_v4(src), c = lds_v4(src + 16u);
-                                float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
-                                if (p.mask) {
-                                    const uint4 mraw = *reinterpret_cast<const uint4 *>(mb + goff);
-                                    const __half *mh = reinterpret_cast<const __half *>(&mraw);
+                    // CB16 store: the haloed positions this chunk owns (halo rows / columns written as zeros), 16 B per
+                    // (position, channel half), lanes along the contiguous position axis
+                    const int lo = chunk == 0 ? 0 : m0 + off_h;
+                    const int hi_pos = end_m == p.M_out ? plane_cb : end_m + off_h;
+                    const int npos = hi_pos - lo;
+                    const size_t base_off = ((((size_t)it.b * p.G + g) * 2) * ij_count + (size_t)it.i * p.d2 + j) * (size_t)plane_cb * 8;
+                    __half *ob = p.out + base_off;
+                    const __half *mb = p.mask + base_off;
+                    for (int e = et; e < 2 * npos; e += 128) {
+                        const int half = e >= npos ? 1 : 0;
+                        const int hp = lo + (e - half * npos);
+                        const int m = hp - off_h;
+                        const size_t goff = ((size_t)half * ij_count * plane_cb + (size_t)hp) * 8;
+                        __align__(16) __half hv[8];
+                        if (m >= m0 && m < end_m && (m % p.P) < p.d4) {
+                            const uint32_t src = osm + (uint32_t)((m - m0) * kW16OutStride + half * 8) * 4u;
+                            const float4 a = lds_v4(src), c = lds_v4(src + 16u);
+                            float v[8] = {a.x, a.y, a.z, a.w, c.x, c.y, c.z, c.w};
+                            if (p.mask) {
+                                const uint4 mraw = *reinterpret_cast<const uint4 *>(mb + goff);
+                                const __half *mh = reinterpret_cast<const __half *>(&mraw);
 #pragma unroll
-                                    for (int c8 = 0; c8 < 8; ++c8) if (!(__half2float(mh[c8]) > 0.f)) v[c8] = 0.f;
-                                }
-#pragma unroll
-                                for (int c8 = 0; c8 < 8; ++c8) {
-                                    float x = v[c8];
-                                    if (p.relu) x = fmaxf(x, 0.f);
-                                    hv[c8] = __float2half_rn((half * 8 + c8) < p.Cout ? x : 0.f);
-                                }
-                            } else {
-#pragma unroll
-                                for (int c8 = 0; c8 < 8; ++c8) hv[c8] = __float2half_rn(0.f);
+                                for (int c8 = 0; c8 < 8; ++c8) if (!(__half2float(mh[c8]) > 0.f)) v[c8] = 0.f;
                             }
-                            *reinterpret_cast<uint4 *>(ob + goff) = *reinterpret_cast<const uint4 *>(hv);
-                            if (p.out_pm) {      // position-major twin: 32 B per position, halves swapped by bit 7 of the in-plane offset
-                                const size_t pm_off = ((((size_t)it.b * p.G + g) * ij_count + (size_t)it.i * p.d2 + j) * plane_cb + hp) * 16 +
-                                                      (size_t)((half ^ ((hp >> 2) & 1)) * 8);
-                                *reinterpret_cast<uint4 *>(p.out_pm + pm_off) = *reinterpret_cast<const uint4 *>(hv);
+#pragma unroll
+                            for (int c8 = 0; c8 < 8; ++c8) {
+                                float x = v[c8];
+                                if (p.relu) x = fmaxf(x, 0.f);
+                                hv[c8] = __float2half_rn((half * 8 + c8) < p.Cout ? x : 0.f);
                             }
+                        } else {
+#pragma unroll
+                            for (int c8 = 0; c8 < 8; ++c8) hv[c8] = __float2half_rn(0.f);
+                        }
+                        *reinterpret_cast<uint4 *>(ob + goff) = *reinterpret_cast<const uint4 *>(hv);
+                        if (p.out_pm) {      // position-major twin: 32 B per position, halves swapped by bit 7 of the in-plane offset
+                            const size_t pm_off = ((((size_t)it.b * p.G + g) * ij_count + (size_t)it.i * p.d2 + j) * plane_cb + hp) * 16 +
+                                                  (size_t)((half ^ ((hp >> 2) & 1)) * 8);
+                            *reinterpret_cast<uint4 *>(p.out_pm + pm_off) = *reinterpret_cast<const uint4 *>(hv);
                         }
                     }
                 }
